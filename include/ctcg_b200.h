@@ -1,0 +1,208 @@
+/*
+ * ctcg_b200.h -- C ABI of the B200-native CTC / CTC-G training-loss engine.
+ *
+ * This is the drop-in boundary for the one hot path of chorowski-lab/pytorch-asr
+ * that this repository replaces: the log-semiring forward-backward over
+ * per-utterance graphs plus the gradient with respect to the logits.  Every
+ * entry point cites the reference interface it stands in for (paths relative
+ * to the reference tree).  Plain pointers and sizes only; no torch types.
+ *
+ * Conventions
+ *   - every function returns a ctcg_status (0 = OK) and never throws;
+ *   - "device" pointers are CUDA global-memory pointers on the current device,
+ *     "host" pointers are ordinary process memory;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream);
+ *     all kernels are stream-ordered, nothing synchronises the device except
+ *     the *_host entry points;
+ *   - logits / log-probs are fp32, time-major contiguous (T, B, V), exactly the
+ *     layout FSTDecoder hands to path_reduction (advanced_decoder.py:488);
+ *   - the caller owns all tensors, the engine owns graph handles.
+ *
+ * There is no CPU fallback behind this ABI: without a CUDA device the compute
+ * entry points return CTCG_ECUDA.
+ */
+#ifndef CTCG_B200_H_
+#define CTCG_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum ctcg_status {
+  CTCG_OK = 0,
+  CTCG_EINVAL = 1,       /* bad argument (shape mismatch, NULL, label out of range) */
+  CTCG_ESTART = 2,       /* start state is not 0        (fst_utils.py:246-248 ValueError) */
+  CTCG_ENONDET = 3,      /* graph not input-deterministic (fst_utils.py:250-252 ValueError) */
+  CTCG_EEPS = 4,         /* epsilon input label          (fst_utils.py:272-274 ValueError) */
+  CTCG_ECUDA = 5,        /* CUDA runtime error / no device */
+  CTCG_ENOMEM = 6,       /* host allocation failed */
+  CTCG_EWORKSPACE = 7,   /* workspace too small: call ctcg_workspace_bytes */
+  CTCG_EUNSUPPORTED = 8, /* configuration outside what the kernels cover */
+  CTCG_ENOTUPLOADED = 9  /* graph used on device before ctcg_graph_upload */
+} ctcg_status;
+
+/* Opaque handle: one graph shared by a whole batch (a decoding / denominator
+ * graph) or one graph per utterance (training / numerator graphs).  Holds CSR
+ * by destination (for alpha) and by source (for beta): row pointers,
+ * {other state, label, weight} per arc, final weights, and the per-graph table
+ * of distinct labels used to gather only the logits an utterance touches. */
+typedef struct ctcg_graph ctcg_graph;
+
+/* Topology of the H o C decoding graph; mirrors CTCGraphGen(context_order,
+ * graph_build_args, num_symbols) -- fst_utils.py:1053-1068 and the keyword
+ * arguments of build_ctc_bigram_decoding_fst, fst_utils.py:729-734. */
+typedef struct ctcg_topology {
+  int32_t context_order;                 /* 1 = mono-char, 2 = bi-char */
+  int32_t num_symbols;                   /* S (blank is symbol 0) */
+  int32_t allow_nonblank_selfloops;      /* default 1 */
+  int32_t use_contextual_blanks;         /* default 0 (CTC-GB sets 1) */
+  int32_t loop_using_symbol_repetitions; /* default 0 */
+} ctcg_topology;
+
+typedef struct ctcg_graph_info {
+  int32_t num_graphs;     /* 1 = shared by the batch */
+  int32_t max_states;
+  int32_t max_in_degree;
+  int32_t max_out_degree;
+  int32_t max_labels;     /* max distinct labels of any one graph */
+  int32_t structured;     /* 1: bi-char decoding graph with factorised fast path */
+  int32_t on_device;      /* device ordinal the graph was uploaded to, or -1 */
+  int32_t reserved;
+  int64_t total_states;
+  int64_t total_arcs;
+} ctcg_graph_info;
+
+/* Normalisation applied to the logits before the path sums; mirrors
+ * FSTDecoder.normalize_by_dim (advanced_decoder.py:444-452) through
+ * get_normalized_acts (ctc_losses.py:29-43). */
+#define CTCG_NORM_NONE 0    /* normalize_by_dim: None -> raw logits (CTC-G / CTC-GB) */
+#define CTCG_NORM_SOFTMAX 1 /* normalize_by_dim: 0    -> log_softmax over all V       */
+#define CTCG_NORM_CONTEXT 2 /* normalize_by_dim: 1    -> log_softmax inside each block of S */
+
+/* ---- graph compilation (host only; callable from DataLoader workers) ------ */
+
+/* Decoding (denominator) graph of a topology.
+ * Replaces build_ctc_mono_decoding_fst / build_ctc_bigram_decoding_fst +
+ * fst_to_matrices (fst_utils.py:679-835, :222-294) and
+ * BaseGraphGen.get_decoding_matrices (fst_utils.py:662-676). */
+int ctcg_decoding_graph(const ctcg_topology* topo, ctcg_graph** out);
+
+/* Training (numerator) graphs: compose(decoding graph, chain(labels_b)) for B
+ * transcripts; labels of utterance b are labels[offsets[b] .. offsets[b+1]).
+ * Labels larger than S are reduced modulo S first (fst_utils.py:595-596).
+ * Replaces BaseGraphGen.get_training_matrices(_batch) (fst_utils.py:603-613,
+ * :647-660) + build_chain_fst (:195-219) + batch_training_graph_matrices
+ * (:491-521). */
+int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels,
+                         const int64_t* offsets, int32_t B, ctcg_graph** out);
+
+/* Import the reference's own padded matrices (the 8-tuple FSTDecoder receives
+ * in batch['graph_matrices'], advanced_decoder.py:457-459): G graphs of N
+ * states, in-degree K_in, out-degree K_out; arcs with weight <= nc_weight/2 are
+ * padding and dropped.  Validates start==0 reachability conventions only. */
+int ctcg_graph_from_padded(const int64_t* pred, const int64_t* lab_in,
+                           const float* w_in, const float* final_w,
+                           const int64_t* succ, const int64_t* lab_out,
+                           const float* w_out, int32_t G, int32_t N,
+                           int32_t K_in, int32_t K_out, float nc_weight,
+                           ctcg_graph** out);
+
+/* Generic arc-list import (any topology: grammar-composed, tri-char ...).
+ * Arcs (src, dst, label, weight=log-prob) of G graphs concatenated;
+ * arc_offsets[G+1], state_counts[G]; final_w concatenated per state
+ * (-inf or <= -1e19 = not final).  Rejects label < 0 (CTCG_EEPS) and
+ * non-deterministic states (CTCG_ENONDET), as fst_to_matrices does. */
+int ctcg_graph_from_arcs(const int32_t* src, const int32_t* dst,
+                         const int32_t* label, const float* weight,
+                         const int64_t* arc_offsets, const int32_t* state_counts,
+                         const float* final_w, int32_t G, ctcg_graph** out);
+
+int ctcg_graph_get_info(const ctcg_graph* g, ctcg_graph_info* info);
+
+/* Dimensions of graph `index` in the reference's padded encoding. */
+int ctcg_graph_padded_dims(const ctcg_graph* g, int32_t index, int32_t* n_states,
+                           int32_t* k_in, int32_t* k_out);
+
+/* Export graph `index` in the exact encoding of fst_to_matrices
+ * (fst_utils.py:280-288): per-state arc lists sorted by (state, label,
+ * weight), padded with (0, 0, nc_weight); out_edges selects succ/pred form.
+ * states/labels are (N, K) int64, weights (N, K) fp32, terminal (N) fp32. */
+int ctcg_graph_export_padded(const ctcg_graph* g, int32_t index, int32_t out_edges,
+                             float nc_weight, int64_t* states, int64_t* labels,
+                             float* weights, float* terminal);
+
+/* Copy the CSR arrays to the current CUDA device (idempotent per device). */
+int ctcg_graph_upload(ctcg_graph* g, void* stream);
+
+void ctcg_graph_free(ctcg_graph* g);
+
+/* ---- loss + gradient (device) -------------------------------------------- */
+
+/* Bytes of device workspace ctcg_loss_fwd_bwd / ctcg_path_sum need. */
+size_t ctcg_workspace_bytes(int32_t T, int32_t B, int32_t V, const ctcg_graph* num,
+                            const ctcg_graph* den);
+
+/* Fused training loss, replaces FSTDecoder.logits' normalisation +
+ * get_fst_loss + the backward of PathLogSumExp (advanced_decoder.py:444-517,
+ * fst_utils.py:400-488):
+ *   loss[b]  = -cost_num_b(lp) + cost_den_b(lp)          (den != NULL)
+ *            = -cost_num_b(lp)                           (den == NULL)
+ *   grad     = d(sum_b grad_scale[b] * loss[b]) / d logits, written in full
+ *              (rows t >= lens[b] are zero), grad_scale NULL = all ones.
+ * lp = logits normalised per `normalize`.  lens_host: B int32 on the host
+ * (the reference keeps act_lens on the CPU); need not be sorted.
+ * grad may be NULL (loss only).  loss/grad_scale are device pointers. */
+int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V,
+                      const int32_t* lens_host, const ctcg_graph* num,
+                      const ctcg_graph* den, int32_t normalize,
+                      int32_t num_symbols, const float* grad_scale, float* loss,
+                      float* grad, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
+/* path_reduction(log_probs, act_lens, graph_matrices, 'logsumexp')
+ * (fst_utils.py:322-347): cost[b] = log-sum over accepting paths of length
+ * lens[b]; grad (nullable) = d cost / d log_probs, dense (T,B,V). */
+int ctcg_path_sum(const float* log_probs, int32_t T, int32_t B, int32_t V,
+                  const int32_t* lens_host, const ctcg_graph* graph, float* cost,
+                  float* grad, void* workspace, size_t workspace_bytes,
+                  void* stream);
+
+/* path_reduction(..., red_kind='viterbi') + the arg-min-of-gradient read-out of
+ * FSTDecoder.decode (fst_utils.py:366-397, advanced_decoder.py:546-554):
+ * score[b] = best accepting path weight, frame_labels (T,B) int32 = label
+ * consumed at each frame on that path (0 for t >= lens[b]). */
+int ctcg_viterbi(const float* log_probs, int32_t T, int32_t B, int32_t V,
+                 const int32_t* lens_host, const ctcg_graph* graph, float* score,
+                 int32_t* frame_labels, void* workspace, size_t workspace_bytes,
+                 void* stream);
+
+/* Number of accepting paths of length lens[b], modulo 2^64 (the
+ * integer counterpart of path_reduction on all-zero log-probs). */
+int ctcg_path_count(int32_t B, const int32_t* lens_host, const ctcg_graph* graph,
+                    uint64_t* counts, void* workspace, size_t workspace_bytes,
+                    void* stream);
+
+/* ---- end-to-end with host buffers ---------------------------------------- */
+
+/* Same as ctcg_loss_fwd_bwd but every buffer is in host memory: copies the
+ * logits to the device, runs the fused path, copies loss (B) and, if non-NULL,
+ * grad (T*B*V) back, and synchronises.  Scratch device memory is cached in the
+ * library between calls.  This is the call a non-torch host would bind. */
+int ctcg_loss_host(const float* logits_host, int32_t T, int32_t B, int32_t V,
+                   const int32_t* lens_host, ctcg_graph* num, ctcg_graph* den,
+                   int32_t normalize, int32_t num_symbols, float* loss_host,
+                   float* grad_host);
+
+const char* ctcg_strerror(int status);
+
+/* Number of kernel launches issued by this library since load (bench.py's
+ * gpu_launches claim is read from here, not guessed). */
+uint64_t ctcg_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTCG_B200_H_ */

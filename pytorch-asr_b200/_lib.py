@@ -1,0 +1,358 @@
+"""ctypes binding of ``libctcg_b200.so`` (the C ABI declared in ``include/ctcg_b200.h``).
+
+There is deliberately no fallback: if the shared library is missing, or a
+compute entry point is called without a CUDA device, this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libctcg_b200.so")
+
+OK, EINVAL, ESTART, ENONDET, EEPS, ECUDA, ENOMEM, EWORKSPACE, EUNSUPPORTED, ENOTUPLOADED = range(10)
+NORM_NONE, NORM_SOFTMAX, NORM_CONTEXT = 0, 1, 2
+
+# every symbol include/ctcg_b200.h declares
+EXPORTS = (
+    "ctcg_decoding_graph", "ctcg_training_graphs", "ctcg_graph_from_padded",
+    "ctcg_graph_from_arcs", "ctcg_graph_get_info", "ctcg_graph_padded_dims",
+    "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
+    "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi",
+    "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
+)
+
+
+class Topology(C.Structure):
+    _fields_ = [("context_order", C.c_int32), ("num_symbols", C.c_int32),
+                ("allow_nonblank_selfloops", C.c_int32),
+                ("use_contextual_blanks", C.c_int32),
+                ("loop_using_symbol_repetitions", C.c_int32)]
+
+
+class GraphInfo(C.Structure):
+    _fields_ = [("num_graphs", C.c_int32), ("max_states", C.c_int32),
+                ("max_in_degree", C.c_int32), ("max_out_degree", C.c_int32),
+                ("max_labels", C.c_int32), ("structured", C.c_int32),
+                ("on_device", C.c_int32), ("reserved", C.c_int32),
+                ("total_states", C.c_int64), ("total_arcs", C.c_int64)]
+
+
+_lib = None
+
+
+def lib():
+    """Load the shared library (once).  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "libctcg_b200.so is not built (%s missing): run `python -c 'import "
+            "__graft_entry__ as g; g.build()'`.  There is no CPU fallback." % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, f32p = C.c_void_p, C.c_int32, C.c_int64, C.c_void_p
+    L.ctcg_decoding_graph.argtypes = [C.POINTER(Topology), C.POINTER(vp)]
+    L.ctcg_training_graphs.argtypes = [C.POINTER(Topology), vp, vp, i32, C.POINTER(vp)]
+    L.ctcg_graph_from_padded.argtypes = [vp] * 7 + [i32] * 4 + [C.c_float, C.POINTER(vp)]
+    L.ctcg_graph_from_arcs.argtypes = [vp] * 7 + [i32, C.POINTER(vp)]
+    L.ctcg_graph_get_info.argtypes = [vp, C.POINTER(GraphInfo)]
+    L.ctcg_graph_padded_dims.argtypes = [vp, i32] + [C.POINTER(i32)] * 3
+    L.ctcg_graph_export_padded.argtypes = [vp, i32, i32, C.c_float, vp, vp, vp, vp]
+    L.ctcg_graph_upload.argtypes = [vp, vp]
+    L.ctcg_graph_free.argtypes = [vp]
+    L.ctcg_graph_free.restype = None
+    L.ctcg_workspace_bytes.argtypes = [i32, i32, i32, vp, vp]
+    L.ctcg_workspace_bytes.restype = C.c_size_t
+    L.ctcg_loss_fwd_bwd.argtypes = [f32p, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp, vp, vp,
+                                    C.c_size_t, vp]
+    L.ctcg_path_sum.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp, C.c_size_t, vp]
+    L.ctcg_viterbi.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp, C.c_size_t, vp]
+    L.ctcg_path_count.argtypes = [i32, vp, vp, vp, vp, C.c_size_t, vp]
+    L.ctcg_loss_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp]
+    L.ctcg_strerror.argtypes = [C.c_int]
+    L.ctcg_strerror.restype = C.c_char_p
+    L.ctcg_launch_count.argtypes = []
+    L.ctcg_launch_count.restype = C.c_uint64
+    for name in EXPORTS:
+        getattr(L, name)
+    _lib = L
+    return L
+
+
+def check(status):
+    """Turn a ctcg_status into the exception the reference would raise."""
+    if status == OK:
+        return
+    msg = lib().ctcg_strerror(status).decode()
+    if status in (ESTART, ENONDET, EEPS):   # fst_utils.py:246-252, :272-274 raise ValueError
+        raise ValueError(msg)
+    if status == EINVAL:
+        raise AssertionError("ctcg: " + msg)  # the reference asserts on shape mismatches
+    raise RuntimeError("ctcg: %s (status %d)" % (msg, status))
+
+
+def launch_count():
+    return int(lib().ctcg_launch_count())
+
+
+def _np_ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _require_cuda(t, what):
+    if not (torch.is_tensor(t) and t.is_cuda):
+        raise RuntimeError("ctcg: %s must be a CUDA tensor -- this engine has no CPU path" % what)
+
+
+class Graph(object):
+    """Owns one ``ctcg_graph*`` (a shared graph or one graph per utterance)."""
+
+    def __init__(self, ptr):
+        self._ptr = C.c_void_p(ptr) if not isinstance(ptr, C.c_void_p) else ptr
+        self._info = None
+
+    def __del__(self):
+        try:
+            if self._ptr and _lib is not None:
+                _lib.ctcg_graph_free(self._ptr)
+        except Exception:
+            pass
+        self._ptr = None
+
+    # -- constructors --------------------------------------------------
+    @staticmethod
+    def _topology(context_order, num_symbols, allow_nonblank_selfloops=True,
+                  use_contextual_blanks=False, loop_using_symbol_repetitions=False,
+                  eval_repeats_in_context=False):
+        assert not eval_repeats_in_context  # fst_utils.py:759-760
+        return Topology(int(context_order), int(num_symbols), int(bool(allow_nonblank_selfloops)),
+                        int(bool(use_contextual_blanks)), int(bool(loop_using_symbol_repetitions)))
+
+    @classmethod
+    def decoding(cls, context_order, num_symbols, **build_args):
+        topo = cls._topology(context_order, num_symbols, **build_args)
+        out = C.c_void_p()
+        check(lib().ctcg_decoding_graph(C.byref(topo), C.byref(out)))
+        return cls(out)
+
+    @classmethod
+    def training(cls, context_order, num_symbols, label_seqs, **build_args):
+        """``label_seqs``: list of 1-D integer sequences (one transcript per utterance)."""
+        topo = cls._topology(context_order, num_symbols, **build_args)
+        seqs = [np.asarray(s, dtype=np.int64).reshape(-1) for s in label_seqs]
+        offsets = np.zeros(len(seqs) + 1, dtype=np.int64)
+        for i, s in enumerate(seqs):
+            offsets[i + 1] = offsets[i] + len(s)
+        flat = (np.concatenate(seqs) if seqs else np.zeros(0, np.int64)).astype(np.int32)
+        flat = np.ascontiguousarray(flat)
+        out = C.c_void_p()
+        check(lib().ctcg_training_graphs(C.byref(topo), _np_ptr(flat), _np_ptr(offsets),
+                                         len(seqs), C.byref(out)))
+        return cls(out)
+
+    @classmethod
+    def from_padded(cls, matrices, nc_weight=-1e20):
+        """From the reference's 4- or 8-tuple of padded (G,N,K) matrices."""
+        mats = [m.detach().cpu().numpy() if torch.is_tensor(m) else np.asarray(m) for m in matrices]
+        pred = np.ascontiguousarray(mats[0], dtype=np.int64)
+        lab = np.ascontiguousarray(mats[1], dtype=np.int64)
+        w = np.ascontiguousarray(mats[2], dtype=np.float32)
+        fin = np.ascontiguousarray(mats[3], dtype=np.float32).reshape(pred.shape[0], pred.shape[1])
+        assert pred.ndim == 3 and lab.shape == pred.shape and w.shape == pred.shape
+        G, N, K = pred.shape
+        out = C.c_void_p()
+        check(lib().ctcg_graph_from_padded(_np_ptr(pred), _np_ptr(lab), _np_ptr(w), _np_ptr(fin),
+                                           None, None, None, G, N, K, 0, float(nc_weight),
+                                           C.byref(out)))
+        return cls(out)
+
+    @classmethod
+    def from_arcs(cls, graphs):
+        """``graphs``: list of ``(n_states, arcs[(src,dst,label,weight)], final[n])``."""
+        src, dst, lab, w, fin, counts, offs = [], [], [], [], [], [], [0]
+        for (n, arcs, final) in graphs:
+            counts.append(n)
+            for a in arcs:
+                src.append(a[0]); dst.append(a[1]); lab.append(a[2]); w.append(a[3])
+            offs.append(len(src))
+            fin.extend(np.asarray(final, dtype=np.float32).tolist())
+        a32 = lambda x: np.ascontiguousarray(np.asarray(x, dtype=np.int32))  # noqa: E731
+        src, dst, lab, counts = a32(src), a32(dst), a32(lab), a32(counts)
+        w = np.ascontiguousarray(np.asarray(w, dtype=np.float32))
+        fin = np.ascontiguousarray(np.asarray(fin, dtype=np.float32))
+        offs = np.ascontiguousarray(np.asarray(offs, dtype=np.int64))
+        out = C.c_void_p()
+        check(lib().ctcg_graph_from_arcs(_np_ptr(src), _np_ptr(dst), _np_ptr(lab), _np_ptr(w),
+                                         _np_ptr(offs), _np_ptr(counts), _np_ptr(fin),
+                                         len(graphs), C.byref(out)))
+        return cls(out)
+
+    # -- inspection ----------------------------------------------------
+    @property
+    def ptr(self):
+        return self._ptr
+
+    def info(self):
+        gi = GraphInfo()
+        check(lib().ctcg_graph_get_info(self._ptr, C.byref(gi)))
+        return gi
+
+    @property
+    def num_graphs(self):
+        return self.info().num_graphs
+
+    def padded_dims(self, index=0):
+        n, ki, ko = C.c_int32(), C.c_int32(), C.c_int32()
+        check(lib().ctcg_graph_padded_dims(self._ptr, index, C.byref(n), C.byref(ki), C.byref(ko)))
+        return n.value, ki.value, ko.value
+
+    def export_padded(self, index=0, out_edges=False, nc_weight=-1e20):
+        """Graph ``index`` in the exact encoding of ``fst_to_matrices`` (numpy)."""
+        n, ki, ko = self.padded_dims(index)
+        k = ko if out_edges else ki
+        states = np.zeros((n, k), dtype=np.int64)
+        labels = np.zeros((n, k), dtype=np.int64)
+        weights = np.zeros((n, k), dtype=np.float32)
+        terminal = np.zeros((n, 1), dtype=np.float32)
+        check(lib().ctcg_graph_export_padded(self._ptr, index, int(out_edges), float(nc_weight),
+                                             _np_ptr(states), _np_ptr(labels), _np_ptr(weights),
+                                             _np_ptr(terminal)))
+        return states, labels, weights, terminal
+
+    def upload(self, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ctcg: no CUDA device -- this engine has no CPU path")
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        with torch.cuda.device(device):
+            check(lib().ctcg_graph_upload(self._ptr, _stream_ptr(device)))
+        return self
+
+
+# ---------------------------------------------------------------------------
+_workspaces = {}
+
+
+def _workspace(device, nbytes):
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _lens_array(act_lens, B):
+    if torch.is_tensor(act_lens):
+        act_lens = act_lens.detach().cpu().numpy()
+    lens = np.ascontiguousarray(np.asarray(act_lens, dtype=np.int32).reshape(-1))
+    assert lens.shape[0] == B, "act_lens must hold one length per utterance"
+    return lens
+
+
+def _prep_logits(x):
+    _require_cuda(x, "logits / log_probs")
+    assert x.dim() == 3, "expected a (T, B, V) tensor"
+    x = x.detach()
+    if x.dtype != torch.float32:
+        x = x.float()
+    return x.contiguous()
+
+
+def loss_fwd_bwd(logits, act_lens, num, den=None, normalize=NORM_NONE, num_symbols=0,
+                 grad_scale=None, need_grad=True):
+    """``ctcg_loss_fwd_bwd``: returns ``(loss (B,), grad (T,B,V) or None)``."""
+    x = _prep_logits(logits)
+    T, B, V = x.shape
+    lens = _lens_array(act_lens, B)
+    dev = x.device
+    with torch.cuda.device(dev):
+        num.upload(dev)
+        if den is not None:
+            den.upload(dev)
+        nbytes = lib().ctcg_workspace_bytes(T, B, V, num.ptr, den.ptr if den is not None else None)
+        ws = _workspace(dev, nbytes)
+        loss = torch.empty(B, dtype=torch.float32, device=dev)
+        grad = torch.empty_like(x) if need_grad else None
+        gs = None
+        if grad_scale is not None:
+            gs = grad_scale.detach().to(device=dev, dtype=torch.float32).contiguous()
+        check(lib().ctcg_loss_fwd_bwd(
+            x.data_ptr(), T, B, V, _np_ptr(lens), num.ptr, den.ptr if den is not None else None,
+            int(normalize), int(num_symbols), gs.data_ptr() if gs is not None else None,
+            loss.data_ptr(), grad.data_ptr() if grad is not None else None,
+            ws.data_ptr(), ws.numel(), _stream_ptr(dev)))
+    return loss, grad
+
+
+def path_sum(log_probs, act_lens, graph, need_grad=True):
+    x = _prep_logits(log_probs)
+    T, B, V = x.shape
+    lens = _lens_array(act_lens, B)
+    dev = x.device
+    with torch.cuda.device(dev):
+        graph.upload(dev)
+        ws = _workspace(dev, lib().ctcg_workspace_bytes(T, B, V, graph.ptr, None))
+        cost = torch.empty(B, dtype=torch.float32, device=dev)
+        grad = torch.empty_like(x) if need_grad else None
+        check(lib().ctcg_path_sum(x.data_ptr(), T, B, V, _np_ptr(lens), graph.ptr, cost.data_ptr(),
+                                  grad.data_ptr() if grad is not None else None,
+                                  ws.data_ptr(), ws.numel(), _stream_ptr(dev)))
+    return cost, grad
+
+
+def viterbi(log_probs, act_lens, graph):
+    x = _prep_logits(log_probs)
+    T, B, V = x.shape
+    lens = _lens_array(act_lens, B)
+    dev = x.device
+    with torch.cuda.device(dev):
+        graph.upload(dev)
+        ws = _workspace(dev, lib().ctcg_workspace_bytes(T, B, V, graph.ptr, None))
+        score = torch.empty(B, dtype=torch.float32, device=dev)
+        labels = torch.empty((T, B), dtype=torch.int32, device=dev)
+        check(lib().ctcg_viterbi(x.data_ptr(), T, B, V, _np_ptr(lens), graph.ptr, score.data_ptr(),
+                                 labels.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev)))
+    return score, labels
+
+
+def path_count(act_lens, graph, device=None):
+    if not torch.cuda.is_available():
+        raise RuntimeError("ctcg: no CUDA device -- this engine has no CPU path")
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    lens = np.ascontiguousarray(np.asarray(act_lens, dtype=np.int32).reshape(-1))
+    B = lens.shape[0]
+    with torch.cuda.device(dev):
+        graph.upload(dev)
+        ws = _workspace(dev, lib().ctcg_workspace_bytes(1, B, 1, None, None))
+        counts = torch.zeros(B, dtype=torch.int64, device=dev)
+        check(lib().ctcg_path_count(B, _np_ptr(lens), graph.ptr, counts.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), _stream_ptr(dev)))
+    return counts.cpu().numpy().view(np.uint64)
+
+
+def loss_host(logits_host, act_lens, num, den=None, normalize=NORM_NONE, num_symbols=0,
+              loss_out=None, grad_out=None, want_grad=True):
+    """``ctcg_loss_host``: host buffers in, host buffers out (copies inside)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("ctcg: no CUDA device -- this engine has no CPU path")
+    x = logits_host
+    assert torch.is_tensor(x) and not x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
+    T, B, V = x.shape
+    lens = _lens_array(act_lens, B)
+    if loss_out is None:
+        loss_out = torch.empty(B, dtype=torch.float32)
+    if want_grad and grad_out is None:
+        grad_out = torch.empty_like(x)
+    check(lib().ctcg_loss_host(x.data_ptr(), T, B, V, _np_ptr(lens), num.ptr,
+                               den.ptr if den is not None else None, int(normalize), int(num_symbols),
+                               loss_out.data_ptr(), grad_out.data_ptr() if want_grad else None))
+    return loss_out, (grad_out if want_grad else None)

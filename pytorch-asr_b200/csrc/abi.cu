@@ -1,0 +1,412 @@
+// Device half of the C ABI: graph upload, workspace planning and the launch
+// sequences of the loss / path-sum / Viterbi / counting entry points.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "device_utils.cuh"
+#include "kernels.cuh"
+
+using namespace ctcg;
+
+namespace {
+
+constexpr size_t kAlign = 256;
+inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
+
+#define CTCG_CUDA(expr)                     \
+  do {                                      \
+    cudaError_t e__ = (expr);               \
+    if (e__ != cudaSuccess) {               \
+      (void)cudaGetLastError();             \
+      return CTCG_ECUDA;                    \
+    }                                       \
+  } while (0)
+
+struct Plan {
+  int nlp = 0;       // compact row pitch (floats), multiple of 4
+  int arow_num = 0;  // alpha row pitch of the numerator
+  int arow_den = 0;
+  size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
+  size_t total = 0;
+};
+
+Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den) {
+  Plan p;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    const size_t o = off;
+    off += align_up(bytes);
+    return o;
+  };
+  const size_t TB = (size_t)std::max(T, 1) * (size_t)std::max(B, 1);
+  p.lens = take((size_t)B * 4);
+  if (num) {
+    p.nlp = pad4(std::max(num->max_labels, 1));
+    p.arow_num = pad4(num->max_states + 2);
+    p.xg = take(TB * p.nlp * 4);
+    p.gg = take(TB * p.nlp * 4);
+    p.alpha_num = take(TB * p.arow_num * 4);
+    p.cost_num = take((size_t)B * 8);
+  }
+  p.rowlse = take(TB * 4);
+  if (den) {
+    p.arow_den = pad4(den->max_states + 2);
+    p.alpha_den = take(TB * p.arow_den * 4);
+    p.cost_den = take((size_t)B * 8);
+  }
+  p.total = off;
+  (void)V;
+  return p;
+}
+
+template <typename T>
+void append(std::vector<unsigned char>* blob, const std::vector<T>& v, size_t* off) {
+  *off = blob->size();
+  const size_t bytes = v.size() * sizeof(T);
+  blob->resize(align_up(blob->size() + std::max<size_t>(bytes, 1)));
+  if (bytes) std::memcpy(blob->data() + *off, v.data(), bytes);
+}
+
+int check_graph(const ctcg_graph* g, int B) {
+  if (!g) return CTCG_EINVAL;
+  if (g->num_graphs != 1 && g->num_graphs != B) return CTCG_EINVAL;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return CTCG_ECUDA;
+  if (!g->dev_blob || g->device != dev) return CTCG_ENOTUPLOADED;
+  return CTCG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ctcg_graph_upload(ctcg_graph* g, void* stream) {
+  if (!g) return CTCG_EINVAL;
+  int dev = -1;
+  CTCG_CUDA(cudaGetDevice(&dev));
+  if (g->dev_blob && g->device == dev) return CTCG_OK;
+  if (g->dev_blob) {
+    cudaFree(g->dev_blob);
+    g->dev_blob = nullptr;
+  }
+  std::vector<unsigned char> blob;
+  size_t o[14];
+  append(&blob, g->state_off, &o[0]);
+  append(&blob, g->lab_off, &o[1]);
+  append(&blob, g->lab_list, &o[2]);
+  append(&blob, g->final_w, &o[3]);
+  append(&blob, g->in_ptr, &o[4]);
+  append(&blob, g->in_src, &o[5]);
+  append(&blob, g->in_lab, &o[6]);
+  append(&blob, g->in_clab, &o[7]);
+  append(&blob, g->in_w, &o[8]);
+  append(&blob, g->out_ptr, &o[9]);
+  append(&blob, g->out_dst, &o[10]);
+  append(&blob, g->out_lab, &o[11]);
+  append(&blob, g->out_clab, &o[12]);
+  append(&blob, g->out_w, &o[13]);
+  void* d = nullptr;
+  CTCG_CUDA(cudaMalloc(&d, blob.size()));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemcpyAsync(d, blob.data(), blob.size(), cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);  // blob is a temporary
+  if (e != cudaSuccess) {
+    cudaFree(d);
+    (void)cudaGetLastError();
+    return CTCG_ECUDA;
+  }
+  unsigned char* p = static_cast<unsigned char*>(d);
+  GraphDev& v = g->dev;
+  v.num_graphs = g->num_graphs;
+  v.max_states = g->max_states;
+  v.max_labels = g->max_labels;
+  v.max_in_degree = g->max_in_degree;
+  v.max_out_degree = g->max_out_degree;
+  v.state_off = reinterpret_cast<const int32_t*>(p + o[0]);
+  v.lab_off = reinterpret_cast<const int32_t*>(p + o[1]);
+  v.lab_list = reinterpret_cast<const int32_t*>(p + o[2]);
+  v.final_w = reinterpret_cast<const float*>(p + o[3]);
+  v.in_ptr = reinterpret_cast<const int32_t*>(p + o[4]);
+  v.in_src = reinterpret_cast<const int32_t*>(p + o[5]);
+  v.in_lab = reinterpret_cast<const int32_t*>(p + o[6]);
+  v.in_clab = reinterpret_cast<const int32_t*>(p + o[7]);
+  v.in_w = reinterpret_cast<const float*>(p + o[8]);
+  v.out_ptr = reinterpret_cast<const int32_t*>(p + o[9]);
+  v.out_dst = reinterpret_cast<const int32_t*>(p + o[10]);
+  v.out_lab = reinterpret_cast<const int32_t*>(p + o[11]);
+  v.out_clab = reinterpret_cast<const int32_t*>(p + o[12]);
+  v.out_w = reinterpret_cast<const float*>(p + o[13]);
+  g->dev_blob = d;
+  g->dev_bytes = blob.size();
+  g->device = dev;
+  return CTCG_OK;
+}
+
+void ctcg_graph_free(ctcg_graph* g) {
+  if (!g) return;
+  if (g->dev_blob) {
+    cudaFree(g->dev_blob);
+    (void)cudaGetLastError();
+  }
+  delete g;
+}
+
+size_t ctcg_workspace_bytes(int32_t T, int32_t B, int32_t V, const ctcg_graph* num, const ctcg_graph* den) {
+  return make_plan(T, B, V, num, den).total;
+}
+
+uint64_t ctcg_launch_count(void) { return g_launches; }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+namespace {
+
+int upload_lens(const Plan& p, void* ws, const int32_t* lens_host, int B, cudaStream_t st, int32_t** out) {
+  int32_t* d = reinterpret_cast<int32_t*>(static_cast<unsigned char*>(ws) + p.lens);
+  CTCG_CUDA(cudaMemcpyAsync(d, lens_host, (size_t)B * 4, cudaMemcpyHostToDevice, st));
+  *out = d;
+  return CTCG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, const int32_t* lens_host,
+                      const ctcg_graph* num, const ctcg_graph* den, int32_t normalize, int32_t num_symbols,
+                      const float* grad_scale, float* loss, float* grad, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+  if (!logits || !lens_host || !loss || !workspace || T < 1 || B < 1 || V < 1) return CTCG_EINVAL;
+  if (normalize < CTCG_NORM_NONE || normalize > CTCG_NORM_CONTEXT) return CTCG_EINVAL;
+  int st_ = check_graph(num, B);
+  if (st_ != CTCG_OK) return st_;
+  if (den && (st_ = check_graph(den, B)) != CTCG_OK) return st_;
+  if (normalize == CTCG_NORM_CONTEXT) {
+    // TODO(next): gradient through the per-context softmax (not used by any WSJ YAML)
+    if (grad || den) return CTCG_EUNSUPPORTED;
+    if (num_symbols < 1 || V % num_symbols != 0) return CTCG_EINVAL;
+  }
+  for (int b = 0; b < B; ++b)
+    if (lens_host[b] < 0 || lens_host[b] > T) return CTCG_EINVAL;
+  if (num->max_label >= V || (den && den->max_label >= V)) return CTCG_EINVAL;
+  const Plan p = make_plan(T, B, V, num, den);
+  if (workspace_bytes < p.total) return CTCG_EWORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  int32_t* lens = nullptr;
+  if ((st_ = upload_lens(p, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
+  float* xg = reinterpret_cast<float*>(ws + p.xg);
+  float* gg = reinterpret_cast<float*>(ws + p.gg);
+  double* cost_num = reinterpret_cast<double*>(ws + p.cost_num);
+  double* cost_den = den ? reinterpret_cast<double*>(ws + p.cost_den) : nullptr;
+  float* rowlse = reinterpret_cast<float*>(ws + p.rowlse);
+
+  // 1. compact the label columns each utterance touches
+  CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp,
+                          normalize == CTCG_NORM_CONTEXT ? 2 : 0, num_symbols, st));
+  // 2. numerator forward-backward on the compact columns
+  PathArgs a{};
+  a.g = num->dev;
+  a.x = xg;
+  a.x_stride_t = p.nlp;
+  a.x_stride_b = (long long)T * p.nlp;
+  a.x_scale = 1.f;
+  a.lens = lens;
+  a.T = T;
+  a.B = B;
+  a.alpha_ws = reinterpret_cast<float*>(ws + p.alpha_num);
+  a.alpha_row = p.arow_num;
+  a.cost = cost_num;
+  a.gout = gg;
+  a.g_stride_t = p.nlp;
+  a.g_stride_b = (long long)T * p.nlp;
+  a.g_width = num->max_labels;
+  a.g_sign = 1.f;
+  a.g_scale = nullptr;
+  a.write_grad = grad != nullptr;
+  CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
+
+  // A per-frame softmax normaliser cancels between numerator and denominator.
+  const bool softmax = (normalize == CTCG_NORM_SOFTMAX) && !den;
+  if (den) {
+    // 3a. denominator path sum over the shared decoding graph, writes +gamma_den rows
+    PathArgs d{};
+    d.g = den->dev;
+    d.x = logits;
+    d.x_stride_t = (long long)B * V;
+    d.x_stride_b = V;
+    d.x_scale = kLog2e;
+    d.lens = lens;
+    d.T = T;
+    d.B = B;
+    d.alpha_ws = reinterpret_cast<float*>(ws + p.alpha_den);
+    d.alpha_row = p.arow_den;
+    d.cost = cost_den;
+    d.gout = grad;
+    d.g_stride_t = (long long)B * V;
+    d.g_stride_b = V;
+    d.g_width = V;
+    d.g_sign = 1.f;
+    d.g_scale = grad_scale;
+    d.write_grad = grad != nullptr;
+    CTCG_CUDA(launch_path_fwd_bwd(d, false, st));
+    if (grad) CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
+  } else if (grad || softmax) {
+    // 3b. one streaming pass: softmax(x) - gamma_num (or -gamma_num), row LSE for the loss
+    CTCG_CUDA(launch_rows(logits, T, B, V, lens, num->dev, gg, p.nlp, softmax ? 1 : 0, grad_scale, grad,
+                          rowlse, st));
+  }
+  // 4. per-utterance loss, fixed order, fp64 accumulation
+  CTCG_CUDA(launch_final(T, B, lens, cost_num, cost_den, softmax ? rowlse : nullptr, loss, st));
+  return CTCG_OK;
+}
+
+int ctcg_path_sum(const float* log_probs, int32_t T, int32_t B, int32_t V, const int32_t* lens_host,
+                  const ctcg_graph* graph, float* cost, float* grad, void* workspace,
+                  size_t workspace_bytes, void* stream) {
+  if (!log_probs || !lens_host || !cost || !workspace || T < 1 || B < 1 || V < 1) return CTCG_EINVAL;
+  int st_ = check_graph(graph, B);
+  if (st_ != CTCG_OK) return st_;
+  for (int b = 0; b < B; ++b)
+    if (lens_host[b] < 0 || lens_host[b] > T) return CTCG_EINVAL;
+  if (graph->max_label >= V) return CTCG_EINVAL;
+  const Plan p = make_plan(T, B, V, graph, nullptr);
+  if (workspace_bytes < p.total) return CTCG_EWORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  int32_t* lens = nullptr;
+  if ((st_ = upload_lens(p, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
+  double* cost64 = reinterpret_cast<double*>(ws + p.cost_num);
+  PathArgs d{};
+  d.g = graph->dev;
+  d.x = log_probs;
+  d.x_stride_t = (long long)B * V;
+  d.x_stride_b = V;
+  d.x_scale = kLog2e;
+  d.lens = lens;
+  d.T = T;
+  d.B = B;
+  d.alpha_ws = reinterpret_cast<float*>(ws + p.alpha_num);
+  d.alpha_row = p.arow_num;
+  d.cost = cost64;
+  d.gout = grad;
+  d.g_stride_t = (long long)B * V;
+  d.g_stride_b = V;
+  d.g_width = V;
+  d.g_sign = 1.f;
+  d.g_scale = nullptr;
+  d.write_grad = grad != nullptr;
+  CTCG_CUDA(launch_path_fwd_bwd(d, false, st));
+  CTCG_CUDA(launch_cost_to_float(B, cost64, cost, st));
+  return CTCG_OK;
+}
+
+int ctcg_viterbi(const float* log_probs, int32_t T, int32_t B, int32_t V, const int32_t* lens_host,
+                 const ctcg_graph* graph, float* score, int32_t* frame_labels, void* workspace,
+                 size_t workspace_bytes, void* stream) {
+  if (!log_probs || !lens_host || !score || !frame_labels || !workspace || T < 1 || B < 1 || V < 1)
+    return CTCG_EINVAL;
+  int st_ = check_graph(graph, B);
+  if (st_ != CTCG_OK) return st_;
+  for (int b = 0; b < B; ++b)
+    if (lens_host[b] < 0 || lens_host[b] > T) return CTCG_EINVAL;
+  if (graph->max_label >= V) return CTCG_EINVAL;
+  const Plan p = make_plan(T, B, V, graph, nullptr);
+  if (workspace_bytes < p.total) return CTCG_EWORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  int32_t* lens = nullptr;
+  if ((st_ = upload_lens(p, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
+  CTCG_CUDA(launch_viterbi(log_probs, T, B, V, lens, graph->dev, reinterpret_cast<int32_t*>(ws + p.alpha_num),
+                           p.arow_num, score, frame_labels, st));
+  return CTCG_OK;
+}
+
+int ctcg_path_count(int32_t B, const int32_t* lens_host, const ctcg_graph* graph, uint64_t* counts,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+  if (!lens_host || !counts || !workspace || B < 1) return CTCG_EINVAL;
+  int st_ = check_graph(graph, B);
+  if (st_ != CTCG_OK) return st_;
+  for (int b = 0; b < B; ++b)
+    if (lens_host[b] < 0) return CTCG_EINVAL;
+  const Plan p = make_plan(1, B, 1, nullptr, nullptr);
+  if (workspace_bytes < p.total) return CTCG_EWORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int32_t* lens = nullptr;
+  if ((st_ = upload_lens(p, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
+  CTCG_CUDA(launch_path_count(B, lens, graph->dev, counts, st));
+  return CTCG_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Host-buffer entry point with cached device scratch.
+namespace {
+
+struct HostCache {
+  std::mutex mu;
+  void* logits = nullptr;
+  void* grad = nullptr;
+  void* loss = nullptr;
+  void* ws = nullptr;
+  size_t logits_bytes = 0, grad_bytes = 0, loss_bytes = 0, ws_bytes = 0;
+  int device = -1;
+};
+HostCache g_cache;
+
+int ensure(void** p, size_t* have, size_t need) {
+  if (*have >= need) return CTCG_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr;
+  *have = 0;
+  CTCG_CUDA(cudaMalloc(p, need));
+  *have = need;
+  return CTCG_OK;
+}
+
+}  // namespace
+
+extern "C" int ctcg_loss_host(const float* logits_host, int32_t T, int32_t B, int32_t V,
+                              const int32_t* lens_host, ctcg_graph* num, ctcg_graph* den, int32_t normalize,
+                              int32_t num_symbols, float* loss_host, float* grad_host) {
+  if (!logits_host || !lens_host || !num || !loss_host || T < 1 || B < 1 || V < 1) return CTCG_EINVAL;
+  std::lock_guard<std::mutex> lock(g_cache.mu);
+  int dev = -1;
+  CTCG_CUDA(cudaGetDevice(&dev));
+  if (g_cache.device != dev) {
+    // scratch belongs to one device; drop it when the caller switches
+    if (g_cache.logits) cudaFree(g_cache.logits);
+    if (g_cache.grad) cudaFree(g_cache.grad);
+    if (g_cache.loss) cudaFree(g_cache.loss);
+    if (g_cache.ws) cudaFree(g_cache.ws);
+    g_cache.logits = g_cache.grad = g_cache.loss = g_cache.ws = nullptr;
+    g_cache.logits_bytes = g_cache.grad_bytes = g_cache.loss_bytes = g_cache.ws_bytes = 0;
+    g_cache.device = dev;
+  }
+  int st_;
+  if ((st_ = ctcg_graph_upload(num, nullptr)) != CTCG_OK) return st_;
+  if (den && (st_ = ctcg_graph_upload(den, nullptr)) != CTCG_OK) return st_;
+  const size_t n = (size_t)T * B * V * 4;
+  if ((st_ = ensure(&g_cache.logits, &g_cache.logits_bytes, n)) != CTCG_OK) return st_;
+  if (grad_host && (st_ = ensure(&g_cache.grad, &g_cache.grad_bytes, n)) != CTCG_OK) return st_;
+  if ((st_ = ensure(&g_cache.loss, &g_cache.loss_bytes, (size_t)B * 4)) != CTCG_OK) return st_;
+  const size_t wsb = ctcg_workspace_bytes(T, B, V, num, den);
+  if ((st_ = ensure(&g_cache.ws, &g_cache.ws_bytes, wsb)) != CTCG_OK) return st_;
+  cudaStream_t st = nullptr;
+  CTCG_CUDA(cudaMemcpyAsync(g_cache.logits, logits_host, n, cudaMemcpyHostToDevice, st));
+  st_ = ctcg_loss_fwd_bwd(static_cast<const float*>(g_cache.logits), T, B, V, lens_host, num, den, normalize,
+                          num_symbols, nullptr, static_cast<float*>(g_cache.loss),
+                          grad_host ? static_cast<float*>(g_cache.grad) : nullptr, g_cache.ws, g_cache.ws_bytes,
+                          st);
+  if (st_ != CTCG_OK) return st_;
+  CTCG_CUDA(cudaMemcpyAsync(loss_host, g_cache.loss, (size_t)B * 4, cudaMemcpyDeviceToHost, st));
+  if (grad_host) CTCG_CUDA(cudaMemcpyAsync(grad_host, g_cache.grad, n, cudaMemcpyDeviceToHost, st));
+  CTCG_CUDA(cudaStreamSynchronize(st));
+  return CTCG_OK;
+}

@@ -1,0 +1,94 @@
+// Internal structures shared by the graph compiler, the C ABI and the kernels.
+#pragma once
+
+#include <cstdint>
+#include <vector>
+
+#include "../../include/ctcg_b200.h"
+
+namespace ctcg {
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr double kLn2 = 0.6931471805599453;
+constexpr float kNegInf = -__builtin_huge_valf();
+constexpr float kDeadWeight = -1e19f;  // anything below is "no connection"
+
+// Device view of a batch of graphs in CSR form (all pointers are device
+// pointers into one allocation).  Graph g owns states
+// [state_off[g], state_off[g+1]) of the per-state arrays and rows
+// [state_off[g]+g, state_off[g+1]+g] of the row-pointer arrays; row pointers
+// hold absolute arc indices.
+struct GraphDev {
+  int32_t num_graphs;
+  int32_t max_states;
+  int32_t max_labels;
+  int32_t max_in_degree;
+  int32_t max_out_degree;
+  const int32_t* state_off;  // [G+1]
+  const int32_t* lab_off;    // [G+1]
+  const int32_t* lab_list;   // distinct labels of graph g, ascending
+  const float* final_w;      // [total_states], natural log, -inf = not final
+  const int32_t* in_ptr;     // CSR by destination
+  const int32_t* in_src;
+  const int32_t* in_lab;     // class id
+  const int32_t* in_clab;    // index into the graph's lab_list
+  const float* in_w;         // natural log
+  const int32_t* out_ptr;    // CSR by source
+  const int32_t* out_dst;
+  const int32_t* out_lab;
+  const int32_t* out_clab;
+  const float* out_w;
+};
+
+// Factorised description of the bi-char decoding graph (fst_utils.py:765-817):
+// alpha_new[(c2,l2)] = p[cls(c2,l2)] * (Q[c2] + loop(c2,l2) * alpha[(c2,l2)]),
+// Q[c2] = [c2 != 0] * sum_c1 alpha[(c1,c2)] + alpha[(c2,0)].
+struct Structured {
+  int32_t kind;  // 0 none, 1 mono decoding, 2 bi-char decoding
+  int32_t S;
+  int32_t allow_nonblank_selfloops;
+  int32_t use_contextual_blanks;
+  int32_t loop_using_symbol_repetitions;
+};
+
+}  // namespace ctcg
+
+struct ctcg_graph {
+  int32_t num_graphs = 0;
+  int32_t max_states = 0, max_in_degree = 0, max_out_degree = 0, max_labels = 0;
+  int32_t max_label = -1;  // largest class id on any arc
+  std::vector<int32_t> state_off, lab_off, lab_list;
+  std::vector<float> final_w;
+  std::vector<int32_t> in_ptr, in_src, in_lab, in_clab;
+  std::vector<float> in_w;
+  std::vector<int32_t> out_ptr, out_dst, out_lab, out_clab;
+  std::vector<float> out_w;
+  ctcg::Structured structured{0, 0, 0, 0, 0};
+  // device mirror
+  int device = -1;
+  void* dev_blob = nullptr;
+  size_t dev_bytes = 0;
+  ctcg::GraphDev dev{};
+};
+
+namespace ctcg {
+
+// One arc of the intermediate (pre-CSR) representation.
+struct Arc {
+  int32_t src, dst, label;
+  float weight;   // log-prob
+  int32_t olabel; // emitted symbol (0 = none); only used while composing
+};
+
+struct RawGraph {
+  int32_t n = 0;
+  std::vector<Arc> arcs;
+  std::vector<float> final_w;  // -inf = not final
+};
+
+int build_decoding(const ctcg_topology& topo, RawGraph* out);
+int compose_with_chain(const RawGraph& dec, const std::vector<std::vector<int32_t>>& dec_out,
+                       const int32_t* labels, int64_t n_labels, RawGraph* out);
+int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out);
+
+}  // namespace ctcg

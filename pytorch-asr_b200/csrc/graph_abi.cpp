@@ -1,0 +1,223 @@
+// extern "C" entry points of the graph compiler (host only, no CUDA calls, so
+// DataLoader worker processes can use them without creating a CUDA context).
+#include <algorithm>
+#include <cmath>
+#include <new>
+#include <tuple>
+
+#include "ctcg_internal.h"
+
+using namespace ctcg;
+
+namespace {
+
+void index_out_arcs(const RawGraph& g, std::vector<std::vector<int32_t>>* out) {
+  out->assign(g.n, {});
+  for (int32_t i = 0; i < static_cast<int32_t>(g.arcs.size()); ++i) (*out)[g.arcs[i].src].push_back(i);
+}
+
+void mark_structured(const ctcg_topology& t, ctcg_graph* g) {
+  g->structured.kind = t.context_order;
+  g->structured.S = t.num_symbols;
+  bool loops = t.allow_nonblank_selfloops != 0;
+  bool ctx = t.use_contextual_blanks != 0;
+  if (t.loop_using_symbol_repetitions) {
+    loops = false;
+    ctx = true;
+  }
+  g->structured.allow_nonblank_selfloops = loops;
+  g->structured.use_contextual_blanks = ctx;
+  g->structured.loop_using_symbol_repetitions = t.loop_using_symbol_repetitions != 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ctcg_decoding_graph(const ctcg_topology* topo, ctcg_graph** out) {
+  if (!topo || !out) return CTCG_EINVAL;
+  try {
+    std::vector<RawGraph> gs(1);
+    int st = build_decoding(*topo, &gs[0]);
+    if (st != CTCG_OK) return st;
+    st = finalize_graphs(gs, out);
+    if (st == CTCG_OK) mark_structured(*topo, *out);
+    return st;
+  } catch (const std::bad_alloc&) {
+    return CTCG_ENOMEM;
+  }
+}
+
+int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels, const int64_t* offsets,
+                         int32_t B, ctcg_graph** out) {
+  if (!topo || !offsets || !out || B < 0) return CTCG_EINVAL;
+  try {
+    RawGraph dec;
+    int st = build_decoding(*topo, &dec);
+    if (st != CTCG_OK) return st;
+    std::vector<std::vector<int32_t>> dec_out;
+    index_out_arcs(dec, &dec_out);
+    std::vector<RawGraph> gs(B);
+    std::vector<int32_t> lab;
+    const int32_t S = topo->num_symbols;
+    for (int32_t b = 0; b < B; ++b) {
+      const int64_t lo = offsets[b], hi = offsets[b + 1];
+      if (hi < lo) return CTCG_EINVAL;
+      lab.assign(labels + lo, labels + hi);
+      // fst_utils.py:595-596: a transcript holding any id above S is taken modulo S
+      bool any_big = false;
+      for (int32_t v : lab) {
+        if (v < 0) return CTCG_EINVAL;
+        any_big |= v > S;
+      }
+      if (any_big)
+        for (int32_t& v : lab) v %= S;
+      st = compose_with_chain(dec, dec_out, lab.data(), static_cast<int64_t>(lab.size()), &gs[b]);
+      if (st != CTCG_OK) return st;
+    }
+    return finalize_graphs(gs, out);
+  } catch (const std::bad_alloc&) {
+    return CTCG_ENOMEM;
+  }
+}
+
+int ctcg_graph_from_padded(const int64_t* pred, const int64_t* lab_in, const float* w_in,
+                           const float* final_w, const int64_t* succ, const int64_t* lab_out,
+                           const float* w_out, int32_t G, int32_t N, int32_t K_in, int32_t K_out,
+                           float nc_weight, ctcg_graph** out) {
+  if (!pred || !lab_in || !w_in || !final_w || !out || G < 1 || N < 1 || K_in < 0) return CTCG_EINVAL;
+  (void)succ;
+  (void)lab_out;
+  (void)w_out;
+  (void)K_out;  // the out-edge half carries the same arcs; the in-edge half is authoritative
+  try {
+    const float dead = nc_weight * 0.5f;
+    std::vector<RawGraph> gs(G);
+    for (int32_t g = 0; g < G; ++g) {
+      RawGraph& r = gs[g];
+      // trailing all-padding states of a batch-padded graph are kept: they are dead and cost nothing
+      r.n = N;
+      r.final_w.resize(N);
+      for (int32_t d = 0; d < N; ++d) {
+        const float f = final_w[static_cast<size_t>(g) * N + d];
+        r.final_w[d] = (f > dead) ? f : kNegInf;
+        for (int32_t k = 0; k < K_in; ++k) {
+          const size_t i = (static_cast<size_t>(g) * N + d) * K_in + k;
+          if (!(w_in[i] > dead)) continue;
+          const int64_t s = pred[i], l = lab_in[i];
+          if (s < 0 || s >= N) return CTCG_EINVAL;
+          if (l < 0) return CTCG_EEPS;
+          r.arcs.push_back({static_cast<int32_t>(s), d, static_cast<int32_t>(l), w_in[i], 0});
+        }
+      }
+    }
+    return finalize_graphs(gs, out);
+  } catch (const std::bad_alloc&) {
+    return CTCG_ENOMEM;
+  }
+}
+
+int ctcg_graph_from_arcs(const int32_t* src, const int32_t* dst, const int32_t* label,
+                         const float* weight, const int64_t* arc_offsets,
+                         const int32_t* state_counts, const float* final_w, int32_t G,
+                         ctcg_graph** out) {
+  if (!src || !dst || !label || !weight || !arc_offsets || !state_counts || !final_w || !out || G < 1)
+    return CTCG_EINVAL;
+  try {
+    std::vector<RawGraph> gs(G);
+    size_t so = 0;
+    for (int32_t g = 0; g < G; ++g) {
+      RawGraph& r = gs[g];
+      r.n = state_counts[g];
+      if (r.n < 1) return CTCG_EINVAL;
+      r.final_w.assign(final_w + so, final_w + so + r.n);
+      so += r.n;
+      for (int64_t i = arc_offsets[g]; i < arc_offsets[g + 1]; ++i) {
+        if (!(weight[i] > kDeadWeight)) continue;
+        r.arcs.push_back({src[i], dst[i], label[i], weight[i], 0});
+      }
+    }
+    return finalize_graphs(gs, out);
+  } catch (const std::bad_alloc&) {
+    return CTCG_ENOMEM;
+  }
+}
+
+int ctcg_graph_get_info(const ctcg_graph* g, ctcg_graph_info* info) {
+  if (!g || !info) return CTCG_EINVAL;
+  info->num_graphs = g->num_graphs;
+  info->max_states = g->max_states;
+  info->max_in_degree = g->max_in_degree;
+  info->max_out_degree = g->max_out_degree;
+  info->max_labels = g->max_labels;
+  info->structured = g->structured.kind == 2 ? 1 : 0;
+  info->on_device = g->device;
+  info->reserved = 0;
+  info->total_states = g->state_off.back();
+  info->total_arcs = static_cast<int64_t>(g->in_src.size());
+  return CTCG_OK;
+}
+
+int ctcg_graph_padded_dims(const ctcg_graph* g, int32_t index, int32_t* n_states, int32_t* k_in,
+                           int32_t* k_out) {
+  if (!g || index < 0 || index >= g->num_graphs) return CTCG_EINVAL;
+  const int32_t so = g->state_off[index], n = g->state_off[index + 1] - so, ro = so + index;
+  int32_t ki = 0, ko = 0;
+  for (int32_t s = 0; s < n; ++s) {
+    ki = std::max(ki, g->in_ptr[ro + s + 1] - g->in_ptr[ro + s]);
+    ko = std::max(ko, g->out_ptr[ro + s + 1] - g->out_ptr[ro + s]);
+  }
+  if (n_states) *n_states = n;
+  if (k_in) *k_in = ki;
+  if (k_out) *k_out = ko;
+  return CTCG_OK;
+}
+
+int ctcg_graph_export_padded(const ctcg_graph* g, int32_t index, int32_t out_edges, float nc_weight,
+                             int64_t* states, int64_t* labels, float* weights, float* terminal) {
+  if (!g || index < 0 || index >= g->num_graphs || !states || !labels || !weights || !terminal)
+    return CTCG_EINVAL;
+  int32_t n, ki, ko;
+  ctcg_graph_padded_dims(g, index, &n, &ki, &ko);
+  const int32_t K = out_edges ? ko : ki;
+  const int32_t so = g->state_off[index], ro = so + index;
+  const int32_t* ptr = out_edges ? g->out_ptr.data() : g->in_ptr.data();
+  const int32_t* other = out_edges ? g->out_dst.data() : g->in_src.data();
+  const int32_t* lab = out_edges ? g->out_lab.data() : g->in_lab.data();
+  const float* w = out_edges ? g->out_w.data() : g->in_w.data();
+  for (int32_t s = 0; s < n; ++s) {
+    terminal[s] = (g->final_w[so + s] > kDeadWeight) ? g->final_w[so + s] : nc_weight;
+    const int32_t lo = ptr[ro + s], hi = ptr[ro + s + 1];
+    for (int32_t k = 0; k < K; ++k) {
+      const size_t o = static_cast<size_t>(s) * K + k;
+      if (lo + k < hi) {
+        states[o] = other[lo + k];
+        labels[o] = lab[lo + k];
+        weights[o] = w[lo + k];
+      } else {
+        states[o] = 0;
+        labels[o] = 0;
+        weights[o] = nc_weight;
+      }
+    }
+  }
+  return CTCG_OK;
+}
+
+const char* ctcg_strerror(int status) {
+  switch (status) {
+    case CTCG_OK: return "ok";
+    case CTCG_EINVAL: return "invalid argument";
+    case CTCG_ESTART: return "FST starting state is not 0";
+    case CTCG_ENONDET: return "FST is not deterministic";
+    case CTCG_EEPS: return "FST has eps-transitions";
+    case CTCG_ECUDA: return "CUDA error (no device, or a runtime call failed)";
+    case CTCG_ENOMEM: return "out of host memory";
+    case CTCG_EWORKSPACE: return "workspace too small";
+    case CTCG_EUNSUPPORTED: return "unsupported configuration";
+    case CTCG_ENOTUPLOADED: return "graph not uploaded to the device";
+    default: return "unknown status";
+  }
+}
+
+}  // extern "C"

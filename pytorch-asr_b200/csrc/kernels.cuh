@@ -1,0 +1,67 @@
+// Launch wrappers of the CUDA kernels (definitions in kernels_*.cu).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "ctcg_internal.h"
+
+namespace ctcg {
+
+// Arguments of the generic log-semiring forward-backward over CSR graphs.
+struct PathArgs {
+  GraphDev g;
+  const float* x;         // scores; element (t, b, l) at x[t*x_stride_t + b*x_stride_b + l]
+  long long x_stride_t;
+  long long x_stride_b;
+  float x_scale;          // multiplies x on load (log2(e) for natural-log input, 1 if prescaled)
+  const int32_t* lens;    // device, [B]
+  int32_t T, B;
+  float* alpha_ws;        // [B][T][row] normalised alpha_t in log2 units, + frame offset (2 floats)
+  int32_t alpha_row;      // floats per row: pad4(max_states + 2)
+  double* cost;           // [B] natural-log path sum
+  float* gout;            // posterior rows; element (t, b, l) at gout[t*g_stride_t + b*g_stride_b + l]
+  long long g_stride_t;
+  long long g_stride_b;
+  int32_t g_width;        // row width written per frame (max_labels or V)
+  float g_sign;
+  const float* g_scale;   // nullable, per-utterance multiplier
+  int32_t write_grad;
+};
+
+// compact = 1: x / gout are the per-utterance compact label columns produced by
+// launch_gather (16-byte aligned rows, prescaled), staged through a cp.async ring.
+cudaError_t launch_path_fwd_bwd(const PathArgs& a, bool compact, cudaStream_t st);
+
+// xg[b][t][j] = logits[t][b][lab_list_b[j]] * log2(e) for t < lens[b]
+cudaError_t launch_gather(const float* logits, int T, int B, int V, const int32_t* lens,
+                          const GraphDev& num, float* xg, int nlp, int normalize, int S,
+                          cudaStream_t st);
+
+// Row pass: mode 1 grad = softmax(x) - scatter(gg), rowlse = logsumexp(x);
+//           mode 0 grad = -scatter(gg).  Rows t >= lens[b] are zeroed.
+cudaError_t launch_rows(const float* logits, int T, int B, int V, const int32_t* lens,
+                        const GraphDev& num, const float* gg, int nlp, int mode,
+                        const float* g_scale, float* grad, float* rowlse, cudaStream_t st);
+
+// grad[t][b][lab_list_b[j]] -= scale_b * gg[b][t][j]
+cudaError_t launch_scatter_sub(int T, int B, int V, const int32_t* lens, const GraphDev& num,
+                               const float* gg, int nlp, const float* g_scale, float* grad,
+                               cudaStream_t st);
+
+// loss[b] = -cost_num[b] + cost_den[b] + sum_{t<len} rowlse[t][b]   (nullable terms skipped)
+cudaError_t launch_final(int T, int B, const int32_t* lens, const double* cost_num,
+                         const double* cost_den, const float* rowlse, float* loss, cudaStream_t st);
+
+cudaError_t launch_cost_to_float(int B, const double* cost, float* out, cudaStream_t st);
+
+cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* lens,
+                           const GraphDev& g, int32_t* back_ws, int row, float* score,
+                           int32_t* frame_labels, cudaStream_t st);
+
+cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uint64_t* counts,
+                              cudaStream_t st);
+
+// Incremented by every launch_* above.
+extern unsigned long long g_launches;
+
+}  // namespace ctcg

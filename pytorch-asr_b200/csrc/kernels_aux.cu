@@ -1,0 +1,189 @@
+// Tropical (Viterbi) and counting semirings on the same CSR skeleton.
+//
+// Viterbi replaces path_reduction(red_kind='viterbi') + the gradient arg-min
+// read-out of FSTDecoder.decode (att_speech/fst_utils.py:366-397,
+// modules/decoders/advanced_decoder.py:546-554) and the dense
+// raw_generic_viterbi back-trace (modules/ctc_losses.py:412-457): instead of
+// autograd through T cloned alphas it keeps one back-pointer per (frame, state)
+// and walks them once.  Ties take the first arc in (src, label, weight) order,
+// which is what torch.max over the reference's sorted arc lists returns.
+//
+// Path counting is the integer counterpart of path_reduction on all-zero
+// log-probs: exact modulo 2^64.
+#include "device_utils.cuh"
+#include "kernels.cuh"
+
+namespace ctcg {
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int NWARP = NT / 32;
+
+__global__ void __launch_bounds__(NT) viterbi_kernel(const float* __restrict__ x, int T, int B, int V,
+                                                     const int32_t* __restrict__ lens, GraphDev g,
+                                                     int32_t* __restrict__ back_ws, int row,
+                                                     float* __restrict__ score, int32_t* __restrict__ frame_labels) {
+  extern __shared__ __align__(16) float vbuf[];  // 2*np + NWARP*2 + NWARP ints
+  const int np = pad4(g.max_states);
+  float* wred = vbuf + 2 * np;
+  float* fval = wred + 2 * NWARP;
+  int* fidx = reinterpret_cast<int*>(fval + NWARP);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int gi = g.num_graphs == 1 ? 0 : b;
+  const int so = g.state_off[gi], n = g.state_off[gi + 1] - so, ro = so + gi;
+  const int len = min(lens[b], T);
+  const int32_t* in_ptr = g.in_ptr + ro;
+  const float* final_w = g.final_w + so;
+  int32_t* back = back_ws + (long long)b * T * row;
+  float* v_cur = vbuf;
+  float* v_nxt = vbuf + np;
+  for (int s = tid; s < n; s += NT) v_cur[s] = s == 0 ? 0.f : neg_inf();
+  if (tid < 2 * NWARP) wred[tid] = 0.f;
+  for (int t = len + tid; t < T; t += NT) frame_labels[(long long)t * B + b] = 0;
+  double c = 0.0;
+  for (int t = 0; t < len; ++t) {
+    __syncthreads();
+    float mx = wred[(t & 1) * NWARP];
+#pragma unroll
+    for (int i = 1; i < NWARP; ++i) mx = fmaxf(mx, wred[(t & 1) * NWARP + i]);
+    if (!(mx > neg_inf())) mx = 0.f;
+    c += (double)mx;
+    const float* xrow = x + ((long long)t * B + b) * V;
+    float lm = neg_inf();
+    for (int s = tid; s < n; s += NT) {
+      float best = neg_inf();
+      int arg = -1;
+      for (int e = in_ptr[s]; e < in_ptr[s + 1]; ++e) {
+        const float v = g.in_w[e] + (v_cur[g.in_src[e]] - mx) + xrow[g.in_lab[e]];
+        if (v > best) {
+          best = v;
+          arg = e;
+        }
+      }
+      v_nxt[s] = best;
+      back[(long long)t * row + s] = arg;
+      lm = fmaxf(lm, best);
+    }
+    lm = warp_max(lm);
+    if (lane == 0) wred[((t + 1) & 1) * NWARP + warp] = lm;
+    float* tmp = v_cur;
+    v_cur = v_nxt;
+    v_nxt = tmp;
+  }
+  __syncthreads();
+  float mx = 0.f;
+  if (len > 0) {
+    mx = wred[(len & 1) * NWARP];
+#pragma unroll
+    for (int i = 1; i < NWARP; ++i) mx = fmaxf(mx, wred[(len & 1) * NWARP + i]);
+    if (!(mx > neg_inf())) mx = 0.f;
+  }
+  c += (double)mx;
+  // best final state, lowest index on ties
+  float bv = neg_inf();
+  int bi = 0x7fffffff;
+  for (int s = tid; s < n; s += NT) {
+    const float v = (v_cur[s] - mx) + final_w[s];
+    if (v > bv) {
+      bv = v;
+      bi = s;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > bv || (ov == bv && oi < bi)) {
+      bv = ov;
+      bi = oi;
+    }
+  }
+  if (lane == 0) {
+    fval[warp] = bv;
+    fidx[warp] = bi;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    for (int i = 1; i < NWARP; ++i)
+      if (fval[i] > bv || (fval[i] == bv && fidx[i] < bi)) {
+        bv = fval[i];
+        bi = fidx[i];
+      }
+    if (!(bv > neg_inf())) {
+      score[b] = -1e20f;
+      for (int t = 0; t < len; ++t) frame_labels[(long long)t * B + b] = 0;
+    } else {
+      score[b] = (float)(c + (double)bv);
+      int s = bi;
+      for (int t = len - 1; t >= 0; --t) {
+        const int e = back[(long long)t * row + s];
+        frame_labels[(long long)t * B + b] = g.in_lab[e];
+        s = g.in_src[e];
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(NT) count_kernel(int B, const int32_t* __restrict__ lens, GraphDev g,
+                                                   unsigned long long* __restrict__ counts) {
+  extern __shared__ __align__(16) unsigned long long cbuf[];  // 2*n + NT
+  const int tid = threadIdx.x;
+  const int b = blockIdx.x;
+  const int gi = g.num_graphs == 1 ? 0 : b;
+  const int so = g.state_off[gi], n = g.state_off[gi + 1] - so, ro = so + gi;
+  const int32_t* in_ptr = g.in_ptr + ro;
+  unsigned long long* cur = cbuf;
+  unsigned long long* nxt = cbuf + g.max_states;
+  unsigned long long* red = cbuf + 2 * g.max_states;
+  for (int s = tid; s < n; s += NT) cur[s] = s == 0 ? 1ull : 0ull;
+  const int len = lens[b];
+  for (int t = 0; t < len; ++t) {
+    __syncthreads();
+    for (int s = tid; s < n; s += NT) {
+      unsigned long long acc = 0;
+      for (int e = in_ptr[s]; e < in_ptr[s + 1]; ++e) acc += cur[g.in_src[e]];
+      nxt[s] = acc;
+    }
+    unsigned long long* tmp = cur;
+    cur = nxt;
+    nxt = tmp;
+  }
+  __syncthreads();
+  unsigned long long acc = 0;
+  for (int s = tid; s < n; s += NT)
+    if (g.final_w[so + s] > kDeadWeight) acc += cur[s];
+  red[tid] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long tot = 0;
+    for (int i = 0; i < NT; ++i) tot += red[i];
+    counts[b] = tot;
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* lens, const GraphDev& g,
+                           int32_t* back_ws, int row, float* score, int32_t* frame_labels, cudaStream_t st) {
+  const size_t smem = (size_t)(2 * pad4(g.max_states) + 4 * NWARP) * 4;
+  if (smem > 200 * 1024) return cudaErrorInvalidConfiguration;
+  cudaError_t e = cudaFuncSetAttribute(viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  viterbi_kernel<<<B, NT, smem, st>>>(x, T, B, V, lens, g, back_ws, row, score, frame_labels);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uint64_t* counts, cudaStream_t st) {
+  const size_t smem = (size_t)(2 * g.max_states + NT) * 8;
+  if (smem > 200 * 1024) return cudaErrorInvalidConfiguration;
+  cudaError_t e = cudaFuncSetAttribute(count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  count_kernel<<<B, NT, smem, st>>>(B, lens, g, reinterpret_cast<unsigned long long*>(counts));
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+}  // namespace ctcg

@@ -1,0 +1,207 @@
+"""Host-side mirror of the FST-based entries of ``att_speech/modules/ctc_losses.py``
+and of the loss glue of ``FSTDecoder`` (``modules/decoders/advanced_decoder.py``).
+
+* :func:`get_normalized_acts`  <- ctc_losses.py:29-43
+* :func:`ctc_fst_loss`         <- ctc_losses.py:617-657   (``ctc_loss_fn`` plugin signature)
+* :func:`ctc_fst_global_loss`  <- ctc_losses.py:663-717
+* :func:`fst_loss`             <- advanced_decoder.py:444-517 fused into one library call
+* :class:`FSTLossMixin`        <- ``FSTDecoder.get_fst_loss`` / ``forward`` (:454-534)
+
+The fused path never materialises ``log_softmax(logits)``, the max-shifted copy,
+``lalphas`` or the dense numerator gradient: the library reads the logits and
+writes d(loss)/d(logits) directly.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+from .fst_utils import CTCGraphGen, PackedGraphs, _as_graph, _check_lens, path_reduction
+
+
+def get_normalized_acts(acts, acts_lens, num_symbols, context_order, normalize_by_dim,
+                        normalize_logits=True):
+    """ctc_losses.py:29-43 (plain torch: only used on the non-fused entry points)."""
+    assert context_order == 1 or num_symbols
+    del acts_lens
+    if normalize_by_dim:
+        act_size = acts.size()
+        new_act_size = (act_size[:2] + (num_symbols,) * context_order)
+        acts = acts.view(*new_act_size)
+        acts = torch.nn.functional.log_softmax(acts, normalize_by_dim + 2)
+        acts = acts.view(*act_size)
+    elif normalize_logits:
+        acts = torch.nn.functional.log_softmax(acts, dim=-1)
+    return acts
+
+
+def _norm_mode(normalize_by_dim):
+    if normalize_by_dim is None:
+        return _lib.NORM_NONE
+    if normalize_by_dim == 0:
+        return _lib.NORM_SOFTMAX
+    return _lib.NORM_CONTEXT
+
+
+class _FstLoss(torch.autograd.Function):
+    """loss_b = -cost_num_b(lp) [+ cost_den_b(lp)], lp = normalise(logits); one call."""
+
+    @staticmethod
+    def forward(ctx, logits, act_lens, num, den, normalize, num_symbols):
+        loss, grad = _lib.loss_fwd_bwd(logits, act_lens, num, den, normalize, num_symbols,
+                                       need_grad=logits.requires_grad)
+        ctx.grads = grad
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        g = ctx.grads
+        ctx.grads = None  # single backward, like the reference's ctx.grads (fst_utils.py:473,484)
+        if grad_output.stride() == (0,):  # .sum().backward(): one broadcast scalar
+            g.mul_(grad_output[0])
+        else:
+            g.mul_(grad_output[None, :, None])
+        return g, None, None, None, None, None
+
+
+def fst_loss(logits, act_lens, numerator, denominator=None, normalize_by_dim=None,
+             num_symbols=0):
+    """Per-utterance loss of ``FSTDecoder.get_fst_loss`` on raw ``fc`` outputs.
+
+    ``numerator`` / ``denominator``: native graphs or the reference's padded
+    matrices; ``denominator=None`` is ``denominator_red: none``.
+    """
+    lens = _check_lens(act_lens)
+    num = _as_graph(numerator)
+    den = _as_graph(denominator) if denominator is not None else None
+    assert num.num_graphs in (1, logits.size(1))
+    return _FstLoss.apply(logits, lens, num, den, _norm_mode(normalize_by_dim), int(num_symbols or 0))
+
+
+def _labels_to_batch(labels, label_lens):
+    seqs, ls = [], 0
+    labels = labels.cpu().numpy() if torch.is_tensor(labels) else np.asarray(labels)
+    for b in range(len(label_lens)):
+        le = ls + int(label_lens[b])
+        seqs.append(labels[ls:le])
+        ls = le
+    return seqs
+
+
+def _numerator_from_batch(other_data_in_batch, labels, label_lens, S, context_order, gg_kwargs):
+    if other_data_in_batch and "graph_matrices" in other_data_in_batch:
+        return _as_graph(other_data_in_batch["graph_matrices"])
+    graph_gen = CTCGraphGen(context_order=context_order, graph_build_args=gg_kwargs,
+                            num_symbols=S, for_forward_only=False)
+    return graph_gen.get_training_graphs(_labels_to_batch(labels, label_lens))
+
+
+def ctc_fst_loss(acts, labels, act_lens, label_lens, num_symbols=0, context_order=1,
+                 normalize_by_dim=None, allow_nonblank_selfloops=True,
+                 loop_using_symbol_repetitions=False, other_data_in_batch=None,
+                 eval_repeats_in_context=False, neg_inf=-1e20):
+    """ctc_losses.py:617-657: normalise, build/fetch the training graphs, -path sum."""
+    assert not (eval_repeats_in_context and loop_using_symbol_repetitions)
+    S = acts.size(2)
+    gg_kwargs = {}
+    if context_order == 2:
+        S = int(round(np.sqrt(S)))
+        gg_kwargs = dict(allow_nonblank_selfloops=allow_nonblank_selfloops,
+                         loop_using_symbol_repetitions=loop_using_symbol_repetitions,
+                         eval_repeats_in_context=eval_repeats_in_context)
+    num = _numerator_from_batch(other_data_in_batch, labels, label_lens, S, context_order, gg_kwargs)
+    # the reference always normalises here (normalize_logits=True): None -> softmax over V
+    mode = _lib.NORM_SOFTMAX if not normalize_by_dim else _lib.NORM_CONTEXT
+    if mode == _lib.NORM_CONTEXT:
+        log_probs = get_normalized_acts(acts, act_lens, num_symbols, context_order, normalize_by_dim)
+        return -path_reduction(log_probs, act_lens, num, neg_inf=neg_inf)
+    return _FstLoss.apply(acts, _check_lens(act_lens), num, None, mode, int(num_symbols or 0))
+
+
+_ctc_fst_cache = {}
+
+
+def ctc_fst_global_loss(acts, labels, act_lens, label_lens, num_symbols=0, context_order=1,
+                        normalize_by_dim=None, allow_nonblank_selfloops=True,
+                        loop_using_symbol_repetitions=False, other_data_in_batch=None,
+                        eval_repeats_in_context=False, neg_inf=-1e20):
+    """ctc_losses.py:663-717: numerator minus the decoding-graph denominator on raw acts."""
+    S = acts.size(2)
+    key = (context_order, S, allow_nonblank_selfloops, loop_using_symbol_repetitions,
+           eval_repeats_in_context)
+    gg_kwargs = {}
+    if context_order == 2:
+        S = int(round(np.sqrt(S)))
+        gg_kwargs = dict(allow_nonblank_selfloops=allow_nonblank_selfloops,
+                         loop_using_symbol_repetitions=loop_using_symbol_repetitions,
+                         eval_repeats_in_context=eval_repeats_in_context)
+    if key not in _ctc_fst_cache:
+        _ctc_fst_cache[key] = _lib.Graph.decoding(context_order, S, **gg_kwargs)
+    den = _ctc_fst_cache[key]
+    num = _numerator_from_batch(other_data_in_batch, labels, label_lens, S, context_order, gg_kwargs)
+    return _FstLoss.apply(acts, _check_lens(act_lens), num, den, _lib.NORM_NONE, 0)
+
+
+class FSTLossMixin(object):
+    """Drop-in replacement of ``FSTDecoder.get_fst_loss`` / ``forward`` / ``logits``.
+
+    Combine with the reference decoder, e.g.::
+
+        class FSTDecoder(FSTLossMixin, att_speech...advanced_decoder.FSTDecoder): pass
+
+    or use :class:`FSTLoss` stand-alone on the output of any ``fc`` layer.  Expects
+    ``self.graph_generator`` (a :class:`CTCGraphGen` of this package),
+    ``self.normalize_by_dim``, ``self.numerator_red``, ``self.denominator_red``,
+    ``self.num_symbols`` as the reference's ``__init__`` sets them (:403-411).
+    """
+
+    def logits(self, encoded, encoded_lens=None, extra_ret=None):
+        # the normalisation of advanced_decoder.py:448-451 is fused into the loss kernel
+        logits = self.fc(encoded)
+        if extra_ret is not None:
+            extra_ret["unnormed_logits"] = logits
+        return logits
+
+    def get_fst_loss(self, logits, encoded_lens, texts, text_lens, other_data_in_batch):
+        gg = self.graph_generator
+        if other_data_in_batch and "graph_matrices" in other_data_in_batch:
+            num = _as_graph(other_data_in_batch["graph_matrices"], gg.nc_weight)
+        else:
+            num = gg.get_training_matrices_batch(texts, text_lens, native=True).graph
+        assert self.numerator_red in ("logsumexp", "logsumexp_fwb", "logsumexp_autodiff")
+        den = None
+        if self.denominator_red != "none":
+            assert self.denominator_red in ("logsumexp", "logsumexp_fwb", "logsumexp_autodiff")
+            den = gg.get_decoding_graph()
+        return _FstLoss.apply(logits, _check_lens(encoded_lens), num, den,
+                              _norm_mode(self.normalize_by_dim), int(self.num_symbols or 0))
+
+    def forward(self, encoded, encoded_lens, texts, text_lens, spkids=None, **other_data_in_batch):
+        logits = self.logits(encoded, encoded_lens)
+        fst_loss_ = self.get_fst_loss(logits, encoded_lens, texts, text_lens, other_data_in_batch).sum()
+        return {"fst_loss": fst_loss_, "loss": fst_loss_}
+
+
+class FSTLoss(FSTLossMixin, torch.nn.Module):
+    """Stand-alone loss head with ``FSTDecoder``'s constructor arguments that
+    matter for the loss (advanced_decoder.py:395-411); ``fc`` defaults to identity
+    so it can be applied to logits directly."""
+
+    def __init__(self, graph_generator, num_symbols=None, normalize_by_dim=None,
+                 numerator_red="logsumexp", denominator_red="logsumexp", fc=None):
+        super(FSTLoss, self).__init__()
+        if isinstance(graph_generator, dict):
+            kw = dict(graph_generator)
+            kw.pop("class_name", None)
+            kw.setdefault("num_symbols", num_symbols)
+            graph_generator = CTCGraphGen(**kw)
+        self.graph_generator = graph_generator
+        self.num_symbols = graph_generator.num_symbols
+        self.context_order = graph_generator.context_order
+        self.normalize_by_dim = normalize_by_dim
+        self.numerator_red = numerator_red
+        self.denominator_red = denominator_red
+        self.fc = fc if fc is not None else torch.nn.Identity()
+        if self.normalize_by_dim not in [None, 0]:
+            assert graph_generator.num_classes == graph_generator.num_symbols ** self.context_order

@@ -1,0 +1,262 @@
+"""Host-side mirror of the hot-path half of ``att_speech/fst_utils.py``.
+
+Same names, argument meaning and error behaviour as the reference, so that
+``att_speech.fst_utils.path_reduction`` can be rebound to this module's and
+``graph_generator.class_name: CTCGraphGen`` can point here:
+
+* :func:`path_reduction`                 <- fst_utils.py:322-397
+* :func:`path_logsumexp`                 <- fst_utils.py:400-488 (``PathLogSumExp``)
+* :func:`batch_training_graph_matrices`  <- fst_utils.py:491-521
+* :func:`make_full_ngram_table`          <- fst_utils.py:524-534
+* :class:`CTCGraphGen`                   <- fst_utils.py:546-676, :1053-1068
+
+Everything numeric runs in the CUDA library behind ``_lib``; graph construction
+runs in its C++ graph compiler (no OpenFst).  No CPU fallback.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import Graph
+
+
+class PackedGraphs(list):
+    """What :meth:`CTCGraphGen.get_training_matrices_batch` returns natively.
+
+    Behaves as the reference's list of padded matrices only on demand (they are
+    materialised lazily through ``ctcg_graph_export_padded``); ``.graph`` is the
+    CSR handle the kernels consume, so no ``(B,N,K)`` int64 tensors are built or
+    copied host-to-device on the training path.
+    """
+
+    def __init__(self, graph, nc_weight=-1e20):
+        super(PackedGraphs, self).__init__()
+        self.graph = graph
+        self.nc_weight = nc_weight
+
+    def to_padded(self, device="cpu"):
+        mats = [padded_matrices(self.graph, i, self.nc_weight) for i in range(self.graph.num_graphs)]
+        return batch_training_graph_matrices(mats, self.nc_weight, device=device)
+
+
+def padded_matrices(graph, index=0, nc_weight=-1e20, for_forward_only=False, device="cpu"):
+    """The reference's 4/8-tuple for one graph (``fst_to_matrices`` encoding)."""
+    mats = [torch.from_numpy(m) for m in graph.export_padded(index, False, nc_weight)]
+    if not for_forward_only:
+        mats += [torch.from_numpy(m) for m in graph.export_padded(index, True, nc_weight)]
+    if device is not None and str(device) != "cpu":
+        mats = [m.to(device) for m in mats]
+    return tuple(mats)
+
+
+def batch_training_graph_matrices(matrices, nc_weight=-1e20, device="cpu"):
+    """fst_utils.py:491-521: pad per-utterance tuples to ``(B, Nmax, Kmax_i)``."""
+    bs = len(matrices)
+    max_n = max(m[0].size(0) for m in matrices)
+    max_ks = [max(m[i].size(1) for m in matrices) for i in range(len(matrices[0]))]
+    out = []
+    for i, m in enumerate(matrices[0]):
+        out.append(torch.full((bs, max_n, max_ks[i]),
+                              0 if m.dtype == torch.int64 else nc_weight,
+                              dtype=m.dtype, device=device))
+    for b, ms in enumerate(matrices):
+        for i, m in enumerate(ms):
+            out[i][b, :m.size(0), :m.size(1)] = m
+    return out
+
+
+def make_full_ngram_table(context_order, num_symbols, num_classes):
+    """fst_utils.py:524-534."""
+    if num_symbols is None:
+        num_symbols = int(round(num_classes ** (1.0 / context_order)))
+    num_classes = num_symbols ** context_order
+    idx = np.arange(num_classes)[:, None]
+    pw = num_symbols ** np.arange(context_order)[::-1][None, :]
+    ngram_to_class = torch.from_numpy((idx // pw) % num_symbols).long()
+    return num_symbols, num_classes, ngram_to_class
+
+
+def _as_graph(graph_matrices, nc_weight=-1e20):
+    if isinstance(graph_matrices, Graph):
+        return graph_matrices
+    if isinstance(graph_matrices, PackedGraphs):
+        return graph_matrices.graph
+    g = getattr(graph_matrices, "_ctcg_graph", None)
+    if g is not None:
+        return g
+    assert len(graph_matrices) in (4, 8)
+    assert all(sm.size(0) == graph_matrices[0].size(0) for sm in graph_matrices)
+    return Graph.from_padded(graph_matrices, nc_weight)
+
+
+class _PathLogSumExp(torch.autograd.Function):
+    """``PathLogSumExp`` (fst_utils.py:400-488): gradients are produced by the
+    forward call and scaled by ``grad_output`` in backward, as in the reference."""
+
+    @staticmethod
+    def forward(ctx, log_probs, act_lens, graph):
+        cost, grads = _lib.path_sum(log_probs, act_lens, graph, need_grad=log_probs.requires_grad)
+        ctx.grads = grads
+        return cost
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return grad_output[None, :, None] * ctx.grads, None, None
+
+
+class _PathViterbi(torch.autograd.Function):
+    """Tropical reduction; its gradient is the indicator of the best path's
+    labels, which is what ``FSTDecoder.decode`` reads (advanced_decoder.py:546-554)."""
+
+    @staticmethod
+    def forward(ctx, log_probs, act_lens, graph):
+        score, labels = _lib.viterbi(log_probs, act_lens, graph)
+        ctx.labels = labels
+        ctx.lens = torch.as_tensor(np.asarray(act_lens, dtype=np.int64))
+        ctx.shape = log_probs.shape
+        return score
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        T, B, V = ctx.shape
+        grad = torch.zeros(ctx.shape, dtype=grad_output.dtype, device=grad_output.device)
+        mask = (torch.arange(T, device=grad.device)[:, None] < ctx.lens.to(grad.device)[None, :])
+        src = (mask.to(grad.dtype) * grad_output[None, :]).unsqueeze(-1)
+        grad.scatter_(2, ctx.labels.long().unsqueeze(-1), src)
+        return grad, None, None
+
+
+def _check_lens(act_lens):
+    lens = act_lens.tolist() if torch.is_tensor(act_lens) else [int(x) for x in act_lens]
+    # fst_utils.py:382,432 -- the reference requires lengths sorted descending
+    assert lens == sorted(lens, reverse=True)
+    return lens
+
+
+def path_logsumexp(log_probs, act_lens, graph_matrices, neg_inf=-1e20):
+    lens = _check_lens(act_lens)
+    _, bs, _ = log_probs.size()
+    graph = _as_graph(graph_matrices, neg_inf)
+    assert graph.num_graphs in (1, bs)
+    return _PathLogSumExp.apply(log_probs, lens, graph)
+
+
+def path_reduction(log_probs, act_lens, graph_matrices, red_kind="logsumexp", neg_inf=-1e20):
+    """Drop-in for ``att_speech.fst_utils.path_reduction`` (fst_utils.py:322-397).
+
+    ``graph_matrices`` may be the reference's list of 4/8 padded tensors (leading
+    dimension B or 1) or a native :class:`Graph` / :class:`PackedGraphs`.
+    Returns a ``(B,)`` tensor differentiable in ``log_probs``.
+    """
+    lens = _check_lens(act_lens)
+    _, bs, _ = log_probs.size()
+    graph = _as_graph(graph_matrices, neg_inf)
+    assert graph.num_graphs in (1, bs)
+    if red_kind in ("logsumexp", "logsumexp_fwb", "logsumexp_autodiff"):
+        return _PathLogSumExp.apply(log_probs, lens, graph)
+    assert red_kind in ("viterbi", "viterbi_autodiff")
+    return _PathViterbi.apply(log_probs, lens, graph)
+
+
+def setattr_matched(obj, var, val):
+    val_orig = getattr(obj, var)
+    if val_orig is not None:
+        assert val_orig == val, ("The value of %s is %s but should be %s" % (var, val_orig, val))
+    else:
+        setattr(obj, var, val)
+
+
+class BaseGraphGen(object):
+    """fst_utils.py:546-676 without OpenFst; ``grammar_fst`` is not supported
+    (it needs an OpenFst binary-file reader: SURVEY 8f #4)."""
+
+    def __init__(self, num_symbols=None, num_classes=None, ngram_to_class_file=None,
+                 context_order=None, nc_weight=-1e20, for_forward_only=False,
+                 grammar_fst=None, vocabulary=None, **kwargs):
+        super(BaseGraphGen, self).__init__(**kwargs)
+        if grammar_fst is not None or ngram_to_class_file is not None:
+            raise NotImplementedError(
+                "grammar_fst / ngram_to_class_file need OpenFst files; build the graph "
+                "elsewhere and pass it through Graph.from_arcs")
+        self.num_classes = num_classes
+        self.num_symbols = num_symbols
+        self.context_order = 1 if context_order is None else context_order
+        num_symbols, num_classes, ngram_to_class = make_full_ngram_table(
+            self.context_order, num_symbols, num_classes)
+        setattr_matched(self, "num_symbols", num_symbols)
+        setattr_matched(self, "num_classes", num_classes)
+        self.ngram_to_class = ngram_to_class
+        self.ngrams = ngram_to_class.tolist()
+        self.grammar_fst_path = None
+        self.nc_weight = nc_weight
+        self.decoding_fst = self.get_decoding_fst()
+        self.decoding_mats = {}
+        self.for_forward_only = for_forward_only
+
+    # -- graphs ----------------------------------------------------------
+    def get_decoding_fst(self):
+        return self.get_hc_fst()
+
+    def get_hc_fst(self):
+        raise NotImplementedError()
+
+    def _build_args(self):
+        return {}
+
+    def get_training_graphs(self, label_seqs):
+        """Native batch of numerator graphs (CSR), one per transcript."""
+        return Graph.training(self.context_order, self.num_symbols, label_seqs, **self._build_args())
+
+    def get_training_fst(self, labels):
+        if torch.is_tensor(labels):
+            labels = labels.cpu().numpy()
+        return self.get_training_graphs([np.asarray(labels)])
+
+    def get_training_matrices(self, labels, device="cpu"):
+        """The reference's 4/8-tuple of padded matrices for one transcript
+        (fst_utils.py:647-660); tagged with the CSR handle they came from."""
+        g = self.get_training_fst(labels)
+        return padded_matrices(g, 0, self.nc_weight, self.for_forward_only, device)
+
+    def get_training_matrices_batch(self, labels, label_lens, device="cpu", native=False):
+        seqs = []
+        for i in range(len(labels)):
+            li = labels[i]
+            if torch.is_tensor(li):
+                li = li.cpu().numpy()
+            seqs.append(np.asarray(li)[:int(label_lens[i])])
+        g = self.get_training_graphs(seqs)
+        if native:
+            return PackedGraphs(g, self.nc_weight)
+        return PackedGraphs(g, self.nc_weight).to_padded(device)
+
+    def get_decoding_matrices(self, device="cpu", out_edges=False):
+        key = str(device)
+        ret = self.decoding_mats.get(key)
+        if ret is None:
+            ret = [m.unsqueeze(0) for m in padded_matrices(
+                self.decoding_fst, 0, self.nc_weight, self.for_forward_only, device)]
+            self.decoding_mats[key] = ret
+        return ret
+
+    def get_decoding_graph(self):
+        return self.decoding_fst
+
+
+class CTCGraphGen(BaseGraphGen):
+    """fst_utils.py:1053-1068 (context orders 1 and 2)."""
+
+    def __init__(self, context_order=None, graph_build_args=None, **kwargs):
+        assert context_order in (1, 2, 3)
+        if context_order == 3:
+            raise NotImplementedError("tri-char topologies enter through Graph.from_arcs")
+        self.graph_build_args = graph_build_args or {}
+        super(CTCGraphGen, self).__init__(context_order=context_order, **kwargs)
+
+    def _build_args(self):
+        return self.graph_build_args if self.context_order == 2 else {}
+
+    def get_hc_fst(self):
+        return Graph.decoding(self.context_order, self.num_symbols, **self._build_args())

@@ -1,0 +1,285 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle and the
+reference's golden vectors.
+
+Tolerances are BASELINE.json's: loss within 1e-5 relative, gradients within 1e-5
+absolute, both against fp64; Viterbi alignments and path counts bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_names, load_golden
+from oracle import engine, graphs
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-5
+GRAD_ATOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def P(lib_built):
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    return lib_built
+
+
+def _rel(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float((np.abs(a - b) / np.maximum(np.abs(b), 1.0)).max())
+
+
+def _run_fused(P, logits, lens, num, den, normalize_by_dim, S=0):
+    x = torch.as_tensor(logits).float().cuda().requires_grad_(True)
+    loss = P.fst_loss(x, lens, num, den, normalize_by_dim=normalize_by_dim, num_symbols=S)
+    loss.sum().backward()
+    torch.cuda.synchronize()
+    return loss.detach().cpu().double().numpy(), x.grad.detach().cpu().double().numpy()
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names() if n != "bi_ctc_context_norm"])
+def test_fused_loss_matches_reference_golden(P, name):
+    d = load_golden(name)
+    gen = P.CTCGraphGen(context_order=d["order"], graph_build_args=d["args"], num_symbols=d["S"])
+    num = gen.get_training_graphs(d["label_seqs"])
+    den = gen.get_decoding_graph() if d["use_den"] else None
+    loss, grad = _run_fused(P, d["logits"], d["lens"].tolist(), num, den, d["normalize_by_dim"], d["S"])
+    assert _rel(loss, d["loss_f64"]) < LOSS_RTOL
+    assert np.abs(grad - d["grad_f64"]).max() < GRAD_ATOL
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_path_reduction_dropin_on_reference_matrices(P, name):
+    """path_reduction fed with the reference's own padded matrices (fst_utils.py:322)."""
+    d = load_golden(name)
+    lens = torch.tensor(d["lens"])
+    lp = torch.log_softmax(torch.as_tensor(d["logits"]).double(), -1)
+    for mats in (d["num_mats"], d["den_mats"]):
+        x = lp.float().cuda().requires_grad_(True)
+        tm = [torch.as_tensor(m) for m in mats]
+        cost = P.path_reduction(x, lens, tm)
+        cost.sum().backward()
+        want, wgrad, _ = engine.path_logsumexp(lp, d["lens"], mats, dtype=torch.float64)
+        assert _rel(cost.detach().cpu(), want) < LOSS_RTOL
+        assert (x.grad.cpu().double() - wgrad).abs().max().item() < GRAD_ATOL
+
+
+def test_context_normalised_loss_through_plugin_signature(P):
+    """ctc_fst_loss with normalize_by_dim=1 (ctc_losses.py:617-657)."""
+    d = load_golden("bi_ctc_context_norm")
+    x = torch.as_tensor(d["logits"]).cuda().requires_grad_(True)
+    labels_cat = torch.as_tensor(np.concatenate([np.asarray(s) for s in d["label_seqs"]]))
+    loss = P.ctc_fst_loss(x, labels_cat, torch.tensor(d["lens"]), torch.tensor(d["text_lens"]),
+                          d["S"], 2, 1, True, False,
+                          {"graph_matrices": [torch.as_tensor(m) for m in d["num_mats"]]})
+    loss.sum().backward()
+    assert _rel(loss.detach().cpu(), d["loss_f64"]) < LOSS_RTOL
+    assert np.abs(x.grad.cpu().double().numpy() - d["grad_f64"]).max() < GRAD_ATOL
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_viterbi_alignment_bit_exact(P, name):
+    d = load_golden(name)
+    gen = P.CTCGraphGen(context_order=d["order"], graph_build_args=d["args"], num_symbols=d["S"])
+    x = torch.as_tensor(d["logits"]).cuda().requires_grad_(True)
+    score = P.path_reduction(x, torch.tensor(d["lens"]), gen.get_decoding_graph(), red_kind="viterbi")
+    (-score.sum()).backward()
+    sel = x.grad.min(-1)[1].cpu().numpy()          # advanced_decoder.py:554
+    assert np.array_equal(sel, d["vit_labels"])
+    assert _rel(score.detach().cpu(), d["vit_score"]) < LOSS_RTOL
+    _, labels = P._lib.viterbi(x, d["lens"].tolist(), gen.get_decoding_graph())
+    assert np.array_equal(labels.cpu().numpy(), d["vit_labels"])
+
+
+def test_path_counts_bit_exact_including_wraparound(P):
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=6)
+    ogen = graphs.GraphGen(2, 6, {})
+    lens = [150, 40, 7, 0]
+    got = P._lib.path_count(lens, gen.get_decoding_graph())
+    g = ogen.decoding_graph
+    arcs = [(a[0], a[1], a[2], a[4]) for a in g.arcs]
+    want = [engine.path_count(g.n, arcs, g.final, n) for n in lens]
+    assert [int(v) for v in got] == want
+    assert want[0] != 0 and 36 ** 150 > 2 ** 64          # the long one wrapped
+    seqs = [[1, 2, 2, 3], [4, 4, 4], [5], [2, 1]]
+    num = gen.get_training_graphs(seqs)
+    lens = [30, 12, 3, 1]
+    got = P._lib.path_count(lens, num)
+    for b, s in enumerate(seqs):
+        tg = ogen.training_graph(s)
+        arcs = [(a[0], a[1], a[2], a[4]) for a in tg.arcs]
+        assert int(got[b]) == engine.path_count(tg.n, arcs, tg.final, lens[b])
+    d = load_golden("bi_ctcg")
+    cnt = P._lib.path_count(d["lens"].tolist(), P.Graph.from_padded(d["num_mats"]))
+    assert np.allclose(np.log(cnt.astype(np.float64)), d["log_count_num"], atol=1e-9)
+
+
+def _random_case(order, S, args, T, B, seed, peaky=False):
+    rng = np.random.default_rng(seed)
+    V = S ** order
+    lens = sorted([T] + rng.integers(int(0.6 * T), T + 1, size=B - 1).tolist(), reverse=True)
+    seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens]
+    logits = (rng.standard_normal((T, B, V)) * 3).astype(np.float32)
+    if peaky:
+        for b in range(B):
+            pos = np.sort(rng.choice(lens[b], size=len(seqs[b]), replace=False))
+            prev = 0
+            for p, s in zip(pos, seqs[b]):
+                logits[p, b, (prev * S + s) if order == 2 else s] += 8
+                prev = s
+    return logits, lens, seqs
+
+
+def _oracle(order, S, args, logits, lens, seqs, use_den, normalize_by_dim):
+    ogen = graphs.GraphGen(order, S, args)
+    U = max(len(s) for s in seqs)
+    lab = np.zeros((len(seqs), U), dtype=np.int64)
+    for i, s in enumerate(seqs):
+        lab[i, :len(s)] = s
+    nm = ogen.get_training_matrices_batch(lab, [len(s) for s in seqs])
+    dm = ogen.get_decoding_matrices() if use_den else None
+    return engine.fst_loss(logits, lens, nm, dm, normalize_by_dim, S, order, dtype=torch.float64)
+
+
+@pytest.mark.parametrize("order,S,args,use_den,nbd,T,B,peaky", [
+    (1, 49, {}, False, 0, 400, 4, False),                         # cfg1 shape, mono CTC
+    (1, 49, {}, True, None, 120, 3, True),                        # mono CTC-G
+    (2, 12, {}, False, 0, 100, 6, False),                         # bi-char CTC
+    (2, 12, {}, True, None, 100, 6, True),                        # CTC-G
+    (2, 12, {"use_contextual_blanks": True}, True, None, 90, 5, False),   # CTC-GB
+    (2, 10, {"loop_using_symbol_repetitions": True}, True, None, 60, 3, False),
+    (2, 10, {"allow_nonblank_selfloops": False}, True, 0, 60, 3, True),   # softmax + den: LSE cancels
+])
+def test_fused_loss_matches_fp64_oracle_random(P, order, S, args, use_den, nbd, T, B, peaky):
+    logits, lens, seqs = _random_case(order, S, args, T, B, seed=1000 + T + B, peaky=peaky)
+    want_loss, want_grad = _oracle(order, S, args, logits, lens, seqs, use_den, nbd)
+    gen = P.CTCGraphGen(context_order=order, graph_build_args=args, num_symbols=S)
+    num = gen.get_training_graphs(seqs)
+    den = gen.get_decoding_graph() if use_den else None
+    loss, grad = _run_fused(P, logits, lens, num, den, nbd, S)
+    assert _rel(loss, want_loss.numpy()) < LOSS_RTOL
+    assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
+
+
+@pytest.mark.parametrize("variant", ["ctc", "ctcg", "ctcgb"])
+def test_full_vocabulary_slice_matches_fp64_oracle(P, variant):
+    """S=49 (V=2401), T=400: two utterances of the BASELINE batch against the fp64 oracle."""
+    args = {"use_contextual_blanks": True} if variant == "ctcgb" else {}
+    use_den, nbd = (False, 0) if variant == "ctc" else (True, None)
+    T = 400 if variant == "ctc" else 120
+    logits, lens, seqs = _random_case(2, 49, args, T, 2, seed=1002)
+    want_loss, want_grad = _oracle(2, 49, args, logits, lens, seqs, use_den, nbd)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=49)
+    loss, grad = _run_fused(P, logits, lens, gen.get_training_graphs(seqs),
+                            gen.get_decoding_graph() if use_den else None, nbd, 49)
+    assert _rel(loss, want_loss.numpy()) < LOSS_RTOL
+    assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
+
+
+@pytest.mark.parametrize("variant,B,T", [("ctc", 64, 400), ("ctcg", 64, 400), ("ctcgb", 32, 800)])
+def test_full_size_properties(P, variant, B, T):
+    """BASELINE-size batches: size-independent properties of the posteriors."""
+    args = {"use_contextual_blanks": True} if variant == "ctcgb" else {}
+    use_den, nbd = (False, 0) if variant == "ctc" else (True, None)
+    logits, lens, seqs = _random_case(2, 49, args, T, B, seed=1003)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=49)
+    num = gen.get_training_graphs(seqs)
+    den = gen.get_decoding_graph() if use_den else None
+    loss, grad = _run_fused(P, logits, lens, num, den, nbd, 49)
+    assert np.isfinite(loss).all() and np.isfinite(grad).all()
+    assert (loss > 0).all()
+    for b in range(0, B, 7):
+        assert np.abs(grad[lens[b]:, b]).max(initial=0.0) == 0.0           # pad rows stay zero
+        assert np.abs(grad[:lens[b], b].sum(-1)).max() < 2e-5               # posteriors sum to one
+    # per-frame shifts of the logits change nothing (softmax / num-den invariance)
+    shift = np.random.default_rng(5).standard_normal((T, B, 1)).astype(np.float32) * 4
+    loss2, grad2 = _run_fused(P, logits + shift, lens, num, den, nbd, 49)
+    assert _rel(loss2, loss) < 2e-5
+    assert np.abs(grad2 - grad).max() < 2e-5
+    # an utterance's result does not depend on its batch neighbours
+    sub = [0, B // 2, B - 1]
+    gsub = gen.get_training_graphs([seqs[i] for i in sub])
+    loss3, grad3 = _run_fused(P, logits[:, sub], [lens[i] for i in sub], gsub, den, nbd, 49)
+    assert _rel(loss3, loss[sub]) < 1e-6
+    assert np.abs(grad3 - grad[:, sub]).max() < 1e-6
+
+
+def test_edge_cases(P):
+    S = 5
+    gen = P.CTCGraphGen(context_order=1, graph_build_args={}, num_symbols=S)
+    ogen = graphs.GraphGen(1, S, {})
+    rng = np.random.default_rng(9)
+    # (a) exactly one path: T == U (no repeats); (b) a repeat needs T >= U+1; (c) B == 1
+    seqs = [[1, 2, 3, 4]]
+    x = (rng.standard_normal((4, 1, S)) * 2).astype(np.float32)
+    loss, grad = _run_fused(P, x, [4], gen.get_training_graphs(seqs), None, 0)
+    lp = torch.log_softmax(torch.as_tensor(x).double(), -1)
+    want = -sum(lp[t, 0, s] for t, s in enumerate(seqs[0]))
+    assert abs(loss[0] - float(want)) < 1e-5
+    # (d) infeasible: T < U.  The reference returns a finite ~1e20-scale loss, never NaN/inf
+    loss, grad = _run_fused(P, x[:3], [3], gen.get_training_graphs(seqs), None, 0)
+    assert np.isfinite(loss).all() and loss[0] > 1e19 and np.isfinite(grad).all()
+    # (e) ragged batch with an empty utterance and a 1-frame utterance
+    seqs = [[1, 1, 2], [3], [4]]
+    lens = [9, 1, 0]
+    x = (rng.standard_normal((9, 3, S)) * 2).astype(np.float32)
+    loss, grad = _run_fused(P, x, lens, gen.get_training_graphs(seqs), gen.get_decoding_graph(), None)
+    U = 3
+    lab = np.zeros((3, U), dtype=np.int64)
+    for i, s in enumerate(seqs):
+        lab[i, :len(s)] = s
+    nm = ogen.get_training_matrices_batch(lab, [3, 1, 1])
+    wl, wg = engine.fst_loss(x, lens, nm, ogen.get_decoding_matrices(), None, dtype=torch.float64)
+    assert _rel(loss[:2], wl.numpy()[:2]) < LOSS_RTOL
+    assert loss[2] > 1e19                      # empty utterance with a non-empty transcript: infeasible
+    assert np.abs(grad[:, :2] - wg.numpy()[:, :2]).max() < GRAD_ATOL
+    assert np.abs(grad[:, 2]).max() == 0.0
+    # (f) the C ABI itself does not need sorted lengths
+    seqs = [[1], [2, 3], [4, 4]]
+    lens_u = [4, 9, 6]
+    num = gen.get_training_graphs(seqs)
+    xc = torch.as_tensor(x).cuda()
+    l_u, g_u = P._lib.loss_fwd_bwd(xc, lens_u, num, None, P.NORM_SOFTMAX)
+    order = [1, 2, 0]
+    l_s, g_s = P._lib.loss_fwd_bwd(xc[:, order].contiguous(), [lens_u[i] for i in order],
+                                   gen.get_training_graphs([seqs[i] for i in order]), None, P.NORM_SOFTMAX)
+    assert torch.allclose(l_u[order], l_s, rtol=1e-6) and torch.allclose(g_u[:, order], g_s, atol=1e-7)
+
+
+def test_host_buffer_entry_point_equals_device_path(P):
+    logits, lens, seqs = _random_case(2, 8, {}, 50, 4, seed=21)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=8)
+    num, den = gen.get_training_graphs(seqs), gen.get_decoding_graph()
+    xh = torch.as_tensor(logits).pin_memory()
+    lh, gh = P._lib.loss_host(xh, lens, num, den, P.NORM_NONE)
+    ld, gd = P._lib.loss_fwd_bwd(xh.cuda(), lens, num, den, P.NORM_NONE)
+    assert torch.equal(lh, ld.cpu()) and torch.equal(gh, gd.cpu())
+    lh2, _ = P._lib.loss_host(xh, lens, num, None, P.NORM_SOFTMAX, want_grad=False)
+    ld2, _ = P._lib.loss_fwd_bwd(xh.cuda(), lens, num, None, P.NORM_SOFTMAX, need_grad=False)
+    assert torch.equal(lh2, ld2.cpu())
+
+
+def test_decoder_module_and_grad_scale(P):
+    logits, lens, seqs = _random_case(2, 7, {}, 40, 3, seed=33)
+    head = P.FSTLoss({"class_name": "CTCGraphGen", "context_order": 2, "graph_build_args": {}},
+                     num_symbols=7)
+    x = torch.as_tensor(logits).cuda().requires_grad_(True)
+    U = max(len(s) for s in seqs)
+    texts = torch.zeros(3, U, dtype=torch.long)
+    for i, s in enumerate(seqs):
+        prev = 0
+        for j, v in enumerate(s):          # bi-char dataset ids: prev*S+cur (egs/wsj/data.py:146-161)
+            texts[i, j] = prev * 7 + v
+            prev = v
+    out = head(x, torch.tensor(lens), texts, torch.tensor([len(s) for s in seqs]))
+    assert set(out) == {"fst_loss", "loss"}
+    (2.5 * out["loss"]).backward()
+    wl, wg = _oracle(2, 7, {}, logits, lens, seqs, True, None)
+    assert abs(out["loss"].item() - wl.sum().item()) / wl.sum().item() < LOSS_RTOL
+    assert np.abs(x.grad.cpu().double().numpy() - 2.5 * wg.numpy()).max() < 2.5 * GRAD_ATOL
+    # per-utterance weights through the C ABI's grad_scale
+    w = torch.tensor([0.5, 2.0, -1.0])
+    gen = head.graph_generator
+    _, g = P._lib.loss_fwd_bwd(x.detach(), lens, gen.get_training_graphs(seqs), gen.get_decoding_graph(),
+                               P.NORM_NONE, grad_scale=w)
+    assert np.abs(g.cpu().double().numpy() - wg.numpy() * w.numpy()[None, :, None]).max() < 2 * GRAD_ATOL
