@@ -202,6 +202,13 @@ const char* ctcg_strerror(int status);
  * gpu_launches claim is read from here, not guessed). */
 uint64_t ctcg_launch_count(void);
 
+/* Per-launch device timing for attribution (CUDA events around every kernel the
+ * library launches while enabled).  collect() synchronises, writes up to
+ * max_records durations in launch order and their ';'-separated kernel names,
+ * clears the log and returns the number of records. */
+void ctcg_profile_enable(int on);
+int ctcg_profile_collect(char* names, size_t names_cap, float* ms, int max_records);
+
 #ifdef __cplusplus
 }
 #endif

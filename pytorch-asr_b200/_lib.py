@@ -24,6 +24,7 @@ EXPORTS = (
     "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
     "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi",
     "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
+    "ctcg_profile_enable", "ctcg_profile_collect",
 )
 
 
@@ -78,6 +79,9 @@ def lib():
     L.ctcg_strerror.restype = C.c_char_p
     L.ctcg_launch_count.argtypes = []
     L.ctcg_launch_count.restype = C.c_uint64
+    L.ctcg_profile_enable.argtypes = [C.c_int]
+    L.ctcg_profile_enable.restype = None
+    L.ctcg_profile_collect.argtypes = [C.c_char_p, C.c_size_t, vp, C.c_int]
     for name in EXPORTS:
         getattr(L, name)
     _lib = L
@@ -98,6 +102,18 @@ def check(status):
 
 def launch_count():
     return int(lib().ctcg_launch_count())
+
+
+def profile(enable):
+    lib().ctcg_profile_enable(int(bool(enable)))
+
+
+def profile_collect(max_records=4096):
+    """[(kernel name, milliseconds)] for every launch since profiling was enabled."""
+    names = C.create_string_buffer(max_records * 32)
+    ms = np.zeros(max_records, dtype=np.float32)
+    n = lib().ctcg_profile_collect(names, len(names), _np_ptr(ms), max_records)
+    return list(zip(names.value.decode().split(";")[:n], ms[:n].tolist()))
 
 
 def _np_ptr(a):

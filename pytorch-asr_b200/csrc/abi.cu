@@ -161,6 +161,12 @@ size_t ctcg_workspace_bytes(int32_t T, int32_t B, int32_t V, const ctcg_graph* n
 
 uint64_t ctcg_launch_count(void) { return g_launches; }
 
+void ctcg_profile_enable(int on) { profile_enable(on != 0); }
+
+int ctcg_profile_collect(char* names, size_t names_cap, float* ms, int max_records) {
+  return profile_collect(names, names_cap, ms, max_records);
+}
+
 }  // extern "C"
 
 // ---------------------------------------------------------------------------

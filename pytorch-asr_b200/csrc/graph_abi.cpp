@@ -2,6 +2,9 @@
 // DataLoader worker processes can use them without creating a CUDA context).
 #include <algorithm>
 #include <cmath>
+#include <map>
+#include <memory>
+#include <mutex>
 #include <new>
 #include <tuple>
 
@@ -14,6 +17,31 @@ namespace {
 void index_out_arcs(const RawGraph& g, std::vector<std::vector<int32_t>>* out) {
   out->assign(g.n, {});
   for (int32_t i = 0; i < static_cast<int32_t>(g.arcs.size()); ++i) (*out)[g.arcs[i].src].push_back(i);
+}
+
+// Decoding graphs are a pure function of the topology: build each once per process
+// (the S=49 bi-char graph has 120k arcs) and share it between calls and threads.
+struct CachedDecoding {
+  RawGraph g;
+  std::vector<std::vector<int32_t>> out;
+};
+std::shared_ptr<const CachedDecoding> cached_decoding(const ctcg_topology& t, int* status) {
+  static std::mutex mu;
+  static std::map<std::tuple<int, int, int, int, int>, std::shared_ptr<const CachedDecoding>> cache;
+  const auto key = std::make_tuple(t.context_order, t.num_symbols, t.allow_nonblank_selfloops != 0,
+                                   t.use_contextual_blanks != 0, t.loop_using_symbol_repetitions != 0);
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) {
+    *status = CTCG_OK;
+    return it->second;
+  }
+  auto c = std::make_shared<CachedDecoding>();
+  *status = build_decoding(t, &c->g);
+  if (*status != CTCG_OK) return nullptr;
+  index_out_arcs(c->g, &c->out);
+  cache[key] = c;
+  return c;
 }
 
 void mark_structured(const ctcg_topology& t, ctcg_graph* g) {
@@ -52,11 +80,11 @@ int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels, const
                          int32_t B, ctcg_graph** out) {
   if (!topo || !offsets || !out || B < 0) return CTCG_EINVAL;
   try {
-    RawGraph dec;
-    int st = build_decoding(*topo, &dec);
+    int st = CTCG_OK;
+    const auto cached = cached_decoding(*topo, &st);
     if (st != CTCG_OK) return st;
-    std::vector<std::vector<int32_t>> dec_out;
-    index_out_arcs(dec, &dec_out);
+    const RawGraph& dec = cached->g;
+    const std::vector<std::vector<int32_t>>& dec_out = cached->out;
     std::vector<RawGraph> gs(B);
     std::vector<int32_t> lab;
     const int32_t S = topo->num_symbols;

@@ -64,4 +64,16 @@ cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uin
 // Incremented by every launch_* above.
 extern unsigned long long g_launches;
 
+// Optional per-launch timing (CUDA events on the launch stream), off by default;
+// bench.py turns it on for a few extra steps after the timed region to attribute
+// the step time to kernels.  Never enabled inside a timed region.
+struct ProfScope {
+  ProfScope(const char* name, cudaStream_t st);
+  ~ProfScope();
+  cudaStream_t st_;
+  int idx_;
+};
+void profile_enable(bool on);
+int profile_collect(char* names, size_t cap, float* ms, int max_records);
+
 }  // namespace ctcg

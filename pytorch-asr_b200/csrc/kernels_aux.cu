@@ -171,6 +171,7 @@ cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* l
   if (smem > 200 * 1024) return cudaErrorInvalidConfiguration;
   cudaError_t e = cudaFuncSetAttribute(viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
+  ProfScope prof("viterbi", st);
   viterbi_kernel<<<B, NT, smem, st>>>(x, T, B, V, lens, g, back_ws, row, score, frame_labels);
   ++g_launches;
   return cudaGetLastError();
@@ -181,6 +182,7 @@ cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uin
   if (smem > 200 * 1024) return cudaErrorInvalidConfiguration;
   cudaError_t e = cudaFuncSetAttribute(count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
+  ProfScope prof("path_count", st);
   count_kernel<<<B, NT, smem, st>>>(B, lens, g, reinterpret_cast<unsigned long long*>(counts));
   ++g_launches;
   return cudaGetLastError();

@@ -14,12 +14,62 @@
 // The time recursion is serial per utterance; states are spread over the CTA,
 // alpha lives in shared memory (double-buffered, one barrier per frame), the
 // frame's scores arrive through an 8-deep cp.async ring in compact mode.
+#include <cstring>
+#include <vector>
+
 #include "device_utils.cuh"
 #include "kernels.cuh"
 
 namespace ctcg {
 
 unsigned long long g_launches = 0;
+
+namespace {
+struct ProfRec {
+  const char* name;
+  cudaEvent_t a, b;
+};
+bool g_prof_on = false;
+std::vector<ProfRec> g_prof;
+}  // namespace
+
+ProfScope::ProfScope(const char* name, cudaStream_t st) : st_(st), idx_(-1) {
+  if (!g_prof_on) return;
+  ProfRec r{name, nullptr, nullptr};
+  if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return;
+  cudaEventRecord(r.a, st);
+  g_prof.push_back(r);
+  idx_ = (int)g_prof.size() - 1;
+}
+ProfScope::~ProfScope() {
+  if (idx_ >= 0) cudaEventRecord(g_prof[idx_].b, st_);
+}
+void profile_enable(bool on) { g_prof_on = on; }
+int profile_collect(char* names, size_t cap, float* ms, int max_records) {
+  int n = 0;
+  size_t off = 0;
+  if (names && cap) names[0] = 0;
+  for (ProfRec& r : g_prof) {
+    cudaEventSynchronize(r.b);
+    float t = 0.f;
+    cudaEventElapsedTime(&t, r.a, r.b);
+    if (n < max_records) {
+      ms[n] = t;
+      const size_t l = strlen(r.name);
+      if (names && off + l + 2 < cap) {
+        memcpy(names + off, r.name, l);
+        names[off + l] = ';';
+        names[off + l + 1] = 0;
+        off += l + 1;
+      }
+      ++n;
+    }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof.clear();
+  return n;
+}
 
 namespace {
 
@@ -40,7 +90,7 @@ __host__ __device__ inline SmemPlan plan_smem(int max_states, int width, int max
   p.xw = compact ? pad4(max_labels) : 0;
   p.ar = compact ? alpha_row : 0;
   p.arcs = stage_arcs;
-  size_t f = 2 * (size_t)p.np + 2 * (size_t)p.gw + 2 * NWARP + (size_t)RING * p.xw + (size_t)RING * p.ar;
+  size_t f = 2 * (size_t)p.np + 2 * (size_t)p.gw + 4 * NWARP + (size_t)RING * p.xw + (size_t)RING * p.ar;
   p.bytes = f * 4 + (size_t)stage_arcs * 24;
   return p;
 }
@@ -69,7 +119,8 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   float* abuf = reinterpret_cast<float*>(smem_raw);
   float* grow = abuf + 2 * P.np;
   float* wred = grow + 2 * P.gw;
-  float* xring = wred + 2 * NWARP;
+  float* wsum = wred + 2 * NWARP;  // per-warp partial sums of the frame's posteriors
+  float* xring = wsum + 2 * NWARP;
   float* aring = xring + RING * P.xw;
   int32_t* s_in_src = reinterpret_cast<int32_t*>(aring + RING * P.ar);
   int32_t* s_in_lab = s_in_src + stage_arcs;
@@ -265,8 +316,15 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
     if (i > 0) {
       float* gr = grow + ((i - 1) & 1) * P.gw;
       float* dst = gb + (long long)(t + 1) * a.g_stride_t;
+      // Every accepting path crosses exactly one arc per frame, so the frame's arc
+      // posteriors sum to one: dividing by their computed sum removes the rounding
+      // drift that alpha_hat/beta_hat/cost accumulate over hundreds of frames.
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < NWARP; ++w) tot += wsum[((i - 1) & 1) * NWARP + w];
+      const float sc = tot > 0.f ? gmul / tot : 0.f;
       for (int j = tid; j < nl; j += NT) {
-        dst[j] = gr[j] * gmul;
+        dst[j] = gr[j] * sc;
         gr[j] = 0.f;
       }
     }
@@ -279,6 +337,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
     const float Kt = (float)(ct + d - cost2);
     float* gr = grow + (i & 1) * P.gw;
     float lm = neg_inf();
+    float gsum = 0.f;
     for (int s = tid; s < n; s += NT) {
       const int lo = out_ptr[s], hi = out_ptr[s + 1];
       float M = neg_inf();
@@ -294,7 +353,10 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
           const float v = out_w[e] * wscale + (b_cur[out_dst[e]] - mxb) + xrow[out_lab[e]] * a.x_scale;
           const float ev = ex2(v - M);
           acc += ev;
-          if (f > 0.f) atomicAdd(&gr[out_lab[e]], ev * f);
+          if (f > 0.f) {
+            atomicAdd(&gr[out_lab[e]], ev * f);
+            gsum += ev * f;
+          }
         }
         r = M + lg2(acc);
       }
@@ -302,7 +364,11 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
       lm = fmaxf(lm, r);
     }
     lm = warp_max(lm);
-    if (lane == 0) wred[((i + 1) & 1) * NWARP + warp] = lm;
+    gsum = warp_sum(gsum);
+    if (lane == 0) {
+      wred[((i + 1) & 1) * NWARP + warp] = lm;
+      wsum[(i & 1) * NWARP + warp] = gsum;
+    }
     float* tmp = b_cur;
     b_cur = b_nxt;
     b_nxt = tmp;
@@ -311,7 +377,11 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   __syncthreads();
   if (len > 0) {
     float* gr = grow + ((len - 1) & 1) * P.gw;
-    for (int j = tid; j < nl; j += NT) gb[j] = gr[j] * gmul;
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < NWARP; ++w) tot += wsum[((len - 1) & 1) * NWARP + w];
+    const float sc = tot > 0.f ? gmul / tot : 0.f;
+    for (int j = tid; j < nl; j += NT) gb[j] = gr[j] * sc;
   }
 }
 
@@ -328,6 +398,7 @@ cudaError_t launch_path_fwd_bwd(const PathArgs& a, bool compact, cudaStream_t st
   if (bound * 24 + (long long)base.bytes <= (long long)budget && bound <= 8192) stage = (int)bound;
   const SmemPlan P = plan_smem(a.g.max_states, a.g_width, a.g.max_labels, a.alpha_row, stage, compact);
   cudaError_t e;
+  ProfScope prof(compact ? "path_fwd_bwd<compact>" : "path_fwd_bwd<dense>", st);
   if (compact) {
     e = cudaFuncSetAttribute(path_fwd_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.bytes);
     if (e != cudaSuccess) return e;

@@ -5,6 +5,8 @@
 // the max-shift / mask / numerator-minus-denominator glue of
 // FSTDecoder.get_fst_loss (modules/decoders/advanced_decoder.py:479-517) and the
 // dense zero-initialised logprobs_grad + scatter_add_ of fst_utils.py:448,468-470.
+#include <algorithm>
+
 #include "device_utils.cuh"
 #include "kernels.cuh"
 
@@ -185,6 +187,7 @@ cudaError_t launch_gather(const float* logits, int T, int B, int V, const int32_
                           float* xg, int nlp, int normalize, int S, cudaStream_t st) {
   const long long rows = (long long)T * B;
   const unsigned grid = (unsigned)((rows + NWARP - 1) / NWARP);
+  ProfScope prof("gather", st);
   gather_kernel<<<grid, NT, 0, st>>>(logits, T, B, V, lens, num, xg, nlp, normalize, S);
   ++g_launches;
   return cudaGetLastError();
@@ -197,6 +200,7 @@ cudaError_t launch_rows(const float* logits, int T, int B, int V, const int32_t*
   const long long rows = (long long)T * B;
   const int per = (V + NT - 1) / NT;
   const unsigned grid = (unsigned)std::min<long long>(rows, 148LL * 8);
+  ProfScope prof("rows", st);
 #define CTCG_ROWS(P)                                                                                          \
   do {                                                                                                        \
     cudaError_t e = cudaFuncSetAttribute(rows_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
@@ -220,6 +224,7 @@ cudaError_t launch_scatter_sub(int T, int B, int V, const int32_t* lens, const G
                                int nlp, const float* g_scale, float* grad, cudaStream_t st) {
   const long long rows = (long long)T * B;
   const unsigned grid = (unsigned)((rows + NWARP - 1) / NWARP);
+  ProfScope prof("scatter_sub", st);
   scatter_sub_kernel<<<grid, NT, 0, st>>>(T, B, V, lens, num, gg, nlp, g_scale, grad);
   ++g_launches;
   return cudaGetLastError();
@@ -228,6 +233,7 @@ cudaError_t launch_scatter_sub(int T, int B, int V, const int32_t* lens, const G
 cudaError_t launch_final(int T, int B, const int32_t* lens, const double* cost_num, const double* cost_den,
                          const float* rowlse, float* loss, cudaStream_t st) {
   const unsigned grid = (unsigned)((B + NWARP - 1) / NWARP);
+  ProfScope prof("final", st);
   final_kernel<<<grid, NT, 0, st>>>(T, B, lens, cost_num, cost_den, rowlse, loss);
   ++g_launches;
   return cudaGetLastError();

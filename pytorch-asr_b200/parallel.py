@@ -1,0 +1,104 @@
+"""Utterance-sharded multi-GPU execution: one process per GPU, no data-path collective.
+
+The reference is single-process / single-GPU (no DataParallel, no
+torch.distributed).  Utterances are independent, so the batch is striped over
+ranks -- utterance ``i`` of the length-sorted batch goes to rank ``i mod G`` so
+every rank sees the same length mix and its shard stays sorted -- each rank runs
+the fused loss on its shard, the gradients stay on the GPU that owns the
+utterance, and the only exchange is one all-reduce (sum) of the 2-element fp64
+vector ``[sum of losses, number of frames]`` per step (NCCL over NVLink on the
+box; gloo in the CPU tests).
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+
+
+def init_from_env(backend=None):
+    """Join the process group described by RANK / WORLD_SIZE / MASTER_* (torchrun).
+    Returns ``(rank, world_size, local_rank)``; a lone process needs no group."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        kwargs = {}
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            kwargs["device_id"] = torch.device("cuda", local)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, **kwargs)
+    return rank, world, local
+
+
+def finalize():
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def stripe(n_items, rank, world):
+    """Indices of the length-sorted batch owned by ``rank`` (i mod G striping)."""
+    return list(range(rank, n_items, world))
+
+
+def shard_batch(lens, seqs, rank, world):
+    """Stripe a length-sorted batch; the shard stays sorted descending."""
+    idx = stripe(len(lens), rank, world)
+    return idx, [lens[i] for i in idx], [seqs[i] for i in idx]
+
+
+def _group_active():
+    return dist.is_initialized() and dist.get_world_size() > 1
+
+
+def reduce_loss(loss_per_utt, n_frames):
+    """All-reduce ``[sum_b loss_b, frames]`` over ranks; returns the 2-element fp64
+    tensor (on the loss's device).  Stream-ordered after the loss kernels; the
+    gradient tensors are untouched, so backprop on each rank can proceed without
+    waiting for it."""
+    buf = torch.zeros(2, dtype=torch.float64, device=loss_per_utt.device)
+    buf[0] = loss_per_utt.double().sum()
+    buf[1] = float(n_frames)
+    if _group_active():
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+    return buf
+
+
+def barrier():
+    if _group_active():
+        dist.barrier()
+
+
+def max_over_ranks(value):
+    if not _group_active():
+        return float(value)
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(value):
+    if not _group_active():
+        return value
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return type(value)(t.item())
+
+
+def sharded_fst_loss(logits_shard, lens_shard, numerator, denominator, normalize_by_dim=None,
+                     num_symbols=0):
+    """Fused loss on this rank's shard + the scalar reduction.
+
+    Returns ``(loss_per_utt (local, differentiable), [global loss sum, global frames])``.
+    """
+    from .ctc_losses import fst_loss
+    loss = fst_loss(logits_shard, lens_shard, numerator, denominator, normalize_by_dim, num_symbols)
+    totals = reduce_loss(loss.detach(), int(sum(int(l) for l in lens_shard)))
+    return loss, totals
