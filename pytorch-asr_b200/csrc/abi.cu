@@ -31,8 +31,18 @@ struct Plan {
   int arow_num = 0;  // alpha row pitch of the numerator
   int arow_den = 0;
   size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
+  size_t pspill = 0, ckpt = 0;
+  BicharPlan bi{};   // bi.ok: the denominator runs on the fused bi-char kernel
   size_t total = 0;
 };
+
+// The factorised kernel covers the bi-char decoding graph of ctcg_decoding_graph (shared by the batch).
+BicharPlan structured_plan(int T, int B, int V, const ctcg_graph* den) {
+  BicharPlan none{};
+  if (!den || den->structured.kind != 2 || den->num_graphs != 1) return none;
+  if (den->structured.S * den->structured.S != V) return none;
+  return bichar_plan(T, B, V, den->structured.S);
+}
 
 Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den) {
   Plan p;
@@ -54,12 +64,17 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
   }
   p.rowlse = take(TB * 4);
   if (den) {
-    p.arow_den = pad4(den->max_states + 2);
-    p.alpha_den = take(TB * p.arow_den * 4);
+    p.bi = structured_plan(T, B, V, den);
     p.cost_den = take((size_t)B * 8);
+    if (p.bi.ok) {
+      p.pspill = take(p.bi.pspill_bytes);
+      p.ckpt = take(p.bi.ckpt_bytes);
+    } else {
+      p.arow_den = pad4(den->max_states + 2);
+      p.alpha_den = take(TB * p.arow_den * 4);
+    }
   }
   p.total = off;
-  (void)V;
   return p;
 }
 
@@ -156,7 +171,10 @@ void ctcg_graph_free(ctcg_graph* g) {
 }
 
 size_t ctcg_workspace_bytes(int32_t T, int32_t B, int32_t V, const ctcg_graph* num, const ctcg_graph* den) {
-  return make_plan(T, B, V, num, den).total;
+  size_t need = make_plan(T, B, V, num, den).total;
+  // ctcg_path_sum on a decoding graph runs the fused bi-char kernel, planned in the denominator slot
+  if (num && !den) need = std::max(need, make_plan(T, B, V, nullptr, num).total);
+  return need;
 }
 
 uint64_t ctcg_launch_count(void) { return g_launches; }
@@ -171,6 +189,36 @@ int ctcg_profile_collect(char* names, size_t names_cap, float* ms, int max_recor
 
 // ---------------------------------------------------------------------------
 namespace {
+
+int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, int V, const int32_t* lens,
+               const ctcg_graph* den, double* cost, float* grad, const float* grad_scale, cudaStream_t st) {
+  BicharArgs a{};
+  a.x = x;
+  a.total = (long long)T * B * V;
+  a.T = T;
+  a.B = B;
+  a.V = V;
+  a.S = den->structured.S;
+  a.lens = lens;
+  a.loops = den->structured.allow_nonblank_selfloops;
+  a.ctx = den->structured.use_contextual_blanks;
+  a.pspill = reinterpret_cast<float*>(ws + p.pspill);
+  a.prowf = p.bi.prowf;
+  a.ckpt = reinterpret_cast<float*>(ws + p.ckpt);
+  a.nck = p.bi.nck;
+  a.cost = cost;
+  a.grad = grad;
+  a.g_scale = grad_scale;
+  a.K = p.bi.K;
+  a.DB = p.bi.DB;
+  a.NR = p.bi.NR;
+  a.rowf = p.bi.rowf;
+  a.nmain = p.bi.nmain;
+  CTCG_CUDA(launch_bichar_den(a, p.bi, st));
+  return CTCG_OK;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 int upload_lens(const Plan& p, void* ws, const int32_t* lens_host, int B, cudaStream_t st, int32_t** out) {
   int32_t* d = reinterpret_cast<int32_t*>(static_cast<unsigned char*>(ws) + p.lens);
@@ -239,7 +287,12 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
 
   // A per-frame softmax normaliser cancels between numerator and denominator.
   const bool softmax = (normalize == CTCG_NORM_SOFTMAX) && !den;
-  if (den) {
+  if (den && p.bi.ok && aligned16(logits) && aligned16(grad)) {
+    // 3a'. factorised bi-char denominator (kernels_bichar.cu), writes +gamma_den rows
+    if ((st_ = run_bichar(p, ws, logits, T, B, V, lens, den, cost_den, grad, grad_scale, st)) != CTCG_OK) return st_;
+    if (grad) CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
+  } else if (den) {
+    if (p.bi.ok) return CTCG_EUNSUPPORTED;  // misaligned tensors: the workspace was planned for the fused kernel
     // 3a. denominator path sum over the shared decoding graph, writes +gamma_den rows
     PathArgs d{};
     d.g = den->dev;
@@ -281,11 +334,20 @@ int ctcg_path_sum(const float* log_probs, int32_t T, int32_t B, int32_t V, const
   for (int b = 0; b < B; ++b)
     if (lens_host[b] < 0 || lens_host[b] > T) return CTCG_EINVAL;
   if (graph->max_label >= V) return CTCG_EINVAL;
-  const Plan p = make_plan(T, B, V, graph, nullptr);
-  if (workspace_bytes < p.total) return CTCG_EWORKSPACE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   int32_t* lens = nullptr;
+  const Plan ps = make_plan(T, B, V, nullptr, graph);
+  if (ps.bi.ok && aligned16(log_probs) && aligned16(grad)) {
+    if (workspace_bytes < ps.total) return CTCG_EWORKSPACE;
+    if ((st_ = upload_lens(ps, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
+    double* c64 = reinterpret_cast<double*>(ws + ps.cost_den);
+    if ((st_ = run_bichar(ps, ws, log_probs, T, B, V, lens, graph, c64, grad, nullptr, st)) != CTCG_OK) return st_;
+    CTCG_CUDA(launch_cost_to_float(B, c64, cost, st));
+    return CTCG_OK;
+  }
+  const Plan p = make_plan(T, B, V, graph, nullptr);
+  if (workspace_bytes < p.total) return CTCG_EWORKSPACE;
   if ((st_ = upload_lens(p, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
   double* cost64 = reinterpret_cast<double*>(ws + p.cost_num);
   PathArgs d{};

@@ -61,6 +61,30 @@ cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* l
 cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uint64_t* counts,
                               cudaStream_t st);
 
+// Arguments of the fused bi-char denominator kernel (kernels_bichar.cu).
+struct BicharArgs {
+  const float* x;          // logits (T, B, V), raw
+  long long total;         // T*B*V
+  int32_t T, B, V, S;
+  const int32_t* lens;     // device [B]
+  int32_t loops, ctx;      // allow_nonblank_selfloops, use_contextual_blanks (after loop_using_symbol_repetitions)
+  float* pspill;           // [B][T][prowf]: P_t[0..S), frame max, k_t, K_{t+1}
+  int32_t prowf;
+  float* ckpt;             // [B][nck][V]: scaled alpha at frames K, 2K, ...
+  int32_t nck;
+  double* cost;            // [B] natural-log path sum over the decoding graph
+  float* grad;             // (T, B, V) nullable: receives g_scale[b] * gamma_den
+  const float* g_scale;    // nullable
+  int32_t K, DB, NR, rowf, nmain;
+};
+// Workspace floats needed per batch (pspill + ckpt); smem plan and launch.
+struct BicharPlan {
+  int32_t ok, K, DB, NR, rowf, nmain, prowf, nck, threads, ru;
+  size_t smem_bytes, pspill_bytes, ckpt_bytes;
+};
+BicharPlan bichar_plan(int T, int B, int V, int S);
+cudaError_t launch_bichar_den(const BicharArgs& a, const BicharPlan& p, cudaStream_t st);
+
 // Incremented by every launch_* above.
 extern unsigned long long g_launches;
 
