@@ -118,7 +118,7 @@ __host__ __device__ inline Smem smem_plan(int NR, int rowf, int nmain, int prowf
   s.rows = o;     o += NR * rowf * 4;
   s.part = o;     o += 2 * (nmain + 1) * PARTW * 4;
   s.prow = o;     o += QRING * prowf * 4;
-  s.maxpart = o;  o += 2 * NPROD * 4;
+  s.maxpart = o;  o += 2 * (NPROD + NRECO) * 4;
   s.tab_e = o;    o += QRING * 4;
   s.tab_a = o;    o += QRING * 4;
   s.freel = o;    o += (NR + 2) * 4;
@@ -161,35 +161,55 @@ __device__ __forceinline__ RowGeo row_geo(int t, int b, int B, int V, long long 
 
 // Production order of the backward sweep: segments of K frames from the last to
 // the first, frames ascending inside a segment (the recompute runs forward in time).
-__device__ __forceinline__ int frame_of_q(int q, int len, int K) {
-  const int J = (len + K - 1) / K;
-  const int L0 = len - (J - 1) * K;
-  if (q < L0) return (J - 1) * K + q;
-  const int qq = q - L0;
-  return (J - 2 - qq / K) * K + qq % K;
-}
-__device__ __forceinline__ int q_of_frame(int t, int len, int K) {
-  const int J = (len + K - 1) / K;
-  const int L0 = len - (J - 1) * K;
-  const int j = t / K;
-  return (j == J - 1) ? (t - j * K) : (L0 + (J - 2 - j) * K + (t - j * K));
-}
+struct ProdCursor {
+  int tau, u, size, K;
+  __device__ __forceinline__ void init(int len, int K_) {
+    K = K_;
+    const int J = (len + K - 1) / K;
+    size = len - (J - 1) * K;
+    tau = (J - 1) * K;
+    u = 0;
+  }
+  __device__ __forceinline__ void next() {
+    ++u;
+    ++tau;
+    if (u == size) {
+      tau -= size + K;
+      u = 0;
+      size = K;
+    }
+  }
+};
+// Consumption order t = len-1, len-2, ...: q is the production index of frame t.
+struct ConsCursor {
+  int q, u, base, size, K;
+  __device__ __forceinline__ void init(int len, int K_) {
+    K = K_;
+    const int J = (len + K - 1) / K;
+    size = len - (J - 1) * K;
+    base = 0;
+    u = size - 1;
+    q = u;
+  }
+  __device__ __forceinline__ void prev() {
+    if (u > 0) {
+      --u;
+      --q;
+    } else {
+      base += size;
+      size = K;
+      u = K - 1;
+      q = base + K - 1;
+    }
+  }
+};
 
-// In-warp reduction of the partial-sum rows: lanes 8k..8k+7 add the NROWS
-// partials of column col[k]; every lane returns the RPW totals.
-__device__ __forceinline__ void reduce_partials(const float* pb, int nrows, const int (&col)[RPW], int lane,
-                                                float (&out)[RPW]) {
-  const int grp = lane >> 3, j8 = lane & 7;
-  int c = col[0];
-#pragma unroll
-  for (int k = 1; k < RPW; ++k) c = (grp == k) ? col[k] : c;
-  float s = 0.f;
-  for (int rr = j8; rr < nrows; rr += 8) s += pb[rr * PARTW + c];
-  s += __shfl_xor_sync(0xffffffffu, s, 4);
-  s += __shfl_xor_sync(0xffffffffu, s, 2);
-  s += __shfl_xor_sync(0xffffffffu, s, 1);
-#pragma unroll
-  for (int k = 0; k < RPW; ++k) out[k] = __shfl_sync(0xffffffffu, s, 8 * k);
+// Keep a value in a register: the compiler may not rematerialise it inside the hot loops.
+__device__ __forceinline__ void pin(int& v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ void pin(float& v) { asm volatile("" : "+f"(v)); }
+__device__ __forceinline__ void pin(float2& v) {
+  pin(v.x);
+  pin(v.y);
 }
 
 // ---- per-CTA context ----------------------------------------------------------
@@ -197,6 +217,7 @@ struct Ctx {
   BicharArgs A;
   int b, len, tid, lane, warp;
   int S, V, T, B, NR, rowf, nmain, prowf, K, DBk, partrows, LEAD;
+  int B3, b3, V3;  // (B, b, V) mod 4: row alignment arithmetic
   float *rows, *part, *prow, *maxpart, *csm, *psp, *ckp;
   int *tab_e, *tab_a, *freel, *phase, *ksm;
   Scal* sc;
@@ -205,11 +226,32 @@ struct Ctx {
   bool loops, ctx;
 };
 
+// Compile-time sizes when the kernel is instantiated for one S (SCT > 0), run-time otherwise.
+template <int SCT>
+struct Dims {
+  int S, V, nmain, partrows, rowf, prowf;
+  __device__ __forceinline__ explicit Dims(const Ctx& c) {
+    if (SCT > 0) {
+      S = SCT;
+      V = SCT * SCT;
+      nmain = 1 + (SCT - 1 + RPW - 1) / RPW;
+      rowf = (SCT * SCT + 3 + 3) & ~3;
+      prowf = (SCT + 3 + 3) & ~3;
+    } else {
+      S = c.S;
+      V = c.V;
+      nmain = c.nmain;
+      rowf = c.rowf;
+      prowf = c.prowf;
+    }
+    partrows = nmain + 1;
+  }
+};
+
 __device__ __forceinline__ void cta_sync() { asm volatile("bar.sync 0;" ::: "memory"); }
 
-__device__ __forceinline__ int row_r(const Ctx& c, int t) {
-  return (int)((((long long)t * c.B + c.b) * c.V) & 3);
-}
+// Offset (floats) of row (t, b) inside its 16-byte aligned window: ((t*B + b) * V) mod 4.
+__device__ __forceinline__ int row_r(const Ctx& c, int t) { return ((((t & 3) * c.B3 + c.b3) & 3) * c.V3) & 3; }
 
 // Every role calls this between the sweeps (same number of barriers on every path).
 // Returns false when there is no backward sweep to run.
@@ -247,36 +289,127 @@ __device__ __forceinline__ void issue_row(const Ctx& c, int t, int row, const fl
   for (int idx = g.nbulk; idx < g.r + c.V; ++idx) dst[idx] = c.A.x[g.w0 + idx];  // <= 3 floats at the tensor's end
 }
 
-// e = exp2((x - m) * log2e) in place over the row's aligned window.
-__device__ __forceinline__ void exp_row(float* rowp, int nfl, int p, float mL) {
+// e = exp2((x - m) * log2e) in place over the row's aligned window (nq float4 per row),
+// shared by NTH threads; all loads are issued before the first store (the compiler
+// cannot reorder them itself: loads and stores alias in shared memory).
+template <int NTH>
+__device__ __forceinline__ void exp_row(float* rowp, int nq, int p, float mL) {
+  constexpr int NQ = (640 + NTH - 1) / NTH;  // rows hold at most 640 float4 (V <= 2500)
   float4* rp = reinterpret_cast<float4*>(rowp);
-  for (int q4 = p; q4 * 4 < nfl; q4 += PTHREADS) {
-    float4 v = rp[q4];
-    v.x = ex2(fmaf(v.x, kLog2e, -mL));
-    v.y = ex2(fmaf(v.y, kLog2e, -mL));
-    v.z = ex2(fmaf(v.z, kLog2e, -mL));
-    v.w = ex2(fmaf(v.w, kLog2e, -mL));
-    rp[q4] = v;
+  float4 v[NQ];
+#pragma unroll
+  for (int j = 0; j < NQ; ++j)
+    if (p + j * NTH < nq) v[j] = rp[p + j * NTH];
+#pragma unroll
+  for (int j = 0; j < NQ; ++j) {
+    v[j].x = ex2(fmaf(v[j].x, kLog2e, -mL));
+    v[j].y = ex2(fmaf(v[j].y, kLog2e, -mL));
+    v[j].z = ex2(fmaf(v[j].z, kLog2e, -mL));
+    v[j].w = ex2(fmaf(v[j].w, kLog2e, -mL));
+  }
+#pragma unroll
+  for (int j = 0; j < NQ; ++j)
+    if (p + j * NTH < nq) rp[p + j * NTH] = v[j];
+}
+
+// Forward sweep of the 8 auxiliary warps (producers + recompute warps): pass A takes the
+// maximum of frame g, pass B turns frame g-1 into e = exp(x - max) in place.
+template <int SCT>
+__device__ __forceinline__ void aux_forward(const Ctx& c, int aw) {
+  constexpr int NTH = (NPROD + NRECO) * 32, NAUX = NPROD + NRECO;
+  constexpr int NQ = (640 + NTH - 1) / NTH;
+  const Dims<SCT> D(c);
+  const int p = aw * 32 + c.lane;
+  const int len = c.len, S = D.S, V = D.V, NR = c.NR, rowf = D.rowf, prowf = D.prowf;
+  int rowA = 0, parA = 0;  // ring row / mbarrier parity of the frame in pass A
+  int rowB = 0;
+  cta_sync();
+  for (int g = 0; g <= len + 2; ++g) {
+    const int f = g - 1;
+    float m = 0.f;
+    if (f >= 0 && f < len) {
+      const float* mp = c.maxpart + (f & 1) * NAUX;
+      m = fmaxf(fmaxf(fmaxf(mp[0], mp[1]), fmaxf(mp[2], mp[3])), fmaxf(fmaxf(mp[4], mp[5]), fmaxf(mp[6], mp[7])));
+      if (!(m > neg_inf())) m = 0.f;
+    }
+    if (g < len) {  // pass A: maximum of frame g (valid elements only)
+      mbar_wait(&c.mbar[rowA], parA);
+      const int r = row_r(c, g);
+      const float4* rp = reinterpret_cast<const float4*>(c.rows + rowA * rowf);
+      const int hi = r + V, nq = (hi + 3) >> 2;
+      float4 v[NQ];
+#pragma unroll
+      for (int j = 0; j < NQ; ++j)
+        if (p + j * NTH < nq) v[j] = rp[p + j * NTH];
+      float mx = neg_inf();
+#pragma unroll
+      for (int j = 0; j < NQ; ++j) {
+        const int i0 = (p + j * NTH) * 4;
+        if (p + j * NTH < nq) {
+          if (i0 >= r && i0 + 3 < hi) {
+            mx = fmaxf(fmaxf(mx, v[j].x), fmaxf(v[j].y, fmaxf(v[j].z, v[j].w)));
+          } else {
+            if (i0 >= r && i0 < hi) mx = fmaxf(mx, v[j].x);
+            if (i0 + 1 >= r && i0 + 1 < hi) mx = fmaxf(mx, v[j].y);
+            if (i0 + 2 >= r && i0 + 2 < hi) mx = fmaxf(mx, v[j].z);
+            if (i0 + 3 >= r && i0 + 3 < hi) mx = fmaxf(mx, v[j].w);
+          }
+        }
+      }
+      mx = warp_max(mx);
+      if (c.lane == 0) c.maxpart[(g & 1) * NAUX + aw] = mx;
+      if (++rowA == NR) {
+        rowA = 0;
+        parA ^= 1;
+      }
+    }
+    if (f >= 0 && f < len) {  // pass B: e = exp(x - max) in place
+      exp_row<NTH>(c.rows + rowB * rowf, (row_r(c, f) + V + 3) >> 2, p, m * kLog2e);
+      if (++rowB == NR) rowB = 0;
+      if (p == 0) {
+        c.sc->msum += (double)m;
+        c.psp[f * prowf + S] = m;
+      }
+    }
+    cta_sync();
   }
 }
 
+// In-warp reduction of the partial-sum rows: lanes 8k..8k+7 add the partials of the
+// group's column (at most 24 rows); returns the group's total in every lane of the group.
+__device__ __forceinline__ float group_sum(const float* pcol, int nrows, int j8) {
+  float s = (j8 < nrows) ? pcol[j8 * PARTW] : 0.f;
+  if (j8 + 8 < nrows) s += pcol[(j8 + 8) * PARTW];
+  if (j8 + 16 < nrows) s += pcol[(j8 + 16) * PARTW];
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  return s;
+}
+
 // ---- main warps: the serial recursion -----------------------------------------
+template <int SCT>
 __device__ __forceinline__ void main_role(const Ctx& c) {
-  const int lane = c.lane, warp = c.warp, S = c.S, K = c.K, len = c.len, nmain = c.nmain;
-  const int partrows = c.partrows, rowf = c.rowf, prowf = c.prowf;
-  // majors M (a strip per warp; warp 0 owns major 0 alone), minors n = lane, lane + 32
-  int Mv[RPW];
-  bool kval[RPW];
-#pragma unroll
-  for (int k = 0; k < RPW; ++k) {
-    Mv[k] = (warp == 0) ? 0 : 1 + (warp - 1) * RPW + k;
-    kval[k] = (warp == 0) ? (k == 0) : (Mv[k] < S);
-    if (!kval[k]) Mv[k] = 0;
-  }
+  const Dims<SCT> D(c);
+  const int S = D.S, nmain = D.nmain, partrows = D.partrows, rowf = D.rowf, prowf = D.prowf;
+  const int lane = c.lane, warp = c.warp, K = c.K, len = c.len, NR = c.NR;
+  // majors M0..M0+nk-1 (a strip per warp; warp 0 owns major 0 alone), minors n = lane, lane + 32
+  const int M0 = (warp == 0) ? 0 : 1 + (warp - 1) * RPW;
+  const int nk = (warp == 0) ? 1 : min(RPW, S - M0);
   const int n0 = lane, n1 = lane + 32;
   const bool nv0 = n0 < S, nv1 = n1 < S;
-  const float2 pm2 = make_float2(nv0 ? 1.f : 0.f, nv1 ? 1.f : 0.f);
   const bool loops = c.loops, ctx = c.ctx;
+  const int grp = lane >> 3, j8 = lane & 7;
+  const int gcol = (grp < nk) ? M0 + grp : 0;  // column this lane group reduces
+  float2 pm2[RPW];                             // validity of (k, slot) as 0/1 factors
+#pragma unroll
+  for (int k = 0; k < RPW; ++k) {
+    pm2[k] = make_float2((k < nk && nv0) ? 1.f : 0.f, (k < nk && nv1) ? 1.f : 0.f);
+    pin(pm2[k]);
+  }
+  int rowi = 0;  // ring row of the frame being consumed
+  const int dr = 0;
+  (void)dr;
 
   {  // ------------------------------ forward: majors = contexts c, minors = letters l
     float2 a2[RPW], m2[RPW];
@@ -284,41 +417,41 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
 #pragma unroll
     for (int k = 0; k < RPW; ++k) {
       a2[k] = make_float2(0.f, 0.f);
-      const int cc = Mv[k];
-      eo0[k] = (kval[k] && nv0 && (n0 != 0 || ctx)) ? cc * S + n0 : 0;  // (c,0) reads the global blank
-      eo1[k] = (kval[k] && nv1) ? cc * S + n1 : 0;
-      m2[k].x = (loops && kval[k] && nv0 && n0 != 0 && n0 != cc) ? 1.f : 0.f;
-      m2[k].y = (loops && kval[k] && nv1 && n1 != cc) ? 1.f : 0.f;
+      const int cc = M0 + k;
+      const bool kv = k < nk;
+      eo0[k] = (kv && nv0 && (n0 != 0 || ctx)) ? cc * S + n0 : 0;  // (c,0) reads the global blank
+      eo1[k] = (kv && nv1) ? cc * S + n1 : 0;
+      m2[k].x = (loops && kv && nv0 && n0 != 0 && n0 != cc) ? 1.f : 0.f;
+      m2[k].y = (loops && kv && nv1 && n1 != cc) ? 1.f : 0.f;
+      pin(eo0[k]);
+      pin(eo1[k]);
+      pin(m2[k]);
     }
+    const float col0 = (lane == 0) ? 0.f : 1.f;  // column 0 is not a context sum
+    int pspo = ((j8 == 0) && grp < nk) ? M0 + grp : -1;
+    pin(pspo);
     if (warp == 0 && lane == 0) {
       a2[0].x = pow2i(TARGET);
       c.part[nmain * PARTW + 0] = a2[0].x;  // extra row of buffer 0 carries a[c][0]
     }
+    int ck = K;  // frames until the next checkpoint
     cta_sync();
     for (int g = 0; g <= len + 2; ++g) {
       const int t = g - 2;
       if (t >= 0 && t < len) {
-        const float* rowp = c.rows + (t % c.NR) * rowf + row_r(c, t);
+        const float* rowp = c.rows + rowi * rowf + row_r(c, t);
+        if (++rowi == NR) rowi = 0;
+        const float* pb = c.part + (t & 1) * partrows * PARTW;
+        const float s = group_sum(pb + gcol, partrows, j8);
         float P[RPW];
-        reduce_partials(c.part + (t & 1) * partrows * PARTW, partrows, Mv, lane, P);
-        if (lane < RPW) {
-          float pv = P[0];
-          int mc = Mv[0];
-          bool ok = kval[0];
 #pragma unroll
-          for (int k = 1; k < RPW; ++k) {
-            pv = (lane == k) ? P[k] : pv;
-            mc = (lane == k) ? Mv[k] : mc;
-            ok = (lane == k) ? kval[k] : ok;
-          }
-          if (ok) c.psp[t * prowf + mc] = pv;
-        }
+        for (int k = 0; k < RPW; ++k) P[k] = __shfl_sync(0xffffffffu, s, 8 * k);
+        if (pspo >= 0) c.psp[t * prowf + pspo] = s;
         const int kk = c.ksm[t & 1];
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
           const float2 e2 = make_float2(rowp[eo0[k]], rowp[eo1[k]]);
-          const float2 P2 = fmul2(splat2(kval[k] ? P[k] : 0.f), pm2);
-          a2[k] = fmul2(e2, ffma2(m2[k], a2[k], P2));
+          a2[k] = fmul2(e2, ffma2(m2[k], a2[k], fmul2(splat2(P[k]), pm2[k])));
         }
         if (kk != 0) {
           const float2 s2 = splat2(pow2i(kk));
@@ -329,19 +462,24 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
 #pragma unroll
         for (int k = 1; k < RPW; ++k) cs = fadd2(cs, a2[k]);
         float* pn = c.part + ((t + 1) & 1) * partrows * PARTW;
-        pn[warp * PARTW + n0] = (lane == 0) ? 0.f : cs.x;  // column 0 is not a context sum
+        pn[warp * PARTW + n0] = cs.x * col0;
         pn[warp * PARTW + n1] = cs.y;
         if (lane == 0) {
-#pragma unroll
-          for (int k = 0; k < RPW; ++k)
-            if (kval[k]) pn[nmain * PARTW + Mv[k]] = a2[k].x;
+          float* ex = pn + nmain * PARTW + M0;
+          ex[0] = a2[0].x;
+          if (nk > 1) ex[1] = a2[1].x;
+          if (nk > 2) ex[2] = a2[2].x;
+          if (nk > 3) ex[3] = a2[3].x;
         }
-        if ((t + 1) % K == 0 && t + 1 < len) {
-          float* cp = c.ckp + (long long)((t + 1) / K) * c.V;
+        if (--ck == 0) {
+          ck = K;
+          if (t + 1 < len) {
+            float* cp = c.ckp + (long long)((t + 1) / K) * D.V + M0 * S;
 #pragma unroll
-          for (int k = 0; k < RPW; ++k) {
-            if (kval[k] && nv0) cp[Mv[k] * S + n0] = a2[k].x;
-            if (kval[k] && nv1) cp[Mv[k] * S + n1] = a2[k].y;
+            for (int k = 0; k < RPW; ++k) {
+              if (k < nk && nv0) cp[k * S + n0] = a2[k].x;
+              if (k < nk && nv1) cp[k * S + n1] = a2[k].y;
+            }
           }
         }
       }
@@ -355,23 +493,31 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
   int eo0[RPW], eo1[RPW], vo0[RPW], vo1[RPW];
 #pragma unroll
   for (int k = 0; k < RPW; ++k) {
-    const int l = Mv[k];
-    const bool v0 = kval[k] && nv0, v1 = kval[k] && nv1;
+    const int l = M0 + k;
+    const bool v0 = k < nk && nv0, v1 = k < nk && nv1;
     b2[k] = make_float2(v0 ? pow2i(TARGET) : 0.f, v1 ? pow2i(TARGET) : 0.f);
     f2[k] = make_float2(0.f, 0.f);
     vo0[k] = v0 ? n0 * S + l : 0;
-    vo1[k] = v1 ? n1 * S + l : 0;
+    vo1[k] = v1 ? n1 * S + l : vo0[k];
     eo0[k] = (v0 && (l != 0 || ctx)) ? n0 * S + l : 0;
     eo1[k] = (v1 && (l != 0 || ctx)) ? n1 * S + l : 0;
     m2[k].x = (loops && v0 && l != 0 && l != n0) ? 1.f : 0.f;
     m2[k].y = (loops && v1 && l != 0 && l != n1) ? 1.f : 0.f;
+    pin(vo0[k]);
+    pin(vo1[k]);
+    pin(eo0[k]);
+    pin(eo1[k]);
+    pin(m2[k]);
   }
+  ConsCursor cur;
+  cur.init(max(len, 1), K);
   const int GEND = len + c.LEAD + 2;
   for (int g = 0; g < GEND; ++g) {
     const int i = g - c.LEAD;
     if (i >= 0 && i < len) {
       const int t = len - 1 - i;
-      const int slot = q_of_frame(t, len, K) & (QRING - 1);
+      const int slot = cur.q & (QRING - 1);
+      cur.prev();
       const int r = row_r(c, t);
       const float* er = c.rows + (c.tab_e[slot] & 0xff) * rowf + r;
       float* ar = c.rows + c.tab_a[slot] * rowf + r;
@@ -380,31 +526,32 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         const float hs = pow2i(c.ksm[i & 1]);
         if (warp == 0) {
           float q0 = 0.f, q1 = 0.f;
+#pragma unroll 4
           for (int rr = 0; rr < nmain; ++rr) {
             q0 += pb[rr * PARTW + n0];
             q1 += pb[rr * PARTW + n1];
           }
-          b2[0] = make_float2(nv0 ? q0 * hs : 0.f, nv1 ? q1 * hs : 0.f);
+          b2[0] = fmul2(make_float2(q0 * hs, q1 * hs), pm2[0]);
         } else {
-          float Q[RPW];
-          reduce_partials(pb, nmain, Mv, lane, Q);
+          const float s = group_sum(pb + gcol, nmain, j8) * hs;
+          const float2 h2 = splat2(hs);
 #pragma unroll
           for (int k = 0; k < RPW; ++k) {
-            const float2 Q2 = fmul2(splat2(kval[k] ? Q[k] * hs : 0.f), pm2);
-            b2[k] = ffma2(fmul2(m2[k], splat2(hs)), f2[k], Q2);
+            const float Qk = __shfl_sync(0xffffffffu, s, 8 * k);
+            b2[k] = ffma2(fmul2(m2[k], h2), f2[k], fmul2(splat2(Qk), pm2[k]));
           }
         }
       }
       // (b) posteriors of frame t and f_t = e_t * b_{t+1}
-      const float c1 = c.csm[(i & 1) * 2], c2 = c.csm[(i & 1) * 2 + 1];
+      const float2 c12 = *reinterpret_cast<const float2*>(c.csm + (i & 1) * 2);
       float2 cs;
       if (warp == 0) {
         const float* pr = c.prow + slot * prowf;
         const float kt = pow2i((int)pr[S + 1]);
         const float2 e2 = make_float2(er[eo0[0]], er[eo1[0]]);
-        const float2 al = fmul2(e2, make_float2(nv0 ? pr[n0] * kt : 0.f, nv1 ? pr[n1] * kt : 0.f));
+        const float2 al = fmul2(fmul2(e2, make_float2(pr[nv0 ? n0 : 0] * kt, pr[nv1 ? n1 : 0] * kt)), pm2[0]);
         f2[0] = fmul2(e2, b2[0]);
-        const float2 gm = fmul2(fmul2(al, splat2(c1)), fmul2(b2[0], splat2(c2)));
+        const float2 gm = fmul2(fmul2(al, splat2(c12.x)), fmul2(b2[0], splat2(c12.y)));
         cs = f2[0];
         if (ctx) {
           if (nv0) ar[vo0[0]] = gm.x;
@@ -416,15 +563,25 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         }
       } else {
         cs = make_float2(0.f, 0.f);
+        const float2 c1 = splat2(c12.x), c2 = splat2(c12.y);
+        float2 e2[RPW], al[RPW];
+#pragma unroll
+        for (int k = 0; k < RPW; ++k) {  // all loads first: they alias the stores below
+          e2[k] = make_float2(er[eo0[k]], er[eo1[k]]);
+          al[k] = make_float2(ar[vo0[k]], ar[vo1[k]]);
+        }
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
-          const float2 e2 = make_float2(er[eo0[k]], er[eo1[k]]);
-          const float2 al = make_float2(ar[vo0[k]], ar[vo1[k]]);
-          f2[k] = fmul2(e2, b2[k]);
-          const float2 gm = fmul2(fmul2(al, splat2(c1)), fmul2(b2[k], splat2(c2)));
-          if (kval[k] && nv0) ar[vo0[k]] = gm.x;
-          if (kval[k] && nv1) ar[vo1[k]] = gm.y;
+          f2[k] = fmul2(e2[k], b2[k]);
+          al[k] = fmul2(fmul2(al[k], c1), fmul2(b2[k], c2));
           cs = fadd2(cs, f2[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < RPW; ++k) {
+          if (k < nk) {
+            if (nv0) ar[vo0[k]] = al[k].x;
+            if (nv1) ar[vo1[k]] = al[k].y;
+          }
         }
       }
       float* pn = c.part + ((i + 1) & 1) * partrows * PARTW;
@@ -436,87 +593,47 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
 }
 
 // ---- producer warps: row maximum and exp in place -------------------------------
+template <int SCT>
 __device__ __forceinline__ void prod_role(const Ctx& c) {
-  const int pw = c.warp - c.nmain;
+  const Dims<SCT> D(c);
+  const int pw = c.warp - D.nmain;
   const int p = pw * 32 + c.lane;
-  const int len = c.len, S = c.S, V = c.V, NR = c.NR;
-  cta_sync();
-  for (int g = 0; g <= len + 2; ++g) {
-    if (g < len) {  // pass A: maximum of frame g (valid elements only)
-      const int row = g % NR;
-      mbar_wait(&c.mbar[row], (g / NR) & 1);
-      const RowGeo ge = row_geo(g, c.b, c.B, V, c.A.total);
-      const float4* rp = reinterpret_cast<const float4*>(c.rows + row * c.rowf);
-      const int lo = ge.r, hi = ge.r + V;
-      float mx = neg_inf();
-      for (int q4 = p; q4 * 4 < ge.nfl; q4 += PTHREADS) {
-        const float4 v = rp[q4];
-        const int i0 = q4 * 4;
-        if (i0 >= lo && i0 + 3 < hi) {
-          mx = fmaxf(fmaxf(mx, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
-        } else {
-          if (i0 >= lo && i0 < hi) mx = fmaxf(mx, v.x);
-          if (i0 + 1 >= lo && i0 + 1 < hi) mx = fmaxf(mx, v.y);
-          if (i0 + 2 >= lo && i0 + 2 < hi) mx = fmaxf(mx, v.z);
-          if (i0 + 3 >= lo && i0 + 3 < hi) mx = fmaxf(mx, v.w);
-        }
-      }
-      mx = warp_max(mx);
-      if (c.lane == 0) c.maxpart[(g & 1) * NPROD + pw] = mx;
-    }
-    const int f = g - 1;
-    if (f >= 0 && f < len) {  // pass B: e = exp(x - max) in place
-      const float* mp = c.maxpart + (f & 1) * NPROD;
-      float m = fmaxf(fmaxf(mp[0], mp[1]), fmaxf(mp[2], mp[3]));
-      if (!(m > neg_inf())) m = 0.f;
-      const RowGeo ge = row_geo(f, c.b, c.B, V, c.A.total);
-      exp_row(c.rows + (f % NR) * c.rowf, ge.nfl, p, m * kLog2e);
-      if (p == 0) {
-        c.sc->msum += (double)m;
-        c.psp[f * c.prowf + S] = m;
-      }
-    }
-    cta_sync();
-  }
+  const int len = c.len, S = D.S, V = D.V, rowf = D.rowf, prowf = D.prowf;
+  aux_forward<SCT>(c, pw);
   if (!between_sweeps(c)) return;
   const int GEND = len + c.LEAD + 2;
+  ProdCursor pc;
+  pc.init(max(len, 1), c.K);
   for (int g = 0; g < GEND; ++g) {
     const int q = g - c.DBk;
     if (q >= 0 && q < len) {
       const int te = c.tab_e[q & (QRING - 1)];
       mbar_wait(&c.mbar[te & 0xff], te >> 8);
-      const int tau = frame_of_q(q, len, c.K);
-      const RowGeo ge = row_geo(tau, c.b, c.B, V, c.A.total);
-      const float mL = c.prow[(q & (QRING - 1)) * c.prowf + S] * kLog2e;
-      exp_row(c.rows + (te & 0xff) * c.rowf, ge.nfl, p, mL);
+      const float mL = c.prow[(q & (QRING - 1)) * prowf + S] * kLog2e;
+      exp_row<PTHREADS>(c.rows + (te & 0xff) * rowf, (row_r(c, pc.tau) + V + 3) >> 2, p, mL);
+      pc.next();
     }
     cta_sync();
   }
 }
 
 // ---- recompute warps: a_{t+1} = 2^k e_t (P_t + loop a_t), elementwise ------------
-template <int RU>
+template <int SCT, int RU>
 __device__ __forceinline__ void reco_role(const Ctx& c) {
-  const int rw = c.warp - c.nmain - NPROD;
-  const int lane = c.lane, len = c.len, S = c.S, V = c.V, K = c.K, T = c.T;
+  const Dims<SCT> D(c);
+  const int rw = c.warp - D.nmain - NPROD;
+  const int lane = c.lane, len = c.len, S = D.S, V = D.V, K = c.K, rowf = D.rowf, prowf = D.prowf;
   const int n0 = lane, n1 = lane + 32;
   const bool nv0 = n0 < S, nv1 = n1 < S;
-  cta_sync();
-  {  // forward sweep: these warps only zero the gradient rows beyond the utterance's end
-    const int nz = (c.A.grad && T > len) ? T - len : 0;
-    const int zper = (nz + len + 2) / (len + 3);
-    for (int g = 0; g <= len + 2; ++g) {
-      for (int z = g * zper + rw; z < (g + 1) * zper && z < nz; z += NRECO) {
-        float* dst = c.A.grad + ((long long)(len + z) * c.B + c.b) * V;
-        for (int j = lane; j < V; j += 32) dst[j] = 0.f;
-      }
-      cta_sync();
-    }
-  }
+  aux_forward<SCT>(c, NPROD + rw);
   if (!between_sweeps(c)) return;
   float2 ra[RU], rnx[RU];
 #pragma unroll
   for (int u = 0; u < RU; ++u) ra[u] = rnx[u] = make_float2(0.f, 0.f);
+  const int o0 = rw * S + (nv0 ? n0 : 0);       // element offsets of row rw; row rw + 4u adds 4u*S
+  const int o1 = rw * S + (nv1 ? n1 : (nv0 ? n0 : 0));
+  const float lp0 = c.loops && nv0 && n0 != 0 ? 1.f : 0.f;
+  const float lp1 = c.loops && nv1 ? 1.f : 0.f;
   auto load_ckpt = [&](int tau) {
     const float* cp = c.ckp + (long long)(tau / K) * V;
 #pragma unroll
@@ -528,21 +645,22 @@ __device__ __forceinline__ void reco_role(const Ctx& c) {
       }
     }
   };
-  if (len > 0) {
-    const int tau0 = frame_of_q(0, len, K);
-    if (tau0 > 0) load_ckpt(tau0);
-  }
+  ProdCursor pc;
+  pc.init(max(len, 1), K);
+  if (len > 0 && pc.tau > 0) load_ckpt(pc.tau);
   const int GEND = len + c.LEAD + 2;
   for (int g = 0; g < GEND; ++g) {
     const int q = g - c.DBk - 1;
     if (q >= 0 && q < len) {
-      const int tau = frame_of_q(q, len, K);
+      const int tau = pc.tau;
+      const bool seg0 = pc.u == 0;
+      pc.next();
       const int r = row_r(c, tau);
-      const float* er = c.rows + (c.tab_e[q & (QRING - 1)] & 0xff) * c.rowf + r;
-      float* ar = c.rows + c.tab_a[q & (QRING - 1)] * c.rowf + r;
-      const float* pr = c.prow + (q & (QRING - 1)) * c.prowf;
+      const float* er = c.rows + (c.tab_e[q & (QRING - 1)] & 0xff) * rowf + r;
+      float* ar = c.rows + c.tab_a[q & (QRING - 1)] * rowf + r;
+      const float* pr = c.prow + (q & (QRING - 1)) * prowf;
       const float scl = pow2i((int)pr[S + 1]);
-      if (tau % K == 0) {
+      if (seg0) {
         if (tau == 0) {
 #pragma unroll
           for (int u = 0; u < RU; ++u) ra[u] = make_float2(0.f, 0.f);
@@ -552,31 +670,51 @@ __device__ __forceinline__ void reco_role(const Ctx& c) {
           for (int u = 0; u < RU; ++u) ra[u] = rnx[u];
         }
       }
+      const float2 sl = make_float2(lp0 * scl, lp1 * scl);
+      // two batches: all shared-memory loads of a batch are issued before its stores
+      constexpr int H0 = (RU + 1) / 2;
 #pragma unroll
-      for (int u = 0; u < RU; ++u) {
-        const int cc = rw + 4 * u;
-        if (cc < S) {
-          const float Pc = pr[cc] * scl;
-          const float2 e2 = make_float2(nv0 ? er[cc * S + n0] : 0.f, nv1 ? er[cc * S + n1] : 0.f);
-          const float2 s2 =
-              make_float2((c.loops && n0 != 0 && n0 != cc) ? scl : 0.f, (c.loops && n1 != cc) ? scl : 0.f);
-          ra[u] = fmul2(e2, ffma2(s2, ra[u], splat2(Pc)));
-          if (nv0) ar[cc * S + n0] = ra[u].x;
-          if (nv1) ar[cc * S + n1] = ra[u].y;
+      for (int h = 0; h < 2; ++h) {
+        const int ub = h ? H0 : 0, ue = h ? RU : H0;
+        float Pc[H0];
+        float2 e2[H0];
+#pragma unroll
+        for (int u = ub; u < ue; ++u) {
+          const int cc = rw + 4 * u;
+          if (cc < S) {
+            Pc[u - ub] = pr[cc];
+            e2[u - ub] = make_float2(er[o0 + 4 * u * S], er[o1 + 4 * u * S]);
+          }
+        }
+#pragma unroll
+        for (int u = ub; u < ue; ++u) {
+          const int cc = rw + 4 * u;
+          if (cc < S) {
+            // the diagonal (c, c) is its own predecessor through P: no explicit loop there
+            const float2 s2 = make_float2(n0 == cc ? 0.f : sl.x, n1 == cc ? 0.f : sl.y);
+            ra[u] = fmul2(e2[u - ub], ffma2(s2, ra[u], splat2(Pc[u - ub] * scl)));
+          }
+        }
+#pragma unroll
+        for (int u = ub; u < ue; ++u) {
+          const int cc = rw + 4 * u;
+          if (cc < S) {
+            if (nv0) ar[o0 + 4 * u * S] = ra[u].x;
+            if (nv1) ar[o1 + 4 * u * S] = ra[u].y;
+          }
         }
       }
-      if (q + 1 < len) {  // prefetch the checkpoint that starts the next production segment
-        const int tn = frame_of_q(q + 1, len, K);
-        if (tn % K == 0 && tn > 0) load_ckpt(tn);
-      }
+      if (q + 1 < len && pc.u == 0 && pc.tau > 0) load_ckpt(pc.tau);  // checkpoint of the next production segment
     }
     cta_sync();
   }
 }
 
 // ---- scale warp: lagged power-of-two rescaling, final cost, posterior constants ----
+template <int SCT>
 __device__ __forceinline__ void scale_role(const Ctx& c) {
-  const int lane = c.lane, len = c.len, S = c.S, partrows = c.partrows, nmain = c.nmain, prowf = c.prowf;
+  const Dims<SCT> D(c);
+  const int lane = c.lane, len = c.len, S = D.S, partrows = D.partrows, nmain = D.nmain, prowf = D.prowf;
   const float inf = __int_as_float(0x7f800000);
   int kcur = 0, Ksum = TARGET;
   cta_sync();
@@ -585,6 +723,7 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
     if (t >= 0 && t <= len) {
       const float* pb = c.part + (t & 1) * partrows * PARTW;
       float s = 0.f;
+#pragma unroll 7
       for (int rr = 0; rr < partrows; ++rr) s += pb[rr * PARTW + lane] + pb[rr * PARTW + lane + 32];
       s = warp_sum(s);
       const bool ok = (s > 0.f) && (s < inf);
@@ -620,6 +759,8 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
   const int E1 = max(-120, min(120, -TARGET - exponent_of(inv_mass)));
   const float c1 = inv_mass * pow2i(E1) * c.gsc;
   int hcur = 0, Hsum = TARGET;
+  ConsCursor cur;  // frame of main step ii = i + 1
+  cur.init(max(len, 1), c.K);
   const int GEND = len + c.LEAD + 2;
   for (int g = 0; g < GEND; ++g) {
     const int i = g - c.LEAD;
@@ -629,6 +770,7 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
       if (i >= 1) {
         const float* pb = c.part + (i & 1) * partrows * PARTW;
         float s = 0.f;
+#pragma unroll 7
         for (int rr = 0; rr < nmain; ++rr) s += pb[rr * PARTW + lane] + pb[rr * PARTW + lane + 32];
         s = warp_sum(s);
         if ((s > 0.f) && (s < inf)) {
@@ -638,7 +780,8 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
       }
       Hsum += hnext;
       hcur = hnext;
-      const int slot = q_of_frame(len - 1 - ii, len, c.K) & (QRING - 1);
+      const int slot = cur.q & (QRING - 1);
+      cur.prev();
       const int te = c.tab_e[slot];
       mbar_wait(&c.mbar[te & 0xff], te >> 8);
       const int EA = klen - (int)c.prow[slot * prowf + S + 2];
@@ -654,14 +797,29 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
 }
 
 // ---- io warp: bulk loads, bulk stores of finished gradient rows, row pool ----------
+template <int SCT>
 __device__ __forceinline__ void io_role(const Ctx& c) {
-  const int lane = c.lane, len = c.len, V = c.V, NR = c.NR, K = c.K;
+  const Dims<SCT> D(c);
+  const int lane = c.lane, len = c.len, V = D.V, NR = c.NR, K = c.K, rowf = D.rowf, prowf = D.prowf;
+  int rowi = 0;
   if (lane == 0)
-    for (int f = 0; f < DF && f < len; ++f) issue_row(c, f, f % NR, nullptr, nullptr);
+    for (int f = 0; f < DF && f < len; ++f) {
+      issue_row(c, f, rowi, nullptr, nullptr);
+      if (++rowi == NR) rowi = 0;
+    }
   cta_sync();
+  const int nz = (c.A.grad && c.T > len) ? c.T - len : 0;  // rows beyond the utterance's end are zero
+  const int zper = (nz + len + 2) / (len + 3);
   for (int g = 0; g <= len + 2; ++g) {
     const int f = g + DF;
-    if (lane == 0 && f < len) issue_row(c, f, f % NR, nullptr, nullptr);
+    if (lane == 0 && f < len) {
+      issue_row(c, f, rowi, nullptr, nullptr);
+      if (++rowi == NR) rowi = 0;
+    }
+    for (int z = g * zper; z < (g + 1) * zper && z < nz; ++z) {
+      float* dst = c.A.grad + ((long long)(len + z) * c.B + c.b) * V;
+      for (int j = lane; j < V; j += 32) dst[j] = 0.f;
+    }
     cta_sync();
   }
   if (!between_sweeps(c)) return;
@@ -679,16 +837,20 @@ __device__ __forceinline__ void io_role(const Ctx& c) {
     c.freel[nf] = row;
     c.sc->nfree = nf + 1;
   };
+  ConsCursor cur;  // frame consumed by main step i of this global step
+  cur.init(max(len, 1), K);
+  ProdCursor pc;   // frame of production index g
+  pc.init(max(len, 1), K);
+  int e1 = -1, a1 = -1, a2 = -1, t1 = 0;  // rows of main steps i-1 (logits, alpha) and i-2 (alpha); frame of i-1
   const int GEND = len + c.LEAD + 2;
   for (int g = 0; g < GEND; ++g) {
     const int i = g - c.LEAD;  // main step of this global step; its frame is len-1-i
     // 1. the logits row consumed by main step i-1 is free again
-    if (lane == 0 && i - 1 >= 0 && i - 1 < len) push_row(c.tab_e[q_of_frame(len - i, len, K) & (QRING - 1)] & 0xff);
+    if (lane == 0 && e1 >= 0) push_row(e1);
     // 2. store the gradient row main step i-1 finished
-    if (i - 1 >= 0 && i - 1 < len) {
-      const int t = len - i;
-      const RowGeo ge = row_geo(t, c.b, c.B, V, c.A.total);
-      const float* src = c.rows + c.tab_a[q_of_frame(t, len, K) & (QRING - 1)] * c.rowf;
+    if (a1 >= 0) {
+      const RowGeo ge = row_geo(t1, c.b, c.B, V, c.A.total);
+      const float* src = c.rows + a1 * rowf;
       float* dst = c.A.grad + ge.w0;
       const int i0 = ge.r ? 4 : 0, i1 = (ge.r + V) & ~3;
       if (lane == 0) {
@@ -707,17 +869,29 @@ __device__ __forceinline__ void io_role(const Ctx& c) {
     if (lane == 0) {
       bulk_commit();
       bulk_wait_read<1>();  // 3. the row stored one step earlier has been read out of shared memory
-      if (i - 2 >= 0 && i - 2 < len) push_row(c.tab_a[q_of_frame(len + 1 - i, len, K) & (QRING - 1)]);
+      if (a2 >= 0) push_row(a2);
       if (g < len) {  // 4. fetch logits row + P row of production index g
         const int row = pop_row();
         const int ph = c.phase[row];
         c.phase[row] = ph ^ 1;
         c.tab_e[g & (QRING - 1)] = row | (ph << 8);
-        const int tau = frame_of_q(g, len, K);
-        issue_row(c, tau, row, c.psp + tau * c.prowf, c.prow + (g & (QRING - 1)) * c.prowf);
+        issue_row(c, pc.tau, row, c.psp + pc.tau * prowf, c.prow + (g & (QRING - 1)) * prowf);
+        pc.next();
       }
       const int qa = g - c.DBk;  // 5. row that receives the recomputed alpha of production index g - DB
       if (qa >= 0 && qa < len) c.tab_a[qa & (QRING - 1)] = pop_row();
+    }
+    // shift the row history by one main step
+    a2 = a1;
+    if (i >= 0 && i < len) {
+      const int slot = cur.q & (QRING - 1);
+      cur.prev();
+      e1 = c.tab_e[slot] & 0xff;
+      a1 = c.tab_a[slot];
+      t1 = len - 1 - i;
+    } else {
+      e1 = -1;
+      a1 = -1;
     }
     cta_sync();
   }
@@ -725,7 +899,7 @@ __device__ __forceinline__ void io_role(const Ctx& c) {
 }
 
 // ---- the kernel ---------------------------------------------------------------
-template <int RU, int MAXT>
+template <int SCT, int RU, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) bichar_den_kernel(const BicharArgs A) {
   extern __shared__ __align__(128) unsigned char smraw[];
   Ctx c;
@@ -738,6 +912,7 @@ __global__ void __launch_bounds__(MAXT, 1) bichar_den_kernel(const BicharArgs A)
   c.prowf = A.prowf; c.K = A.K; c.DBk = A.DB;
   c.partrows = A.nmain + 1;
   c.LEAD = A.DB + 1 + A.K;
+  c.B3 = A.B & 3; c.b3 = c.b & 3; c.V3 = A.V & 3;
   c.len = min(A.lens[c.b], A.T);
   const Smem L = smem_plan(A.NR, A.rowf, A.nmain, A.prowf);
   c.rows = reinterpret_cast<float*>(smraw + L.rows);
@@ -770,11 +945,11 @@ __global__ void __launch_bounds__(MAXT, 1) bichar_den_kernel(const BicharArgs A)
   }
   cta_sync();
   const int w = c.warp, nm = A.nmain;
-  if (w < nm) main_role(c);
-  else if (w < nm + NPROD) prod_role(c);
-  else if (w < nm + NPROD + NRECO) reco_role<RU>(c);
-  else if (w == nm + NPROD + NRECO) scale_role(c);
-  else io_role(c);
+  if (w < nm) main_role<SCT>(c);
+  else if (w < nm + NPROD) prod_role<SCT>(c);
+  else if (w < nm + NPROD + NRECO) reco_role<SCT, RU>(c);
+  else if (w == nm + NPROD + NRECO) scale_role<SCT>(c);
+  else io_role<SCT>(c);
 }
 
 }  // namespace
@@ -816,17 +991,18 @@ BicharPlan bichar_plan(int T, int B, int V, int S) {
 cudaError_t launch_bichar_den(const BicharArgs& a, const BicharPlan& p, cudaStream_t st) {
   ProfScope prof("bichar_den", st);
   cudaError_t e = cudaSuccess;
-  if (p.ru <= 9) {
-    e = cudaFuncSetAttribute(bichar_den_kernel<9, 736>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)p.smem_bytes);
-    if (e != cudaSuccess) return e;
-    bichar_den_kernel<9, 736><<<a.B, p.threads, p.smem_bytes, st>>>(a);
-  } else {
-    e = cudaFuncSetAttribute(bichar_den_kernel<13, 736>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)p.smem_bytes);
-    if (e != cudaSuccess) return e;
-    bichar_den_kernel<13, 736><<<a.B, p.threads, p.smem_bytes, st>>>(a);
-  }
+#define CTCG_BICHAR(SCT, RU)                                                                              \
+  do {                                                                                                    \
+    e = cudaFuncSetAttribute(bichar_den_kernel<SCT, RU, 736>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                             (int)p.smem_bytes);                                                          \
+    if (e != cudaSuccess) return e;                                                                       \
+    bichar_den_kernel<SCT, RU, 736><<<a.B, p.threads, p.smem_bytes, st>>>(a);                             \
+  } while (0)
+  if (a.S == 49) CTCG_BICHAR(49, 13);       // the WSJ character set (egs/wsj/vocabulary.txt)
+  else if (a.S == 36) CTCG_BICHAR(36, 9);   // BASELINE.json's nominal V = 1296
+  else if (p.ru <= 9) CTCG_BICHAR(0, 9);
+  else CTCG_BICHAR(0, 13);
+#undef CTCG_BICHAR
   ++g_launches;
   return cudaGetLastError();
 }
