@@ -76,6 +76,8 @@ struct BicharArgs {
   float* grad;             // (T, B, V) nullable: receives g_scale[b] * gamma_den
   const float* g_scale;    // nullable
   int32_t K, DB, NR, rowf, nmain;
+  long long* trace;        // diagnostics only (CTCG_BICHAR_TRACE): [warps][trace_steps][2] clocks of CTA 0
+  int32_t trace_steps;
 };
 // Workspace floats needed per batch (pspill + ckpt); smem plan and launch.
 struct BicharPlan {

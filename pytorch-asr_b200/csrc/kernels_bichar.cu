@@ -27,6 +27,8 @@
 //   io warp      issues cp.async.bulk loads (UBLKCP), bulk-stores gradient rows,
 //                zero-fills the rows beyond the utterance's end
 #include <cstdio>
+#include <cstdlib>
+#include <vector>
 
 #include "device_utils.cuh"
 #include "kernels.cuh"
@@ -118,7 +120,7 @@ __host__ __device__ inline Smem smem_plan(int NR, int rowf, int nmain, int prowf
   s.rows = o;     o += NR * rowf * 4;
   s.part = o;     o += 2 * (nmain + 1) * PARTW * 4;
   s.prow = o;     o += QRING * prowf * 4;
-  s.maxpart = o;  o += 2 * (NPROD + NRECO) * 4;
+  s.maxpart = o;  o += 2 * NPROD * 4;
   s.tab_e = o;    o += QRING * 4;
   s.tab_a = o;    o += QRING * 4;
   s.freel = o;    o += (NR + 2) * 4;
@@ -224,6 +226,8 @@ struct Ctx {
   uint64_t* mbar;
   float gsc;
   bool loops, ctx;
+  long long* trace;  // optional per-step timeline of CTA 0 (CTCG_BICHAR_TRACE), else null
+  int trace_steps;
 };
 
 // Compile-time sizes when the kernel is instantiated for one S (SCT > 0), run-time otherwise.
@@ -249,6 +253,21 @@ struct Dims {
 };
 
 __device__ __forceinline__ void cta_sync() { asm volatile("bar.sync 0;" ::: "memory"); }
+
+// Barrier of the per-frame loops.  With tracing on, lane 0 of every warp of CTA 0 stamps
+// the clock when its work of the step ends (before the barrier) and when the barrier releases.
+__device__ __forceinline__ void step_sync(const Ctx& c, int& n) {
+  if (c.trace) {
+    const bool rec = c.b == 0 && c.lane == 0 && n < c.trace_steps;
+    long long* tr = c.trace + ((long long)c.warp * c.trace_steps + (rec ? n : 0)) * 2;
+    if (rec) tr[0] = clock64();
+    cta_sync();  // one barrier instruction for the whole warp: no divergence around it
+    if (rec) tr[1] = clock64();
+    ++n;
+  } else {
+    cta_sync();
+  }
+}
 
 // Offset (floats) of row (t, b) inside its 16-byte aligned window: ((t*B + b) * V) mod 4.
 __device__ __forceinline__ int row_r(const Ctx& c, int t) { return ((((t & 3) * c.B3 + c.b3) & 3) * c.V3) & 3; }
@@ -289,92 +308,6 @@ __device__ __forceinline__ void issue_row(const Ctx& c, int t, int row, const fl
   for (int idx = g.nbulk; idx < g.r + c.V; ++idx) dst[idx] = c.A.x[g.w0 + idx];  // <= 3 floats at the tensor's end
 }
 
-// e = exp2((x - m) * log2e) in place over the row's aligned window (nq float4 per row),
-// shared by NTH threads; all loads are issued before the first store (the compiler
-// cannot reorder them itself: loads and stores alias in shared memory).
-template <int NTH>
-__device__ __forceinline__ void exp_row(float* rowp, int nq, int p, float mL) {
-  constexpr int NQ = (640 + NTH - 1) / NTH;  // rows hold at most 640 float4 (V <= 2500)
-  float4* rp = reinterpret_cast<float4*>(rowp);
-  float4 v[NQ];
-#pragma unroll
-  for (int j = 0; j < NQ; ++j)
-    if (p + j * NTH < nq) v[j] = rp[p + j * NTH];
-#pragma unroll
-  for (int j = 0; j < NQ; ++j) {
-    v[j].x = ex2(fmaf(v[j].x, kLog2e, -mL));
-    v[j].y = ex2(fmaf(v[j].y, kLog2e, -mL));
-    v[j].z = ex2(fmaf(v[j].z, kLog2e, -mL));
-    v[j].w = ex2(fmaf(v[j].w, kLog2e, -mL));
-  }
-#pragma unroll
-  for (int j = 0; j < NQ; ++j)
-    if (p + j * NTH < nq) rp[p + j * NTH] = v[j];
-}
-
-// Forward sweep of the 8 auxiliary warps (producers + recompute warps): pass A takes the
-// maximum of frame g, pass B turns frame g-1 into e = exp(x - max) in place.
-template <int SCT>
-__device__ __forceinline__ void aux_forward(const Ctx& c, int aw) {
-  constexpr int NTH = (NPROD + NRECO) * 32, NAUX = NPROD + NRECO;
-  constexpr int NQ = (640 + NTH - 1) / NTH;
-  const Dims<SCT> D(c);
-  const int p = aw * 32 + c.lane;
-  const int len = c.len, S = D.S, V = D.V, NR = c.NR, rowf = D.rowf, prowf = D.prowf;
-  int rowA = 0, parA = 0;  // ring row / mbarrier parity of the frame in pass A
-  int rowB = 0;
-  cta_sync();
-  for (int g = 0; g <= len + 2; ++g) {
-    const int f = g - 1;
-    float m = 0.f;
-    if (f >= 0 && f < len) {
-      const float* mp = c.maxpart + (f & 1) * NAUX;
-      m = fmaxf(fmaxf(fmaxf(mp[0], mp[1]), fmaxf(mp[2], mp[3])), fmaxf(fmaxf(mp[4], mp[5]), fmaxf(mp[6], mp[7])));
-      if (!(m > neg_inf())) m = 0.f;
-    }
-    if (g < len) {  // pass A: maximum of frame g (valid elements only)
-      mbar_wait(&c.mbar[rowA], parA);
-      const int r = row_r(c, g);
-      const float4* rp = reinterpret_cast<const float4*>(c.rows + rowA * rowf);
-      const int hi = r + V, nq = (hi + 3) >> 2;
-      float4 v[NQ];
-#pragma unroll
-      for (int j = 0; j < NQ; ++j)
-        if (p + j * NTH < nq) v[j] = rp[p + j * NTH];
-      float mx = neg_inf();
-#pragma unroll
-      for (int j = 0; j < NQ; ++j) {
-        const int i0 = (p + j * NTH) * 4;
-        if (p + j * NTH < nq) {
-          if (i0 >= r && i0 + 3 < hi) {
-            mx = fmaxf(fmaxf(mx, v[j].x), fmaxf(v[j].y, fmaxf(v[j].z, v[j].w)));
-          } else {
-            if (i0 >= r && i0 < hi) mx = fmaxf(mx, v[j].x);
-            if (i0 + 1 >= r && i0 + 1 < hi) mx = fmaxf(mx, v[j].y);
-            if (i0 + 2 >= r && i0 + 2 < hi) mx = fmaxf(mx, v[j].z);
-            if (i0 + 3 >= r && i0 + 3 < hi) mx = fmaxf(mx, v[j].w);
-          }
-        }
-      }
-      mx = warp_max(mx);
-      if (c.lane == 0) c.maxpart[(g & 1) * NAUX + aw] = mx;
-      if (++rowA == NR) {
-        rowA = 0;
-        parA ^= 1;
-      }
-    }
-    if (f >= 0 && f < len) {  // pass B: e = exp(x - max) in place
-      exp_row<NTH>(c.rows + rowB * rowf, (row_r(c, f) + V + 3) >> 2, p, m * kLog2e);
-      if (++rowB == NR) rowB = 0;
-      if (p == 0) {
-        c.sc->msum += (double)m;
-        c.psp[f * prowf + S] = m;
-      }
-    }
-    cta_sync();
-  }
-}
-
 // In-warp reduction of the partial-sum rows: lanes 8k..8k+7 add the partials of the
 // group's column (at most 24 rows); returns the group's total in every lane of the group.
 __device__ __forceinline__ float group_sum(const float* pcol, int nrows, int j8) {
@@ -387,10 +320,31 @@ __device__ __forceinline__ float group_sum(const float* pcol, int nrows, int j8)
   return s;
 }
 
+// Shared-memory accesses through 32-bit shared-space addresses (one IADD per access,
+// immediates folded by ptxas); volatile keeps them ordered against the barriers.
+__device__ __forceinline__ float lds(unsigned a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float4 lds4(unsigned a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v)); }
+
+// e = exp(x - m) for a pair: exp2(x * log2e - m * log2e)
+__device__ __forceinline__ float2 exp_pair(float x0, float x1, float nmL) {
+  const float2 y = ffma2(make_float2(x0, x1), splat2(kLog2e), splat2(nmL));
+  return make_float2(ex2(y.x), ex2(y.y));
+}
+
 // ---- main warps: the serial recursion -----------------------------------------
 template <int SCT>
 __device__ __forceinline__ void main_role(const Ctx& c) {
   const Dims<SCT> D(c);
+  int nstep = 0;
   const int S = D.S, nmain = D.nmain, partrows = D.partrows, rowf = D.rowf, prowf = D.prowf;
   const int lane = c.lane, warp = c.warp, K = c.K, len = c.len, NR = c.NR;
   // majors M0..M0+nk-1 (a strip per warp; warp 0 owns major 0 alone), minors n = lane, lane + 32
@@ -401,48 +355,50 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
   const bool loops = c.loops, ctx = c.ctx;
   const int grp = lane >> 3, j8 = lane & 7;
   const int gcol = (grp < nk) ? M0 + grp : 0;  // column this lane group reduces
-  float2 pm2[RPW];                             // validity of (k, slot) as 0/1 factors
-#pragma unroll
-  for (int k = 0; k < RPW; ++k) {
-    pm2[k] = make_float2((k < nk && nv0) ? 1.f : 0.f, (k < nk && nv1) ? 1.f : 0.f);
-    pin(pm2[k]);
-  }
-  int rowi = 0;  // ring row of the frame being consumed
-  const int dr = 0;
-  (void)dr;
+  const unsigned rows_a = smem_u32(c.rows), part_a = smem_u32(c.part);
+  const unsigned rowb = rowf * 4, partb = partrows * PARTW * 4;
 
   {  // ------------------------------ forward: majors = contexts c, minors = letters l
     float2 a2[RPW], m2[RPW];
-    int eo0[RPW], eo1[RPW];
+    unsigned a0[RPW], a1[RPW];  // byte offsets of the element's label inside the logits row
 #pragma unroll
     for (int k = 0; k < RPW; ++k) {
       a2[k] = make_float2(0.f, 0.f);
-      const int cc = M0 + k;
       const bool kv = k < nk;
-      eo0[k] = (kv && nv0 && (n0 != 0 || ctx)) ? cc * S + n0 : 0;  // (c,0) reads the global blank
-      eo1[k] = (kv && nv1) ? cc * S + n1 : 0;
+      const int cc = kv ? M0 + k : 0;
+      a0[k] = (nv0 && (n0 != 0 || ctx)) ? (cc * S + n0) * 4 : 0;  // (c,0) reads the global blank
+      a1[k] = (cc * S + n1) * 4;  // an invalid slot reads past the row (inside shared memory); never used
       m2[k].x = (loops && kv && nv0 && n0 != 0 && n0 != cc) ? 1.f : 0.f;
       m2[k].y = (loops && kv && nv1 && n1 != cc) ? 1.f : 0.f;
-      pin(eo0[k]);
-      pin(eo1[k]);
       pin(m2[k]);
     }
     const float col0 = (lane == 0) ? 0.f : 1.f;  // column 0 is not a context sum
-    int pspo = ((j8 == 0) && grp < nk) ? M0 + grp : -1;
-    pin(pspo);
+    const int pspo = ((j8 == 0) && grp < nk) ? M0 + grp : -1;
+    const float gmask = (grp < nk) ? 1.f : 0.f;
     if (warp == 0 && lane == 0) {
       a2[0].x = pow2i(TARGET);
       c.part[nmain * PARTW + 0] = a2[0].x;  // extra row of buffer 0 carries a[c][0]
     }
-    int ck = K;  // frames until the next checkpoint
+    int ck = K;            // frames until the next checkpoint
+    unsigned rowoff = 0;   // byte offset of the ring row being consumed
     cta_sync();
-    for (int g = 0; g <= len + 2; ++g) {
-      const int t = g - 2;
+    for (int g = 0; g <= len + 1; ++g) {
+      const int t = g - 1;
       if (t >= 0 && t < len) {
-        const float* rowp = c.rows + rowi * rowf + row_r(c, t);
-        if (++rowi == NR) rowi = 0;
-        const float* pb = c.part + (t & 1) * partrows * PARTW;
-        const float s = group_sum(pb + gcol, partrows, j8);
+        const unsigned base = rows_a + rowoff + row_r(c, t) * 4;
+        rowoff += rowb;
+        if (rowoff == NR * rowb) rowoff = 0;
+        const float4 mp = lds4(smem_u32(c.maxpart) + (t & 1) * 16);
+        float m = fmaxf(fmaxf(mp.x, mp.y), fmaxf(mp.z, mp.w));
+        if (!(m > neg_inf())) m = 0.f;
+        const float nmL = -m * kLog2e;
+        float xr0[RPW], xr1[RPW];
+#pragma unroll
+        for (int k = 0; k < RPW; ++k) {
+          xr0[k] = lds(base + a0[k]);
+          xr1[k] = lds(base + a1[k]);
+        }
+        const float s = group_sum(c.part + (t & 1) * partrows * PARTW + gcol, partrows, j8) * gmask;
         float P[RPW];
 #pragma unroll
         for (int k = 0; k < RPW; ++k) P[k] = __shfl_sync(0xffffffffu, s, 8 * k);
@@ -450,8 +406,8 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         const int kk = c.ksm[t & 1];
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
-          const float2 e2 = make_float2(rowp[eo0[k]], rowp[eo1[k]]);
-          a2[k] = fmul2(e2, ffma2(m2[k], a2[k], fmul2(splat2(P[k]), pm2[k])));
+          const float2 e2 = exp_pair(xr0[k], xr1[k], nmL);
+          a2[k] = fmul2(e2, ffma2(m2[k], a2[k], splat2(P[k])));
         }
         if (kk != 0) {
           const float2 s2 = splat2(pow2i(kk));
@@ -461,15 +417,15 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         float2 cs = a2[0];
 #pragma unroll
         for (int k = 1; k < RPW; ++k) cs = fadd2(cs, a2[k]);
-        float* pn = c.part + ((t + 1) & 1) * partrows * PARTW;
-        pn[warp * PARTW + n0] = cs.x * col0;
-        pn[warp * PARTW + n1] = cs.y;
+        const unsigned pn = part_a + ((t + 1) & 1) * partb;
+        sts(pn + (warp * PARTW + n0) * 4, cs.x * col0);
+        sts(pn + (warp * PARTW + n1) * 4, cs.y);
         if (lane == 0) {
-          float* ex = pn + nmain * PARTW + M0;
-          ex[0] = a2[0].x;
-          if (nk > 1) ex[1] = a2[1].x;
-          if (nk > 2) ex[2] = a2[2].x;
-          if (nk > 3) ex[3] = a2[3].x;
+          const unsigned ex = pn + (nmain * PARTW + M0) * 4;
+          sts(ex, a2[0].x);
+          if (nk > 1) sts(ex + 4, a2[1].x);
+          if (nk > 2) sts(ex + 8, a2[2].x);
+          if (nk > 3) sts(ex + 12, a2[3].x);
         }
         if (--ck == 0) {
           ck = K;
@@ -483,32 +439,31 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
           }
         }
       }
-      cta_sync();
+      step_sync(c, nstep);
     }
   }
   if (!between_sweeps(c)) return;
 
   // -------------------------------- backward: majors = letters l, minors = contexts c
   float2 b2[RPW], f2[RPW], m2[RPW];
-  int eo0[RPW], eo1[RPW], vo0[RPW], vo1[RPW];
+  unsigned eo0[RPW], eo1[RPW], vo0[RPW], vo1[RPW];
 #pragma unroll
   for (int k = 0; k < RPW; ++k) {
-    const int l = M0 + k;
-    const bool v0 = k < nk && nv0, v1 = k < nk && nv1;
+    const bool kv = k < nk;
+    const int l = kv ? M0 + k : 0;
+    const bool v0 = kv && nv0, v1 = kv && nv1;
     b2[k] = make_float2(v0 ? pow2i(TARGET) : 0.f, v1 ? pow2i(TARGET) : 0.f);
     f2[k] = make_float2(0.f, 0.f);
-    vo0[k] = v0 ? n0 * S + l : 0;
-    vo1[k] = v1 ? n1 * S + l : vo0[k];
-    eo0[k] = (v0 && (l != 0 || ctx)) ? n0 * S + l : 0;
-    eo1[k] = (v1 && (l != 0 || ctx)) ? n1 * S + l : 0;
+    vo0[k] = (nv0 ? n0 * S + l : 0) * 4;
+    vo1[k] = (nv1 ? n1 * S + l : 0) * 4;
+    eo0[k] = (l != 0 || ctx) ? vo0[k] : 0;
+    eo1[k] = (l != 0 || ctx) ? vo1[k] : 0;
     m2[k].x = (loops && v0 && l != 0 && l != n0) ? 1.f : 0.f;
     m2[k].y = (loops && v1 && l != 0 && l != n1) ? 1.f : 0.f;
-    pin(vo0[k]);
-    pin(vo1[k]);
-    pin(eo0[k]);
-    pin(eo1[k]);
     pin(m2[k]);
   }
+  const float2 pm = make_float2(nv0 ? 1.f : 0.f, nv1 ? 1.f : 0.f);
+  const float gmask = (grp < nk) ? 1.f : 0.f;
   ConsCursor cur;
   cur.init(max(len, 1), K);
   const int GEND = len + c.LEAD + 2;
@@ -518,9 +473,15 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
       const int t = len - 1 - i;
       const int slot = cur.q & (QRING - 1);
       cur.prev();
-      const int r = row_r(c, t);
-      const float* er = c.rows + (c.tab_e[slot] & 0xff) * rowf + r;
-      float* ar = c.rows + c.tab_a[slot] * rowf + r;
+      const unsigned r4 = row_r(c, t) * 4;
+      const unsigned er = rows_a + (c.tab_e[slot] & 0xff) * rowb + r4;
+      const unsigned ar = rows_a + c.tab_a[slot] * rowb + r4;
+      float2 e2[RPW], al[RPW];
+#pragma unroll
+      for (int k = 0; k < RPW; ++k) {  // all loads first: they alias the stores below
+        e2[k] = make_float2(lds(er + eo0[k]), lds(er + eo1[k]));
+        al[k] = make_float2(lds(ar + vo0[k]), lds(ar + vo1[k]));
+      }
       if (i > 0) {  // (a) b_{t+1} = 2^h (Q + loop * f_{t+1}) from the partials of the previous step
         const float* pb = c.part + (i & 1) * partrows * PARTW;
         const float hs = pow2i(c.ksm[i & 1]);
@@ -531,14 +492,14 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
             q0 += pb[rr * PARTW + n0];
             q1 += pb[rr * PARTW + n1];
           }
-          b2[0] = fmul2(make_float2(q0 * hs, q1 * hs), pm2[0]);
+          b2[0] = fmul2(make_float2(q0 * hs, q1 * hs), pm);
         } else {
-          const float s = group_sum(pb + gcol, nmain, j8) * hs;
+          const float s = group_sum(pb + gcol, nmain, j8) * (hs * gmask);
           const float2 h2 = splat2(hs);
 #pragma unroll
           for (int k = 0; k < RPW; ++k) {
             const float Qk = __shfl_sync(0xffffffffu, s, 8 * k);
-            b2[k] = ffma2(fmul2(m2[k], h2), f2[k], fmul2(splat2(Qk), pm2[k]));
+            b2[k] = ffma2(fmul2(m2[k], h2), f2[k], splat2(Qk));
           }
         }
       }
@@ -548,28 +509,21 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
       if (warp == 0) {
         const float* pr = c.prow + slot * prowf;
         const float kt = pow2i((int)pr[S + 1]);
-        const float2 e2 = make_float2(er[eo0[0]], er[eo1[0]]);
-        const float2 al = fmul2(fmul2(e2, make_float2(pr[nv0 ? n0 : 0] * kt, pr[nv1 ? n1 : 0] * kt)), pm2[0]);
-        f2[0] = fmul2(e2, b2[0]);
-        const float2 gm = fmul2(fmul2(al, splat2(c12.x)), fmul2(b2[0], splat2(c12.y)));
+        const float2 a_ = fmul2(fmul2(e2[0], make_float2(pr[nv0 ? n0 : 0] * kt, pr[nv1 ? n1 : 0] * kt)), pm);
+        f2[0] = fmul2(e2[0], b2[0]);
+        const float2 gm = fmul2(fmul2(a_, splat2(c12.x)), fmul2(b2[0], splat2(c12.y)));
         cs = f2[0];
         if (ctx) {
-          if (nv0) ar[vo0[0]] = gm.x;
-          if (nv1) ar[vo1[0]] = gm.y;
+          if (nv0) sts(ar + vo0[0], gm.x);
+          if (nv1) sts(ar + vo1[0], gm.y);
         } else {  // one global blank: its posterior is the sum over the S blank states
           const float tot = warp_sum(gm.x + gm.y);
-          if (nv0) ar[vo0[0]] = (lane == 0) ? tot : 0.f;
-          if (nv1) ar[vo1[0]] = 0.f;
+          if (nv0) sts(ar + vo0[0], (lane == 0) ? tot : 0.f);
+          if (nv1) sts(ar + vo1[0], 0.f);
         }
       } else {
         cs = make_float2(0.f, 0.f);
         const float2 c1 = splat2(c12.x), c2 = splat2(c12.y);
-        float2 e2[RPW], al[RPW];
-#pragma unroll
-        for (int k = 0; k < RPW; ++k) {  // all loads first: they alias the stores below
-          e2[k] = make_float2(er[eo0[k]], er[eo1[k]]);
-          al[k] = make_float2(ar[vo0[k]], ar[vo1[k]]);
-        }
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
           f2[k] = fmul2(e2[k], b2[k]);
@@ -579,66 +533,99 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
           if (k < nk) {
-            if (nv0) ar[vo0[k]] = al[k].x;
-            if (nv1) ar[vo1[k]] = al[k].y;
+            if (nv0) sts(ar + vo0[k], al[k].x);
+            if (nv1) sts(ar + vo1[k], al[k].y);
           }
         }
       }
-      float* pn = c.part + ((i + 1) & 1) * partrows * PARTW;
-      pn[warp * PARTW + n0] = cs.x;
-      pn[warp * PARTW + n1] = cs.y;
+      const unsigned pn = part_a + ((i + 1) & 1) * partb + warp * PARTW * 4;
+      sts(pn + n0 * 4, cs.x);
+      sts(pn + n1 * 4, cs.y);
     }
-    cta_sync();
+    step_sync(c, nstep);
   }
 }
 
-// ---- producer warps: row maximum and exp in place -------------------------------
-template <int SCT>
-__device__ __forceinline__ void prod_role(const Ctx& c) {
-  const Dims<SCT> D(c);
-  const int pw = c.warp - D.nmain;
-  const int p = pw * 32 + c.lane;
-  const int len = c.len, S = D.S, V = D.V, rowf = D.rowf, prowf = D.prowf;
-  aux_forward<SCT>(c, pw);
-  if (!between_sweeps(c)) return;
-  const int GEND = len + c.LEAD + 2;
-  ProdCursor pc;
-  pc.init(max(len, 1), c.K);
-  for (int g = 0; g < GEND; ++g) {
-    const int q = g - c.DBk;
-    if (q >= 0 && q < len) {
-      const int te = c.tab_e[q & (QRING - 1)];
-      mbar_wait(&c.mbar[te & 0xff], te >> 8);
-      const float mL = c.prow[(q & (QRING - 1)) * prowf + S] * kLog2e;
-      exp_row<PTHREADS>(c.rows + (te & 0xff) * rowf, (row_r(c, pc.tau) + V + 3) >> 2, p, mL);
-      pc.next();
-    }
-    cta_sync();
-  }
-}
-
-// ---- recompute warps: a_{t+1} = 2^k e_t (P_t + loop a_t), elementwise ------------
+// ---- auxiliary warps ------------------------------------------------------------
+// forward sweep : warps 0..3 take the maximum of the frame that the main warps consume in
+//                 the next step; warps 4..7 zero the gradient rows beyond the utterance's end.
+// backward sweep: all 8 turn a landed logits row into e = exp(x - max) (in place) and the
+//                 recomputed a_{t+1} = 2^k e_t (P_t + loop a_t) (own row), elementwise.
 template <int SCT, int RU>
-__device__ __forceinline__ void reco_role(const Ctx& c) {
+__device__ __forceinline__ void aux_role(const Ctx& c) {
+  constexpr int NAUX = NPROD + NRECO;
   const Dims<SCT> D(c);
-  const int rw = c.warp - D.nmain - NPROD;
-  const int lane = c.lane, len = c.len, S = D.S, V = D.V, K = c.K, rowf = D.rowf, prowf = D.prowf;
+  int nstep = 0;
+  const int aw = c.warp - D.nmain;
+  const int lane = c.lane, len = c.len, S = D.S, V = D.V, K = c.K, NR = c.NR, rowf = D.rowf, prowf = D.prowf;
+  const unsigned rows_a = smem_u32(c.rows), rowb = rowf * 4;
+  cta_sync();
+  if (aw < NPROD) {
+    constexpr int NQ = (640 + PTHREADS - 1) / PTHREADS;  // rows hold at most 640 float4 (V <= 2500)
+    const int p = aw * 32 + lane;
+    int rowA = 0, parA = 0;  // ring row / mbarrier parity of the frame
+    for (int g = 0; g <= len + 1; ++g) {
+      if (g < len) {
+        mbar_wait(&c.mbar[rowA], parA);
+        const int r = row_r(c, g);
+        const unsigned rp = rows_a + rowA * rowb;
+        const int hi = r + V, nq = (hi + 3) >> 2;
+        float4 v[NQ];
+#pragma unroll
+        for (int j = 0; j < NQ; ++j)
+          if (p + j * PTHREADS < nq) v[j] = lds4(rp + (p + j * PTHREADS) * 16);
+        float mx = neg_inf();
+#pragma unroll
+        for (int j = 0; j < NQ; ++j) {
+          const int i0 = (p + j * PTHREADS) * 4;
+          if (p + j * PTHREADS < nq) {
+            if (i0 >= r && i0 + 3 < hi) {
+              mx = fmaxf(fmaxf(mx, v[j].x), fmaxf(v[j].y, fmaxf(v[j].z, v[j].w)));
+            } else {  // first / last float4 of the window: mask the neighbours' floats
+              if (i0 >= r && i0 < hi) mx = fmaxf(mx, v[j].x);
+              if (i0 + 1 >= r && i0 + 1 < hi) mx = fmaxf(mx, v[j].y);
+              if (i0 + 2 >= r && i0 + 2 < hi) mx = fmaxf(mx, v[j].z);
+              if (i0 + 3 >= r && i0 + 3 < hi) mx = fmaxf(mx, v[j].w);
+            }
+          }
+        }
+        mx = warp_max(mx);
+        if (lane == 0) c.maxpart[(g & 1) * 4 + aw] = mx;
+        if (++rowA == NR) {
+          rowA = 0;
+          parA ^= 1;
+        }
+      }
+      step_sync(c, nstep);
+    }
+  } else {
+    const int zw = aw - NPROD;
+    const int nz = (c.A.grad && c.T > len) ? c.T - len : 0;
+    const int zper = (nz + len + 1) / (len + 2);
+    for (int g = 0; g <= len + 1; ++g) {
+      for (int z = g * zper + zw; z < (g + 1) * zper && z < nz; z += NRECO) {
+        float* dst = c.A.grad + ((long long)(len + z) * c.B + c.b) * V;
+        for (int j = lane; j < V; j += 32) dst[j] = 0.f;
+      }
+      step_sync(c, nstep);
+    }
+  }
+  if (!between_sweeps(c)) return;
+
   const int n0 = lane, n1 = lane + 32;
   const bool nv0 = n0 < S, nv1 = n1 < S;
-  aux_forward<SCT>(c, NPROD + rw);
-  if (!between_sweeps(c)) return;
   float2 ra[RU], rnx[RU];
 #pragma unroll
   for (int u = 0; u < RU; ++u) ra[u] = rnx[u] = make_float2(0.f, 0.f);
-  const int o0 = rw * S + (nv0 ? n0 : 0);       // element offsets of row rw; row rw + 4u adds 4u*S
-  const int o1 = rw * S + (nv1 ? n1 : (nv0 ? n0 : 0));
+  const unsigned o0 = (aw * S + (nv0 ? n0 : 0)) * 4;  // element offsets of row aw; row aw + 8u adds 8u*S
+  const unsigned o1 = (aw * S + (nv1 ? n1 : (nv0 ? n0 : 0))) * 4;
   const float lp0 = c.loops && nv0 && n0 != 0 ? 1.f : 0.f;
   const float lp1 = c.loops && nv1 ? 1.f : 0.f;
   auto load_ckpt = [&](int tau) {
     const float* cp = c.ckp + (long long)(tau / K) * V;
 #pragma unroll
     for (int u = 0; u < RU; ++u) {
-      const int cc = rw + 4 * u;
+      const int cc = aw + NAUX * u;
       if (cc < S) {
         if (nv0) rnx[u].x = cp[cc * S + n0];
         if (nv1) rnx[u].y = cp[cc * S + n1];
@@ -650,63 +637,68 @@ __device__ __forceinline__ void reco_role(const Ctx& c) {
   if (len > 0 && pc.tau > 0) load_ckpt(pc.tau);
   const int GEND = len + c.LEAD + 2;
   for (int g = 0; g < GEND; ++g) {
-    const int q = g - c.DBk - 1;
+    const int q = g - c.DBk;
     if (q >= 0 && q < len) {
       const int tau = pc.tau;
       const bool seg0 = pc.u == 0;
       pc.next();
-      const int r = row_r(c, tau);
-      const float* er = c.rows + (c.tab_e[q & (QRING - 1)] & 0xff) * rowf + r;
-      float* ar = c.rows + c.tab_a[q & (QRING - 1)] * rowf + r;
+      const int te = c.tab_e[q & (QRING - 1)];
+      const unsigned r4 = row_r(c, tau) * 4;
+      const unsigned er = rows_a + (te & 0xff) * rowb + r4;
+      const unsigned ar = rows_a + c.tab_a[q & (QRING - 1)] * rowb + r4;
+      mbar_wait(&c.mbar[te & 0xff], te >> 8);
       const float* pr = c.prow + (q & (QRING - 1)) * prowf;
       const float scl = pow2i((int)pr[S + 1]);
+      const float nmL = -pr[S] * kLog2e;
       if (seg0) {
         if (tau == 0) {
 #pragma unroll
           for (int u = 0; u < RU; ++u) ra[u] = make_float2(0.f, 0.f);
-          if (rw == 0 && lane == 0) ra[0].x = pow2i(TARGET);
+          if (aw == 0 && lane == 0) ra[0].x = pow2i(TARGET);
         } else {
 #pragma unroll
           for (int u = 0; u < RU; ++u) ra[u] = rnx[u];
         }
       }
       const float2 sl = make_float2(lp0 * scl, lp1 * scl);
-      // two batches: all shared-memory loads of a batch are issued before its stores
-      constexpr int H0 = (RU + 1) / 2;
+      float Pc[RU];
+      float2 x2[RU];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int ub = h ? H0 : 0, ue = h ? RU : H0;
-        float Pc[H0];
-        float2 e2[H0];
-#pragma unroll
-        for (int u = ub; u < ue; ++u) {
-          const int cc = rw + 4 * u;
-          if (cc < S) {
-            Pc[u - ub] = pr[cc];
-            e2[u - ub] = make_float2(er[o0 + 4 * u * S], er[o1 + 4 * u * S]);
-          }
+      for (int u = 0; u < RU; ++u) {  // all shared-memory loads before the first store
+        const int cc = aw + NAUX * u;
+        if (cc < S) {
+          Pc[u] = pr[cc];
+          x2[u] = make_float2(lds(er + o0 + NAUX * u * S * 4), lds(er + o1 + NAUX * u * S * 4));
         }
+      }
 #pragma unroll
-        for (int u = ub; u < ue; ++u) {
-          const int cc = rw + 4 * u;
-          if (cc < S) {
-            // the diagonal (c, c) is its own predecessor through P: no explicit loop there
-            const float2 s2 = make_float2(n0 == cc ? 0.f : sl.x, n1 == cc ? 0.f : sl.y);
-            ra[u] = fmul2(e2[u - ub], ffma2(s2, ra[u], splat2(Pc[u - ub] * scl)));
-          }
+      for (int u = 0; u < RU; ++u) {
+        const int cc = aw + NAUX * u;
+        if (cc < S) {
+          const float2 e2 = exp_pair(x2[u].x, x2[u].y, nmL);
+          // the diagonal (c, c) is its own predecessor through P: no explicit loop there
+          const float2 s2 = make_float2(n0 == cc ? 0.f : sl.x, n1 == cc ? 0.f : sl.y);
+          ra[u] = fmul2(e2, ffma2(s2, ra[u], splat2(Pc[u] * scl)));
+          x2[u] = e2;
         }
+      }
 #pragma unroll
-        for (int u = ub; u < ue; ++u) {
-          const int cc = rw + 4 * u;
-          if (cc < S) {
-            if (nv0) ar[o0 + 4 * u * S] = ra[u].x;
-            if (nv1) ar[o1 + 4 * u * S] = ra[u].y;
+      for (int u = 0; u < RU; ++u) {
+        const int cc = aw + NAUX * u;
+        if (cc < S) {
+          if (nv0) {
+            sts(er + o0 + NAUX * u * S * 4, x2[u].x);
+            sts(ar + o0 + NAUX * u * S * 4, ra[u].x);
+          }
+          if (nv1) {
+            sts(er + o1 + NAUX * u * S * 4, x2[u].y);
+            sts(ar + o1 + NAUX * u * S * 4, ra[u].y);
           }
         }
       }
       if (q + 1 < len && pc.u == 0 && pc.tau > 0) load_ckpt(pc.tau);  // checkpoint of the next production segment
     }
-    cta_sync();
+    step_sync(c, nstep);
   }
 }
 
@@ -714,22 +706,29 @@ __device__ __forceinline__ void reco_role(const Ctx& c) {
 template <int SCT>
 __device__ __forceinline__ void scale_role(const Ctx& c) {
   const Dims<SCT> D(c);
+  int nstep = 0;
   const int lane = c.lane, len = c.len, S = D.S, partrows = D.partrows, nmain = D.nmain, prowf = D.prowf;
   const float inf = __int_as_float(0x7f800000);
   int kcur = 0, Ksum = TARGET;
   cta_sync();
-  for (int g = 0; g <= len + 2; ++g) {
-    const int t = g - 2;
+  const bool cv0 = lane < S, cv1 = lane + 32 < S;  // partial columns >= S hold unused (possibly non-finite) values
+  for (int g = 0; g <= len + 1; ++g) {
+    const int t = g - 1;
     if (t >= 0 && t <= len) {
       const float* pb = c.part + (t & 1) * partrows * PARTW;
       float s = 0.f;
 #pragma unroll 7
-      for (int rr = 0; rr < partrows; ++rr) s += pb[rr * PARTW + lane] + pb[rr * PARTW + lane + 32];
+      for (int rr = 0; rr < partrows; ++rr) s += (cv0 ? pb[rr * PARTW + lane] : 0.f) + (cv1 ? pb[rr * PARTW + lane + 32] : 0.f);
       s = warp_sum(s);
       const bool ok = (s > 0.f) && (s < inf);
       if (t < len) {
         const int Knext = Ksum + kcur;  // K_{t+1}: alpha_{t+1} = a_{t+1} 2^-K_{t+1} exp(sum of maxima)
         if (lane == 0) {
+          const float* mp = c.maxpart + (t & 1) * 4;  // frame maximum found by the producer warps
+          float m = fmaxf(fmaxf(mp[0], mp[1]), fmaxf(mp[2], mp[3]));
+          if (!(m > neg_inf())) m = 0.f;
+          c.sc->msum += (double)m;
+          c.psp[t * prowf + S] = m;
           c.psp[t * prowf + S + 1] = (float)kcur;
           c.psp[t * prowf + S + 2] = (float)Knext;
         }
@@ -751,7 +750,7 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
         c.sc->klen = Ksum;
       }
     }
-    cta_sync();
+    step_sync(c, nstep);
   }
   if (!between_sweeps(c)) return;
   const float inv_mass = c.sc->inv_mass;
@@ -771,7 +770,7 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
         const float* pb = c.part + (i & 1) * partrows * PARTW;
         float s = 0.f;
 #pragma unroll 7
-        for (int rr = 0; rr < nmain; ++rr) s += pb[rr * PARTW + lane] + pb[rr * PARTW + lane + 32];
+        for (int rr = 0; rr < nmain; ++rr) s += (cv0 ? pb[rr * PARTW + lane] : 0.f) + (cv1 ? pb[rr * PARTW + lane + 32] : 0.f);
         s = warp_sum(s);
         if ((s > 0.f) && (s < inf)) {
           const int ex = exponent_of(s) + hcur;
@@ -792,7 +791,7 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
         c.csm[(ii & 1) * 2 + 1] = pow2i(E2);
       }
     }
-    cta_sync();
+    step_sync(c, nstep);
   }
 }
 
@@ -800,6 +799,7 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
 template <int SCT>
 __device__ __forceinline__ void io_role(const Ctx& c) {
   const Dims<SCT> D(c);
+  int nstep = 0;
   const int lane = c.lane, len = c.len, V = D.V, NR = c.NR, K = c.K, rowf = D.rowf, prowf = D.prowf;
   int rowi = 0;
   if (lane == 0)
@@ -808,19 +808,13 @@ __device__ __forceinline__ void io_role(const Ctx& c) {
       if (++rowi == NR) rowi = 0;
     }
   cta_sync();
-  const int nz = (c.A.grad && c.T > len) ? c.T - len : 0;  // rows beyond the utterance's end are zero
-  const int zper = (nz + len + 2) / (len + 3);
-  for (int g = 0; g <= len + 2; ++g) {
+  for (int g = 0; g <= len + 1; ++g) {
     const int f = g + DF;
     if (lane == 0 && f < len) {
       issue_row(c, f, rowi, nullptr, nullptr);
       if (++rowi == NR) rowi = 0;
     }
-    for (int z = g * zper; z < (g + 1) * zper && z < nz; ++z) {
-      float* dst = c.A.grad + ((long long)(len + z) * c.B + c.b) * V;
-      for (int j = lane; j < V; j += 32) dst[j] = 0.f;
-    }
-    cta_sync();
+    step_sync(c, nstep);
   }
   if (!between_sweeps(c)) return;
   auto pop_row = [&]() -> int {
@@ -878,7 +872,7 @@ __device__ __forceinline__ void io_role(const Ctx& c) {
         issue_row(c, pc.tau, row, c.psp + pc.tau * prowf, c.prow + (g & (QRING - 1)) * prowf);
         pc.next();
       }
-      const int qa = g - c.DBk;  // 5. row that receives the recomputed alpha of production index g - DB
+      const int qa = g - c.DBk + 1;  // 5. row that receives the recomputed alpha in the next step
       if (qa >= 0 && qa < len) c.tab_a[qa & (QRING - 1)] = pop_row();
     }
     // shift the row history by one main step
@@ -893,7 +887,7 @@ __device__ __forceinline__ void io_role(const Ctx& c) {
       e1 = -1;
       a1 = -1;
     }
-    cta_sync();
+    step_sync(c, nstep);
   }
   if (lane == 0) bulk_wait_all<0>();
 }
@@ -911,7 +905,7 @@ __global__ void __launch_bounds__(MAXT, 1) bichar_den_kernel(const BicharArgs A)
   c.S = A.S; c.V = A.V; c.T = A.T; c.B = A.B; c.NR = A.NR; c.rowf = A.rowf; c.nmain = A.nmain;
   c.prowf = A.prowf; c.K = A.K; c.DBk = A.DB;
   c.partrows = A.nmain + 1;
-  c.LEAD = A.DB + 1 + A.K;
+  c.LEAD = A.DB + A.K;
   c.B3 = A.B & 3; c.b3 = c.b & 3; c.V3 = A.V & 3;
   c.len = min(A.lens[c.b], A.T);
   const Smem L = smem_plan(A.NR, A.rowf, A.nmain, A.prowf);
@@ -932,6 +926,8 @@ __global__ void __launch_bounds__(MAXT, 1) bichar_den_kernel(const BicharArgs A)
   c.ckp = A.ckpt + (long long)c.b * A.nck * A.V;
   c.loops = A.loops != 0;
   c.ctx = A.ctx != 0;
+  c.trace = A.trace;
+  c.trace_steps = A.trace_steps;
 
   for (int i = c.tid; i < 2 * c.partrows * PARTW; i += blockDim.x) c.part[i] = 0.f;
   if (c.tid == 0) {
@@ -946,8 +942,7 @@ __global__ void __launch_bounds__(MAXT, 1) bichar_den_kernel(const BicharArgs A)
   cta_sync();
   const int w = c.warp, nm = A.nmain;
   if (w < nm) main_role<SCT>(c);
-  else if (w < nm + NPROD) prod_role<SCT>(c);
-  else if (w < nm + NPROD + NRECO) reco_role<SCT, RU>(c);
+  else if (w < nm + NPROD + NRECO) aux_role<SCT, RU>(c);
   else if (w == nm + NPROD + NRECO) scale_role<SCT>(c);
   else io_role<SCT>(c);
 }
@@ -963,8 +958,8 @@ BicharPlan bichar_plan(int T, int B, int V, int S) {
   p.threads = (p.nmain + NPROD + NRECO + 2) * 32;
   p.rowf = pad4(V + 3);
   p.prowf = pad4(S + 3);
-  p.ru = (S + 3) / 4;
-  if (p.ru > 13 || p.threads > 736) return p;  // S <= 49 with the kernels instantiated below
+  p.ru = (S + 7) / 8;
+  if (p.ru > 7 || p.threads > 736) return p;  // S <= 49 with the kernels instantiated below
   const int budget = 227 * 1024;
   int NR = 0;
   for (int n = 40; n >= 12; --n) {
@@ -974,9 +969,9 @@ BicharPlan bichar_plan(int T, int B, int V, int S) {
     }
   }
   if (NR < 12) return p;
-  // rows needed by the backward sweep: 2K + DB + 5
-  p.DB = (NR >= 25) ? 4 : 3;
-  p.K = (NR - p.DB - 5) / 2;
+  // rows in flight in the backward sweep: 2K + DB + 4 ("row pool")
+  p.DB = 2;
+  p.K = (NR - p.DB - 4) / 2;
   if (p.K > 8) p.K = 8;
   if (p.K < 2 || NR < DF + 3) return p;
   p.NR = NR;
@@ -988,7 +983,19 @@ BicharPlan bichar_plan(int T, int B, int V, int S) {
   return p;
 }
 
-cudaError_t launch_bichar_den(const BicharArgs& a, const BicharPlan& p, cudaStream_t st) {
+cudaError_t launch_bichar_den(const BicharArgs& a_in, const BicharPlan& p, cudaStream_t st) {
+  BicharArgs a = a_in;
+  // CTCG_BICHAR_TRACE=<file>: per-step clock stamps of every warp of CTA 0 (profiles/trace_roles.py reads it).
+  const char* trace_path = getenv("CTCG_BICHAR_TRACE");
+  const int warps = p.threads / 32;
+  a.trace = nullptr;
+  a.trace_steps = 0;
+  if (trace_path && trace_path[0]) {
+    a.trace_steps = 2 * a.T + 64;
+    const size_t bytes = (size_t)warps * a.trace_steps * 2 * sizeof(long long);
+    if (cudaMalloc(&a.trace, bytes) != cudaSuccess) return cudaGetLastError();
+    cudaMemsetAsync(a.trace, 0, bytes, st);
+  }
   ProfScope prof("bichar_den", st);
   cudaError_t e = cudaSuccess;
 #define CTCG_BICHAR(SCT, RU)                                                                              \
@@ -998,13 +1005,27 @@ cudaError_t launch_bichar_den(const BicharArgs& a, const BicharPlan& p, cudaStre
     if (e != cudaSuccess) return e;                                                                       \
     bichar_den_kernel<SCT, RU, 736><<<a.B, p.threads, p.smem_bytes, st>>>(a);                             \
   } while (0)
-  if (a.S == 49) CTCG_BICHAR(49, 13);       // the WSJ character set (egs/wsj/vocabulary.txt)
-  else if (a.S == 36) CTCG_BICHAR(36, 9);   // BASELINE.json's nominal V = 1296
-  else if (p.ru <= 9) CTCG_BICHAR(0, 9);
-  else CTCG_BICHAR(0, 13);
+  if (a.S == 49) CTCG_BICHAR(49, 7);       // the WSJ character set (egs/wsj/vocabulary.txt)
+  else if (a.S == 36) CTCG_BICHAR(36, 5);   // BASELINE.json's nominal V = 1296
+  else if (p.ru <= 5) CTCG_BICHAR(0, 5);
+  else CTCG_BICHAR(0, 7);
 #undef CTCG_BICHAR
   ++g_launches;
-  return cudaGetLastError();
+  e = cudaGetLastError();
+  if (a.trace) {
+    const size_t n = (size_t)warps * a.trace_steps * 2;
+    std::vector<long long> host(n);
+    cudaStreamSynchronize(st);
+    cudaMemcpy(host.data(), a.trace, n * sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaFree(a.trace);
+    if (FILE* f = fopen(trace_path, "wb")) {
+      const int hdr[4] = {warps, a.trace_steps, p.nmain, a.T};
+      fwrite(hdr, sizeof(int), 4, f);
+      fwrite(host.data(), sizeof(long long), n, f);
+      fclose(f);
+    }
+  }
+  return e;
 }
 
 }  // namespace ctcg
