@@ -109,7 +109,7 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
     g->dev_blob = nullptr;
   }
   std::vector<unsigned char> blob;
-  size_t o[14];
+  size_t o[18];
   append(&blob, g->state_off, &o[0]);
   append(&blob, g->lab_off, &o[1]);
   append(&blob, g->lab_list, &o[2]);
@@ -124,6 +124,10 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   append(&blob, g->out_lab, &o[11]);
   append(&blob, g->out_clab, &o[12]);
   append(&blob, g->out_w, &o[13]);
+  append(&blob, g->lab_ptr, &o[14]);
+  append(&blob, g->lab_src, &o[15]);
+  append(&blob, g->lab_dst, &o[16]);
+  append(&blob, g->lab_w, &o[17]);
   void* d = nullptr;
   CTCG_CUDA(cudaMalloc(&d, blob.size()));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -155,6 +159,12 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   v.out_lab = reinterpret_cast<const int32_t*>(p + o[11]);
   v.out_clab = reinterpret_cast<const int32_t*>(p + o[12]);
   v.out_w = reinterpret_cast<const float*>(p + o[13]);
+  v.lab_ptr = reinterpret_cast<const int32_t*>(p + o[14]);
+  v.lab_src = reinterpret_cast<const int32_t*>(p + o[15]);
+  v.lab_dst = reinterpret_cast<const int32_t*>(p + o[16]);
+  v.lab_w = reinterpret_cast<const float*>(p + o[17]);
+  v.max_arcs = g->max_arcs;
+  v.unit_weights = g->unit_weights;
   g->dev_blob = d;
   g->dev_bytes = blob.size();
   g->device = dev;
@@ -269,7 +279,7 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   a.x = xg;
   a.x_stride_t = p.nlp;
   a.x_stride_b = (long long)T * p.nlp;
-  a.x_scale = 1.f;
+  a.x_scale = kLog2e;
   a.lens = lens;
   a.T = T;
   a.B = B;
@@ -283,7 +293,8 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   a.g_sign = 1.f;
   a.g_scale = nullptr;
   a.write_grad = grad != nullptr;
-  CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
+  if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
+  else CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
 
   // A per-frame softmax normaliser cancels between numerator and denominator.
   const bool softmax = (normalize == CTCG_NORM_SOFTMAX) && !den;

@@ -38,6 +38,14 @@ struct GraphDev {
   const int32_t* out_lab;
   const int32_t* out_clab;
   const float* out_w;
+  // arcs grouped by compact label (deterministic posterior sums): graph g owns rows
+  // [lab_off[g]+g, lab_off[g+1]+g] of lab_ptr; entries are absolute arc indices
+  const int32_t* lab_ptr;
+  const int32_t* lab_src;
+  const int32_t* lab_dst;
+  const float* lab_w;
+  int32_t max_arcs;      // most arcs of any one graph
+  int32_t unit_weights;  // every arc weight is 0 (semiring One)
 };
 
 // Factorised description of the bi-char decoding graph (fst_utils.py:765-817):
@@ -63,6 +71,10 @@ struct ctcg_graph {
   std::vector<float> in_w;
   std::vector<int32_t> out_ptr, out_dst, out_lab, out_clab;
   std::vector<float> out_w;
+  std::vector<int32_t> lab_ptr, lab_src, lab_dst;
+  std::vector<float> lab_w;
+  int32_t max_arcs = 0;
+  int32_t unit_weights = 1;
   ctcg::Structured structured{0, 0, 0, 0, 0};
   // device mirror
   int device = -1;

@@ -192,6 +192,9 @@ int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out) {
   g->out_lab.resize(total_arcs);
   g->out_clab.resize(total_arcs);
   g->out_w.resize(total_arcs);
+  g->lab_src.resize(total_arcs);
+  g->lab_dst.resize(total_arcs);
+  g->lab_w.resize(total_arcs);
   int32_t arc_base = 0;
   std::vector<int32_t> idx;
   for (int32_t gi = 0; gi < G; ++gi) {
@@ -280,6 +283,26 @@ int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out) {
         g->in_w[arc_base + i] = a.weight;
       }
     }
+    // by compact label (then source, destination): fixed summation order of the posteriors
+    std::sort(idx.begin(), idx.end(), [&](int32_t x, int32_t y) {
+      const Arc &a = r.arcs[x], &b = r.arcs[y];
+      return std::tie(a.label, a.src, a.dst, a.weight) < std::tie(b.label, b.src, b.dst, b.weight);
+    });
+    {
+      const int32_t nl = static_cast<int32_t>(labs.size());
+      std::vector<int32_t> cnt(nl + 1, 0);
+      for (const Arc& a : r.arcs) cnt[clab(a.label) + 1]++;
+      for (int32_t j = 0; j < nl; ++j) cnt[j + 1] += cnt[j];
+      for (int32_t j = 0; j <= nl; ++j) g->lab_ptr.push_back(arc_base + cnt[j]);
+      for (int32_t i = 0; i < na; ++i) {
+        const Arc& a = r.arcs[idx[i]];
+        g->lab_src[arc_base + i] = a.src;
+        g->lab_dst[arc_base + i] = a.dst;
+        g->lab_w[arc_base + i] = a.weight;
+        if (a.weight != 0.f) g->unit_weights = 0;
+      }
+    }
+    g->max_arcs = std::max(g->max_arcs, na);
     arc_base += na;
   }
   *out = g;

@@ -32,6 +32,11 @@ struct PathArgs {
 // launch_gather (16-byte aligned rows, prescaled), staged through a cp.async ring.
 cudaError_t launch_path_fwd_bwd(const PathArgs& a, bool compact, cudaStream_t st);
 
+// Warp-per-utterance linear-domain variant for small graphs (kernels_num.cu); same arguments
+// as the compact mode above.
+bool num_lin_supported(const PathArgs& a);
+cudaError_t launch_num_lin(const PathArgs& a, cudaStream_t st);
+
 // xg[b][t][j] = logits[t][b][lab_list_b[j]] * log2(e) for t < lens[b]
 cudaError_t launch_gather(const float* logits, int T, int B, int V, const int32_t* lens,
                           const GraphDev& num, float* xg, int nlp, int normalize, int S,

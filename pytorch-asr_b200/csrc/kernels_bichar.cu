@@ -45,6 +45,7 @@ constexpr int TARGET = 60;    // scaled mass is kept near 2^TARGET
 constexpr int BAND = 20;
 constexpr int QRING = 32;     // frames-in-flight tables (power of two, > 2*K + D + 5)
 constexpr int DF = 8;         // TMA lookahead of the forward sweep (frames)
+constexpr int TRS = 8;        // clock stamps per warp and step in a CTCG_BICHAR_TRACE capture
 
 // ---- PTX wrappers -----------------------------------------------------------
 __device__ __forceinline__ unsigned smem_u32(const void* p) {
@@ -208,6 +209,7 @@ struct ConsCursor {
 
 // Keep a value in a register: the compiler may not rematerialise it inside the hot loops.
 __device__ __forceinline__ void pin(int& v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ void pin(unsigned& v) { asm volatile("" : "+r"(v)); }
 __device__ __forceinline__ void pin(float& v) { asm volatile("" : "+f"(v)); }
 __device__ __forceinline__ void pin(float2& v) {
   pin(v.x);
@@ -259,13 +261,22 @@ __device__ __forceinline__ void cta_sync() { asm volatile("bar.sync 0;" ::: "mem
 __device__ __forceinline__ void step_sync(const Ctx& c, int& n) {
   if (c.trace) {
     const bool rec = c.b == 0 && c.lane == 0 && n < c.trace_steps;
-    long long* tr = c.trace + ((long long)c.warp * c.trace_steps + (rec ? n : 0)) * 2;
+    long long* tr = c.trace + ((long long)c.warp * c.trace_steps + (rec ? n : 0)) * TRS;
     if (rec) tr[0] = clock64();
     cta_sync();  // one barrier instruction for the whole warp: no divergence around it
     if (rec) tr[1] = clock64();
     ++n;
   } else {
     cta_sync();
+  }
+}
+
+// Intermediate stamp `slot` (2..TRS-1) of the current step, taken once `dep` is available.
+__device__ __forceinline__ void tstamp(const Ctx& c, int n, int slot, float dep) {
+  if (c.trace && c.b == 0 && c.lane == 0 && n < c.trace_steps) {
+    long long t;
+    asm volatile("{ .reg .f32 d; mov.f32 d, %1; mov.u64 %0, %%clock64; }" : "=l"(t) : "f"(dep));
+    c.trace[((long long)c.warp * c.trace_steps + n) * TRS + slot] = t;
   }
 }
 
@@ -340,6 +351,17 @@ __device__ __forceinline__ float2 exp_pair(float x0, float x1, float nmL) {
   return make_float2(ex2(y.x), ex2(y.y));
 }
 
+// Same with a shared-space address of the lane's first partial (row j8 of the group's column).
+__device__ __forceinline__ float group_sum_a(unsigned a, int nrows, int j8) {
+  float s = (j8 < nrows) ? lds(a) : 0.f;
+  if (j8 + 8 < nrows) s += lds(a + 8 * PARTW * 4);
+  if (j8 + 16 < nrows) s += lds(a + 16 * PARTW * 4);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  return s;
+}
+
 // ---- main warps: the serial recursion -----------------------------------------
 template <int SCT>
 __device__ __forceinline__ void main_role(const Ctx& c) {
@@ -371,10 +393,21 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
       m2[k].x = (loops && kv && nv0 && n0 != 0 && n0 != cc) ? 1.f : 0.f;
       m2[k].y = (loops && kv && nv1 && n1 != cc) ? 1.f : 0.f;
       pin(m2[k]);
+      pin(a0[k]);
+      pin(a1[k]);
     }
-    const float col0 = (lane == 0) ? 0.f : 1.f;  // column 0 is not a context sum
-    const int pspo = ((j8 == 0) && grp < nk) ? M0 + grp : -1;
-    const float gmask = (grp < nk) ? 1.f : 0.f;
+    float col0 = (lane == 0) ? 0.f : 1.f;  // column 0 is not a context sum
+    int pspo = ((j8 == 0) && grp < nk) ? M0 + grp : -1;
+    float gmask = (grp < nk) ? 1.f : 0.f;
+    unsigned gaddr = part_a + (gcol + j8 * PARTW) * 4;           // this lane's first partial of its group column
+    unsigned paddr = part_a + (warp * PARTW + n0) * 4;           // this warp's partial row, slot 0
+    unsigned xaddr = part_a + (nmain * PARTW + M0) * 4;          // extra row entries of this warp
+    pin(col0);
+    pin(pspo);
+    pin(gmask);
+    pin(gaddr);
+    pin(paddr);
+    pin(xaddr);
     if (warp == 0 && lane == 0) {
       a2[0].x = pow2i(TARGET);
       c.part[nmain * PARTW + 0] = a2[0].x;  // extra row of buffer 0 carries a[c][0]
@@ -392,13 +425,16 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         float m = fmaxf(fmaxf(mp.x, mp.y), fmaxf(mp.z, mp.w));
         if (!(m > neg_inf())) m = 0.f;
         const float nmL = -m * kLog2e;
+        tstamp(c, nstep, 2, nmL);
         float xr0[RPW], xr1[RPW];
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
           xr0[k] = lds(base + a0[k]);
           xr1[k] = lds(base + a1[k]);
         }
-        const float s = group_sum(c.part + (t & 1) * partrows * PARTW + gcol, partrows, j8) * gmask;
+        tstamp(c, nstep, 3, xr0[0] + xr1[RPW - 1]);
+        const float s = group_sum_a(gaddr + (t & 1) * partb, partrows, j8) * gmask;
+        tstamp(c, nstep, 4, s);
         float P[RPW];
 #pragma unroll
         for (int k = 0; k < RPW; ++k) P[k] = __shfl_sync(0xffffffffu, s, 8 * k);
@@ -417,11 +453,12 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         float2 cs = a2[0];
 #pragma unroll
         for (int k = 1; k < RPW; ++k) cs = fadd2(cs, a2[k]);
-        const unsigned pn = part_a + ((t + 1) & 1) * partb;
-        sts(pn + (warp * PARTW + n0) * 4, cs.x * col0);
-        sts(pn + (warp * PARTW + n1) * 4, cs.y);
+        tstamp(c, nstep, 5, cs.x + cs.y);
+        const unsigned pno = ((t + 1) & 1) * partb;
+        sts(paddr + pno, cs.x * col0);
+        sts(paddr + pno + 128, cs.y);
         if (lane == 0) {
-          const unsigned ex = pn + (nmain * PARTW + M0) * 4;
+          const unsigned ex = xaddr + pno;
           sts(ex, a2[0].x);
           if (nk > 1) sts(ex + 4, a2[1].x);
           if (nk > 2) sts(ex + 8, a2[2].x);
@@ -461,9 +498,19 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
     m2[k].x = (loops && v0 && l != 0 && l != n0) ? 1.f : 0.f;
     m2[k].y = (loops && v1 && l != 0 && l != n1) ? 1.f : 0.f;
     pin(m2[k]);
+    pin(eo0[k]);
+    pin(eo1[k]);
+    pin(vo0[k]);
+    pin(vo1[k]);
   }
-  const float2 pm = make_float2(nv0 ? 1.f : 0.f, nv1 ? 1.f : 0.f);
-  const float gmask = (grp < nk) ? 1.f : 0.f;
+  float2 pm = make_float2(nv0 ? 1.f : 0.f, nv1 ? 1.f : 0.f);
+  float gmask = (grp < nk) ? 1.f : 0.f;
+  unsigned gaddr = part_a + (gcol + j8 * PARTW) * 4;
+  unsigned paddr = part_a + (warp * PARTW + n0) * 4;
+  pin(pm);
+  pin(gmask);
+  pin(gaddr);
+  pin(paddr);
   ConsCursor cur;
   cur.init(max(len, 1), K);
   const int GEND = len + c.LEAD + 2;
@@ -494,7 +541,7 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
           }
           b2[0] = fmul2(make_float2(q0 * hs, q1 * hs), pm);
         } else {
-          const float s = group_sum(pb + gcol, nmain, j8) * (hs * gmask);
+          const float s = group_sum_a(gaddr + (i & 1) * partb, nmain, j8) * (hs * gmask);
           const float2 h2 = splat2(hs);
 #pragma unroll
           for (int k = 0; k < RPW; ++k) {
@@ -538,9 +585,9 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
           }
         }
       }
-      const unsigned pn = part_a + ((i + 1) & 1) * partb + warp * PARTW * 4;
-      sts(pn + n0 * 4, cs.x);
-      sts(pn + n1 * 4, cs.y);
+      const unsigned pno = ((i + 1) & 1) * partb;
+      sts(paddr + pno, cs.x);
+      sts(paddr + pno + 128, cs.y);
     }
     step_sync(c, nstep);
   }
@@ -617,10 +664,18 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
   float2 ra[RU], rnx[RU];
 #pragma unroll
   for (int u = 0; u < RU; ++u) ra[u] = rnx[u] = make_float2(0.f, 0.f);
-  const unsigned o0 = (aw * S + (nv0 ? n0 : 0)) * 4;  // element offsets of row aw; row aw + 8u adds 8u*S
-  const unsigned o1 = (aw * S + (nv1 ? n1 : (nv0 ? n0 : 0))) * 4;
-  const float lp0 = c.loops && nv0 && n0 != 0 ? 1.f : 0.f;
-  const float lp1 = c.loops && nv1 ? 1.f : 0.f;
+  unsigned o0 = (aw * S + (nv0 ? n0 : 0)) * 4;  // element offsets of row aw; row aw + 8u adds 8u*S
+  unsigned o1 = (aw * S + (nv1 ? n1 : (nv0 ? n0 : 0))) * 4;
+  pin(o0);
+  pin(o1);
+  // explicit self-loop of state (c, l): l != 0 and l != c (the diagonal loops through P)
+  float2 lm[RU];
+#pragma unroll
+  for (int u = 0; u < RU; ++u) {
+    const int cc = aw + NAUX * u;
+    lm[u] = make_float2((c.loops && nv0 && n0 != 0 && n0 != cc) ? 1.f : 0.f, (c.loops && nv1 && n1 != cc) ? 1.f : 0.f);
+    pin(lm[u]);
+  }
   auto load_ckpt = [&](int tau) {
     const float* cp = c.ckp + (long long)(tau / K) * V;
 #pragma unroll
@@ -648,7 +703,7 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
       const unsigned ar = rows_a + c.tab_a[q & (QRING - 1)] * rowb + r4;
       mbar_wait(&c.mbar[te & 0xff], te >> 8);
       const float* pr = c.prow + (q & (QRING - 1)) * prowf;
-      const float scl = pow2i((int)pr[S + 1]);
+      const int kq = (int)pr[S + 1];
       const float nmL = -pr[S] * kLog2e;
       if (seg0) {
         if (tau == 0) {
@@ -660,7 +715,6 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
           for (int u = 0; u < RU; ++u) ra[u] = rnx[u];
         }
       }
-      const float2 sl = make_float2(lp0 * scl, lp1 * scl);
       float Pc[RU];
       float2 x2[RU];
 #pragma unroll
@@ -675,12 +729,14 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
       for (int u = 0; u < RU; ++u) {
         const int cc = aw + NAUX * u;
         if (cc < S) {
-          const float2 e2 = exp_pair(x2[u].x, x2[u].y, nmL);
-          // the diagonal (c, c) is its own predecessor through P: no explicit loop there
-          const float2 s2 = make_float2(n0 == cc ? 0.f : sl.x, n1 == cc ? 0.f : sl.y);
-          ra[u] = fmul2(e2, ffma2(s2, ra[u], splat2(Pc[u] * scl)));
-          x2[u] = e2;
+          x2[u] = exp_pair(x2[u].x, x2[u].y, nmL);
+          ra[u] = fmul2(x2[u], ffma2(lm[u], ra[u], splat2(Pc[u])));
         }
+      }
+      if (kq != 0) {  // rare: the forward sweep rescaled at this frame
+        const float2 s2 = splat2(pow2i(kq));
+#pragma unroll
+        for (int u = 0; u < RU; ++u) ra[u] = fmul2(ra[u], s2);
       }
 #pragma unroll
       for (int u = 0; u < RU; ++u) {
@@ -992,7 +1048,7 @@ cudaError_t launch_bichar_den(const BicharArgs& a_in, const BicharPlan& p, cudaS
   a.trace_steps = 0;
   if (trace_path && trace_path[0]) {
     a.trace_steps = 2 * a.T + 64;
-    const size_t bytes = (size_t)warps * a.trace_steps * 2 * sizeof(long long);
+    const size_t bytes = (size_t)warps * a.trace_steps * TRS * sizeof(long long);
     if (cudaMalloc(&a.trace, bytes) != cudaSuccess) return cudaGetLastError();
     cudaMemsetAsync(a.trace, 0, bytes, st);
   }
@@ -1013,13 +1069,13 @@ cudaError_t launch_bichar_den(const BicharArgs& a_in, const BicharPlan& p, cudaS
   ++g_launches;
   e = cudaGetLastError();
   if (a.trace) {
-    const size_t n = (size_t)warps * a.trace_steps * 2;
+    const size_t n = (size_t)warps * a.trace_steps * TRS;
     std::vector<long long> host(n);
     cudaStreamSynchronize(st);
     cudaMemcpy(host.data(), a.trace, n * sizeof(long long), cudaMemcpyDeviceToHost);
     cudaFree(a.trace);
     if (FILE* f = fopen(trace_path, "wb")) {
-      const int hdr[4] = {warps, a.trace_steps, p.nmain, a.T};
+      const int hdr[4] = {warps, a.trace_steps, p.nmain, TRS};
       fwrite(hdr, sizeof(int), 4, f);
       fwrite(host.data(), sizeof(long long), n, f);
       fclose(f);

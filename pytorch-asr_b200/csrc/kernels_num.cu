@@ -1,0 +1,451 @@
+// Numerator (per-utterance training graph) forward-backward: one CTA per utterance
+// (8 recursion warps + 2 helper warps), log2 domain, sm_100a.
+//
+// Reference semantics: PathLogSumExp.forward/backward (att_speech/fst_utils.py:400-488)
+// on the graphs of BaseGraphGen.get_training_matrices (fst_utils.py:647-660): N = 2U+1
+// states with at most 3 arcs into / out of a state.
+//
+// Why the log domain here and plain scaled numbers in the denominator kernel: a
+// training graph is a chain, so alpha_t of the states that carry the posterior mass can
+// sit hundreds of binary orders below max_s alpha_t[s] (measured: below 2^-126 at T=400
+// on random logits) -- a per-frame rescale cannot keep alpha * beta representable.
+// In the decoding graph every state reaches every other within two frames, which
+// bounds that ratio by the frame's logit spread.
+//
+// Shape of a frame step: the recursion warps do one barrier, a handful of shared-memory
+// loads and one 4-way log-sum-exp per state -- no shuffles, no atomics.  Everything
+// that needs a reduction runs one step behind on the helper warps: warp NC/32 issues the
+// cp.async ring and reduces the frame maximum that normalises the step after next (an
+// INTEGER, so that subtracting it is exact); warp NC/32+1 sums the posterior row of the
+// previous step (arcs grouped by label on the host: fixed order, no atomics; a label
+// with many arcs -- the blank -- leaves one partial per thread), normalises it to sum
+// one and writes it out.
+//
+// Input: the compact label columns xg[b][t][j] = logits[t][b][lab_list_b[j]] (natural log;
+// multiplied by log2(e) inside an fma so that the input is rounded once) written by
+// gather_kernel; output: cost[b] (natural log) and the compact posterior rows
+// gout[b][t][j], which the row / scatter kernels fold into the dense gradient.
+#include "device_utils.cuh"
+#include "kernels.cuh"
+
+namespace ctcg {
+namespace {
+
+constexpr int NC = 256;        // recursion threads
+constexpr int NTH = NC + 64;   // + the io warp and the row warp
+constexpr int NWARPS = NTH / 32;
+constexpr int W_IO = NC / 32;
+constexpr int W_ROW = NC / 32 + 1;
+constexpr int XR = 8;        // cp.async ring depth (frames)
+constexpr int DEG = 4;       // arcs packed per state
+constexpr int HEAVY = 12;    // labels with more arcs leave one partial per recursion thread
+constexpr int NHMAX = 4;     // at most this many labels take that route; the rest loop
+constexpr unsigned NOARC = 0xffffffffu;
+
+struct NumPlan {
+  int in_pk, out_pk, in_w, out_w, lab_ptr, lab_pk, lab_w, a0, a1, fin, gr, hl, hx, hp, red, xring, aring;
+  int bytes;
+};
+
+__host__ __device__ inline NumPlan num_plan(int maxN, int maxA, int maxL, int nlp, int arow, bool unit) {
+  NumPlan p;
+  int o = 0;
+  auto take = [&](int bytes) {
+    const int at = o;
+    o += (bytes + 15) & ~15;
+    return at;
+  };
+  p.in_pk = take(maxN * DEG * 4);
+  p.out_pk = take(maxN * DEG * 4);
+  p.in_w = unit ? 0 : take(maxN * DEG * 4);
+  p.out_w = unit ? 0 : take(maxN * DEG * 4);
+  p.lab_ptr = take((maxL + 1) * 4);
+  p.lab_pk = take(maxA * 4);
+  p.lab_w = unit ? 0 : take(maxA * 4);
+  p.a0 = take(maxN * 4);
+  p.a1 = take(maxN * 4);
+  p.fin = take(maxN * 4);
+  p.gr = take(2 * maxL * 4);
+  p.hl = take(NHMAX * 4);
+  p.hx = take(maxL * 4);
+  p.hp = take(2 * NHMAX * NC * 4);
+  p.red = take((4 + 2 * NWARPS) * 4);
+  p.xring = take(XR * nlp * 4);
+  p.aring = take(XR * arow * 4);
+  p.bytes = o;
+  return p;
+}
+
+// log2(sum_k 2^v[k]) over DEG terms (-inf = absent)
+__device__ __forceinline__ float lse4(const float (&v)[DEG]) {
+  const float M = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
+  if (!(M > neg_inf())) return neg_inf();
+  const float s = ex2(v[0] - M) + ex2(v[1] - M) + ex2(v[2] - M) + ex2(v[3] - M);
+  return M + lg2(s);
+}
+
+// 2^(a + b + k) with the rounding error of a + b carried along (two-sum): a and b sit
+// tens of binary orders below zero where one fp32 ulp is ~1e-5, k brings the sum back
+// to <= 0.
+__device__ __forceinline__ float post_term(float a, float b, float k) {
+  const float s = a + b;
+  const float bb = s - a;
+  float err = (a - (s - bb)) + (b - bb);
+  err = (s > neg_inf()) ? err : 0.f;
+  return ex2((s + k) + err);
+}
+
+__device__ __forceinline__ void bar_all() { asm volatile("bar.sync 0;" ::: "memory"); }
+
+template <bool UNIT>
+__global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const int maxN, const int maxA, const int maxL) {
+  extern __shared__ __align__(16) unsigned char sm[];
+  const GraphDev& g = a.g;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int gi = (g.num_graphs == 1) ? 0 : b;
+  const int so = g.state_off[gi];
+  const int n = g.state_off[gi + 1] - so;
+  const int ro = so + gi;
+  const int lo = g.lab_off[gi];
+  const int nl = g.lab_off[gi + 1] - lo;
+  const int len = min(a.lens[b], a.T);
+  const int nlp = (int)a.x_stride_t, arow = a.alpha_row;
+  const NumPlan P = num_plan(maxN, maxA, maxL, nlp, arow, UNIT);
+  uint4* in_pk = reinterpret_cast<uint4*>(sm + P.in_pk);
+  uint4* out_pk = reinterpret_cast<uint4*>(sm + P.out_pk);
+  float4* in_w = reinterpret_cast<float4*>(sm + P.in_w);
+  float4* out_w = reinterpret_cast<float4*>(sm + P.out_w);
+  int* lab_ptr = reinterpret_cast<int*>(sm + P.lab_ptr);
+  unsigned* lab_pk = reinterpret_cast<unsigned*>(sm + P.lab_pk);
+  float* lab_w = reinterpret_cast<float*>(sm + P.lab_w);
+  float* abuf0 = reinterpret_cast<float*>(sm + P.a0);
+  float* abuf1 = reinterpret_cast<float*>(sm + P.a1);
+  float* fin = reinterpret_cast<float*>(sm + P.fin);
+  float* gr = reinterpret_cast<float*>(sm + P.gr);
+  int* hl = reinterpret_cast<int*>(sm + P.hl);
+  int* hx = reinterpret_cast<int*>(sm + P.hx);
+  float* hp = reinterpret_cast<float*>(sm + P.hp);
+  float* wred = reinterpret_cast<float*>(sm + P.red);  // [2] frame normalisers (integers)
+  int* nheavy = reinterpret_cast<int*>(wred + 2);
+  float* scr = wred + 4;                               // [2 * NWARPS] scratch
+  float* xring = reinterpret_cast<float*>(sm + P.xring);
+  float* aring = reinterpret_cast<float*>(sm + P.aring);
+
+  // ---- graph -> shared memory: DEG arcs per state in one 16-byte word ----
+  const int arc0 = g.in_ptr[ro];
+  const int narcs = g.in_ptr[ro + n] - arc0;
+  for (int s = tid; s < n; s += NTH) {
+    unsigned pi[DEG], po[DEG];
+    float wi[DEG], wo[DEG];
+#pragma unroll
+    for (int k = 0; k < DEG; ++k) {
+      const int ei = g.in_ptr[ro + s] + k, eo = g.out_ptr[ro + s] + k;
+      const bool vi = ei < g.in_ptr[ro + s + 1], vo = eo < g.out_ptr[ro + s + 1];
+      pi[k] = vi ? ((unsigned)g.in_src[ei] | ((unsigned)g.in_clab[ei] << 16)) : NOARC;
+      po[k] = vo ? ((unsigned)g.out_dst[eo] | ((unsigned)g.out_clab[eo] << 16)) : NOARC;
+      wi[k] = (vi && !UNIT) ? g.in_w[ei] * kLog2e : 0.f;
+      wo[k] = (vo && !UNIT) ? g.out_w[eo] * kLog2e : 0.f;
+    }
+    in_pk[s] = make_uint4(pi[0], pi[1], pi[2], pi[3]);
+    out_pk[s] = make_uint4(po[0], po[1], po[2], po[3]);
+    if (!UNIT) {
+      in_w[s] = make_float4(wi[0], wi[1], wi[2], wi[3]);
+      out_w[s] = make_float4(wo[0], wo[1], wo[2], wo[3]);
+    }
+    const float f = g.final_w[so + s];
+    fin[s] = (f > kDeadWeight) ? f * kLog2e : neg_inf();
+    abuf0[s] = (s == 0) ? 0.f : neg_inf();
+  }
+  for (int j = tid; j <= nl; j += NTH) lab_ptr[j] = g.lab_ptr[lo + gi + j] - arc0;
+  for (int e = tid; e < narcs; e += NTH) {
+    lab_pk[e] = (unsigned)g.lab_src[arc0 + e] | ((unsigned)g.lab_dst[arc0 + e] << 16);
+    if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
+  }
+  if (tid < 2) wred[tid] = 0.f;
+  const float* xb = a.x + (long long)b * a.x_stride_b;
+  float* aw = a.alpha_ws + (long long)b * a.T * arow;
+  const int xchunks = nlp / 4, achunks = arow / 4;
+  bar_all();
+  if (warp == W_ROW) {  // labels with many arcs (the blank), ascending
+    int cnt = 0;
+    for (int base = 0; base < nl; base += 32) {
+      const int j = base + lane;
+      const bool hv = j < nl && (lab_ptr[j + 1] - lab_ptr[j]) > HEAVY;
+      const unsigned m = __ballot_sync(0xffffffffu, hv);
+      const int idx = cnt + __popc(m & ((1u << lane) - 1u));
+      if (j < nl) hx[j] = (hv && idx < NHMAX) ? idx : -1;
+      if (hv && idx < NHMAX) hl[idx] = j;
+      cnt += __popc(m);
+    }
+    if (lane == 0) *nheavy = min(cnt, NHMAX);
+  }
+
+  // =============================== forward ===============================
+  float* a_cur = abuf0;
+  float* a_nxt = abuf1;
+  double c = 0.0;  // alpha_t = alpha_hat_t + c (log2 units); identical in every thread
+  if (warp == W_IO) {
+    auto issue_x = [&](int t, int slot) {
+      if (t >= 0 && t < len) {
+        const float* src = xb + (long long)t * nlp;
+        float* dst = xring + slot * nlp;
+        for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
+      }
+      cp_async_commit();
+    };
+    for (int i = 0; i < XR - 1; ++i) issue_x(i, i);
+    cp_async_wait<XR - 2>();
+    float cur = 0.f;
+    for (int t = 0; t < len; ++t) {
+      bar_all();
+      issue_x(t + XR - 1, (t + XR - 1) % XR);
+      // normaliser of step t + 1: floor(max alpha_hat_t), one step behind the recursion
+      float m = neg_inf();
+      for (int s = lane; s < n; s += 32) m = fmaxf(m, a_cur[s]);
+      m = floorf(warp_max(m));
+      // the normaliser in flight (cur) has not reached a_cur yet: subtract it (dead-beat, keeps
+      // max alpha_hat within two frames' increments of zero)
+      cur = (m > neg_inf()) ? m - cur : 0.f;
+      if (lane == 0) wred[(t + 1) & 1] = cur;
+      cp_async_wait<XR - 2>();
+      float* tmp = a_cur;
+      a_cur = a_nxt;
+      a_nxt = tmp;
+    }
+    cp_async_wait<0>();
+  } else if (warp == W_ROW) {
+    for (int t = 0; t < len; ++t) bar_all();
+    if (len & 1) {
+      float* tmp = a_cur;
+      a_cur = a_nxt;
+      a_nxt = tmp;
+    }
+  } else {
+    for (int t = 0; t < len; ++t) {
+      bar_all();
+      const float mx = wred[t & 1];
+      c += (double)mx;
+      const float* xrow = xring + (t % XR) * nlp;
+      float* ar = aw + (long long)t * arow;
+      if (tid == 0) {
+        const float hi = (float)c;
+        ar[arow - 2] = hi;
+        ar[arow - 1] = (float)(c - (double)hi);
+      }
+      for (int s = tid; s < n; s += NC) {
+        ar[s] = a_cur[s] - mx;
+        const uint4 pk = in_pk[s];
+        const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
+        float v[DEG];
+#pragma unroll
+        for (int k = 0; k < DEG; ++k) {
+          const unsigned q = (pkk[k] == NOARC) ? 0u : pkk[k];
+          const float val = fmaf(xrow[q >> 16], kLog2e, a_cur[q & 0xffffu] - mx);
+          v[k] = (pkk[k] == NOARC) ? neg_inf() : val;
+        }
+        if (!UNIT) {
+          const float4 w = in_w[s];
+          v[0] += w.x;
+          v[1] += w.y;
+          v[2] += w.z;
+          v[3] += w.w;
+        }
+        a_nxt[s] = lse4(v);
+      }
+      float* tmp = a_cur;
+      a_cur = a_nxt;
+      a_nxt = tmp;
+    }
+  }
+  bar_all();
+  // terminal: cost = c_len + LSE_n(alpha_hat_len[n] + final[n])
+  float tm = neg_inf();
+  for (int s = tid; s < n; s += NTH) tm = fmaxf(tm, a_cur[s] + fin[s]);
+  tm = warp_max(tm);
+  if (lane == 0) scr[warp] = tm;
+  bar_all();
+  float TM = scr[0];
+#pragma unroll
+  for (int w = 1; w < NWARPS; ++w) TM = fmaxf(TM, scr[w]);
+  float ts = 0.f;
+  if (TM > neg_inf())
+    for (int s = tid; s < n; s += NTH) ts += ex2(a_cur[s] + fin[s] - TM);
+  ts = warp_sum(ts);
+  if (lane == 0) scr[NWARPS + warp] = ts;
+  bar_all();
+  float TS = 0.f;
+#pragma unroll
+  for (int w = 0; w < NWARPS; ++w) TS += scr[NWARPS + w];
+  const bool feasible = TM > neg_inf() && TS > 0.f;
+  const double cost2 = feasible ? (c + (double)TM + (double)lg2(TS)) : 0.0;  // meaningful in the recursion warps
+  if (tid == 0) a.cost[b] = feasible ? cost2 * kLn2 : -1e20;
+  if (!a.write_grad) return;
+  float* gb = a.gout + (long long)b * a.g_stride_b;
+  if (!feasible) {
+    for (int t = 0; t < len; ++t)
+      for (int j = tid; j < nl; j += NTH) gb[(long long)t * a.g_stride_t + j] = 0.f;
+    return;
+  }
+
+  // =============================== backward ==============================
+  const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
+  float* b_cur = a_nxt;  // the buffer not holding alpha_len
+  float* b_nxt = a_cur;
+  for (int s = tid; s < n; s += NTH) b_cur[s] = fin[s];
+  if (tid < 2) wred[tid] = 0.f;
+  const int nh = *nheavy;
+  bar_all();
+  if (warp == W_IO) {
+    auto issue_b = [&](int i, int slot) {
+      if (i >= 0 && i < len) {
+        const int t = len - 1 - i;
+        const float* src = xb + (long long)t * nlp;
+        float* dst = xring + slot * nlp;
+        for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
+        const float* asrc = aw + (long long)t * arow;
+        float* adst = aring + slot * arow;
+        for (int cc = lane; cc < achunks; cc += 32) cp_async16(adst + 4 * cc, asrc + 4 * cc);
+      }
+      cp_async_commit();
+    };
+    for (int i = 0; i < XR - 1; ++i) issue_b(i, i);
+    cp_async_wait<XR - 2>();
+    float cur = 0.f;
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      issue_b(i + XR - 1, (i + XR - 1) % XR);
+      float m = neg_inf();
+      for (int s = lane; s < n; s += 32) m = fmaxf(m, b_cur[s]);
+      m = floorf(warp_max(m));
+      cur = (m > neg_inf()) ? m - cur : 0.f;
+      if (lane == 0) wred[(i + 1) & 1] = cur;
+      cp_async_wait<XR - 2>();
+      float* tmp = b_cur;
+      b_cur = b_nxt;
+      b_nxt = tmp;
+    }
+    cp_async_wait<0>();
+    bar_all();
+  } else if (warp == W_ROW) {
+    // finishes the posterior row of iteration i - 1 while the recursion warps run iteration i
+    auto finish = [&](int i) {
+      float* grp = gr + (i & 1) * maxL;
+      const float* hpp = hp + (i & 1) * NHMAX * NC;
+      float tot = 0.f;
+      for (int h = 0; h < nh; ++h) {
+        float v = 0.f;
+#pragma unroll
+        for (int k = 0; k < NC / 32; ++k) v += hpp[h * NC + k * 32 + lane];
+        v = warp_sum(v);
+        if (lane == 0) grp[hl[h]] = v;
+        tot += v;  // identical in every lane
+      }
+      __syncwarp();
+      float ls = 0.f;
+      for (int j = lane; j < nl; j += 32) ls += (hx[j] < 0) ? grp[j] : 0.f;
+      tot += warp_sum(ls);
+      const float sc = tot > 0.f ? gmul / tot : 0.f;
+      float* dst = gb + (long long)(len - 1 - i) * a.g_stride_t;
+      for (int j = lane; j < nl; j += 32) dst[j] = grp[j] * sc;
+    };
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      if (i > 0) finish(i - 1);
+    }
+    bar_all();
+    if (len > 0) finish(len - 1);
+  } else {
+    double d = 0.0;  // beta_{t+1} = beta_hat + d
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      const float mxb = wred[i & 1];
+      const float* xrow = xring + (i % XR) * nlp;
+      const float* at = aring + (i % XR) * arow;
+      const double ct = (double)at[arow - 2] + (double)at[arow - 1];
+      const float Kt = (float)(ct + d - cost2);
+      d += (double)mxb;
+      float* grw = gr + (i & 1) * maxL;
+      float* hpw = hp + (i & 1) * NHMAX * NC;
+      // posteriors: gamma[j] = sum_{arcs labelled j} 2^(x[j] + w + alpha_t[src] + beta_{t+1}[dst] - cost);
+      // every term is a probability (<= 1), so no running maximum is needed
+      for (int j = tid; j < nl; j += NC) {
+        float acc = 0.f;
+        if (hx[j] < 0) {
+          const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
+          const float kx = fmaf(xrow[j], kLog2e, Kt);
+          for (int e = e0; e < e1; ++e) {
+            const unsigned pk = lab_pk[e];
+            acc += post_term(at[pk & 0xffffu], b_cur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+          }
+        }
+        grw[j] = acc;
+      }
+      for (int h = 0; h < nh; ++h) {
+        const int j = hl[h];
+        const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
+        const float kx = fmaf(xrow[j], kLog2e, Kt);
+        float acc = 0.f;
+        for (int e = e0 + tid; e < e1; e += NC) {
+          const unsigned pk = lab_pk[e];
+          acc += post_term(at[pk & 0xffffu], b_cur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+        }
+        hpw[h * NC + tid] = acc;
+      }
+      // beta_t[s] = LSE_{arcs out of s}(w + x[label] + beta_{t+1}[dst])
+      for (int s = tid; s < n; s += NC) {
+        const uint4 pk = out_pk[s];
+        const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
+        float v[DEG];
+#pragma unroll
+        for (int k = 0; k < DEG; ++k) {
+          const unsigned q = (pkk[k] == NOARC) ? 0u : pkk[k];
+          const float val = fmaf(xrow[q >> 16], kLog2e, b_cur[q & 0xffffu] - mxb);
+          v[k] = (pkk[k] == NOARC) ? neg_inf() : val;
+        }
+        if (!UNIT) {
+          const float4 w = out_w[s];
+          v[0] += w.x;
+          v[1] += w.y;
+          v[2] += w.z;
+          v[3] += w.w;
+        }
+        b_nxt[s] = lse4(v);
+      }
+      float* tmp = b_cur;
+      b_cur = b_nxt;
+      b_nxt = tmp;
+    }
+    bar_all();
+  }
+}
+
+}  // namespace
+
+bool num_lin_supported(const PathArgs& a) {
+  if (a.g.max_states > 65535 || a.g.max_labels > 65535 || a.g.max_arcs < 1) return false;
+  if (a.g.max_in_degree > DEG || a.g.max_out_degree > DEG) return false;
+  const NumPlan P = num_plan(a.g.max_states, a.g.max_arcs, a.g.max_labels, (int)a.x_stride_t, a.alpha_row,
+                             a.g.unit_weights != 0);
+  return P.bytes <= 200 * 1024;
+}
+
+cudaError_t launch_num_lin(const PathArgs& a, cudaStream_t st) {
+  const bool unit = a.g.unit_weights != 0;
+  const NumPlan P = num_plan(a.g.max_states, a.g.max_arcs, a.g.max_labels, (int)a.x_stride_t, a.alpha_row, unit);
+  ProfScope prof("num_log", st);
+  cudaError_t e;
+  if (unit) {
+    e = cudaFuncSetAttribute(num_log_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P.bytes);
+    if (e != cudaSuccess) return e;
+    num_log_kernel<true><<<a.B, NTH, P.bytes, st>>>(a, a.g.max_states, a.g.max_arcs, a.g.max_labels);
+  } else {
+    e = cudaFuncSetAttribute(num_log_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P.bytes);
+    if (e != cudaSuccess) return e;
+    num_log_kernel<false><<<a.B, NTH, P.bytes, st>>>(a, a.g.max_states, a.g.max_arcs, a.g.max_labels);
+  }
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+}  // namespace ctcg

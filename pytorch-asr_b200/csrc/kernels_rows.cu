@@ -18,7 +18,7 @@ constexpr int NT = 256;
 constexpr int NWARP = NT / 32;
 
 // ---------------------------------------------------------------------------
-// xg[b][t][j] = normalise(logits[t][b][:])[lab_list_b[j]] * log2(e); one warp per (t, b) row.
+// xg[b][t][j] = normalise(logits[t][b][:])[lab_list_b[j]] (natural log); one warp per (t, b) row.
 // normalize: 0/1 -> raw logits (a softmax normaliser is per-frame and is added
 // to the loss by the row pass instead); 2 -> minus the LSE of the label's context block.
 __global__ void __launch_bounds__(NT) gather_kernel(const float* __restrict__ logits, int T, int B, int V,
@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(NT) gather_kernel(const float* __restrict__ lo
       for (int k = 0; k < S; ++k) s += __expf(blk[k] - m);
       v -= m + __logf(s);
     }
-    dst[j] = v * kLog2e;
+    dst[j] = v;
   }
 }
 
