@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -228,6 +229,40 @@ int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, i
   return CTCG_OK;
 }
 
+// The numerator (B small CTAs) and the denominator (B large CTAs) are independent until
+// the final subtraction and neither fills 148 SMs at training batch sizes, so the
+// denominator runs on a side stream, forked from and joined back into the caller's stream
+// with events (legal inside a stream capture).  One side stream per host thread and
+// device; CTCG_SERIAL=1 keeps everything on the caller's stream.
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  bool ok = false;
+};
+
+SideStream* side_stream() {
+  static const bool serial = [] {
+    const char* e = std::getenv("CTCG_SERIAL");
+    return e && e[0] == '1';
+  }();
+  if (serial) return nullptr;
+  constexpr int kMaxDev = 64;
+  thread_local SideStream table[kMaxDev];
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return nullptr;
+  SideStream& s = table[dev];
+  if (!s.ok) {
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    s.ok = true;
+  }
+  return &s;
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 int upload_lens(const Plan& p, void* ws, const int32_t* lens_host, int B, cudaStream_t st, int32_t** out) {
@@ -270,40 +305,70 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   double* cost_den = den ? reinterpret_cast<double*>(ws + p.cost_den) : nullptr;
   float* rowlse = reinterpret_cast<float*>(ws + p.rowlse);
 
-  // 1. compact the label columns each utterance touches
-  CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp,
-                          normalize == CTCG_NORM_CONTEXT ? 2 : 0, num_symbols, st));
-  // 2. numerator forward-backward on the compact columns
-  PathArgs a{};
-  a.g = num->dev;
-  a.x = xg;
-  a.x_stride_t = p.nlp;
-  a.x_stride_b = (long long)T * p.nlp;
-  a.x_scale = kLog2e;
-  a.lens = lens;
-  a.T = T;
-  a.B = B;
-  a.alpha_ws = reinterpret_cast<float*>(ws + p.alpha_num);
-  a.alpha_row = p.arow_num;
-  a.cost = cost_num;
-  a.gout = gg;
-  a.g_stride_t = p.nlp;
-  a.g_stride_b = (long long)T * p.nlp;
-  a.g_width = num->max_labels;
-  a.g_sign = 1.f;
-  a.g_scale = nullptr;
-  a.write_grad = grad != nullptr;
-  if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
-  else CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
-
   // A per-frame softmax normaliser cancels between numerator and denominator.
   const bool softmax = (normalize == CTCG_NORM_SOFTMAX) && !den;
-  if (den && p.bi.ok && aligned16(logits) && aligned16(grad)) {
-    // 3a'. factorised bi-char denominator (kernels_bichar.cu), writes +gamma_den rows
-    if ((st_ = run_bichar(p, ws, logits, T, B, V, lens, den, cost_den, grad, grad_scale, st)) != CTCG_OK) return st_;
+  const bool fused_den = den && p.bi.ok && aligned16(logits) && aligned16(grad);
+  if (den && p.bi.ok && !fused_den) return CTCG_EUNSUPPORTED;  // misaligned tensors: the workspace was planned for the fused kernel
+  SideStream* side = fused_den ? side_stream() : nullptr;
+  if (fused_den) {
+    // 1'. factorised bi-char denominator (kernels_bichar.cu), writes +gamma_den rows; concurrent with 1-2
+    cudaStream_t ds = st;
+    if (side) {
+      CTCG_CUDA(cudaEventRecord(side->fork, st));
+      CTCG_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
+      ds = side->stream;
+    }
+    st_ = run_bichar(p, ws, logits, T, B, V, lens, den, cost_den, grad, grad_scale, ds);
+    if (side) CTCG_CUDA(cudaEventRecord(side->join, side->stream));
+  }
+  // joins the side stream back (also on failure, so that a capture is never left forked)
+  auto join = [&]() -> int {
+    if (!side) return CTCG_OK;
+    CTCG_CUDA(cudaStreamWaitEvent(st, side->join, 0));
+    return CTCG_OK;
+  };
+  if (st_ != CTCG_OK) {
+    (void)join();
+    return st_;
+  }
+  st_ = [&]() -> int {
+    // 1. compact the label columns each utterance touches
+    CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp,
+                            normalize == CTCG_NORM_CONTEXT ? 2 : 0, num_symbols, st));
+    // 2. numerator forward-backward on the compact columns
+    PathArgs a{};
+    a.g = num->dev;
+    a.x = xg;
+    a.x_stride_t = p.nlp;
+    a.x_stride_b = (long long)T * p.nlp;
+    a.x_scale = kLog2e;
+    a.lens = lens;
+    a.T = T;
+    a.B = B;
+    a.alpha_ws = reinterpret_cast<float*>(ws + p.alpha_num);
+    a.alpha_row = p.arow_num;
+    a.cost = cost_num;
+    a.gout = gg;
+    a.g_stride_t = p.nlp;
+    a.g_stride_b = (long long)T * p.nlp;
+    a.g_width = num->max_labels;
+    a.g_sign = 1.f;
+    a.g_scale = nullptr;
+    a.write_grad = grad != nullptr;
+    if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
+    else CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
+    return CTCG_OK;
+  }();
+  {
+    const int js = join();
+    if (st_ != CTCG_OK) return st_;
+    if (js != CTCG_OK) return js;
+  }
+
+  if (fused_den) {
+    // 3a'. gamma_den - gamma_num
     if (grad) CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
   } else if (den) {
-    if (p.bi.ok) return CTCG_EUNSUPPORTED;  // misaligned tensors: the workspace was planned for the fused kernel
     // 3a. denominator path sum over the shared decoding graph, writes +gamma_den rows
     PathArgs d{};
     d.g = den->dev;

@@ -12,14 +12,18 @@
 // In the decoding graph every state reaches every other within two frames, which
 // bounds that ratio by the frame's logit spread.
 //
-// Shape of a frame step: the recursion warps do one barrier, a handful of shared-memory
-// loads and one 4-way log-sum-exp per state -- no shuffles, no atomics.  Everything
-// that needs a reduction runs one step behind on the helper warps: warp NC/32 issues the
-// cp.async ring and reduces the frame maximum that normalises the step after next (an
-// INTEGER, so that subtracting it is exact); warp NC/32+1 sums the posterior row of the
-// previous step (arcs grouped by label on the host: fixed order, no atomics; a label
-// with many arcs -- the blank -- leaves one partial per thread), normalises it to sum
-// one and writes it out.
+// The kernel is latency bound (one short dependent chain per frame, 2T frames), so the
+// CTA is cut into roles that each keep their chain short, one barrier per frame:
+//   state warps (8)  one state per thread: 4-way log-sum-exp over the packed arcs, then
+//                    floor(max) of the new values through REDUX + one shared atomicMax --
+//                    an INTEGER normaliser, so subtracting it next frame is exact;
+//   label warps (4)  backward only: posterior of one label per thread, arcs grouped by
+//                    label on the host (fixed order, no atomics);
+//   heavy warps (4)  backward only: labels with many arcs (the blank), one arc per thread;
+//   io warp          cp.async ring, the fp64 running offsets (c, d) and the per-frame
+//                    scalar 2^Kt the posteriors are scaled by, one frame ahead;
+//   row warp         sums the previous frame's posterior row, normalises it to sum one
+//                    and writes it out.
 //
 // Input: the compact label columns xg[b][t][j] = logits[t][b][lab_list_b[j]] (natural log;
 // multiplied by log2(e) inside an fma so that the input is rounded once) written by
@@ -31,16 +35,22 @@
 namespace ctcg {
 namespace {
 
-constexpr int NC = 256;        // recursion threads
-constexpr int NTH = NC + 64;   // + the io warp and the row warp
+constexpr int NS = 256;                 // state threads
+constexpr int NLB = 128;                // label threads
+constexpr int NHV = 128;                // heavy-label threads
+constexpr int W_LAB = NS / 32;          // first label warp
+constexpr int W_HV = (NS + NLB) / 32;   // first heavy warp
+constexpr int W_IO = (NS + NLB + NHV) / 32;
+constexpr int W_ROW = W_IO + 1;
+constexpr int NTH = (W_ROW + 1) * 32;
 constexpr int NWARPS = NTH / 32;
-constexpr int W_IO = NC / 32;
-constexpr int W_ROW = NC / 32 + 1;
-constexpr int XR = 8;        // cp.async ring depth (frames)
-constexpr int DEG = 4;       // arcs packed per state
-constexpr int HEAVY = 12;    // labels with more arcs leave one partial per recursion thread
-constexpr int NHMAX = 4;     // at most this many labels take that route; the rest loop
+constexpr int NFWD = NS + 32;  // threads that take part in the forward sweep (state warps + io)
+constexpr int XR = 8;          // cp.async ring depth (frames)
+constexpr int DEG = 4;         // arcs packed per state
+constexpr int HEAVY = 12;      // labels with more arcs go to the heavy warps
+constexpr int NHMAX = 4;       // at most this many labels take that route; the rest loop
 constexpr unsigned NOARC = 0xffffffffu;
+constexpr int IMIN = -2147483647 - 1;
 
 struct NumPlan {
   int in_pk, out_pk, in_w, out_w, lab_ptr, lab_pk, lab_w, a0, a1, fin, gr, hl, hx, hp, red, xring, aring;
@@ -68,20 +78,20 @@ __host__ __device__ inline NumPlan num_plan(int maxN, int maxA, int maxL, int nl
   p.gr = take(2 * maxL * 4);
   p.hl = take(NHMAX * 4);
   p.hx = take(maxL * 4);
-  p.hp = take(2 * NHMAX * NC * 4);
-  p.red = take((4 + 2 * NWARPS) * 4);
+  p.hp = take(2 * NHMAX * NHV * 4);
+  p.red = take((16 + 2 * NWARPS) * 4);
   p.xring = take(XR * nlp * 4);
   p.aring = take(XR * arow * 4);
   p.bytes = o;
   return p;
 }
 
-// log2(sum_k 2^v[k]) over DEG terms (-inf = absent)
+// log2(sum_k 2^v[k]) over DEG terms (-inf = absent), branch free
 __device__ __forceinline__ float lse4(const float (&v)[DEG]) {
   const float M = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
-  if (!(M > neg_inf())) return neg_inf();
-  const float s = ex2(v[0] - M) + ex2(v[1] - M) + ex2(v[2] - M) + ex2(v[3] - M);
-  return M + lg2(s);
+  const float Ms = (M > neg_inf()) ? M : 0.f;
+  const float s = (ex2(v[0] - Ms) + ex2(v[1] - Ms)) + (ex2(v[2] - Ms) + ex2(v[3] - Ms));
+  return Ms + lg2(s);  // lg2(0) = -inf
 }
 
 // 2^(a + b + k) with the rounding error of a + b carried along (two-sum): a and b sit
@@ -96,6 +106,14 @@ __device__ __forceinline__ float post_term(float a, float b, float k) {
 }
 
 __device__ __forceinline__ void bar_all() { asm volatile("bar.sync 0;" ::: "memory"); }
+__device__ __forceinline__ void bar_fwd() { asm volatile("bar.sync 1, %0;" ::"n"(NFWD) : "memory"); }
+
+// floor(max over the warp) as an integer; -inf saturates to IMIN
+__device__ __forceinline__ int warp_floor_max(float v) {
+  return __reduce_max_sync(0xffffffffu, __float2int_rd(v));
+}
+__device__ __forceinline__ float norm_of(int m) { return (m == IMIN) ? 0.f : (float)m; }
+__device__ __forceinline__ int next3(int r) { return r == 2 ? 0 : r + 1; }
 
 template <bool UNIT>
 __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const int maxN, const int maxA, const int maxL) {
@@ -126,9 +144,10 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
   int* hl = reinterpret_cast<int*>(sm + P.hl);
   int* hx = reinterpret_cast<int*>(sm + P.hx);
   float* hp = reinterpret_cast<float*>(sm + P.hp);
-  float* wred = reinterpret_cast<float*>(sm + P.red);  // [2] frame normalisers (integers)
-  int* nheavy = reinterpret_cast<int*>(wred + 2);
-  float* scr = wred + 4;                               // [2 * NWARPS] scratch
+  int* wmax = reinterpret_cast<int*>(sm + P.red);  // [3] floor(max) of the frame, rotating slots
+  int* nheavy = wmax + 3;
+  float* kt = reinterpret_cast<float*>(wmax + 4);  // [2] posterior scale exponent of the frame
+  float* scr = reinterpret_cast<float*>(wmax + 16);  // [2 * NWARPS] scratch
   float* xring = reinterpret_cast<float*>(sm + P.xring);
   float* aring = reinterpret_cast<float*>(sm + P.aring);
 
@@ -162,7 +181,7 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
     lab_pk[e] = (unsigned)g.lab_src[arc0 + e] | ((unsigned)g.lab_dst[arc0 + e] << 16);
     if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
   }
-  if (tid < 2) wred[tid] = 0.f;
+  if (tid < 3) wmax[tid] = (tid == 0) ? 0 : IMIN;  // max alpha_0 = 0
   const float* xb = a.x + (long long)b * a.x_stride_b;
   float* aw = a.alpha_ws + (long long)b * a.T * arow;
   const int xchunks = nlp / 4, achunks = arow / 4;
@@ -184,56 +203,17 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
   // =============================== forward ===============================
   float* a_cur = abuf0;
   float* a_nxt = abuf1;
-  double c = 0.0;  // alpha_t = alpha_hat_t + c (log2 units); identical in every thread
-  if (warp == W_IO) {
-    auto issue_x = [&](int t, int slot) {
-      if (t >= 0 && t < len) {
-        const float* src = xb + (long long)t * nlp;
-        float* dst = xring + slot * nlp;
-        for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
-      }
-      cp_async_commit();
-    };
-    for (int i = 0; i < XR - 1; ++i) issue_x(i, i);
-    cp_async_wait<XR - 2>();
-    float cur = 0.f;
+  double c = 0.0;  // io warp: alpha_t = alpha_hat_t + c (log2 units)
+  if (warp < W_LAB) {
+    int r = 0;
     for (int t = 0; t < len; ++t) {
-      bar_all();
-      issue_x(t + XR - 1, (t + XR - 1) % XR);
-      // normaliser of step t + 1: floor(max alpha_hat_t), one step behind the recursion
-      float m = neg_inf();
-      for (int s = lane; s < n; s += 32) m = fmaxf(m, a_cur[s]);
-      m = floorf(warp_max(m));
-      // the normaliser in flight (cur) has not reached a_cur yet: subtract it (dead-beat, keeps
-      // max alpha_hat within two frames' increments of zero)
-      cur = (m > neg_inf()) ? m - cur : 0.f;
-      if (lane == 0) wred[(t + 1) & 1] = cur;
-      cp_async_wait<XR - 2>();
-      float* tmp = a_cur;
-      a_cur = a_nxt;
-      a_nxt = tmp;
-    }
-    cp_async_wait<0>();
-  } else if (warp == W_ROW) {
-    for (int t = 0; t < len; ++t) bar_all();
-    if (len & 1) {
-      float* tmp = a_cur;
-      a_cur = a_nxt;
-      a_nxt = tmp;
-    }
-  } else {
-    for (int t = 0; t < len; ++t) {
-      bar_all();
-      const float mx = wred[t & 1];
-      c += (double)mx;
+      bar_fwd();
+      const float mx = norm_of(wmax[r]);
+      r = next3(r);
       const float* xrow = xring + (t % XR) * nlp;
       float* ar = aw + (long long)t * arow;
-      if (tid == 0) {
-        const float hi = (float)c;
-        ar[arow - 2] = hi;
-        ar[arow - 1] = (float)(c - (double)hi);
-      }
-      for (int s = tid; s < n; s += NC) {
+      float lm = neg_inf();
+      for (int s = tid; s < n; s += NS) {
         ar[s] = a_cur[s] - mx;
         const uint4 pk = in_pk[s];
         const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
@@ -251,8 +231,46 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
           v[2] += w.z;
           v[3] += w.w;
         }
-        a_nxt[s] = lse4(v);
+        const float res = lse4(v);
+        a_nxt[s] = res;
+        lm = fmaxf(lm, res);
       }
+      const int wm = warp_floor_max(lm);
+      if (lane == 0) atomicMax(&wmax[r], wm);
+      float* tmp = a_cur;
+      a_cur = a_nxt;
+      a_nxt = tmp;
+    }
+  } else {
+    if (warp == W_IO) {
+      auto issue_x = [&](int t, int slot) {
+        if (t >= 0 && t < len) {
+          const float* src = xb + (long long)t * nlp;
+          float* dst = xring + slot * nlp;
+          for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
+        }
+        cp_async_commit();
+      };
+      for (int i = 0; i < XR - 1; ++i) issue_x(i, i);
+      cp_async_wait<XR - 2>();
+      int r = 0;
+      for (int t = 0; t < len; ++t) {
+        bar_fwd();
+        issue_x(t + XR - 1, (t + XR - 1) % XR);
+        c += (double)norm_of(wmax[r]);
+        r = next3(r);
+        if (lane == 0) {
+          float* ar = aw + (long long)t * arow;
+          const float hi = (float)c;
+          ar[arow - 2] = hi;
+          ar[arow - 1] = (float)(c - (double)hi);
+          wmax[next3(r)] = IMIN;  // the slot the state warps fill during the next frame
+        }
+        cp_async_wait<XR - 2>();
+      }
+      cp_async_wait<0>();
+    }
+    if (len & 1) {
       float* tmp = a_cur;
       a_cur = a_nxt;
       a_nxt = tmp;
@@ -278,8 +296,8 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
 #pragma unroll
   for (int w = 0; w < NWARPS; ++w) TS += scr[NWARPS + w];
   const bool feasible = TM > neg_inf() && TS > 0.f;
-  const double cost2 = feasible ? (c + (double)TM + (double)lg2(TS)) : 0.0;  // meaningful in the recursion warps
-  if (tid == 0) a.cost[b] = feasible ? cost2 * kLn2 : -1e20;
+  const double cost2 = feasible ? (c + (double)TM + (double)lg2(TS)) : 0.0;  // meaningful in the io warp only
+  if (warp == W_IO && lane == 0) a.cost[b] = feasible ? cost2 * kLn2 : -1e20;
   if (!a.write_grad) return;
   float* gb = a.gout + (long long)b * a.g_stride_b;
   if (!feasible) {
@@ -293,107 +311,19 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
   float* b_cur = a_nxt;  // the buffer not holding alpha_len
   float* b_nxt = a_cur;
   for (int s = tid; s < n; s += NTH) b_cur[s] = fin[s];
-  if (tid < 2) wred[tid] = 0.f;
+  if (tid < 3) wmax[tid] = (tid == 0) ? 0 : IMIN;  // the first frame is not normalised
   const int nh = *nheavy;
-  bar_all();
-  if (warp == W_IO) {
-    auto issue_b = [&](int i, int slot) {
-      if (i >= 0 && i < len) {
-        const int t = len - 1 - i;
-        const float* src = xb + (long long)t * nlp;
-        float* dst = xring + slot * nlp;
-        for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
-        const float* asrc = aw + (long long)t * arow;
-        float* adst = aring + slot * arow;
-        for (int cc = lane; cc < achunks; cc += 32) cp_async16(adst + 4 * cc, asrc + 4 * cc);
-      }
-      cp_async_commit();
-    };
-    for (int i = 0; i < XR - 1; ++i) issue_b(i, i);
-    cp_async_wait<XR - 2>();
-    float cur = 0.f;
-    for (int i = 0; i < len; ++i) {
-      bar_all();
-      issue_b(i + XR - 1, (i + XR - 1) % XR);
-      float m = neg_inf();
-      for (int s = lane; s < n; s += 32) m = fmaxf(m, b_cur[s]);
-      m = floorf(warp_max(m));
-      cur = (m > neg_inf()) ? m - cur : 0.f;
-      if (lane == 0) wred[(i + 1) & 1] = cur;
-      cp_async_wait<XR - 2>();
-      float* tmp = b_cur;
-      b_cur = b_nxt;
-      b_nxt = tmp;
-    }
-    cp_async_wait<0>();
+  if (warp < W_LAB) {
+    // ---- state warps: beta_t[s] = LSE_{arcs out of s}(w + x[label] + beta_{t+1}[dst]) ----
     bar_all();
-  } else if (warp == W_ROW) {
-    // finishes the posterior row of iteration i - 1 while the recursion warps run iteration i
-    auto finish = [&](int i) {
-      float* grp = gr + (i & 1) * maxL;
-      const float* hpp = hp + (i & 1) * NHMAX * NC;
-      float tot = 0.f;
-      for (int h = 0; h < nh; ++h) {
-        float v = 0.f;
-#pragma unroll
-        for (int k = 0; k < NC / 32; ++k) v += hpp[h * NC + k * 32 + lane];
-        v = warp_sum(v);
-        if (lane == 0) grp[hl[h]] = v;
-        tot += v;  // identical in every lane
-      }
-      __syncwarp();
-      float ls = 0.f;
-      for (int j = lane; j < nl; j += 32) ls += (hx[j] < 0) ? grp[j] : 0.f;
-      tot += warp_sum(ls);
-      const float sc = tot > 0.f ? gmul / tot : 0.f;
-      float* dst = gb + (long long)(len - 1 - i) * a.g_stride_t;
-      for (int j = lane; j < nl; j += 32) dst[j] = grp[j] * sc;
-    };
+    int r = 0;
     for (int i = 0; i < len; ++i) {
       bar_all();
-      if (i > 0) finish(i - 1);
-    }
-    bar_all();
-    if (len > 0) finish(len - 1);
-  } else {
-    double d = 0.0;  // beta_{t+1} = beta_hat + d
-    for (int i = 0; i < len; ++i) {
-      bar_all();
-      const float mxb = wred[i & 1];
+      const float mxb = norm_of(wmax[r]);
+      r = next3(r);
       const float* xrow = xring + (i % XR) * nlp;
-      const float* at = aring + (i % XR) * arow;
-      const double ct = (double)at[arow - 2] + (double)at[arow - 1];
-      const float Kt = (float)(ct + d - cost2);
-      d += (double)mxb;
-      float* grw = gr + (i & 1) * maxL;
-      float* hpw = hp + (i & 1) * NHMAX * NC;
-      // posteriors: gamma[j] = sum_{arcs labelled j} 2^(x[j] + w + alpha_t[src] + beta_{t+1}[dst] - cost);
-      // every term is a probability (<= 1), so no running maximum is needed
-      for (int j = tid; j < nl; j += NC) {
-        float acc = 0.f;
-        if (hx[j] < 0) {
-          const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
-          const float kx = fmaf(xrow[j], kLog2e, Kt);
-          for (int e = e0; e < e1; ++e) {
-            const unsigned pk = lab_pk[e];
-            acc += post_term(at[pk & 0xffffu], b_cur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
-          }
-        }
-        grw[j] = acc;
-      }
-      for (int h = 0; h < nh; ++h) {
-        const int j = hl[h];
-        const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
-        const float kx = fmaf(xrow[j], kLog2e, Kt);
-        float acc = 0.f;
-        for (int e = e0 + tid; e < e1; e += NC) {
-          const unsigned pk = lab_pk[e];
-          acc += post_term(at[pk & 0xffffu], b_cur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
-        }
-        hpw[h * NC + tid] = acc;
-      }
-      // beta_t[s] = LSE_{arcs out of s}(w + x[label] + beta_{t+1}[dst])
-      for (int s = tid; s < n; s += NC) {
+      float lm = neg_inf();
+      for (int s = tid; s < n; s += NS) {
         const uint4 pk = out_pk[s];
         const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
         float v[DEG];
@@ -410,13 +340,150 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
           v[2] += w.z;
           v[3] += w.w;
         }
-        b_nxt[s] = lse4(v);
+        const float res = lse4(v);
+        b_nxt[s] = res;
+        lm = fmaxf(lm, res);
+      }
+      const int wm = warp_floor_max(lm);
+      if (lane == 0) atomicMax(&wmax[r], wm);
+      float* tmp = b_cur;
+      b_cur = b_nxt;
+      b_nxt = tmp;
+    }
+    bar_all();
+  } else if (warp < W_HV) {
+    // ---- label warps: gamma[j] = sum_{arcs labelled j} 2^(x[j] + w + alpha_t[src] + beta_{t+1}[dst] - cost);
+    // every term is a probability (<= 1), so no running maximum is needed ----
+    const int j0 = tid - NS;
+    bar_all();
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      const float Kt = kt[i & 1];
+      const float* xrow = xring + (i % XR) * nlp;
+      const float* at = aring + (i % XR) * arow;
+      float* grw = gr + (i & 1) * maxL;
+      for (int j = j0; j < nl; j += NLB) {
+        float acc = 0.f;
+        if (hx[j] < 0) {
+          const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
+          const float kx = fmaf(xrow[j], kLog2e, Kt);
+          for (int e = e0; e < e1; ++e) {
+            const unsigned pk = lab_pk[e];
+            acc += post_term(at[pk & 0xffffu], b_cur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+          }
+        }
+        grw[j] = acc;  // zero for a heavy label: the row warp fills it in
       }
       float* tmp = b_cur;
       b_cur = b_nxt;
       b_nxt = tmp;
     }
     bar_all();
+  } else if (warp < W_IO) {
+    // ---- heavy warps: one arc of a many-arc label per thread, partial sums to the row warp ----
+    const int k0 = tid - NS - NLB;
+    bar_all();
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      const float Kt = kt[i & 1];
+      const float* xrow = xring + (i % XR) * nlp;
+      const float* at = aring + (i % XR) * arow;
+      float* hpw = hp + (i & 1) * NHMAX * NHV;
+      for (int h = 0; h < nh; ++h) {
+        const int j = hl[h];
+        const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
+        const float kx = fmaf(xrow[j], kLog2e, Kt);
+        float acc = 0.f;
+        for (int e = e0 + k0; e < e1; e += NHV) {
+          const unsigned pk = lab_pk[e];
+          acc += post_term(at[pk & 0xffffu], b_cur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+        }
+        hpw[h * NHV + k0] = acc;
+      }
+      float* tmp = b_cur;
+      b_cur = b_nxt;
+      b_nxt = tmp;
+    }
+    bar_all();
+  } else if (warp == W_IO) {
+    auto issue_b = [&](int i, int slot) {
+      if (i >= 0 && i < len) {
+        const int t = len - 1 - i;
+        const float* src = xb + (long long)t * nlp;
+        float* dst = xring + slot * nlp;
+        for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
+        const float* asrc = aw + (long long)t * arow;
+        float* adst = aring + slot * arow;
+        for (int cc = lane; cc < achunks; cc += 32) cp_async16(adst + 4 * cc, asrc + 4 * cc);
+      }
+      cp_async_commit();
+    };
+    // Kt of frame i = c_t + d_i - cost (fp64), d_i = sum of the beta normalisers before iteration i
+    auto publish_kt = [&](int i, double d) {
+      if (i < len) {
+        const float* at = aring + (i % XR) * arow;
+        const double ct = (double)at[arow - 2] + (double)at[arow - 1];
+        if (lane == 0) kt[i & 1] = (float)(ct + d - cost2);
+      }
+    };
+    for (int i = 0; i < XR - 1; ++i) issue_b(i, i);
+    cp_async_wait<XR - 2>();
+    __syncwarp();
+    double d = 0.0;  // beta_{t+1} = beta_hat + d
+    publish_kt(0, d);
+    bar_all();
+    int r = 0;
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      issue_b(i + XR - 1, (i + XR - 1) % XR);
+      d += (double)norm_of(wmax[r]);
+      r = next3(r);
+      if (lane == 0) wmax[next3(r)] = IMIN;
+      cp_async_wait<XR - 2>();
+      __syncwarp();
+      publish_kt(i + 1, d);
+    }
+    cp_async_wait<0>();
+    bar_all();
+  } else {
+    // ---- row warp: finishes the posterior row of iteration i - 1 while the others run iteration i ----
+    auto finish = [&](int i) {
+      float* grp = gr + (i & 1) * maxL;
+      const float* hpp = hp + (i & 1) * NHMAX * NHV;
+      float ls = 0.f;
+      for (int j = lane; j < nl; j += 32) ls += grp[j];
+      float v0 = 0.f;
+      if (nh > 0) {
+#pragma unroll
+        for (int k = 0; k < NHV / 32; ++k) v0 += hpp[k * 32 + lane];
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {  // two independent chains, interleaved
+        ls += __shfl_xor_sync(0xffffffffu, ls, o);
+        v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+      }
+      float tot = ls + v0;
+      if (nh > 0 && lane == 0) grp[hl[0]] = v0;
+      for (int h = 1; h < nh; ++h) {
+        float v = 0.f;
+#pragma unroll
+        for (int k = 0; k < NHV / 32; ++k) v += hpp[h * NHV + k * 32 + lane];
+        v = warp_sum(v);
+        if (lane == 0) grp[hl[h]] = v;
+        tot += v;  // identical in every lane
+      }
+      __syncwarp();
+      const float sc = tot > 0.f ? gmul / tot : 0.f;
+      float* dst = gb + (long long)(len - 1 - i) * a.g_stride_t;
+      for (int j = lane; j < nl; j += 32) dst[j] = grp[j] * sc;
+    };
+    bar_all();
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      if (i > 0) finish(i - 1);
+    }
+    bar_all();
+    if (len > 0) finish(len - 1);
   }
 }
 
