@@ -35,6 +35,8 @@ WORKLOADS = {
     "cfg4": ("CTC-GB contextual blanks", 2, 49, 256, 800, {"use_contextual_blanks": True}, None, True),
     "cfg5": ("CTC-G sweep shard", 2, 49, 256, 800, {}, None, True),
 }
+# dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_ncu_full_summary.md)
+NCU_TRAFFIC = {("cfg3", "bichar_den"): 617771008}
 CFG_INDEX = {"cfg1": 1, "cfg2": 2, "cfg2s": 2, "cfg3": 3, "cfg4": 4, "cfg5": 5}
 
 
@@ -65,9 +67,38 @@ class ClockSampler(object):
         self._stop = threading.Event()
         self._thr = None
 
+    def _nvml(self):
+        """Fast path: NVML in-process (sub-millisecond per sample)."""
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            h = N.nvmlDeviceGetHandleByIndex(self.index)
+            mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+            bits = {"hw_slowdown": N.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": N.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": N.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": N.nvmlClocksThrottleReasonSwPowerCap}
+
+            def sample():
+                sm = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)
+                r = N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                pw = N.nvmlDeviceGetPowerUsage(h) / 1000.0
+                return [str(sm), str(mx), str(pw)] + ["Active" if (r & bits[k]) else "Not Active" for k in
+                                                       ("hw_slowdown", "hw_thermal_slowdown",
+                                                        "sw_thermal_slowdown", "sw_power_cap")]
+            sample()
+            return sample
+        except Exception:
+            return None
+
     def _run(self):
+        sample = self._nvml()
         while not self._stop.is_set():
             try:
+                if sample is not None:
+                    self.rows.append(sample())
+                    self._stop.wait(0.002)
+                    continue
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True,
                                      timeout=5).stdout.strip()
@@ -153,16 +184,20 @@ def run_reference(args):
     for _ in range(max(args.warmup, 0) and 1):
         cpu_path_time(batch, sample_b, threads)
     times, frames = [], 0
+    budget_s = float(os.environ.get("CTCG_REFERENCE_BUDGET_S", "120"))   # keep the arm within minutes
     for _ in range(args.steps):
         dt, frames = cpu_path_time(batch, sample_b, threads)
         times.append(dt)
+        if sum(times) > budget_s:
+            break
     total = sum(times)
     value = frames * len(times) / total
     sample = "first %d of %d utterances of %s, T=%d, V=%d, fp32" % (
         sample_b, batch["B"], args.workload, batch["T"], batch["V"])
     line = {
         "impl": "reference", "metric": "CTC(-G) loss+grad utterance-frames/sec", "value": value,
-        "unit": "utterance-frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1),
+        "unit": "utterance-frames/s", "n_gpus": args.gpus, "steps": len(times), "steps_requested": args.steps,
+        "warmup": min(args.warmup, 1),
         "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.workload, batch, args.gpus),
@@ -178,8 +213,10 @@ def workload_config(workload, batch, n_gpus):
                 workload, batch["name"], batch["B"], batch["T"], batch["V"], batch["S"]),
             "global_batch": batch["B"] * n_gpus, "frames_per_step_per_gpu": int(sum(batch["lens"])),
             "parallelism": "utterance-sharded dp%d" % n_gpus,
-            "l2": "logits+grad per step (%.0f MB) exceed the 126 MB L2; 3 input buffers rotated"
-                  % (2 * batch["T"] * batch["B"] * batch["V"] * 4 / 1e6)}
+            "l2": ("logits+grad per step (%.0f MB) exceed the 126 MB L2; 3 input buffers rotated"
+                   if 2 * batch["T"] * batch["B"] * batch["V"] * 4 > 126e6 else
+                   "logits+grad per step (%.0f MB) fit the 126 MB L2 (parity-size workload, not the bench "
+                   "configuration); 3 input buffers rotated") % (2 * batch["T"] * batch["B"] * batch["V"] * 4 / 1e6)}
 
 
 def run_ours(args):
@@ -250,9 +287,10 @@ def run_ours(args):
 
     # ---- per-kernel attribution (outside the timed regions) --------------------------------
     kern = {}
+    nprof_steps = 10
     if rank == 0:
         P._lib.profile(True)
-        nprof = 5
+        nprof = nprof_steps
         for i in range(nprof):
             P._lib.loss_fwd_bwd(xs[i % NBUF], lens, num, den, mode, S)
         for name, t in P._lib.profile_collect():
@@ -268,11 +306,21 @@ def run_ours(args):
     alg_bytes = 8.0 * V * frames                     # read V logits + write V gradients per valid frame
     dom = max(kern, key=kern.get) if kern else None
     step_gbs = alg_bytes / (ms_per_step * 1e-3) / 1e9
-    roof = {"bound": "hbm", "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak,
-            "traffic": None, "peak_source": peak_src,
-            "scope": "whole step (all kernels of one loss+grad call) on one GPU; algorithmic bytes = 8*V*sum(len)",
-            "dominant_kernel": dom, "kernel_ms": {k: round(v, 4) for k, v in kern.items()},
-            "dominant_kernel_share": (kern[dom] / sum(kern.values())) if kern else None}
+    # dominant kernel: one launch processes the whole batch (all `frames` utterance-frames)
+    dom_gbs = alg_bytes / (kern[dom] * 1e-3) / 1e9 if dom else step_gbs
+    # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+    # (profiles/r01_ncu_full_summary.md); only captured for the default workload
+    traffic = NCU_TRAFFIC.get((args.workload, dom))
+    roof = {"bound": "hbm", "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak,
+            "traffic": traffic, "peak_source": peak_src,
+            "kernel": dom, "algorithmic_bytes_per_launch": alg_bytes,
+            "scope": "dominant kernel: algorithmic bytes of one launch (8*V*sum(len)) / its mean CUDA-event "
+                     "duration over %d steps run right after the timed region" % nprof_steps,
+            "kernel_ms": {k: round(v, 4) for k, v in kern.items()},
+            "dominant_kernel_share": (kern[dom] / sum(kern.values())) if kern else None,
+            "step_achieved": step_gbs, "step_frac": step_gbs / peak,
+            "concurrency": "bichar_den runs on a side stream concurrently with gather+num_log"
+                           if "bichar_den" in kern else "single stream"}
     line = {
         "metric": "CTC(-G) loss+grad utterance-frames/sec", "value": value, "unit": "utterance-frames/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -302,8 +350,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -176,6 +176,26 @@ def test_full_vocabulary_slice_matches_fp64_oracle(P, variant):
     assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
 
 
+@pytest.mark.parametrize("S,args", [(49, {}), (49, {"use_contextual_blanks": True}), (36, {}),
+                                    (11, {"allow_nonblank_selfloops": False})])
+def test_fused_bichar_kernel_equals_generic_csr_kernel(P, S, args):
+    """The factorised bi-char denominator kernel against the generic CSR kernel on the same
+    decoding graph (imported arc by arc through the reference's padded matrices, which drops
+    the topology tag and with it the fused route)."""
+    T, B = 64, 3
+    logits, lens, seqs = _random_case(2, S, args, T, B, seed=77 + S)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
+    den = gen.get_decoding_graph()
+    mats = den.export_padded(0, out_edges=False) + den.export_padded(0, out_edges=True)
+    generic = P.Graph.from_padded([torch.as_tensor(m)[None] for m in mats])
+    x = torch.from_numpy(logits).cuda()
+    c_fused, g_fused = P._lib.path_sum(x, lens, den)
+    c_gen, g_gen = P._lib.path_sum(x, lens, generic)
+    assert _rel(c_fused.cpu().numpy(), c_gen.cpu().numpy()) < 2e-6
+    assert (g_fused - g_gen).abs().max().item() < 5e-6
+    assert (g_fused[lens[-1]:, -1] == 0).all()
+
+
 @pytest.mark.parametrize("variant,B,T", [("ctc", 64, 400), ("ctcg", 64, 400), ("ctcgb", 32, 800)])
 def test_full_size_properties(P, variant, B, T):
     """BASELINE-size batches: size-independent properties of the posteriors."""
