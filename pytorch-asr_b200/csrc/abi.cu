@@ -96,6 +96,47 @@ int check_graph(const ctcg_graph* g, int B) {
   return CTCG_OK;
 }
 
+// Pinned staging buffers for graph uploads (one small ring per host thread): the host copy
+// into a slot is synchronous, the H2D copy out of it is asynchronous; a slot is reused only
+// after its previous copy has completed.
+cudaError_t stage_and_copy(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  struct Slot {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaEvent_t done = nullptr;
+  };
+  constexpr int kSlots = 4;
+  thread_local Slot ring[kSlots];
+  thread_local int next = 0;
+  Slot& s = ring[next];
+  next = (next + 1) % kSlots;
+  cudaError_t e;
+  if (!s.done && (e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)) != cudaSuccess) return e;
+  if ((e = cudaEventSynchronize(s.done)) != cudaSuccess) return e;  // never-recorded events are complete
+  if (s.cap < bytes) {
+    if (s.p) cudaFreeHost(s.p);
+    s.p = nullptr;
+    s.cap = 0;
+    const size_t cap = std::max<size_t>(bytes + bytes / 2, size_t{1} << 20);
+    if ((e = cudaHostAlloc(&s.p, cap, cudaHostAllocDefault)) != cudaSuccess) return e;
+    s.cap = cap;
+  }
+  std::memcpy(s.p, src, bytes);
+  if ((e = cudaMemcpyAsync(dst, s.p, bytes, cudaMemcpyHostToDevice, st)) != cudaSuccess) return e;
+  return cudaEventRecord(s.done, st);
+}
+
+// The blob is freed in stream order on the stream it was uploaded on: every kernel that read it
+// was launched on that stream (or joined back into it) before the handle is released.
+void free_blob(ctcg_graph* g) {
+  if (!g->dev_blob) return;
+  if (!g->dev_async || cudaFreeAsync(g->dev_blob, static_cast<cudaStream_t>(g->dev_stream)) != cudaSuccess) {
+    (void)cudaGetLastError();
+    cudaFree(g->dev_blob);
+  }
+  (void)cudaGetLastError();
+}
+
 }  // namespace
 
 extern "C" {
@@ -106,7 +147,7 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   CTCG_CUDA(cudaGetDevice(&dev));
   if (g->dev_blob && g->device == dev) return CTCG_OK;
   if (g->dev_blob) {
-    cudaFree(g->dev_blob);
+    free_blob(g);
     g->dev_blob = nullptr;
   }
   std::vector<unsigned char> blob;
@@ -129,16 +170,25 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   append(&blob, g->lab_src, &o[15]);
   append(&blob, g->lab_dst, &o[16]);
   append(&blob, g->lab_w, &o[17]);
-  void* d = nullptr;
-  CTCG_CUDA(cudaMalloc(&d, blob.size()));
+  // Stream-ordered allocation and a pinned staging ring: nothing here waits for work already
+  // queued on the stream (e.g. the H2D copy of the logits), so graph upload overlaps it.
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  cudaError_t e = cudaMemcpyAsync(d, blob.data(), blob.size(), cudaMemcpyHostToDevice, st);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);  // blob is a temporary
+  void* d = nullptr;
+  bool async_alloc = true;
+  if (cudaMallocAsync(&d, blob.size(), st) != cudaSuccess) {
+    (void)cudaGetLastError();
+    async_alloc = false;
+    CTCG_CUDA(cudaMalloc(&d, blob.size()));
+  }
+  cudaError_t e = stage_and_copy(d, blob.data(), blob.size(), st);
   if (e != cudaSuccess) {
-    cudaFree(d);
+    if (async_alloc) cudaFreeAsync(d, st);
+    else cudaFree(d);
     (void)cudaGetLastError();
     return CTCG_ECUDA;
   }
+  g->dev_stream = stream;
+  g->dev_async = async_alloc;
   unsigned char* p = static_cast<unsigned char*>(d);
   GraphDev& v = g->dev;
   v.num_graphs = g->num_graphs;
@@ -174,10 +224,7 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
 
 void ctcg_graph_free(ctcg_graph* g) {
   if (!g) return;
-  if (g->dev_blob) {
-    cudaFree(g->dev_blob);
-    (void)cudaGetLastError();
-  }
+  if (g->dev_blob) free_blob(g);
   delete g;
 }
 
@@ -267,7 +314,7 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 int upload_lens(const Plan& p, void* ws, const int32_t* lens_host, int B, cudaStream_t st, int32_t** out) {
   int32_t* d = reinterpret_cast<int32_t*>(static_cast<unsigned char*>(ws) + p.lens);
-  CTCG_CUDA(cudaMemcpyAsync(d, lens_host, (size_t)B * 4, cudaMemcpyHostToDevice, st));
+  CTCG_CUDA(stage_and_copy(d, lens_host, (size_t)B * 4, st));  // pinned staging: no implicit stream sync
   *out = d;
   return CTCG_OK;
 }

@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cstdint>
+#include <functional>
 #include <vector>
 
 #include "../../include/ctcg_b200.h"
@@ -80,6 +81,8 @@ struct ctcg_graph {
   int device = -1;
   void* dev_blob = nullptr;
   size_t dev_bytes = 0;
+  void* dev_stream = nullptr;  // stream the blob was allocated on (stream-ordered free)
+  bool dev_async = false;
   ctcg::GraphDev dev{};
 };
 
@@ -99,8 +102,18 @@ struct RawGraph {
 };
 
 int build_decoding(const ctcg_topology& topo, RawGraph* out);
+// first[s * (nol + 1) + v] = position in dec_out[s] of the first arc with output label >= v
+// (dec_out[s] is sorted by output label), v = 0..nol; empty when the table would be too large
+struct OlabelIndex {
+  int32_t nol = 0;
+  std::vector<int32_t> first;
+};
+void index_olabels(const RawGraph& dec, const std::vector<std::vector<int32_t>>& dec_out, OlabelIndex* out);
 int compose_with_chain(const RawGraph& dec, const std::vector<std::vector<int32_t>>& dec_out,
-                       const int32_t* labels, int64_t n_labels, RawGraph* out);
+                       const int32_t* labels, int64_t n_labels, RawGraph* out,
+                       const OlabelIndex* oi = nullptr);
 int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out);
+// fn(0..n-1) on a few host threads (CTCG_HOST_THREADS, default min(8, hardware)); fn must not throw
+void parallel_for(int32_t n, const std::function<void(int32_t)>& fn);
 
 }  // namespace ctcg

@@ -2,6 +2,9 @@
 // DataLoader worker processes can use them without creating a CUDA context).
 #include <algorithm>
 #include <cmath>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -24,6 +27,7 @@ void index_out_arcs(const RawGraph& g, std::vector<std::vector<int32_t>>* out) {
 struct CachedDecoding {
   RawGraph g;
   std::vector<std::vector<int32_t>> out;
+  OlabelIndex oi;
 };
 std::shared_ptr<const CachedDecoding> cached_decoding(const ctcg_topology& t, int* status) {
   static std::mutex mu;
@@ -40,6 +44,7 @@ std::shared_ptr<const CachedDecoding> cached_decoding(const ctcg_topology& t, in
   *status = build_decoding(t, &c->g);
   if (*status != CTCG_OK) return nullptr;
   index_out_arcs(c->g, &c->out);
+  index_olabels(c->g, c->out, &c->oi);
   cache[key] = c;
   return c;
 }
@@ -81,29 +86,47 @@ int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels, const
   if (!topo || !offsets || !out || B < 0) return CTCG_EINVAL;
   try {
     int st = CTCG_OK;
+    const auto t_0 = std::chrono::steady_clock::now();
     const auto cached = cached_decoding(*topo, &st);
     if (st != CTCG_OK) return st;
+    const auto t_1 = std::chrono::steady_clock::now();
     const RawGraph& dec = cached->g;
     const std::vector<std::vector<int32_t>>& dec_out = cached->out;
     std::vector<RawGraph> gs(B);
-    std::vector<int32_t> lab;
+    std::vector<int> status(B, CTCG_OK);
     const int32_t S = topo->num_symbols;
-    for (int32_t b = 0; b < B; ++b) {
-      const int64_t lo = offsets[b], hi = offsets[b + 1];
-      if (hi < lo) return CTCG_EINVAL;
-      lab.assign(labels + lo, labels + hi);
-      // fst_utils.py:595-596: a transcript holding any id above S is taken modulo S
-      bool any_big = false;
-      for (int32_t v : lab) {
-        if (v < 0) return CTCG_EINVAL;
-        any_big |= v > S;
+    for (int32_t b = 0; b < B; ++b)
+      if (offsets[b + 1] < offsets[b]) return CTCG_EINVAL;
+    parallel_for(B, [&](int32_t b) {
+      try {
+        std::vector<int32_t> lab(labels + offsets[b], labels + offsets[b + 1]);
+        // fst_utils.py:595-596: a transcript holding any id above S is taken modulo S
+        bool any_big = false;
+        for (int32_t v : lab) {
+          if (v < 0) {
+            status[b] = CTCG_EINVAL;
+            return;
+          }
+          any_big |= v > S;
+        }
+        if (any_big)
+          for (int32_t& v : lab) v %= S;
+        status[b] = compose_with_chain(dec, dec_out, lab.data(), static_cast<int64_t>(lab.size()), &gs[b], &cached->oi);
+      } catch (const std::bad_alloc&) {
+        status[b] = CTCG_ENOMEM;
       }
-      if (any_big)
-        for (int32_t& v : lab) v %= S;
-      st = compose_with_chain(dec, dec_out, lab.data(), static_cast<int64_t>(lab.size()), &gs[b]);
-      if (st != CTCG_OK) return st;
-    }
-    return finalize_graphs(gs, out);
+    });
+    for (int32_t b = 0; b < B; ++b)
+      if (status[b] != CTCG_OK) return status[b];
+    const auto t_2 = std::chrono::steady_clock::now();
+    const int rc = finalize_graphs(gs, out);
+    const auto t_3 = std::chrono::steady_clock::now();
+    if (std::getenv("CTCG_HOST_TIMING"))
+      std::fprintf(stderr, "cached %.3f compose %.3f finalize %.3f ms\n",
+                   std::chrono::duration<double, std::milli>(t_1 - t_0).count(),
+                   std::chrono::duration<double, std::milli>(t_2 - t_1).count(),
+                   std::chrono::duration<double, std::milli>(t_3 - t_2).count());
+    return rc;
   } catch (const std::bad_alloc&) {
     return CTCG_ENOMEM;
   }
