@@ -259,6 +259,7 @@ __device__ __forceinline__ void cta_sync() { asm volatile("bar.sync 0;" ::: "mem
 // Barrier of the per-frame loops.  With tracing on, lane 0 of every warp of CTA 0 stamps
 // the clock when its work of the step ends (before the barrier) and when the barrier releases.
 __device__ __forceinline__ void step_sync(const Ctx& c, int& n) {
+#ifdef CTCG_BICHAR_TRACE_BUILD
   if (c.trace) {
     const bool rec = c.b == 0 && c.lane == 0 && n < c.trace_steps;
     long long* tr = c.trace + ((long long)c.warp * c.trace_steps + (rec ? n : 0)) * TRS;
@@ -266,22 +267,28 @@ __device__ __forceinline__ void step_sync(const Ctx& c, int& n) {
     cta_sync();  // one barrier instruction for the whole warp: no divergence around it
     if (rec) tr[1] = clock64();
     ++n;
-  } else {
-    cta_sync();
+    return;
   }
+#endif
+  cta_sync();
 }
 
 // Intermediate stamp `slot` (2..TRS-1) of the current step, taken once `dep` is available.
+// Compiled in only with -DCTCG_BICHAR_TRACE_BUILD (the stamps cost ~3 % of the instructions).
 __device__ __forceinline__ void tstamp(const Ctx& c, int n, int slot, float dep) {
+#ifdef CTCG_BICHAR_TRACE_BUILD
   if (c.trace && c.b == 0 && c.lane == 0 && n < c.trace_steps) {
     long long t;
     asm volatile("{ .reg .f32 d; mov.f32 d, %1; mov.u64 %0, %%clock64; }" : "=l"(t) : "f"(dep));
     c.trace[((long long)c.warp * c.trace_steps + n) * TRS + slot] = t;
   }
+#endif
 }
 
 // Offset (floats) of row (t, b) inside its 16-byte aligned window: ((t*B + b) * V) mod 4.
 __device__ __forceinline__ int row_r(const Ctx& c, int t) { return ((((t & 3) * c.B3 + c.b3) & 3) * c.V3) & 3; }
+// The same in bytes for consecutive frames: r4(t + 1) = (r4(t) + d4) & 12 with d4 = 4 * ((B * V) mod 4).
+__device__ __forceinline__ unsigned row_d4(const Ctx& c) { return (unsigned)((c.B3 * c.V3) & 3) * 4u; }
 
 // Every role calls this between the sweeps (same number of barriers on every path).
 // Returns false when there is no backward sweep to run.
@@ -414,17 +421,25 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
     }
     int ck = K;            // frames until the next checkpoint
     unsigned rowoff = 0;   // byte offset of the ring row being consumed
+    unsigned r4 = row_r(c, 0) * 4;  // byte offset of the row inside its aligned window
+    const unsigned d4 = row_d4(c);
+    float* pspw = c.psp + (pspo >= 0 ? pspo : 0);  // this lane's slot of the P spill row of frame t
+    const unsigned ksm_a = smem_u32(c.ksm), maxp_a = smem_u32(c.maxpart);
     cta_sync();
     for (int g = 0; g <= len + 1; ++g) {
       const int t = g - 1;
       if (t >= 0 && t < len) {
-        const unsigned base = rows_a + rowoff + row_r(c, t) * 4;
+        const unsigned base = rows_a + rowoff + r4;
+        r4 = (r4 + d4) & 12u;
         rowoff += rowb;
         if (rowoff == NR * rowb) rowoff = 0;
-        const float4 mp = lds4(smem_u32(c.maxpart) + (t & 1) * 16);
+        const float4 mp = lds4(maxp_a + (t & 1) * 16);
+        int kk;
+        asm volatile("ld.shared.s32 %0, [%1];" : "=r"(kk) : "r"(ksm_a + (t & 1) * 4));
         float m = fmaxf(fmaxf(mp.x, mp.y), fmaxf(mp.z, mp.w));
         if (!(m > neg_inf())) m = 0.f;
-        const float nmL = -m * kLog2e;
+        // a rescale by 2^kk rides in the exponent of e: exp2(x*log2e - m*log2e + kk)
+        const float nmL = fmaf(m, -kLog2e, (float)kk);
         tstamp(c, nstep, 2, nmL);
         float xr0[RPW], xr1[RPW];
 #pragma unroll
@@ -438,17 +453,12 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         float P[RPW];
 #pragma unroll
         for (int k = 0; k < RPW; ++k) P[k] = __shfl_sync(0xffffffffu, s, 8 * k);
-        if (pspo >= 0) c.psp[t * prowf + pspo] = s;
-        const int kk = c.ksm[t & 1];
+        if (pspo >= 0) *pspw = s;
+        pspw += prowf;
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
           const float2 e2 = exp_pair(xr0[k], xr1[k], nmL);
           a2[k] = fmul2(e2, ffma2(m2[k], a2[k], splat2(P[k])));
-        }
-        if (kk != 0) {
-          const float2 s2 = splat2(pow2i(kk));
-#pragma unroll
-          for (int k = 0; k < RPW; ++k) a2[k] = fmul2(a2[k], s2);
         }
         float2 cs = a2[0];
 #pragma unroll
@@ -482,8 +492,13 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
   if (!between_sweeps(c)) return;
 
   // -------------------------------- backward: majors = letters l, minors = contexts c
+  // Element (c, l) of a row sits at byte (c*S + l)*4: with c = lane (+32) and l = M0 + k the four
+  // majors of a lane are consecutive floats, so one base address per slot serves all k as an
+  // immediate offset.  Warp 0 (l = 0) reads the one global blank at offset 0 unless blanks are
+  // contextual.  FULL: every warp but warp 0 owns exactly RPW letters (S = 49, 37, ...).
+  constexpr bool FULL = (SCT > 0) && ((SCT - 1) % RPW == 0);
+  constexpr bool WIDE = (SCT >= 32);  // slot 0 (c = lane) is always a valid context
   float2 b2[RPW], f2[RPW], m2[RPW];
-  unsigned eo0[RPW], eo1[RPW], vo0[RPW], vo1[RPW];
 #pragma unroll
   for (int k = 0; k < RPW; ++k) {
     const bool kv = k < nk;
@@ -491,22 +506,22 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
     const bool v0 = kv && nv0, v1 = kv && nv1;
     b2[k] = make_float2(v0 ? pow2i(TARGET) : 0.f, v1 ? pow2i(TARGET) : 0.f);
     f2[k] = make_float2(0.f, 0.f);
-    vo0[k] = (nv0 ? n0 * S + l : 0) * 4;
-    vo1[k] = (nv1 ? n1 * S + l : 0) * 4;
-    eo0[k] = (l != 0 || ctx) ? vo0[k] : 0;
-    eo1[k] = (l != 0 || ctx) ? vo1[k] : 0;
     m2[k].x = (loops && v0 && l != 0 && l != n0) ? 1.f : 0.f;
     m2[k].y = (loops && v1 && l != 0 && l != n1) ? 1.f : 0.f;
     pin(m2[k]);
-    pin(eo0[k]);
-    pin(eo1[k]);
-    pin(vo0[k]);
-    pin(vo1[k]);
   }
+  // invalid slots read element 0 of the row (finite after the exp pass); their products are masked
+  unsigned vb0 = (nv0 ? n0 * S + M0 : 0) * 4, vb1 = (nv1 ? n1 * S + M0 : 0) * 4;
+  unsigned eb0 = (warp == 0 && !ctx) ? 0u : vb0, eb1 = (warp == 0 && !ctx) ? 0u : vb1;
+  const bool st0 = WIDE ? true : nv0, st1 = nv1;
   float2 pm = make_float2(nv0 ? 1.f : 0.f, nv1 ? 1.f : 0.f);
   float gmask = (grp < nk) ? 1.f : 0.f;
   unsigned gaddr = part_a + (gcol + j8 * PARTW) * 4;
   unsigned paddr = part_a + (warp * PARTW + n0) * 4;
+  pin(vb0);
+  pin(vb1);
+  pin(eb0);
+  pin(eb1);
   pin(pm);
   pin(gmask);
   pin(gaddr);
@@ -514,25 +529,35 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
   ConsCursor cur;
   cur.init(max(len, 1), K);
   const int GEND = len + c.LEAD + 2;
+  const unsigned d4 = row_d4(c);
+  unsigned r4 = row_r(c, max(len - 1, 0)) * 4;
+  const unsigned tabe_a = smem_u32(c.tab_e), taba_a = smem_u32(c.tab_a), ksm_a = smem_u32(c.ksm),
+                 csm_a = smem_u32(c.csm);
   for (int g = 0; g < GEND; ++g) {
     const int i = g - c.LEAD;
     if (i >= 0 && i < len) {
-      const int t = len - 1 - i;
       const int slot = cur.q & (QRING - 1);
       cur.prev();
-      const unsigned r4 = row_r(c, t) * 4;
-      const unsigned er = rows_a + (c.tab_e[slot] & 0xff) * rowb + r4;
-      const unsigned ar = rows_a + c.tab_a[slot] * rowb + r4;
+      int te, ta, hk;
+      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(te) : "r"(tabe_a + slot * 4));
+      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(ta) : "r"(taba_a + slot * 4));
+      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(hk) : "r"(ksm_a + (i & 1) * 4));
+      const unsigned er = rows_a + (te & 0xff) * rowb + r4;
+      const unsigned ar = rows_a + ta * rowb + r4;
+      r4 = (r4 - d4) & 12u;  // frame t - 1 comes next
+      const unsigned e0 = er + eb0, e1 = er + eb1, q0a = ar + vb0, q1a = ar + vb1;
       float2 e2[RPW], al[RPW];
 #pragma unroll
       for (int k = 0; k < RPW; ++k) {  // all loads first: they alias the stores below
-        e2[k] = make_float2(lds(er + eo0[k]), lds(er + eo1[k]));
-        al[k] = make_float2(lds(ar + vo0[k]), lds(ar + vo1[k]));
+        // an absent major (k >= nk) re-reads major 0 of the warp: in bounds, result unused
+        const unsigned ko = (FULL || k < nk) ? 4u * k : 0u;
+        e2[k] = make_float2(lds(e0 + ko), lds(e1 + ko));
+        al[k] = make_float2(lds(q0a + ko), lds(q1a + ko));
       }
       if (i > 0) {  // (a) b_{t+1} = 2^h (Q + loop * f_{t+1}) from the partials of the previous step
-        const float* pb = c.part + (i & 1) * partrows * PARTW;
-        const float hs = pow2i(c.ksm[i & 1]);
+        const float hs = pow2i(hk);
         if (warp == 0) {
+          const float* pb = c.part + (i & 1) * partrows * PARTW;
           float q0 = 0.f, q1 = 0.f;
 #pragma unroll 4
           for (int rr = 0; rr < nmain; ++rr) {
@@ -551,7 +576,8 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         }
       }
       // (b) posteriors of frame t and f_t = e_t * b_{t+1}
-      const float2 c12 = *reinterpret_cast<const float2*>(c.csm + (i & 1) * 2);
+      float2 c12;
+      asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(c12.x), "=f"(c12.y) : "r"(csm_a + (i & 1) * 8));
       float2 cs;
       if (warp == 0) {
         const float* pr = c.prow + slot * prowf;
@@ -561,12 +587,12 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         const float2 gm = fmul2(fmul2(a_, splat2(c12.x)), fmul2(b2[0], splat2(c12.y)));
         cs = f2[0];
         if (ctx) {
-          if (nv0) sts(ar + vo0[0], gm.x);
-          if (nv1) sts(ar + vo1[0], gm.y);
+          if (nv0) sts(q0a, gm.x);
+          if (nv1) sts(q1a, gm.y);
         } else {  // one global blank: its posterior is the sum over the S blank states
           const float tot = warp_sum(gm.x + gm.y);
-          if (nv0) sts(ar + vo0[0], (lane == 0) ? tot : 0.f);
-          if (nv1) sts(ar + vo1[0], 0.f);
+          if (nv0) sts(q0a, (lane == 0) ? tot : 0.f);
+          if (nv1) sts(q1a, 0.f);
         }
       } else {
         cs = make_float2(0.f, 0.f);
@@ -579,9 +605,9 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         }
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
-          if (k < nk) {
-            if (nv0) sts(ar + vo0[k], al[k].x);
-            if (nv1) sts(ar + vo1[k], al[k].y);
+          if (FULL || k < nk) {
+            if (st0) sts(q0a + 4 * k, al[k].x);
+            if (st1) sts(q1a + 4 * k, al[k].y);
           }
         }
       }
@@ -690,6 +716,9 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
   ProdCursor pc;
   pc.init(max(len, 1), K);
   if (len > 0 && pc.tau > 0) load_ckpt(pc.tau);
+  constexpr bool WIDE = (SCT >= 32);  // slot 0 (l = lane) is always a valid letter
+  // row aw + NAUX*u exists for every auxiliary warp when NAUX*(u+1) <= S: known at compile time
+  auto row_ok = [&](int u) { return (SCT > 0 && NAUX * (u + 1) <= SCT) ? true : (aw + NAUX * u < S); };
   const int GEND = len + c.LEAD + 2;
   for (int g = 0; g < GEND; ++g) {
     const int q = g - c.DBk;
@@ -704,7 +733,8 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
       mbar_wait(&c.mbar[te & 0xff], te >> 8);
       const float* pr = c.prow + (q & (QRING - 1)) * prowf;
       const int kq = (int)pr[S + 1];
-      const float nmL = -pr[S] * kLog2e;
+      const float mq = pr[S];
+      const float nmL = -mq * kLog2e;
       if (seg0) {
         if (tau == 0) {
 #pragma unroll
@@ -719,30 +749,34 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
       float2 x2[RU];
 #pragma unroll
       for (int u = 0; u < RU; ++u) {  // all shared-memory loads before the first store
-        const int cc = aw + NAUX * u;
-        if (cc < S) {
-          Pc[u] = pr[cc];
+        if (row_ok(u)) {
+          Pc[u] = pr[aw + NAUX * u];
           x2[u] = make_float2(lds(er + o0 + NAUX * u * S * 4), lds(er + o1 + NAUX * u * S * 4));
         }
       }
+      if (kq == 0) {
 #pragma unroll
-      for (int u = 0; u < RU; ++u) {
-        const int cc = aw + NAUX * u;
-        if (cc < S) {
-          x2[u] = exp_pair(x2[u].x, x2[u].y, nmL);
-          ra[u] = fmul2(x2[u], ffma2(lm[u], ra[u], splat2(Pc[u])));
+        for (int u = 0; u < RU; ++u) {
+          if (row_ok(u)) {
+            x2[u] = exp_pair(x2[u].x, x2[u].y, nmL);
+            ra[u] = fmul2(x2[u], ffma2(lm[u], ra[u], splat2(Pc[u])));
+          }
+        }
+      } else {  // rare: the forward sweep rescaled at this frame, through the exponent like it did
+        const float nmLk = fmaf(mq, -kLog2e, (float)kq);
+#pragma unroll
+        for (int u = 0; u < RU; ++u) {
+          if (row_ok(u)) {
+            const float2 es = exp_pair(x2[u].x, x2[u].y, nmLk);
+            x2[u] = exp_pair(x2[u].x, x2[u].y, nmL);
+            ra[u] = fmul2(es, ffma2(lm[u], ra[u], splat2(Pc[u])));
+          }
         }
       }
-      if (kq != 0) {  // rare: the forward sweep rescaled at this frame
-        const float2 s2 = splat2(pow2i(kq));
-#pragma unroll
-        for (int u = 0; u < RU; ++u) ra[u] = fmul2(ra[u], s2);
-      }
 #pragma unroll
       for (int u = 0; u < RU; ++u) {
-        const int cc = aw + NAUX * u;
-        if (cc < S) {
-          if (nv0) {
+        if (row_ok(u)) {
+          if (WIDE || nv0) {
             sts(er + o0 + NAUX * u * S * 4, x2[u].x);
             sts(ar + o0 + NAUX * u * S * 4, ra[u].x);
           }
