@@ -333,8 +333,9 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   if (st_ != CTCG_OK) return st_;
   if (den && (st_ = check_graph(den, B)) != CTCG_OK) return st_;
   if (normalize == CTCG_NORM_CONTEXT) {
-    // TODO(next): gradient through the per-context softmax (not used by any WSJ YAML)
-    if (grad || den) return CTCG_EUNSUPPORTED;
+    // with a denominator the dense posteriors would also have to pass through the block
+    // softmax; no reference configuration combines the two
+    if (den) return CTCG_EUNSUPPORTED;
     if (num_symbols < 1 || V % num_symbols != 0) return CTCG_EINVAL;
   }
   for (int b = 0; b < B; ++b)
@@ -438,6 +439,9 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     d.write_grad = grad != nullptr;
     CTCG_CUDA(launch_path_fwd_bwd(d, false, st));
     if (grad) CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
+  } else if (grad && normalize == CTCG_NORM_CONTEXT) {
+    // 3c. block softmax chain rule: softmax_block(x) * sum_block(gamma_num) - gamma_num
+    CTCG_CUDA(launch_rows_ctx(logits, T, B, V, num_symbols, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
   } else if (grad || softmax) {
     // 3b. one streaming pass: softmax(x) - gamma_num (or -gamma_num), row LSE for the loss
     CTCG_CUDA(launch_rows(logits, T, B, V, lens, num->dev, gg, p.nlp, softmax ? 1 : 0, grad_scale, grad,

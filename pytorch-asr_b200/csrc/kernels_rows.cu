@@ -137,6 +137,57 @@ __global__ void __launch_bounds__(NT) rows_kernel(const float* __restrict__ logi
   }
 }
 
+// normalize_by_dim = 1 (get_normalized_acts, ctc_losses.py:36-40): log_softmax inside each
+// context block of S labels.  With lp = x - LSE_block(x) the chain rule gives
+//   dL/dx[v] = softmax_block(x)[v] * sum_{u in block(v)} gamma[u] - gamma[v],   L = -cost_num(lp).
+// One CTA per row at a time, one warp per context block; gamma is sparse (delta[V] in shared memory).
+__global__ void __launch_bounds__(NT) rows_ctx_kernel(const float* __restrict__ logits, int T, int B, int V, int S,
+                                                      const int32_t* __restrict__ lens, GraphDev g,
+                                                      const float* __restrict__ gg, int nlp,
+                                                      const float* __restrict__ g_scale,
+                                                      float* __restrict__ grad) {
+  extern __shared__ __align__(16) float delta[];  // [V]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int j = tid; j < V; j += NT) delta[j] = 0.f;
+  __syncthreads();
+  const long long rows = (long long)T * B;
+  const int nblk = V / S;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int t = (int)(row / B), b = (int)(row % B);
+    float* out = grad + row * V;
+    if (t >= lens[b]) {
+      for (int j = tid; j < V; j += NT) st_stream(out + j, 0.f);
+      continue;
+    }
+    const float scale = g_scale ? g_scale[b] : 1.f;
+    const int gi = g.num_graphs == 1 ? 0 : b;
+    const int lo = g.lab_off[gi], nl = g.lab_off[gi + 1] - lo;
+    const float* grow = gg + ((long long)b * T + t) * nlp;
+    for (int j = tid; j < nl; j += NT) delta[g.lab_list[lo + j]] = grow[j];
+    __syncthreads();
+    const float* x = logits + row * V;
+    for (int c = warp; c < nblk; c += NWARP) {
+      const float* xb = x + c * S;
+      float m = neg_inf(), G = 0.f;
+      for (int l = lane; l < S; l += 32) {
+        m = fmaxf(m, xb[l]);
+        G += delta[c * S + l];
+      }
+      m = warp_max(m);
+      G = warp_sum(G);
+      float sum = 0.f;
+      for (int l = lane; l < S; l += 32) sum += ex2((xb[l] - m) * kLog2e);
+      sum = warp_sum(sum);
+      const float w = G / sum;
+      for (int l = lane; l < S; l += 32)
+        st_stream(out + c * S + l, (ex2((xb[l] - m) * kLog2e) * w - delta[c * S + l]) * scale);
+    }
+    __syncthreads();
+    for (int j = tid; j < nl; j += NT) delta[g.lab_list[lo + j]] = 0.f;
+    __syncthreads();
+  }
+}
+
 __global__ void __launch_bounds__(NT) scatter_sub_kernel(int T, int B, int V, const int32_t* __restrict__ lens,
                                                          GraphDev g, const float* __restrict__ gg, int nlp,
                                                          const float* __restrict__ g_scale,
@@ -216,6 +267,19 @@ cudaError_t launch_rows(const float* logits, int T, int B, int V, const int32_t*
   else if (per <= 32) CTCG_ROWS(32);
   else return cudaErrorInvalidConfiguration;
 #undef CTCG_ROWS
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_rows_ctx(const float* logits, int T, int B, int V, int S, const int32_t* lens, const GraphDev& num,
+                            const float* gg, int nlp, const float* g_scale, float* grad, cudaStream_t st) {
+  const size_t smem = (size_t)pad4(V) * 4;
+  const long long rows = (long long)T * B;
+  const unsigned grid = (unsigned)std::min<long long>(rows, 148LL * 8);
+  ProfScope prof("rows_ctx", st);
+  cudaError_t e = cudaFuncSetAttribute(rows_ctx_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  rows_ctx_kernel<<<grid, NT, smem, st>>>(logits, T, B, V, S, lens, num, gg, nlp, g_scale, grad);
   ++g_launches;
   return cudaGetLastError();
 }

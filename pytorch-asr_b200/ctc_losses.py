@@ -113,10 +113,9 @@ def ctc_fst_loss(acts, labels, act_lens, label_lens, num_symbols=0, context_orde
     num = _numerator_from_batch(other_data_in_batch, labels, label_lens, S, context_order, gg_kwargs)
     # the reference always normalises here (normalize_logits=True): None -> softmax over V
     mode = _lib.NORM_SOFTMAX if not normalize_by_dim else _lib.NORM_CONTEXT
-    if mode == _lib.NORM_CONTEXT:
-        log_probs = get_normalized_acts(acts, act_lens, num_symbols, context_order, normalize_by_dim)
-        return -path_reduction(log_probs, act_lens, num, neg_inf=neg_inf)
-    return _FstLoss.apply(acts, _check_lens(act_lens), num, None, mode, int(num_symbols or 0))
+    # per-context softmax (normalize_by_dim=1) is fused too: block LSE in the gather, chain rule in
+    # the row pass; the block size is the number of symbols
+    return _FstLoss.apply(acts, _check_lens(act_lens), num, None, mode, int(num_symbols or S))
 
 
 _ctc_fst_cache = {}

@@ -37,7 +37,7 @@ def _run_fused(P, logits, lens, num, den, normalize_by_dim, S=0):
     return loss.detach().cpu().double().numpy(), x.grad.detach().cpu().double().numpy()
 
 
-@pytest.mark.parametrize("name", [n for n in golden_names() if n != "bi_ctc_context_norm"])
+@pytest.mark.parametrize("name", golden_names())
 def test_fused_loss_matches_reference_golden(P, name):
     d = load_golden(name)
     gen = P.CTCGraphGen(context_order=d["order"], graph_build_args=d["args"], num_symbols=d["S"])
@@ -149,6 +149,8 @@ def _oracle(order, S, args, logits, lens, seqs, use_den, normalize_by_dim):
     (2, 12, {"use_contextual_blanks": True}, True, None, 90, 5, False),   # CTC-GB
     (2, 10, {"loop_using_symbol_repetitions": True}, True, None, 60, 3, False),
     (2, 10, {"allow_nonblank_selfloops": False}, True, 0, 60, 3, True),   # softmax + den: LSE cancels
+    (2, 12, {"use_contextual_blanks": True}, False, 1, 80, 4, False),     # per-context softmax (normalize_by_dim=1)
+    (2, 49, {"use_contextual_blanks": True}, False, 1, 50, 2, True),
 ])
 def test_fused_loss_matches_fp64_oracle_random(P, order, S, args, use_den, nbd, T, B, peaky):
     logits, lens, seqs = _random_case(order, S, args, T, B, seed=1000 + T + B, peaky=peaky)
