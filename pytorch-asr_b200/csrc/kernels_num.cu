@@ -29,6 +29,8 @@
 // multiplied by log2(e) inside an fma so that the input is rounded once) written by
 // gather_kernel; output: cost[b] (natural log) and the compact posterior rows
 // gout[b][t][j], which the row / scatter kernels fold into the dense gradient.
+#include <algorithm>
+
 #include "device_utils.cuh"
 #include "kernels.cuh"
 
@@ -72,8 +74,8 @@ __host__ __device__ inline NumPlan num_plan(int maxN, int maxA, int maxL, int nl
   p.lab_ptr = take((maxL + 1) * 4);
   p.lab_pk = take(maxA * 4);
   p.lab_w = unit ? 0 : take(maxA * 4);
-  p.a0 = take(maxN * 4);
-  p.a1 = take(maxN * 4);
+  p.a0 = take((maxN + 1) * 4);  // + one slot that stays -inf: the far end of an absent arc
+  p.a1 = take((maxN + 1) * 4);
   p.fin = take(maxN * 4);
   p.gr = take(2 * maxL * 4);
   p.hl = take(NHMAX * 4);
@@ -115,7 +117,20 @@ __device__ __forceinline__ int warp_floor_max(float v) {
 __device__ __forceinline__ float norm_of(int m) { return (m == IMIN) ? 0.f : (float)m; }
 __device__ __forceinline__ int next3(int r) { return r == 2 ? 0 : r + 1; }
 
-template <bool UNIT>
+// SPT > 0: every state thread owns states tid, tid + NS, ... (at most SPT) and every label thread
+// labels j0, j0 + NLB, ... (at most SPT) for the whole utterance and keeps their arcs in
+// registers as shared-memory byte offsets (no per-frame unpacking); SPT = 0: generic loops.
+constexpr int LARC = 4;  // arcs of a label kept in registers; a label with more takes the loop
+
+__device__ __forceinline__ float lds_f(unsigned a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v)); }
+__device__ __forceinline__ unsigned sm_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+
+template <bool UNIT, int SPT>
 __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const int maxN, const int maxA, const int maxL) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
@@ -182,6 +197,7 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
     if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
   }
   if (tid < 3) wmax[tid] = (tid == 0) ? 0 : IMIN;  // max alpha_0 = 0
+  if (tid == 0) abuf0[maxN] = abuf1[maxN] = neg_inf();
   const float* xb = a.x + (long long)b * a.x_stride_b;
   float* aw = a.alpha_ws + (long long)b * a.T * arow;
   const int xchunks = nlp / 4, achunks = arow / 4;
@@ -204,7 +220,69 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
   float* a_cur = abuf0;
   float* a_nxt = abuf1;
   double c = 0.0;  // io warp: alpha_t = alpha_hat_t + c (log2 units)
-  if (warp < W_LAB) {
+  if (SPT > 0 && warp < W_LAB) {
+    // arcs into the thread's states as byte offsets: .x source state in the alpha buffer
+    // (an absent arc points at the -inf slot), .y label in the logits row
+    constexpr int NSP = SPT > 0 ? SPT : 1;
+    unsigned so4[NSP][DEG], lo4[NSP][DEG];
+    float wi[NSP][DEG];
+    float* arp[NSP];
+#pragma unroll
+    for (int i = 0; i < NSP; ++i) {
+      const int s = tid + i * NS;
+      const uint4 pk = (s < n) ? in_pk[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
+      const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
+      const float4 w = (!UNIT && s < n) ? in_w[s] : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float ww[DEG] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int k = 0; k < DEG; ++k) {
+        so4[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 4u : (pkk[k] & 0xffffu) * 4u;
+        lo4[i][k] = (pkk[k] == NOARC) ? 0u : (pkk[k] >> 16) * 4u;
+        wi[i][k] = ww[k];
+      }
+      arp[i] = aw + (s < n ? s : 0);
+    }
+    unsigned ac = sm_u32(a_cur), an = sm_u32(a_nxt);
+    const unsigned xr0 = sm_u32(xring), wm_a = sm_u32(wmax);
+    int r = 0, slot = 0;
+    for (int t = 0; t < len; ++t) {
+      bar_fwd();
+      int wmi;
+      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(wmi) : "r"(wm_a + r * 4));
+      const float mx = norm_of(wmi);
+      r = next3(r);
+      const unsigned xa = xr0 + slot * nlp * 4;
+      slot = (slot + 1 == XR) ? 0 : slot + 1;
+      float lm = neg_inf();
+#pragma unroll
+      for (int i = 0; i < NSP; ++i) {
+        const int s = tid + i * NS;
+        float v[DEG];
+#pragma unroll
+        for (int k = 0; k < DEG; ++k) {
+          v[k] = fmaf(lds_f(xa + lo4[i][k]), kLog2e, lds_f(ac + so4[i][k]) - mx);
+          if (!UNIT) v[k] += wi[i][k];
+        }
+        const float res = lse4(v);
+        if (s < n) {
+          *arp[i] = lds_f(ac + s * 4) - mx;
+          sts_f(an + s * 4, res);
+        }
+        arp[i] += arow;
+        lm = fmaxf(lm, res);
+      }
+      const int wm = warp_floor_max(lm);
+      if (lane == 0) atomicMax(&wmax[r], wm);
+      const unsigned tmp = ac;
+      ac = an;
+      an = tmp;
+    }
+    if (len & 1) {
+      float* tmp = a_cur;
+      a_cur = a_nxt;
+      a_nxt = tmp;
+    }
+  } else if (warp < W_LAB) {
     int r = 0;
     for (int t = 0; t < len; ++t) {
       bar_fwd();
@@ -313,7 +391,59 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
   for (int s = tid; s < n; s += NTH) b_cur[s] = fin[s];
   if (tid < 3) wmax[tid] = (tid == 0) ? 0 : IMIN;  // the first frame is not normalised
   const int nh = *nheavy;
-  if (warp < W_LAB) {
+  if (SPT > 0 && warp < W_LAB) {
+    // ---- state warps, arcs out of the thread's states in registers ----
+    constexpr int NSP = SPT > 0 ? SPT : 1;
+    unsigned do4[NSP][DEG], lo4[NSP][DEG];
+    float wo[NSP][DEG];
+#pragma unroll
+    for (int i = 0; i < NSP; ++i) {
+      const int s = tid + i * NS;
+      const uint4 pk = (s < n) ? out_pk[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
+      const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
+      const float4 w = (!UNIT && s < n) ? out_w[s] : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float ww[DEG] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int k = 0; k < DEG; ++k) {
+        do4[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 4u : (pkk[k] & 0xffffu) * 4u;
+        lo4[i][k] = (pkk[k] == NOARC) ? 0u : (pkk[k] >> 16) * 4u;
+        wo[i][k] = ww[k];
+      }
+    }
+    unsigned bc = sm_u32(b_cur), bn = sm_u32(b_nxt);
+    const unsigned xr0 = sm_u32(xring), wm_a = sm_u32(wmax);
+    bar_all();
+    int r = 0, slot = 0;
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      int wmi;
+      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(wmi) : "r"(wm_a + r * 4));
+      const float mxb = norm_of(wmi);
+      r = next3(r);
+      const unsigned xa = xr0 + slot * nlp * 4;
+      slot = (slot + 1 == XR) ? 0 : slot + 1;
+      float lm = neg_inf();
+#pragma unroll
+      for (int q = 0; q < NSP; ++q) {
+        const int s = tid + q * NS;
+        float v[DEG];
+#pragma unroll
+        for (int k = 0; k < DEG; ++k) {
+          v[k] = fmaf(lds_f(xa + lo4[q][k]), kLog2e, lds_f(bc + do4[q][k]) - mxb);
+          if (!UNIT) v[k] += wo[q][k];
+        }
+        const float res = lse4(v);
+        if (s < n) sts_f(bn + s * 4, res);
+        lm = fmaxf(lm, res);
+      }
+      const int wm = warp_floor_max(lm);
+      if (lane == 0) atomicMax(&wmax[r], wm);
+      const unsigned tmp = bc;
+      bc = bn;
+      bn = tmp;
+    }
+    bar_all();
+  } else if (warp < W_LAB) {
     // ---- state warps: beta_t[s] = LSE_{arcs out of s}(w + x[label] + beta_{t+1}[dst]) ----
     bar_all();
     int r = 0;
@@ -349,6 +479,77 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
       float* tmp = b_cur;
       b_cur = b_nxt;
       b_nxt = tmp;
+    }
+    bar_all();
+  } else if (SPT > 0 && warp < W_HV) {
+    // ---- label warps, the (at most LARC) arcs of the thread's labels in registers; an absent arc
+    // ends in the -inf slot of the beta buffer.  Labels with more arcs take the loop. ----
+    constexpr int NSP = SPT > 0 ? SPT : 1;
+    const int j0 = tid - NS;
+    unsigned sa[NSP][LARC], da[NSP][LARC];
+    float wl[NSP][LARC];
+    int kind[NSP];  // 0: nothing to do (no such label / heavy), 1: registers, 2: loop
+#pragma unroll
+    for (int q = 0; q < NSP; ++q) {
+      const int j = j0 + q * NLB;
+      kind[q] = 0;
+#pragma unroll
+      for (int k = 0; k < LARC; ++k) {
+        sa[q][k] = 0u;
+        da[q][k] = (unsigned)maxN * 4u;
+        wl[q][k] = 0.f;
+      }
+      if (j < nl && hx[j] < 0) {
+        const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
+        kind[q] = (e1 - e0 <= LARC) ? 1 : 2;
+        if (kind[q] == 1) {
+#pragma unroll
+          for (int k = 0; k < LARC; ++k) {
+            if (e0 + k < e1) {
+              const unsigned pk = lab_pk[e0 + k];
+              sa[q][k] = (pk & 0xffffu) * 4u;
+              da[q][k] = (pk >> 16) * 4u;
+              if (!UNIT) wl[q][k] = lab_w[e0 + k];
+            }
+          }
+        }
+      }
+    }
+    unsigned bc = sm_u32(b_cur), bn = sm_u32(b_nxt);
+    const unsigned xr0 = sm_u32(xring), ar0 = sm_u32(aring), kt_a = sm_u32(kt), gr_a = sm_u32(gr);
+    bar_all();
+    int slot = 0;
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      const float Kt = lds_f(kt_a + (i & 1) * 4);
+      const unsigned xa = xr0 + slot * nlp * 4, ata = ar0 + slot * arow * 4;
+      slot = (slot + 1 == XR) ? 0 : slot + 1;
+      const unsigned grw = gr_a + (i & 1) * maxL * 4;
+#pragma unroll
+      for (int q = 0; q < NSP; ++q) {
+        const int j = j0 + q * NLB;
+        if (j < nl) {
+          float acc = 0.f;
+          if (kind[q] == 1) {
+            const float kx = fmaf(lds_f(xa + j * 4), kLog2e, Kt);
+#pragma unroll
+            for (int k = 0; k < LARC; ++k)
+              acc += post_term(lds_f(ata + sa[q][k]), lds_f(bc + da[q][k]), UNIT ? kx : kx + wl[q][k]);
+          } else if (kind[q] == 2) {
+            const float* at = aring + (i % XR) * arow;
+            const float* bcur = (i & 1) ? b_nxt : b_cur;
+            const float kx = fmaf(lds_f(xa + j * 4), kLog2e, Kt);
+            for (int e = lab_ptr[j]; e < lab_ptr[j + 1]; ++e) {
+              const unsigned pk = lab_pk[e];
+              acc += post_term(at[pk & 0xffffu], bcur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+            }
+          }
+          sts_f(grw + j * 4, acc);  // zero for a heavy label: the row warp fills it in
+        }
+      }
+      const unsigned tmp = bc;
+      bc = bn;
+      bn = tmp;
     }
     bar_all();
   } else if (warp < W_HV) {
@@ -497,22 +698,26 @@ bool num_lin_supported(const PathArgs& a) {
   return P.bytes <= 200 * 1024;
 }
 
+template <bool UNIT, int SPT>
+static cudaError_t launch_one(const PathArgs& a, int bytes, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(num_log_kernel<UNIT, SPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  num_log_kernel<UNIT, SPT><<<a.B, NTH, bytes, st>>>(a, a.g.max_states, a.g.max_arcs, a.g.max_labels);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_num_lin(const PathArgs& a, cudaStream_t st) {
   const bool unit = a.g.unit_weights != 0;
   const NumPlan P = num_plan(a.g.max_states, a.g.max_arcs, a.g.max_labels, (int)a.x_stride_t, a.alpha_row, unit);
   ProfScope prof("num_log", st);
+  // states / labels per thread: register-resident arcs up to 2 per thread, generic loops beyond
+  const int spt = std::max((a.g.max_states + NS - 1) / NS, (a.g.max_labels + NLB - 1) / NLB);
   cudaError_t e;
-  if (unit) {
-    e = cudaFuncSetAttribute(num_log_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P.bytes);
-    if (e != cudaSuccess) return e;
-    num_log_kernel<true><<<a.B, NTH, P.bytes, st>>>(a, a.g.max_states, a.g.max_arcs, a.g.max_labels);
-  } else {
-    e = cudaFuncSetAttribute(num_log_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P.bytes);
-    if (e != cudaSuccess) return e;
-    num_log_kernel<false><<<a.B, NTH, P.bytes, st>>>(a, a.g.max_states, a.g.max_arcs, a.g.max_labels);
-  }
+  if (spt <= 1) e = unit ? launch_one<true, 1>(a, P.bytes, st) : launch_one<false, 1>(a, P.bytes, st);
+  else if (spt == 2) e = unit ? launch_one<true, 2>(a, P.bytes, st) : launch_one<false, 2>(a, P.bytes, st);
+  else e = unit ? launch_one<true, 0>(a, P.bytes, st) : launch_one<false, 0>(a, P.bytes, st);
   ++g_launches;
-  return cudaGetLastError();
+  return e;
 }
 
 }  // namespace ctcg
