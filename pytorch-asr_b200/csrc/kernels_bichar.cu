@@ -596,11 +596,11 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
         }
       } else {
         cs = make_float2(0.f, 0.f);
-        const float2 c1 = splat2(c12.x), c2 = splat2(c12.y);
+        const float2 c2 = splat2(c12.y);  // c1 is already in the alpha row (auxiliary warps)
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
           f2[k] = fmul2(e2[k], b2[k]);
-          al[k] = fmul2(fmul2(al[k], c1), fmul2(b2[k], c2));
+          al[k] = fmul2(al[k], fmul2(b2[k], c2));
           cs = fadd2(cs, f2[k]);
         }
 #pragma unroll
@@ -687,6 +687,10 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
 
   const int n0 = lane, n1 = lane + 32;
   const bool nv0 = n0 < S, nv1 = n1 < S;
+  // posterior constant c1 = gscale / mass * 2^E1 (the scale warp's formula): folded into the alpha
+  // rows here so that the main warps spend one multiply less per element
+  const float inv_mass_ = c.sc->inv_mass;
+  const float2 c1v = splat2(inv_mass_ * pow2i(max(-120, min(120, -TARGET - exponent_of(inv_mass_)))) * c.gsc);
   float2 ra[RU], rnx[RU];
 #pragma unroll
   for (int u = 0; u < RU; ++u) ra[u] = rnx[u] = make_float2(0.f, 0.f);
@@ -776,13 +780,14 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
 #pragma unroll
       for (int u = 0; u < RU; ++u) {
         if (row_ok(u)) {
+          const float2 as = fmul2(ra[u], c1v);
           if (WIDE || nv0) {
             sts(er + o0 + NAUX * u * S * 4, x2[u].x);
-            sts(ar + o0 + NAUX * u * S * 4, ra[u].x);
+            sts(ar + o0 + NAUX * u * S * 4, as.x);
           }
           if (nv1) {
             sts(er + o1 + NAUX * u * S * 4, x2[u].y);
-            sts(ar + o1 + NAUX * u * S * 4, ra[u].y);
+            sts(ar + o1 + NAUX * u * S * 4, as.y);
           }
         }
       }

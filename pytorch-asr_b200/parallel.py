@@ -56,16 +56,32 @@ def _group_active():
     return dist.is_initialized() and dist.get_world_size() > 1
 
 
-def reduce_loss(loss_per_utt, n_frames):
+_side_streams = {}
+
+
+def reduce_loss(loss_per_utt, n_frames, blocking=True):
     """All-reduce ``[sum_b loss_b, frames]`` over ranks; returns the 2-element fp64
     tensor (on the loss's device).  Stream-ordered after the loss kernels; the
     gradient tensors are untouched, so backprop on each rank can proceed without
-    waiting for it."""
+    waiting for it.  ``blocking=False`` (CUDA only) runs the collective on a side
+    stream: the caller's stream is not held up by the NCCL launch latency, and the
+    result must be read after a device (or ``torch.cuda.current_stream().wait_stream``)
+    synchronisation."""
     buf = torch.zeros(2, dtype=torch.float64, device=loss_per_utt.device)
     buf[0] = loss_per_utt.double().sum()
     buf[1] = float(n_frames)
     if _group_active():
-        dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+        if not blocking and buf.is_cuda:
+            dev = buf.device
+            side = _side_streams.get(dev.index)
+            if side is None:
+                side = _side_streams[dev.index] = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+            buf.record_stream(side)
+        else:
+            dist.all_reduce(buf, op=dist.ReduceOp.SUM)
     return buf
 
 
