@@ -26,6 +26,7 @@ struct PathArgs {
   float g_sign;
   const float* g_scale;   // nullable, per-utterance multiplier
   int32_t write_grad;
+  int32_t dbg;            // timing experiments only (CTCG_NUM_DEBUG bit mask: roles skip their work); 0 in production
 };
 
 // compact = 1: x / gout are the per-utterance compact label columns produced by
@@ -85,6 +86,7 @@ struct BicharArgs {
   int32_t K, DB, NR, rowf, nmain;
   long long* trace;        // diagnostics only (CTCG_BICHAR_TRACE): [warps][trace_steps][2] clocks of CTA 0
   int32_t trace_steps;
+  int32_t dbg;             // timing experiments only (CTCG_BICHAR_DEBUG bit mask: roles skip their work)
 };
 // Workspace floats needed per batch (pspill + ckpt); smem plan and launch.
 struct BicharPlan {

@@ -428,7 +428,7 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
     cta_sync();
     for (int g = 0; g <= len + 1; ++g) {
       const int t = g - 1;
-      if (t >= 0 && t < len) {
+      if (t >= 0 && t < len && !(c.A.dbg & 4)) {
         const unsigned base = rows_a + rowoff + r4;
         r4 = (r4 + d4) & 12u;
         rowoff += rowb;
@@ -535,7 +535,7 @@ __device__ __forceinline__ void main_role(const Ctx& c) {
                  csm_a = smem_u32(c.csm);
   for (int g = 0; g < GEND; ++g) {
     const int i = g - c.LEAD;
-    if (i >= 0 && i < len) {
+    if (i >= 0 && i < len && !(c.A.dbg & 2)) {
       const int slot = cur.q & (QRING - 1);
       cur.prev();
       int te, ta, hk;
@@ -638,7 +638,7 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
     const int p = aw * 32 + lane;
     int rowA = 0, parA = 0;  // ring row / mbarrier parity of the frame
     for (int g = 0; g <= len + 1; ++g) {
-      if (g < len) {
+      if (g < len && !(c.A.dbg & 8)) {
         mbar_wait(&c.mbar[rowA], parA);
         const int r = row_r(c, g);
         const unsigned rp = rows_a + rowA * rowb;
@@ -726,7 +726,7 @@ __device__ __forceinline__ void aux_role(const Ctx& c) {
   const int GEND = len + c.LEAD + 2;
   for (int g = 0; g < GEND; ++g) {
     const int q = g - c.DBk;
-    if (q >= 0 && q < len) {
+    if (q >= 0 && q < len && !(c.A.dbg & 1)) {
       const int tau = pc.tau;
       const bool seg0 = pc.u == 0;
       pc.next();
@@ -809,7 +809,7 @@ __device__ __forceinline__ void scale_role(const Ctx& c) {
   const bool cv0 = lane < S, cv1 = lane + 32 < S;  // partial columns >= S hold unused (possibly non-finite) values
   for (int g = 0; g <= len + 1; ++g) {
     const int t = g - 1;
-    if (t >= 0 && t <= len) {
+    if (t >= 0 && t <= len && !((c.A.dbg & 32) && t < len)) {
       const float* pb = c.part + (t & 1) * partrows * PARTW;
       float s = 0.f;
 #pragma unroll 7
@@ -937,7 +937,7 @@ __device__ __forceinline__ void io_role(const Ctx& c) {
     // 1. the logits row consumed by main step i-1 is free again
     if (lane == 0 && e1 >= 0) push_row(e1);
     // 2. store the gradient row main step i-1 finished
-    if (a1 >= 0) {
+    if (a1 >= 0 && !(c.A.dbg & 16)) {
       const RowGeo ge = row_geo(t1, c.b, c.B, V, c.A.total);
       const float* src = c.rows + a1 * rowf;
       float* dst = c.A.grad + ge.w0;
@@ -1085,6 +1085,13 @@ cudaError_t launch_bichar_den(const BicharArgs& a_in, const BicharPlan& p, cudaS
   const int warps = p.threads / 32;
   a.trace = nullptr;
   a.trace_steps = 0;
+  {
+    static const int dbg = [] {
+      const char* e = getenv("CTCG_BICHAR_DEBUG");
+      return e ? atoi(e) : 0;
+    }();
+    a.dbg = dbg;
+  }
   if (trace_path && trace_path[0]) {
     a.trace_steps = 2 * a.T + 64;
     const size_t bytes = (size_t)warps * a.trace_steps * TRS * sizeof(long long);

@@ -30,6 +30,7 @@
 // gather_kernel; output: cost[b] (natural log) and the compact posterior rows
 // gout[b][t][j], which the row / scatter kernels fold into the dense gradient.
 #include <algorithm>
+#include <cstdlib>
 
 #include "device_utils.cuh"
 #include "kernels.cuh"
@@ -334,7 +335,7 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
       int r = 0;
       for (int t = 0; t < len; ++t) {
         bar_fwd();
-        issue_x(t + XR - 1, (t + XR - 1) % XR);
+        if (!(a.dbg & 64)) issue_x(t + XR - 1, (t + XR - 1) % XR);
         c += (double)norm_of(wmax[r]);
         r = next3(r);
         if (lane == 0) {
@@ -344,7 +345,7 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
           ar[arow - 1] = (float)(c - (double)hi);
           wmax[next3(r)] = IMIN;  // the slot the state warps fill during the next frame
         }
-        cp_async_wait<XR - 2>();
+        if (!(a.dbg & 64)) cp_async_wait<XR - 2>();
       }
       cp_async_wait<0>();
     }
@@ -423,6 +424,7 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
       const unsigned xa = xr0 + slot * nlp * 4;
       slot = (slot + 1 == XR) ? 0 : slot + 1;
       float lm = neg_inf();
+      if (a.dbg & 8) continue;
 #pragma unroll
       for (int q = 0; q < NSP; ++q) {
         const int s = tid + q * NS;
@@ -525,6 +527,7 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
       const unsigned xa = xr0 + slot * nlp * 4, ata = ar0 + slot * arow * 4;
       slot = (slot + 1 == XR) ? 0 : slot + 1;
       const unsigned grw = gr_a + (i & 1) * maxL * 4;
+      if (a.dbg & 2) continue;
 #pragma unroll
       for (int q = 0; q < NSP; ++q) {
         const int j = j0 + q * NLB;
@@ -578,6 +581,76 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
       float* tmp = b_cur;
       b_cur = b_nxt;
       b_nxt = tmp;
+    }
+    bar_all();
+  } else if (SPT > 0 && warp < W_IO) {
+    // ---- heavy warps, the thread's (at most HARC) arcs of the first heavy label -- the blank --
+    // in registers; further heavy labels, or a longer one, take the loop ----
+    constexpr int HARC = 4;
+    const int k0 = tid - NS - NLB;
+    unsigned sa[HARC], da[HARC];
+    float wl[HARC];
+    int hj = 0;
+    bool fast = false;
+#pragma unroll
+    for (int q = 0; q < HARC; ++q) {
+      sa[q] = 0u;
+      da[q] = (unsigned)maxN * 4u;
+      wl[q] = 0.f;
+    }
+    if (nh > 0) {
+      hj = hl[0];
+      const int e0 = lab_ptr[hj], e1 = lab_ptr[hj + 1];
+      fast = (e1 - e0) <= HARC * NHV;
+      if (fast) {
+#pragma unroll
+        for (int q = 0; q < HARC; ++q) {
+          const int e = e0 + k0 + q * NHV;
+          if (e < e1) {
+            const unsigned pk = lab_pk[e];
+            sa[q] = (pk & 0xffffu) * 4u;
+            da[q] = (pk >> 16) * 4u;
+            if (!UNIT) wl[q] = lab_w[e];
+          }
+        }
+      }
+    }
+    unsigned bc = sm_u32(b_cur), bn = sm_u32(b_nxt);
+    const unsigned xr0 = sm_u32(xring), ar0 = sm_u32(aring), kt_a = sm_u32(kt), hp_a = sm_u32(hp);
+    bar_all();
+    int slot = 0;
+    for (int i = 0; i < len; ++i) {
+      bar_all();
+      const float Kt = lds_f(kt_a + (i & 1) * 4);
+      const unsigned xa = xr0 + slot * nlp * 4, ata = ar0 + slot * arow * 4;
+      const float* xrow = xring + slot * nlp;
+      const float* at = aring + slot * arow;
+      const float* bcur = (i & 1) ? b_nxt : b_cur;
+      slot = (slot + 1 == XR) ? 0 : slot + 1;
+      const unsigned hpw = hp_a + (i & 1) * NHMAX * NHV * 4;
+      if (a.dbg & 4) continue;
+      if (fast) {
+        const float kx = fmaf(lds_f(xa + hj * 4), kLog2e, Kt);
+        float acc = 0.f;
+#pragma unroll
+        for (int q = 0; q < HARC; ++q)
+          acc += post_term(lds_f(ata + sa[q]), lds_f(bc + da[q]), UNIT ? kx : kx + wl[q]);
+        sts_f(hpw + k0 * 4, acc);
+      }
+      for (int h = fast ? 1 : 0; h < nh; ++h) {
+        const int j = hl[h];
+        const int e0 = lab_ptr[j], e1 = lab_ptr[j + 1];
+        const float kx = fmaf(xrow[j], kLog2e, Kt);
+        float acc = 0.f;
+        for (int e = e0 + k0; e < e1; e += NHV) {
+          const unsigned pk = lab_pk[e];
+          acc += post_term(at[pk & 0xffffu], bcur[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+        }
+        sts_f(hpw + (h * NHV + k0) * 4, acc);
+      }
+      const unsigned tmp = bc;
+      bc = bn;
+      bn = tmp;
     }
     bar_all();
   } else if (warp < W_IO) {
@@ -636,13 +709,13 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
     int r = 0;
     for (int i = 0; i < len; ++i) {
       bar_all();
-      issue_b(i + XR - 1, (i + XR - 1) % XR);
+      if (!(a.dbg & 32)) issue_b(i + XR - 1, (i + XR - 1) % XR);
       d += (double)norm_of(wmax[r]);
       r = next3(r);
       if (lane == 0) wmax[next3(r)] = IMIN;
-      cp_async_wait<XR - 2>();
+      if (!(a.dbg & 32)) cp_async_wait<XR - 2>();
       __syncwarp();
-      publish_kt(i + 1, d);
+      if (!(a.dbg & 16)) publish_kt(i + 1, d);
     }
     cp_async_wait<0>();
     bar_all();
@@ -681,7 +754,7 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
     bar_all();
     for (int i = 0; i < len; ++i) {
       bar_all();
-      if (i > 0) finish(i - 1);
+      if (i > 0 && !(a.dbg & 1)) finish(i - 1);
     }
     bar_all();
     if (len > 0) finish(len - 1);
@@ -706,7 +779,13 @@ static cudaError_t launch_one(const PathArgs& a, int bytes, cudaStream_t st) {
   return cudaGetLastError();
 }
 
-cudaError_t launch_num_lin(const PathArgs& a, cudaStream_t st) {
+cudaError_t launch_num_lin(const PathArgs& a_in, cudaStream_t st) {
+  PathArgs a = a_in;
+  static const int dbg = [] {
+    const char* e = std::getenv("CTCG_NUM_DEBUG");
+    return e ? std::atoi(e) : 0;
+  }();
+  a.dbg = dbg;
   const bool unit = a.g.unit_weights != 0;
   const NumPlan P = num_plan(a.g.max_states, a.g.max_arcs, a.g.max_labels, (int)a.x_stride_t, a.alpha_row, unit);
   ProfScope prof("num_log", st);
