@@ -85,6 +85,36 @@ def reduce_loss(loss_per_utt, n_frames, blocking=True):
     return buf
 
 
+class LossMeter(object):
+    """Running ``[sum of losses, frames]`` of this rank, kept on the device; ``total()`` does the
+    one all-reduce when the trainer actually wants the number (a logging interval, an epoch).
+    Utterances are independent, so nothing has to be exchanged per step."""
+
+    def __init__(self, device, fold_every=256):
+        self.acc = torch.zeros((), dtype=torch.float64, device=device)
+        self.frames = 0
+        self.pending = []              # per-step (B,) loss tensors, summed lazily: no kernel per step
+        self.fold_every = fold_every
+
+    def add(self, loss_per_utt, n_frames):
+        self.pending.append(loss_per_utt.detach())
+        self.frames += int(n_frames)
+        if len(self.pending) >= self.fold_every:
+            self._fold()
+
+    def _fold(self):
+        if self.pending:
+            self.acc += torch.cat([p.reshape(-1) for p in self.pending]).sum(dtype=torch.float64)
+            self.pending = []
+
+    def total(self):
+        self._fold()
+        buf = torch.stack([self.acc, torch.tensor(float(self.frames), dtype=torch.float64, device=self.acc.device)])
+        if _group_active():
+            dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+        return buf
+
+
 def barrier():
     if _group_active():
         dist.barrier()

@@ -59,6 +59,11 @@ def _worker(rank, world, port, out):
     assert lens_s == sorted(lens_s, reverse=True)             # a shard stays sorted
     loss = _oracle_loss(S, logits[:, idx], lens_s, seqs_s)
     tot = parallel.reduce_loss(loss, sum(lens_s))
+    meter = parallel.LossMeter(torch.device("cpu"))       # running scalar, one all-reduce on demand
+    meter.add(loss, sum(lens_s))
+    meter.add(loss, sum(lens_s))
+    mtot = meter.total()
+    assert abs(float(mtot[0]) - 2 * float(tot[0])) < 1e-9 * abs(float(tot[0])) and float(mtot[1]) == 2 * float(tot[1])
     mx = parallel.max_over_ranks(float(rank + 1))
     sm = parallel.sum_over_ranks(len(idx))
     parallel.barrier()
