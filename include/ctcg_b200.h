@@ -196,6 +196,25 @@ int ctcg_loss_host(const float* logits_host, int32_t T, int32_t B, int32_t V,
                    int32_t normalize, int32_t num_symbols, float* loss_host,
                    float* grad_host);
 
+/* ---- logits post-processing of ctc_forward.py ------------------------------ */
+
+#define CTCG_POST_TRANSFER_HASH 1   /* --transfer-hash-prob   (ctc_forward.py:96-103) */
+#define CTCG_POST_IMITATE_BIPHONES 2 /* --imitate-biphones     (:107-115)  V -> V*V columns */
+#define CTCG_POST_BLOCK_NORMALIZE 4 /* --block-normalize      (:116-120)  V = S*S */
+#define CTCG_POST_BLOCK_MARGINALIZE 8 /* --block-marginalize  (:121-128)  V = S*S -> S columns */
+
+/* Number of output columns for `flags` (V*V, V or sqrt(V)); 0 if V is not a square where one
+ * is needed. */
+int ctcg_logits_post_width(int32_t V, int32_t flags);
+
+/* The array transformations ctc_forward.py applies to the model's (T, B, V) log-probabilities
+ * before writing them out (ctc_forward.py:96-128), with the reference's precedence of the
+ * flags (imitate_biphones, else block_normalize, else block_marginalize) and its EPSILON =
+ * 1e-30; fp32 like the numpy code.  log_probs and out are device pointers, out holds
+ * T*B*ctcg_logits_post_width(V, flags) floats and must not alias log_probs. */
+int ctcg_logits_post(const float* log_probs, int32_t T, int32_t B, int32_t V, int32_t flags,
+                     float* out, void* stream);
+
 const char* ctcg_strerror(int status);
 
 /* Number of kernel launches issued by this library since load (bench.py's

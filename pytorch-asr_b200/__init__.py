@@ -8,12 +8,14 @@ this package).  Layout:
 * ``_lib.py``        ctypes binding of ``libctcg_b200.so`` (``include/ctcg_b200.h``)
 * ``fst_utils.py``   mirror of ``att_speech/fst_utils.py`` (path_reduction, CTCGraphGen)
 * ``ctc_losses.py``  mirror of the FST losses + ``FSTDecoder`` loss glue
+* ``ctc_forward.py`` mirror of the logits post-processing of the reference's ctc_forward.py
 * ``parallel.py``    utterance-sharded multi-GPU driver (one process per GPU)
 """
 from . import _lib  # noqa: F401
 from ._lib import Graph, NORM_CONTEXT, NORM_NONE, NORM_SOFTMAX  # noqa: F401
 from .fst_utils import (CTCGraphGen, PackedGraphs, batch_training_graph_matrices,  # noqa: F401
                         make_full_ngram_table, padded_matrices, path_logsumexp, path_reduction)
+from .ctc_forward import postprocess_logprobs  # noqa: F401
 from .ctc_losses import (FSTLoss, FSTLossMixin, ctc_fst_global_loss, ctc_fst_loss,  # noqa: F401
                          fst_loss, get_normalized_acts)
 
@@ -21,5 +23,5 @@ __all__ = [
     "Graph", "CTCGraphGen", "PackedGraphs", "path_reduction", "path_logsumexp",
     "batch_training_graph_matrices", "padded_matrices", "make_full_ngram_table",
     "fst_loss", "ctc_fst_loss", "ctc_fst_global_loss", "get_normalized_acts",
-    "FSTLoss", "FSTLossMixin", "NORM_NONE", "NORM_SOFTMAX", "NORM_CONTEXT",
+    "FSTLoss", "FSTLossMixin", "NORM_NONE", "NORM_SOFTMAX", "NORM_CONTEXT", "postprocess_logprobs",
 ]

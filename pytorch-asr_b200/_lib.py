@@ -24,7 +24,7 @@ EXPORTS = (
     "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
     "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi",
     "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
-    "ctcg_profile_enable", "ctcg_profile_collect",
+    "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
 
 
@@ -75,6 +75,9 @@ def lib():
     L.ctcg_viterbi.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp, C.c_size_t, vp]
     L.ctcg_path_count.argtypes = [i32, vp, vp, vp, vp, C.c_size_t, vp]
     L.ctcg_loss_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp]
+    L.ctcg_logits_post_width.argtypes = [i32, i32]
+    L.ctcg_logits_post_width.restype = i32
+    L.ctcg_logits_post.argtypes = [f32p, i32, i32, i32, i32, vp, vp]
     L.ctcg_strerror.argtypes = [C.c_int]
     L.ctcg_strerror.restype = C.c_char_p
     L.ctcg_launch_count.argtypes = []
@@ -353,6 +356,22 @@ def path_count(act_lens, graph, device=None):
         check(lib().ctcg_path_count(B, _np_ptr(lens), graph.ptr, counts.data_ptr(),
                                     ws.data_ptr(), ws.numel(), _stream_ptr(dev)))
     return counts.cpu().numpy().view(np.uint64)
+
+
+POST_TRANSFER_HASH, POST_IMITATE_BIPHONES, POST_BLOCK_NORMALIZE, POST_BLOCK_MARGINALIZE = 1, 2, 4, 8
+
+
+def logits_post(log_probs, flags):
+    """``ctcg_logits_post``: the array transformations of ctc_forward.py:96-128 on the device."""
+    x = _prep_logits(log_probs)
+    T, B, V = x.shape
+    W = lib().ctcg_logits_post_width(V, int(flags))
+    if W < 1:
+        raise ValueError("ctcg: %d classes are not a square number of symbols" % V)
+    out = torch.empty((T, B, W), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib().ctcg_logits_post(x.data_ptr(), T, B, V, int(flags), out.data_ptr(), _stream_ptr(x.device)))
+    return out
 
 
 def loss_host(logits_host, act_lens, num, den=None, normalize=NORM_NONE, num_symbols=0,

@@ -452,6 +452,41 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   return CTCG_OK;
 }
 
+int ctcg_logits_post_width(int32_t V, int32_t flags) {
+  if (V < 1) return 0;
+  if (flags & CTCG_POST_IMITATE_BIPHONES) return (V <= 46340) ? V * V : 0;
+  if (flags & (CTCG_POST_BLOCK_NORMALIZE | CTCG_POST_BLOCK_MARGINALIZE)) {
+    int32_t S = 1;
+    while ((long long)S * S < V) ++S;
+    if (S * S != V) return 0;
+    return (flags & CTCG_POST_BLOCK_NORMALIZE) ? V : S;
+  }
+  return V;
+}
+
+int ctcg_logits_post(const float* log_probs, int32_t T, int32_t B, int32_t V, int32_t flags, float* out,
+                     void* stream) {
+  if (!log_probs || !out || T < 1 || B < 1 || V < 1 || log_probs == out) return CTCG_EINVAL;
+  const int32_t W = ctcg_logits_post_width(V, flags);
+  if (W < 1) return CTCG_EINVAL;
+  const bool transfer = (flags & CTCG_POST_TRANSFER_HASH) != 0;
+  if (transfer && V < 4) return CTCG_EINVAL;
+  int mode = 0, S = 0, tile_norm = 0;
+  if (flags & CTCG_POST_IMITATE_BIPHONES) {
+    mode = 1;
+    tile_norm = (flags & CTCG_POST_BLOCK_NORMALIZE) ? 0 : 1;
+  } else if (flags & CTCG_POST_BLOCK_NORMALIZE) {
+    mode = 2;
+    S = ctcg_logits_post_width(V, CTCG_POST_BLOCK_MARGINALIZE);
+  } else if (flags & CTCG_POST_BLOCK_MARGINALIZE) {
+    mode = 3;
+    S = W;
+  }
+  CTCG_CUDA(launch_post(log_probs, (long long)T * B, V, S, mode, transfer ? 1 : 0, tile_norm, out,
+                        static_cast<cudaStream_t>(stream)));
+  return CTCG_OK;
+}
+
 int ctcg_path_sum(const float* log_probs, int32_t T, int32_t B, int32_t V, const int32_t* lens_host,
                   const ctcg_graph* graph, float* cost, float* grad, void* workspace,
                   size_t workspace_bytes, void* stream) {

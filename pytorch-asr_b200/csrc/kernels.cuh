@@ -52,6 +52,8 @@ cudaError_t launch_rows(const float* logits, int T, int B, int V, const int32_t*
 // grad[t][b][lab_list_b[j]] -= scale_b * gg[b][t][j]
 cudaError_t launch_rows_ctx(const float* logits, int T, int B, int V, int S, const int32_t* lens, const GraphDev& num,
                             const float* gg, int nlp, const float* g_scale, float* grad, cudaStream_t st);
+cudaError_t launch_post(const float* in, long long rows, int V, int S, int mode, int transfer, int tile_normalize,
+                        float* out, cudaStream_t st);
 cudaError_t launch_scatter_sub(int T, int B, int V, const int32_t* lens, const GraphDev& num,
                                const float* gg, int nlp, const float* g_scale, float* grad,
                                cudaStream_t st);

@@ -306,3 +306,27 @@ def test_decoder_module_and_grad_scale(P):
     _, g = P._lib.loss_fwd_bwd(x.detach(), lens, gen.get_training_graphs(seqs), gen.get_decoding_graph(),
                                P.NORM_NONE, grad_scale=w)
     assert np.abs(g.cpu().double().numpy() - wg.numpy() * w.numpy()[None, :, None]).max() < 2 * GRAD_ATOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("flags", [
+    {}, {"transfer_hash_prob": True}, {"block_normalize": True}, {"block_marginalize": True},
+    {"transfer_hash_prob": True, "block_normalize": True}, {"transfer_hash_prob": True, "block_marginalize": True},
+    {"imitate_biphones": True}, {"imitate_biphones": True, "block_normalize": True},
+    {"imitate_biphones": True, "transfer_hash_prob": True},
+])
+def test_ctc_forward_postprocessing(P, flags):
+    """postprocess_logprobs against the numpy statements of ctc_forward.py:96-128 (fp64 oracle; the
+    reference itself computes in float32, tolerance 1e-5 absolute on log-probabilities)."""
+    from oracle import postprocess as pp
+    rng = np.random.default_rng(17)
+    mono = flags.get("imitate_biphones", False)
+    S, T, B = (49, 37, 3)
+    V = S if mono else S * S
+    lp = torch.log_softmax(torch.from_numpy(rng.standard_normal((T, B, V)).astype(np.float32) * 3), -1)
+    got = P.postprocess_logprobs(lp.cuda(), **flags).cpu().double().numpy()
+    want = pp.postprocess(lp.numpy(), **flags)
+    assert got.shape == want.shape
+    assert np.abs(got - want).max() < 1e-5
+    ref32 = pp.postprocess(lp.numpy(), dtype=np.float32, **flags)        # what the reference would write
+    assert np.abs(got - ref32).max() < 2e-5

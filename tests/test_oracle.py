@@ -111,3 +111,27 @@ def test_oracle_equals_reference_live():
     c.sum().backward()
     c2, g2, _ = engine.path_logsumexp(lp, lens, mm)
     assert torch.equal(c.detach(), c2) and torch.equal(lp.grad, g2)
+
+
+def test_postprocess_oracle_properties():
+    """oracle/postprocess.py (ctc_forward.py:96-128): normalisations sum to one, the '#' mass
+    moves to the blank, marginals average the contexts; float32 (the reference's dtype) agrees
+    with float64."""
+    from oracle import postprocess as pp
+    rng = np.random.default_rng(3)
+    S = 5
+    lp = np.log(rng.dirichlet(np.ones(S * S), size=(6, 2))).astype(np.float32)
+    o = pp.postprocess(lp, block_normalize=True)
+    assert np.allclose(np.exp(o).reshape(6, 2, S, S).sum(-1), 1.0, atol=1e-12)
+    o = pp.postprocess(lp, block_marginalize=True)
+    assert o.shape == (6, 2, S) and np.allclose(np.exp(o).sum(-1), 1.0 / S, atol=1e-12)
+    mono = np.log(rng.dirichlet(np.ones(S), size=(6, 2)))
+    o = pp.postprocess(mono, imitate_biphones=True)
+    assert o.shape == (6, 2, S * S) and np.allclose(np.exp(o).sum(-1), 1.0, atol=1e-12)
+    assert np.allclose(pp.postprocess(mono, imitate_biphones=True, block_normalize=True), np.tile(mono, (1, 1, S)))
+    o = pp.postprocess(lp, transfer_hash_prob=True)
+    assert np.allclose(np.exp(o[:, :, 0]), np.exp(lp[:, :, 0].astype(np.float64)) + np.exp(lp[:, :, 3].astype(np.float64)),
+                       rtol=1e-6)
+    assert np.allclose(o[:, :, 3], np.log(1e-30))
+    for kw in ({"block_normalize": True}, {"block_marginalize": True}, {"transfer_hash_prob": True, "block_normalize": True}):
+        assert np.abs(pp.postprocess(lp, dtype=np.float32, **kw) - pp.postprocess(lp, **kw)).max() < 1e-5
