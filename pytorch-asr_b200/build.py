@@ -18,7 +18,7 @@ LIB = os.path.join(HERE, "libctcg_b200.so")
 STAMP = os.path.join(HERE, "build", "sources.sha256")
 
 SOURCES = ["graph.cpp", "graph_abi.cpp", "abi.cu", "kernels_path.cu", "kernels_rows.cu",
-           "kernels_aux.cu", "kernels_bichar.cu", "kernels_num.cu", "kernels_post.cu"]
+           "kernels_aux.cu", "kernels_bichar.cu", "kernels_bisweep.cu", "kernels_num.cu", "kernels_post.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

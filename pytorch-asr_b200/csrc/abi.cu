@@ -33,11 +33,21 @@ struct Plan {
   int arow_den = 0;
   size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
   size_t pspill = 0, ckpt = 0;
-  BicharPlan bi{};   // bi.ok: the denominator runs on the fused bi-char kernel
+  size_t spill2 = 0, ckpt2 = 0, fin = 0;
+  BicharPlan bi{};   // bi.ok: the denominator runs on the factorised bi-char kernels
+  BisweepPlan sw{};  // split-sweep kernels (default); bi describes the single-CTA kernel (CTCG_BICHAR_LEGACY=1)
   size_t total = 0;
 };
 
-// The factorised kernel covers the bi-char decoding graph of ctcg_decoding_graph (shared by the batch).
+bool legacy_bichar() {
+  static const bool on = [] {
+    const char* e = std::getenv("CTCG_BICHAR_LEGACY");
+    return e && e[0] == '1';
+  }();
+  return on;
+}
+
+// The factorised kernels cover the bi-char decoding graph of ctcg_decoding_graph (shared by the batch).
 BicharPlan structured_plan(int T, int B, int V, const ctcg_graph* den) {
   BicharPlan none{};
   if (!den || den->structured.kind != 2 || den->num_graphs != 1) return none;
@@ -67,9 +77,14 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
   if (den) {
     p.bi = structured_plan(T, B, V, den);
     p.cost_den = take((size_t)B * 8);
+    if (p.bi.ok) p.sw = bisweep_plan(T, B, V, den->structured.S);
+    if (p.bi.ok && !p.sw.ok) p.bi.ok = 0;
     if (p.bi.ok) {
-      p.pspill = take(p.bi.pspill_bytes);
-      p.ckpt = take(p.bi.ckpt_bytes);
+      p.pspill = take(std::max(p.bi.pspill_bytes, p.sw.spill_bytes));
+      p.ckpt = take(std::max(p.bi.ckpt_bytes, p.sw.ckpt_bytes));
+      p.spill2 = take(p.sw.spill_bytes);
+      p.ckpt2 = take(p.sw.ckpt_bytes);
+      p.fin = take((size_t)B * sizeof(BiFin));
     } else {
       p.arow_den = pad4(den->max_states + 2);
       p.alpha_den = take(TB * p.arow_den * 4);
@@ -250,6 +265,34 @@ namespace {
 
 int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, int V, const int32_t* lens,
                const ctcg_graph* den, double* cost, float* grad, const float* grad_scale, cudaStream_t st) {
+  if (!legacy_bichar()) {
+    BisweepArgs s{};
+    s.x = x;
+    s.total = (long long)T * B * V;
+    s.T = T;
+    s.B = B;
+    s.V = V;
+    s.S = den->structured.S;
+    s.lens = lens;
+    s.loops = den->structured.allow_nonblank_selfloops;
+    s.ctx = den->structured.use_contextual_blanks;
+    s.spill[0] = reinterpret_cast<float*>(ws + p.pspill);
+    s.spill[1] = reinterpret_cast<float*>(ws + p.spill2);
+    s.ck[0] = reinterpret_cast<float*>(ws + p.ckpt);
+    s.ck[1] = reinterpret_cast<float*>(ws + p.ckpt2);
+    s.prowf = p.sw.prowf;
+    s.nck = p.sw.nck;
+    s.K = p.sw.K;
+    s.cost = cost;
+    s.fin = reinterpret_cast<BiFin*>(ws + p.fin);
+    s.grad = grad;
+    s.g_scale = grad_scale;
+    s.nmain = p.sw.nmain;
+    s.rowf = p.sw.rowf;
+    s.estride = p.sw.estride;
+    CTCG_CUDA(launch_bisweep(s, p.sw, st));
+    return CTCG_OK;
+  }
   BicharArgs a{};
   a.x = x;
   a.total = (long long)T * B * V;

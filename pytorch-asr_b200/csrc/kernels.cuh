@@ -98,6 +98,36 @@ struct BicharPlan {
 BicharPlan bichar_plan(int T, int B, int V, int S);
 cudaError_t launch_bichar_den(const BicharArgs& a, const BicharPlan& p, cudaStream_t st);
 
+// Split-sweep bi-char denominator (kernels_bisweep.cu): forward and backward recursions on
+// separate CTAs at the same time, then an elementwise combine over the whole GPU.
+struct BiFin {
+  float inv_mass;   // 1 / (scaled total mass); 0 when no path is accepted
+  int32_t kfinal;   // exponent of the scaled total mass
+  int32_t dead;     // no accepting path: cost -1e20, zero gradient
+  int32_t pad;
+};
+struct BisweepArgs {
+  const float* x;          // logits (T, B, V), raw
+  long long total;         // T*B*V
+  int32_t T, B, V, S;
+  const int32_t* lens;     // device [B]
+  int32_t loops, ctx;      // allow_nonblank_selfloops, use_contextual_blanks (after loop_using_symbol_repetitions)
+  float* spill[2];         // [B][T][prowf]: vector entering frame t (P_t / Q_{t+1}), frame max, k_t, exponent
+  float* ck[2];            // [B][nck][V]: per-state values every K frames (explicit self-loops only)
+  int32_t prowf, nck, K;
+  double* cost;            // [B] natural-log path sum over the decoding graph
+  BiFin* fin;              // [B]
+  float* grad;             // (T, B, V) nullable: receives g_scale[b] * gamma_den
+  const float* g_scale;    // nullable
+  int32_t nmain, rowf, estride;
+};
+struct BisweepPlan {
+  int32_t ok, K, nck, nmain, threads, rowf, prowf, estride;
+  size_t smem_bytes, spill_bytes, ckpt_bytes;
+};
+BisweepPlan bisweep_plan(int T, int B, int V, int S);
+cudaError_t launch_bisweep(const BisweepArgs& a, const BisweepPlan& p, cudaStream_t st);
+
 // Incremented by every launch_* above.
 extern unsigned long long g_launches;
 
