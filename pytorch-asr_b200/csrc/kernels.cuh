@@ -120,6 +120,7 @@ struct BisweepArgs {
   float* grad;             // (T, B, V) nullable: receives g_scale[b] * gamma_den
   const float* g_scale;    // nullable
   int32_t nmain, rowf, estride;
+  int32_t dbg;             // timing experiments only (CTCG_SWEEP_DEBUG bit mask); 0 in production
 };
 struct BisweepPlan {
   int32_t ok, K, nck, nmain, threads, rowf, prowf, estride;

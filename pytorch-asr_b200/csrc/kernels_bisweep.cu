@@ -155,7 +155,7 @@ struct SDims {
     S = SCT > 0 ? SCT : a.S;
     V = S * S;
     PF = S | 1;             // odd pitch: the 8 scalar e loads of a main thread are conflict-free
-    ZO = pad4(S * PF);      // a 16-byte chunk of zeros behind the e rows, then e0[64]
+    ZO = pad4(S * PF);      // a 16-byte chunk of zeros behind the e rows
   }
 };
 
@@ -228,7 +228,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     }
 #pragma unroll
     for (int h = 0; h < 4; ++h) m2[h] = make_float2(mk[2 * h], mk[2 * h + 1]);
-    const unsigned e0o = (unsigned)(ZO + 4 + ((ctx && gv) ? g : 0)) * 4u;
+    const unsigned e0o = (unsigned)((ctx && gv) ? g * PF : 0) * 4u;  // blank class of context g (class 0 when global)
     const unsigned rc0 = (unsigned)(4 * k8) * 4u, rc1 = (unsigned)(4 * (k8 + 8)) * 4u;
     float2 val[4];
 #pragma unroll
@@ -245,6 +245,8 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     }
     int es = 0, esn = 0;           // e stage of this frame
     unsigned epar = 0;             // parity of the stage the NEXT frame waits on
+    long long tw = 0, tb = 0, tt0 = clock64();
+    const bool tim = (A.dbg & 256) && b == 0 && tid == 0;
     for (int f = 0; f < len; ++f) {
       const int t = frame_t(f);
       // prefetch the next frame's e values (registers evn); its stage is ready several frames ahead
@@ -253,7 +255,9 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       unsigned eparn = epar;
       if (esn == NE) { esn = 0; eparn ^= 1; }
       if (f + 1 < len) {
+        long long c0 = tim ? clock64() : 0;
         mbar_wait(e_full(esn), eparn);
+        if (tim) tw += clock64() - c0;
         const unsigned eb = eb_a + esn * estride * 4;
 #pragma unroll
         for (int s = 0; s < 8; ++s) evn[s] = lds(eb + eo[s]);
@@ -275,6 +279,13 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         }
       }
       const unsigned rb = rb_a + (f & 1) * RBW * 4;
+      if (A.dbg & 1) {  // timing experiment: barriers and hand-shakes only
+        if (lane == 0) mbar_arrive(e_empty(es));
+        named_sync(1, NB);
+        es = esn;
+        epar = eparn;
+        continue;
+      }
       const float4 r0 = lds4(rb + rc0), r1 = lds4(rb + rc1);
       const int kk = ldsi(kf_a + (f & 3) * 4);
       val[0] = fmul2(make_float2(ev[0], ev[1]), ffma2(m2[0], val[0], make_float2(r0.x, r0.y)));
@@ -297,13 +308,18 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       Rown = Rn;
       if (k8 == 0 && gv) sts(rb_a + ((f + 1) & 1) * RBW * 4 + g * 4, Rn);
       if (lane == 0) mbar_arrive(e_empty(es));
-      named_sync(1, NB);
+      {
+        long long c0 = tim ? clock64() : 0;
+        named_sync(1, NB);
+        if (tim) tb += clock64() - c0;
+      }
 #pragma unroll
       for (int s = 0; s < 8; ++s) ev[s] = evn[s];
       e0 = e0n;
       es = esn;
       epar = eparn;
     }
+    if (tim) printf("sweep dir %d main: total %lld  wait_e_full %lld  barrier %lld  (len %d)\n", DIR, clock64() - tt0, tw, tb, len);
   } else if (warp == nmain) {
     // ============================ scale / spill warp ============================
     int kcur = 0, knext = 0, Kcum = TARGET;
@@ -315,6 +331,13 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     for (int f = 0; f < len; ++f) {
       const int t = frame_t(f);
       const unsigned rb = rb_a + (f & 1) * RBW * 4;
+      if (A.dbg & 8) {
+        mbar_wait(e_full(es), epar);
+        if (lane == 0) mbar_arrive(e_empty(es));
+        if (++es == NE) { es = 0; epar ^= 1; }
+        named_sync(1, NB);
+        continue;
+      }
       const float v0 = lds(rb + lane * 4), v1 = lds(rb + (lane + 32) * 4);
       float* sp = spill + (long long)t * prowf;
       if (lane < S) sp[lane] = v0;
@@ -364,36 +387,49 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     const int pw = warp - nmain - 1;
     constexpr int NQ = SCT > 0 ? (SCT * SCT + 31) / 32 : 1;
     const int B3 = B & 3, b3 = b & 3, V3 = V & 3;
+    long long pw1 = 0, pw2 = 0, pw3 = 0, pt0 = clock64();
+    const bool ptim = (A.dbg & 256) && b == 0 && pw == 0 && lane == 0;
     for (int f = pw; f < len; f += NPROD) {
       const int t = frame_t(f);
       const int rs = f % NRAW, es = f % NE;
       const int r = ((((t & 3) * B3 + b3) & 3) * V3) & 3;  // ((t*B + b) * V) mod 4
       const unsigned src = raw_a + (rs * rowf + r) * 4;
       const unsigned dst = eb_a + es * estride * 4;
-      mbar_wait(raw_full(rs), (f / NRAW) & 1);
+      long long c1 = 0;
+      {
+        long long c0 = ptim ? clock64() : 0;
+        mbar_wait(raw_full(rs), (f / NRAW) & 1);
+        if (ptim) { c1 = clock64(); pw1 += c1 - c0; }
+      }
       if (SCT > 0) {
         float xr[NQ];
         float mx = neg_inf();
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
           const int v = q * 32 + lane;
+          if (A.dbg & 16) { xr[q] = 0.f; continue; }
           xr[q] = (q * 32 + 31 < V || v < V) ? lds(src + v * 4) : neg_inf();
           mx = fmaxf(mx, xr[q]);
         }
         mx = warp_max(mx);  // every lane's loads have landed in registers here
+        if (ptim) pw3 += clock64() - c1;
         if (lane == 0) mbar_arrive(raw_empty(rs));
         if (!(mx > neg_inf())) mx = 0.f;
         const float nmL = -mx * kLog2e;
-        if (f >= NE) mbar_wait(e_empty(es), ((f / NE) - 1) & 1);
-        int c = 0, l = lane;
-        while (l >= S) { l -= S; ++c; }
+        {
+          long long c0 = ptim ? clock64() : 0;
+          if (f >= NE) mbar_wait(e_empty(es), ((f / NE) - 1) & 1);
+          if (ptim) pw2 += clock64() - c0;
+        }
+        // class v = c*S + l lands at c*PF + l: the same index when S is odd (PF = S).  The l = 0
+        // positions hold the blank classes' e0; the main warps never read them as states.
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
+          if (A.dbg & 2) break;
+          const int v = q * 32 + lane;
           const float e = ex2(fmaf(xr[q], kLog2e, nmL));
-          const unsigned o = (l == 0) ? (unsigned)(ZO + 4 + c) : (unsigned)(c * PF + l);
-          if (q * 32 + 31 < V || q * 32 + lane < V) sts(dst + o * 4, e);
-          l += 32;
-          while (l >= S) { l -= S; ++c; }
+          const int vp = (SCT & 1) ? v : v + v / SCT;
+          if (q * 32 + 31 < V || v < V) sts(dst + vp * 4, e);
         }
         if (lane == 0) sts(mb_a + es * 4, mx);
       } else {
@@ -406,8 +442,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         for (int v = lane; v < V; v += 32) {
           const int c = v / S, l = v - c * S;
           const float e = ex2(fmaf(lds(src + v * 4), kLog2e, nmL));
-          const unsigned o = (l == 0) ? (unsigned)(ZO + 4 + c) : (unsigned)(c * PF + l);
-          sts(dst + o * 4, e);
+          sts(dst + (c * PF + l) * 4, e);
         }
         __syncwarp();
         if (lane == 0) {
@@ -418,21 +453,33 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       __syncwarp();
       if (lane == 0) mbar_arrive(e_full(es));
     }
+    if (ptim) printf("sweep dir %d producer 0: total %lld  wait_raw_full %lld  wait_e_empty %lld  load+max %lld\n", DIR, clock64() - pt0, pw1, pw2, pw3);
   } else {
     // ============================ io lane: TMA row loads ============================
     if (lane == 0) {
+      long long iw = 0, it0 = clock64();
+      const bool itim = (A.dbg & 256) && b == 0;
       for (int f = 0; f < len; ++f) {
         const int rs = f % NRAW;
-        if (f >= NRAW) mbar_wait(raw_empty(rs), ((f / NRAW) - 1) & 1);
+        {
+          long long c0 = itim ? clock64() : 0;
+          if (f >= NRAW) mbar_wait(raw_empty(rs), ((f / NRAW) - 1) & 1);
+          if (itim) iw += clock64() - c0;
+        }
         const RowGeo gq = row_geo(frame_t(f), b, B, V, A.total);
         const unsigned dst = raw_a + rs * rowf * 4;
         // <= 3 floats at the very end of the tensor do not fill a 16-byte chunk: plain stores, made
         // visible to the producers by the release of the arrive below
         for (int idx = gq.nbulk; idx < gq.r + V; ++idx) sts(dst + idx * 4, A.x[gq.w0 + idx]);
+        if (A.dbg & 32) {
+          mbar_arrive(raw_full(rs));
+          continue;
+        }
         fence_async_smem();
         mbar_expect_tx(raw_full(rs), gq.nbulk * 4);
         bulk_g2s(dst, A.x + gq.w0, gq.nbulk * 4, raw_full(rs));
       }
+      if (itim) printf("sweep dir %d io: total %lld  wait_raw_empty %lld\n", DIR, clock64() - it0, iw);
     }
   }
 }
@@ -559,7 +606,7 @@ BisweepPlan bisweep_plan(int T, int B, int V, int S) {
   p.rowf = pad4(V + 3);
   p.prowf = pad4(S + 3);
   const int PF = S | 1;
-  p.estride = pad4(S * PF) + 4 + 64;
+  p.estride = pad4(S * PF) + 4;
   p.K = KSEG;
   p.nck = (T + p.K - 1) / p.K + 1;
   p.smem_bytes = sweep_smem(p.rowf, p.estride).bytes;
@@ -570,9 +617,17 @@ BisweepPlan bisweep_plan(int T, int B, int V, int S) {
   return p;
 }
 
-cudaError_t launch_bisweep(const BisweepArgs& a, const BisweepPlan& p, cudaStream_t st) {
+cudaError_t launch_bisweep(const BisweepArgs& a_in, const BisweepPlan& p, cudaStream_t st) {
   cudaError_t e = cudaSuccess;
-  const dim3 grid(a.B, a.grad ? 2 : 1);
+  BisweepArgs a = a_in;
+  {
+    static const int dbg = [] {
+      const char* v = getenv("CTCG_SWEEP_DEBUG");
+      return v ? atoi(v) : 0;
+    }();
+    a.dbg = dbg;  // timing experiments only: roles skip their work, results invalid
+  }
+  const dim3 grid(a.B, (a.grad && !(a.dbg & 4)) ? 2 : 1);
   {
     ProfScope prof("bisweep", st);
 #define CTCG_SWEEP(SCT, MAXT)                                                                               \
