@@ -290,6 +290,7 @@ int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, i
     s.nmain = p.sw.nmain;
     s.rowf = p.sw.rowf;
     s.estride = p.sw.estride;
+    s.epad = p.sw.epad;
     CTCG_CUDA(launch_bisweep(s, p.sw, st));
     return CTCG_OK;
   }

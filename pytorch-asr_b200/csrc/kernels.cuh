@@ -119,11 +119,11 @@ struct BisweepArgs {
   BiFin* fin;              // [B]
   float* grad;             // (T, B, V) nullable: receives g_scale[b] * gamma_den
   const float* g_scale;    // nullable
-  int32_t nmain, rowf, estride;
+  int32_t nmain, rowf, estride, epad;
   int32_t dbg;             // timing experiments only (CTCG_SWEEP_DEBUG bit mask); 0 in production
 };
 struct BisweepPlan {
-  int32_t ok, K, nck, nmain, threads, rowf, prowf, estride;
+  int32_t ok, K, nck, nmain, threads, rowf, prowf, estride, epad;
   size_t smem_bytes, spill_bytes, ckpt_bytes;
 };
 BisweepPlan bisweep_plan(int T, int B, int V, int S);

@@ -40,7 +40,7 @@ namespace ctcg {
 namespace {
 
 constexpr int NPROD = 4;     // producer warps
-constexpr int NRAW = 12;     // TMA landing rows in flight
+constexpr int NRAW = 10;     // TMA landing rows in flight
 constexpr int NE = 6;        // e rows ahead of the recursion
 constexpr int TARGET = 60;   // the spilled vectors are kept near 2^TARGET
 constexpr int BAND = 20;
@@ -115,69 +115,67 @@ __device__ __forceinline__ int exponent_of(float v) {  // floor(log2 v) for norm
 
 // ---- shared-memory plan of a sweep CTA ------------------------------------------
 struct SwSmem {
-  int raw, eb, rbuf, mbuf, kflag, mbar, bytes;
+  int raw, eb, edb, rbuf, msum, kflag, mbar, bytes;
 };
-__host__ __device__ inline SwSmem sweep_smem(int rowf, int estride) {
+__host__ __device__ inline SwSmem sweep_smem(int rowf, int estride, int epad) {
   SwSmem s;
   int o = 0;
   s.raw = o;    o += NRAW * rowf * 4;
-  s.eb = o;     o += NE * estride * 4;
+  s.eb = o;     o += (NE * estride + epad) * 4;   // e rows of NE frames, then zeros (over-reads of the last stage)
+  s.edb = o;    o += NE * RBW * 4;                // per frame: e0[c] + e[c][c]
   s.rbuf = o;   o += 2 * RBW * 4;
-  s.mbuf = o;   o += 8 * 4;
+  s.msum = o;   o += NPROD * 8;  // per-producer sums of the frame maxima (fp64)
   s.kflag = o;  o += 4 * 4;
   o = (o + 15) & ~15;
-  s.mbar = o;   o += (2 * NRAW + 2 * NE) * 8;
+  s.mbar = o;   o += (2 * NRAW + 2 * NE + 1) * 8;
   s.bytes = o;
   return s;
 }
 
-// Geometry of one (t, b) logits row inside its 16-byte aligned window.
-struct RowGeo {
-  long long w0;   // first float of the window (multiple of 4)
-  int r;          // row starts at window float r (0..3)
-  int nbulk;      // floats fetched by the bulk copy (multiple of 4)
-};
-__device__ __forceinline__ RowGeo row_geo(int t, int b, int B, int V, long long total) {
-  RowGeo g;
-  const long long i0 = ((long long)t * B + b) * V;
-  g.r = (int)(i0 & 3);
-  g.w0 = i0 - g.r;
-  const int nfl = pad4(g.r + V);
-  const long long room = (total - g.w0) & ~3LL;
-  g.nbulk = (int)(room < (long long)nfl ? room : (long long)nfl);
-  return g;
-}
-
 template <int SCT>
 struct SDims {
-  int S, V, PF, ZO;
+  int S, V, PF;
   __device__ __forceinline__ explicit SDims(const BisweepArgs& a) {
     S = SCT > 0 ? SCT : a.S;
     V = S * S;
-    PF = S | 1;             // odd pitch: the 8 scalar e loads of a main thread are conflict-free
-    ZO = pad4(S * PF);      // a 16-byte chunk of zeros behind the e rows
+    PF = S | 1;  // odd row pitch: the scalar e loads of the main warps are bank-conflict free in both directions
   }
 };
 
 // ---- one sweep (DIR 0: forward in time, P vectors; DIR 1: backward in time, Q vectors) ------
+//
+// Main-warp layout: context/letter group g = warp*8 + (lane & 7), k4 = lane >> 3; a thread owns the
+// 16 states o = 32*(s >> 3) + 8*k4 + (s & 7), s = 0..15, of its group (DIR 0: state (c=o, l=g), DIR 1:
+// state (c=g, l=o)); the group's sum is two xor-shuffles (8, 16) away.  States that do not exist are
+// neutral without any masking: o >= S meets R[o] = 0, and the producers zero the blank column (c, 0)
+// and the diagonal (c, c) of every e row after folding them into ed[c] = e0[c] + e[c][c]:
+//     R'[g] = sum_o val'[o] + ed[g] * R[g]
+// (the diagonal state has no explicit self-loop and the blank state none either, so both are functions
+// of R[g] alone).
 template <int SCT, int DIR>
 __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* smraw) {
   const SDims<SCT> D(A);
-  const int S = D.S, V = D.V, PF = D.PF, ZO = D.ZO;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int S = D.S, V = D.V, PF = D.PF;
+  const int tid = threadIdx.x, lane = tid & 31;
   const int b = blockIdx.x, B = A.B;
   const int len = min(A.lens[b], A.T);
   const int nmain = A.nmain;
+  // Role order by hardware warp id: producers, io, main, scale.  The warp schedulers favour the
+  // lower ids when several warps are ready, and the producers must never starve behind main warps
+  // that are spinning on the very rows the producers have yet to deliver.
+  const int hw = tid >> 5;
+  const int warp = hw >= NPROD + 1 ? hw - (NPROD + 1) : hw + nmain + 1;
   const int rowf = A.rowf, estride = A.estride, prowf = A.prowf;
   const bool loops = A.loops != 0, ctx = A.ctx != 0;
-  const SwSmem L = sweep_smem(rowf, estride);
+  const SwSmem L = sweep_smem(rowf, estride, A.epad);
   const unsigned sm0 = smem_u32(smraw);
-  const unsigned raw_a = sm0 + L.raw, eb_a = sm0 + L.eb, rb_a = sm0 + L.rbuf, mb_a = sm0 + L.mbuf,
+  const unsigned raw_a = sm0 + L.raw, eb_a = sm0 + L.eb, ed_a = sm0 + L.edb, rb_a = sm0 + L.rbuf,
                  kf_a = sm0 + L.kflag, bar_a = sm0 + L.mbar;
   auto raw_full = [&](int s) { return bar_a + s * 8; };
   auto raw_empty = [&](int s) { return bar_a + (NRAW + s) * 8; };
   auto e_full = [&](int s) { return bar_a + (2 * NRAW + s) * 8; };
   auto e_empty = [&](int s) { return bar_a + (2 * NRAW + NE + s) * 8; };
+  const unsigned prod_done = bar_a + (2 * NRAW + 2 * NE) * 8;
   const int NB = (nmain + 1) * 32;  // threads of the per-frame barrier: main warps + scale warp
   float* spill = A.spill[DIR] + (long long)b * A.T * prowf;
   float* ck = A.ck[DIR] + (long long)b * A.nck * V;
@@ -185,7 +183,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
   // ---- init ----
   {
     float* ebf = reinterpret_cast<float*>(smraw + L.eb);
-    for (int i = tid; i < NE * estride; i += blockDim.x) ebf[i] = 0.f;  // pads, l = 0 slots, zero chunks
+    for (int i = tid; i < NE * estride + A.epad + NE * RBW; i += blockDim.x) ebf[i] = 0.f;  // e rows, pad, ed
     float* rb = reinterpret_cast<float*>(smraw + L.rbuf);
     for (int i = tid; i < 2 * RBW; i += blockDim.x) {
       const int g = i & (RBW - 1);
@@ -201,8 +199,9 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       }
       for (int s = 0; s < NE; ++s) {
         mbar_init(e_full(s), 1);
-        mbar_init(e_empty(s), nmain + 1);
+        mbar_init(e_empty(s), nmain);
       }
+      mbar_init(prod_done, NPROD);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
   }
@@ -211,167 +210,151 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
 
   if (warp < nmain) {
     // ============================ main warps: the recursion ============================
-    const int g = warp * 4 + (lane >> 3), k8 = lane & 7;
+    const int g = warp * 8 + (lane & 7), k4 = lane >> 3;
     const bool gv = g < S;
-    unsigned eo[8];   // byte offsets of the 8 states' classes inside an e stage
-    float2 m2[4];     // explicit self-loop masks
-    float mk[8];
+    // byte offset of slot 0 inside an e stage; slot s adds the compile-time constant soff(s)
+    const unsigned ebase = (DIR == 0) ? (unsigned)(8 * k4 * PF + g) * 4u : (unsigned)(g * PF + 8 * k4) * 4u;
+    auto soff = [&](int s) { return (unsigned)((32 * (s >> 3) + (s & 7)) * (DIR == 0 ? PF : 1)) * 4u; };
+    const unsigned edo = (unsigned)(gv ? g : 0) * 4u;
+    const unsigned rc = (unsigned)(8 * k4) * 4u;  // this thread's R chunks: floats 8*k4 + {0..7} and + 32
+    const float2 lf2 = splat2(loops ? 1.f : 0.f);
+    float2 val[8];
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
-      const int o = 4 * (k8 + 8 * (s >> 2)) + (s & 3);
-      bool valid;
-      int c, l;
-      if (DIR == 0) { c = o; l = g; valid = gv && o < S && g >= 1; }
-      else          { c = g; l = o; valid = gv && o < S && o >= 1; }
-      eo[s] = valid ? (unsigned)(c * PF + l) * 4u : (unsigned)(ZO + (s & 3)) * 4u;
-      mk[s] = (valid && loops && c != l) ? 1.f : 0.f;
-    }
-#pragma unroll
-    for (int h = 0; h < 4; ++h) m2[h] = make_float2(mk[2 * h], mk[2 * h + 1]);
-    const unsigned e0o = (unsigned)((ctx && gv) ? g * PF : 0) * 4u;  // blank class of context g (class 0 when global)
-    const unsigned rc0 = (unsigned)(4 * k8) * 4u, rc1 = (unsigned)(4 * (k8 + 8)) * 4u;
-    float2 val[4];
-#pragma unroll
-    for (int h = 0; h < 4; ++h) val[h] = make_float2(0.f, 0.f);
+    for (int h = 0; h < 8; ++h) val[h] = make_float2(0.f, 0.f);
     float Rown = (DIR == 0) ? (g == 0 ? pow2i(TARGET) : 0.f) : (gv ? pow2i(TARGET) : 0.f);
-    float ev[8], e0 = 0.f;
+    float evA[16], evB[16], edA = 0.f, edB = 0.f;
+    int es = 0;          // e stage of the frame being prefetched
+    unsigned epar = 0;
+    int ckc = !loops ? 0x7fffffff : (DIR == 0 ? KSEG : (len & (KSEG - 1)));  // frames until the next checkpoint
+    auto prefetch = [&](float (&ev)[16], float& ed) {
+      mbar_wait(e_full(es), epar);
+      const unsigned eb = eb_a + es * estride * 4 + ebase;
 #pragma unroll
-    for (int s = 0; s < 8; ++s) ev[s] = 0.f;
-    if (len > 0) {
-      mbar_wait(e_full(0), 0);
-#pragma unroll
-      for (int s = 0; s < 8; ++s) ev[s] = lds(eb_a + eo[s]);
-      e0 = lds(eb_a + e0o);
-    }
-    int es = 0, esn = 0;           // e stage of this frame
-    unsigned epar = 0;             // parity of the stage the NEXT frame waits on
-    long long tw = 0, tb = 0, tt0 = clock64();
-    const bool tim = (A.dbg & 256) && b == 0 && tid == 0;
-    for (int f = 0; f < len; ++f) {
-      const int t = frame_t(f);
-      // prefetch the next frame's e values (registers evn); its stage is ready several frames ahead
-      float evn[8], e0n = 0.f;
-      esn = es + 1;
-      unsigned eparn = epar;
-      if (esn == NE) { esn = 0; eparn ^= 1; }
-      if (f + 1 < len) {
-        long long c0 = tim ? clock64() : 0;
-        mbar_wait(e_full(esn), eparn);
-        if (tim) tw += clock64() - c0;
-        const unsigned eb = eb_a + esn * estride * 4;
-#pragma unroll
-        for (int s = 0; s < 8; ++s) evn[s] = lds(eb + eo[s]);
-        e0n = lds(eb + e0o);
-      } else {
-#pragma unroll
-        for (int s = 0; s < 8; ++s) evn[s] = 0.f;
-      }
-      // checkpoint of the per-state values entering this frame (explicit self-loops only)
-      if (loops && (DIR == 0 ? (t > 0 && (t & (KSEG - 1)) == 0) : ((t & (KSEG - 1)) == KSEG - 1))) {
+      for (int s = 0; s < 16; ++s) ev[s] = lds(eb + soff(s));
+      ed = lds(ed_a + es * RBW * 4 + edo);
+      if (++es == NE) { es = 0; epar ^= 1; }
+    };
+    long long mseg[5] = {0, 0, 0, 0, 0}, mprev = clock64();
+    const bool mtim = (A.dbg & 256) && b == 0 && lane == 0 && warp == 0;
+#define MSEG(i)                          \
+  if (mtim) {                            \
+    const long long now_ = clock64();    \
+    mseg[i] += now_ - mprev;             \
+    mprev = now_;                        \
+  }
+    auto step = [&](int f, const float (&ev)[16], const float ed, float (&evn)[16], float& edn) {
+      const unsigned rb = rb_a + (f & 1) * RBW * 4 + rc;
+      const float4 r0 = lds4(rb), r1 = lds4(rb + 16), r2 = lds4(rb + 128), r3 = lds4(rb + 144);
+      const int kk = ldsi(kf_a + (f & 3) * 4);
+      MSEG(0)
+      if (f + 1 < len) prefetch(evn, edn);  // next frame's e values: ready several frames ahead
+      MSEG(1)
+      if (ckc == 0) {  // checkpoint of the per-state values entering this frame (explicit self-loops only)
+        const int t = frame_t(f);
         float* cp = ck + (long long)(t / KSEG) * V;
 #pragma unroll
-        for (int s = 0; s < 8; ++s) {
-          const int o = 4 * (k8 + 8 * (s >> 2)) + (s & 3);
+        for (int s = 0; s < 16; ++s) {
+          const int o = 32 * (s >> 3) + 8 * k4 + (s & 7);
           const bool valid = gv && o < S && (DIR == 0 ? g >= 1 : o >= 1);
           const int cls = DIR == 0 ? o * S + g : g * S + o;
           const float v = (s & 1) ? val[s >> 1].y : val[s >> 1].x;
           if (valid) cp[cls] = v;
         }
+        ckc = KSEG;
       }
-      const unsigned rb = rb_a + (f & 1) * RBW * 4;
-      if (A.dbg & 1) {  // timing experiment: barriers and hand-shakes only
-        if (lane == 0) mbar_arrive(e_empty(es));
-        named_sync(1, NB);
-        es = esn;
-        epar = eparn;
-        continue;
-      }
-      const float4 r0 = lds4(rb + rc0), r1 = lds4(rb + rc1);
-      const int kk = ldsi(kf_a + (f & 3) * 4);
-      val[0] = fmul2(make_float2(ev[0], ev[1]), ffma2(m2[0], val[0], make_float2(r0.x, r0.y)));
-      val[1] = fmul2(make_float2(ev[2], ev[3]), ffma2(m2[1], val[1], make_float2(r0.z, r0.w)));
-      val[2] = fmul2(make_float2(ev[4], ev[5]), ffma2(m2[2], val[2], make_float2(r1.x, r1.y)));
-      val[3] = fmul2(make_float2(ev[6], ev[7]), ffma2(m2[3], val[3], make_float2(r1.z, r1.w)));
-      const float2 s2 = fadd2(fadd2(val[0], val[1]), fadd2(val[2], val[3]));
+      --ckc;
+      val[0] = fmul2(make_float2(ev[0], ev[1]), ffma2(lf2, val[0], make_float2(r0.x, r0.y)));
+      val[1] = fmul2(make_float2(ev[2], ev[3]), ffma2(lf2, val[1], make_float2(r0.z, r0.w)));
+      val[2] = fmul2(make_float2(ev[4], ev[5]), ffma2(lf2, val[2], make_float2(r1.x, r1.y)));
+      val[3] = fmul2(make_float2(ev[6], ev[7]), ffma2(lf2, val[3], make_float2(r1.z, r1.w)));
+      val[4] = fmul2(make_float2(ev[8], ev[9]), ffma2(lf2, val[4], make_float2(r2.x, r2.y)));
+      val[5] = fmul2(make_float2(ev[10], ev[11]), ffma2(lf2, val[5], make_float2(r2.z, r2.w)));
+      val[6] = fmul2(make_float2(ev[12], ev[13]), ffma2(lf2, val[6], make_float2(r3.x, r3.y)));
+      val[7] = fmul2(make_float2(ev[14], ev[15]), ffma2(lf2, val[7], make_float2(r3.z, r3.w)));
+      const float2 s2 = fadd2(fadd2(fadd2(val[0], val[1]), fadd2(val[2], val[3])),
+                              fadd2(fadd2(val[4], val[5]), fadd2(val[6], val[7])));
       float tot = s2.x + s2.y;
-      tot += __shfl_xor_sync(0xffffffffu, tot, 1);
-      tot += __shfl_xor_sync(0xffffffffu, tot, 2);
-      tot += __shfl_xor_sync(0xffffffffu, tot, 4);
-      float Rn = fmaf(e0, Rown, tot);
+      tot += __shfl_xor_sync(0xffffffffu, tot, 8);
+      tot += __shfl_xor_sync(0xffffffffu, tot, 16);
+      float Rn = fmaf(ed, Rown, tot);
       if (kk != 0) {  // rare: power-of-two rescale decided two frames ago
         const float sc = pow2i(kk);
         const float2 sc2 = splat2(sc);
 #pragma unroll
-        for (int h = 0; h < 4; ++h) val[h] = fmul2(val[h], sc2);
+        for (int h = 0; h < 8; ++h) val[h] = fmul2(val[h], sc2);
         Rn *= sc;
       }
       Rown = Rn;
-      if (k8 == 0 && gv) sts(rb_a + ((f + 1) & 1) * RBW * 4 + g * 4, Rn);
-      if (lane == 0) mbar_arrive(e_empty(es));
-      {
-        long long c0 = tim ? clock64() : 0;
-        named_sync(1, NB);
-        if (tim) tb += clock64() - c0;
+      MSEG(2)
+      if (k4 == 0 && gv) sts(rb_a + ((f + 1) & 1) * RBW * 4 + g * 4, Rn);
+      if (lane == 0) mbar_arrive(e_empty(f % NE));
+      MSEG(3)
+      named_sync(1, NB);
+      MSEG(4)
+    };
+    const long long mt0 = clock64();
+    if (!(A.dbg & 1)) {
+      if (len > 0) prefetch(evA, edA);
+      int f = 0;
+      for (; f + 1 < len; f += 2) {
+        step(f, evA, edA, evB, edB);
+        step(f + 1, evB, edB, evA, edA);
       }
-#pragma unroll
-      for (int s = 0; s < 8; ++s) ev[s] = evn[s];
-      e0 = e0n;
-      es = esn;
-      epar = eparn;
+      if (f < len) step(f, evA, edA, evB, edB);
+    } else {  // timing experiment: hand-shakes and barriers only
+      for (int f = 0; f < len; ++f) {
+        mbar_wait(e_full(es), epar);
+        if (++es == NE) { es = 0; epar ^= 1; }
+        if (lane == 0) mbar_arrive(e_empty(f % NE));
+        named_sync(1, NB);
+      }
     }
-    if (tim) printf("sweep dir %d main: total %lld  wait_e_full %lld  barrier %lld  (len %d)\n", DIR, clock64() - tt0, tw, tb, len);
+    if (mtim) printf("sweep dir %d main: total %lld (len %d)  Rloads %lld  prefetch %lld  math %lld  store+arrive %lld  barrier %lld\n", DIR, clock64() - mt0, len, mseg[0], mseg[1], mseg[2], mseg[3], mseg[4]);
+#undef MSEG
   } else if (warp == nmain) {
     // ============================ scale / spill warp ============================
+    // Per frame: spill the vector entering the frame, decide the rescale of the frame after next from
+    // its largest entry (one REDUX on the float bits: the entries are non-negative).  Nothing here
+    // waits for anything but the frame barrier, so the main warps never wait for this warp.
     int kcur = 0, knext = 0, Kcum = TARGET;
-    double msum = 0.0;
-    int es = 0;
-    unsigned epar = 0;
     const float inf = __int_as_float(0x7f800000);
     bool dead = false;
     for (int f = 0; f < len; ++f) {
-      const int t = frame_t(f);
-      const unsigned rb = rb_a + (f & 1) * RBW * 4;
-      if (A.dbg & 8) {
-        mbar_wait(e_full(es), epar);
-        if (lane == 0) mbar_arrive(e_empty(es));
-        if (++es == NE) { es = 0; epar ^= 1; }
-        named_sync(1, NB);
-        continue;
+      if (!(A.dbg & 8)) {
+        const int t = frame_t(f);
+        const unsigned rb = rb_a + (f & 1) * RBW * 4;
+        const float v0 = lds(rb + lane * 4), v1 = lds(rb + (lane + 32) * 4);
+        const float mx = __int_as_float(__reduce_max_sync(0xffffffffu, max(__float_as_int(v0), __float_as_int(v1))));
+        int knext2 = 0;
+        if (mx > 0.f && mx < inf) {
+          const int ex = exponent_of(mx) + kcur + knext;
+          if (ex > TARGET + BAND || ex < TARGET - BAND) knext2 = max(-120, min(120, TARGET - ex));
+        } else {
+          dead = true;
+        }
+        if (lane == 0) stsi(kf_a + ((f + 2) & 3) * 4, knext2);
+        float* sp = spill + (long long)t * prowf;
+        if (lane < S) sp[lane] = v0;
+        if (lane + 32 < S) sp[lane + 32] = v1;
+        if (lane == 0) {
+          sp[S + 1] = (float)kcur;
+          sp[S + 2] = (float)Kcum;
+        }
+        Kcum += kcur;
+        kcur = knext;
+        knext = knext2;
       }
-      const float v0 = lds(rb + lane * 4), v1 = lds(rb + (lane + 32) * 4);
-      float* sp = spill + (long long)t * prowf;
-      if (lane < S) sp[lane] = v0;
-      if (lane + 32 < S) sp[lane + 32] = v1;
-      const float mx = warp_max(fmaxf(v0, v1));
-      int knext2 = 0;
-      if (mx > 0.f && mx < inf) {
-        const int ex = exponent_of(mx) + kcur + knext;
-        if (ex > TARGET + BAND || ex < TARGET - BAND) knext2 = max(-120, min(120, TARGET - ex));
-      } else {
-        dead = true;
-      }
-      mbar_wait(e_full(es), epar);
-      const float m = lds(mb_a + es * 4);
-      if (lane == 0) {
-        msum += (double)m;
-        sp[S] = m;
-        sp[S + 1] = (float)kcur;
-        sp[S + 2] = (float)Kcum;
-        stsi(kf_a + ((f + 2) & 3) * 4, knext2);
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(e_empty(es));
-      Kcum += kcur;
-      kcur = knext;
-      knext = knext2;
-      if (++es == NE) { es = 0; epar ^= 1; }
       named_sync(1, NB);
     }
     if (DIR == 0) {  // total mass = sum_c P_len[c]; cost = log(mass) - K ln2 + sum of the frame maxima
       const unsigned rb = rb_a + (len & 1) * RBW * 4;
       const float v0 = lds(rb + lane * 4), v1 = lds(rb + (lane + 32) * 4);
       const float s = warp_sum(v0 + v1);
+      mbar_wait(prod_done, 0);
       if (lane == 0) {
+        const double* mp = reinterpret_cast<const double*>(smraw + L.msum);
+        double msum = 0.0;
+        for (int i = 0; i < NPROD; ++i) msum += mp[i];
         const bool ok = !dead && (s > 0.f) && (s < inf);
         A.cost[b] = ok ? (log((double)s) - (double)Kcum * kLn2 + msum) : -1e20;  // the reference's sentinel
         BiFin fin;
@@ -387,53 +370,58 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     const int pw = warp - nmain - 1;
     constexpr int NQ = SCT > 0 ? (SCT * SCT + 31) / 32 : 1;
     const int B3 = B & 3, b3 = b & 3, V3 = V & 3;
-    long long pw1 = 0, pw2 = 0, pw3 = 0, pt0 = clock64();
+    double msum = 0.0;
+    const bool skip_ld = (A.dbg & 16) != 0, skip_ex = (A.dbg & 2) != 0;
+    long long seg[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
     const bool ptim = (A.dbg & 256) && b == 0 && pw == 0 && lane == 0;
+#define PSEG(i)                          \
+  if (ptim) {                            \
+    const long long now_ = clock64();    \
+    seg[i] += now_ - tprev;              \
+    tprev = now_;                        \
+  }
     for (int f = pw; f < len; f += NPROD) {
       const int t = frame_t(f);
       const int rs = f % NRAW, es = f % NE;
+      PSEG(0)
       const int r = ((((t & 3) * B3 + b3) & 3) * V3) & 3;  // ((t*B + b) * V) mod 4
       const unsigned src = raw_a + (rs * rowf + r) * 4;
       const unsigned dst = eb_a + es * estride * 4;
-      long long c1 = 0;
-      {
-        long long c0 = ptim ? clock64() : 0;
-        mbar_wait(raw_full(rs), (f / NRAW) & 1);
-        if (ptim) { c1 = clock64(); pw1 += c1 - c0; }
-      }
+      mbar_wait(raw_full(rs), (f / NRAW) & 1);
+      PSEG(1)
+      float mx = neg_inf();
       if (SCT > 0) {
         float xr[NQ];
-        float mx = neg_inf();
+        if (!skip_ld) {
 #pragma unroll
-        for (int q = 0; q < NQ; ++q) {
-          const int v = q * 32 + lane;
-          if (A.dbg & 16) { xr[q] = 0.f; continue; }
-          xr[q] = (q * 32 + 31 < V || v < V) ? lds(src + v * 4) : neg_inf();
-          mx = fmaxf(mx, xr[q]);
+          for (int q = 0; q < NQ; ++q) {
+            const int v = q * 32 + lane;
+            xr[q] = (q * 32 + 31 < V || v < V) ? lds(src + v * 4) : neg_inf();
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < NQ; ++q) xr[q] = 0.f;
         }
+#pragma unroll
+        for (int q = 0; q + 1 < NQ; q += 2) mx = fmaxf(mx, fmaxf(xr[q], xr[q + 1]));
+        if (NQ & 1) mx = fmaxf(mx, xr[NQ - 1]);
         mx = warp_max(mx);  // every lane's loads have landed in registers here
-        if (ptim) pw3 += clock64() - c1;
         if (lane == 0) mbar_arrive(raw_empty(rs));
         if (!(mx > neg_inf())) mx = 0.f;
         const float nmL = -mx * kLog2e;
-        {
-          long long c0 = ptim ? clock64() : 0;
-          if (f >= NE) mbar_wait(e_empty(es), ((f / NE) - 1) & 1);
-          if (ptim) pw2 += clock64() - c0;
-        }
-        // class v = c*S + l lands at c*PF + l: the same index when S is odd (PF = S).  The l = 0
-        // positions hold the blank classes' e0; the main warps never read them as states.
+        PSEG(2)
+        if (f >= NE) mbar_wait(e_empty(es), ((f / NE) - 1) & 1);
+        PSEG(3)
+        // class v = c*S + l lands at c*PF + l: the same index when S is odd (PF = S)
+        if (!skip_ex)
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
-          if (A.dbg & 2) break;
           const int v = q * 32 + lane;
           const float e = ex2(fmaf(xr[q], kLog2e, nmL));
-          const int vp = (SCT & 1) ? v : v + v / SCT;
+          const int vp = (SCT & 1) ? v : v + v / (SCT > 0 ? SCT : 1);
           if (q * 32 + 31 < V || v < V) sts(dst + vp * 4, e);
         }
-        if (lane == 0) sts(mb_a + es * 4, mx);
       } else {
-        float mx = neg_inf();
         for (int v = lane; v < V; v += 32) mx = fmaxf(mx, lds(src + v * 4));
         mx = warp_max(mx);
         if (!(mx > neg_inf())) mx = 0.f;
@@ -445,41 +433,70 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
           sts(dst + (c * PF + l) * 4, e);
         }
         __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(raw_empty(rs));
-          sts(mb_a + es * 4, mx);
+        if (lane == 0) mbar_arrive(raw_empty(rs));
+      }
+      PSEG(4)
+      // fold the blank column and the diagonal into ed[c] = e0[c] + e[c][c], then zero them in the row
+      __syncwarp();
+      float e0c[2], egg[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int c = lane + 32 * h;
+        e0c[h] = egg[h] = 0.f;
+        if (c < S) {
+          e0c[h] = lds(dst + (ctx ? c * PF : 0) * 4);
+          if (c >= 1) egg[h] = lds(dst + (c * PF + c) * 4);
         }
       }
       __syncwarp();
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int c = lane + 32 * h;
+        if (c < S) {
+          sts(ed_a + (es * RBW + c) * 4, e0c[h] + egg[h]);
+          sts(dst + (c * PF) * 4, 0.f);
+          sts(dst + (c * PF + c) * 4, 0.f);
+        }
+      }
+      if (lane == 0) {
+        spill[(long long)t * prowf + S] = mx;  // frame maximum, read by the combine kernel
+        msum += (double)mx;
+      }
+      __syncwarp();
       if (lane == 0) mbar_arrive(e_full(es));
+      PSEG(5)
     }
-    if (ptim) printf("sweep dir %d producer 0: total %lld  wait_raw_full %lld  wait_e_empty %lld  load+max %lld\n", DIR, clock64() - pt0, pw1, pw2, pw3);
+    if (ptim) printf("sweep dir %d producer 0: loop-top %lld  wait_raw_full %lld  load+max %lld  wait_e_empty %lld  exp+store %lld  fixup+arrive %lld\n", DIR, seg[0], seg[1], seg[2], seg[3], seg[4], seg[5]);
+#undef PSEG
+    if (lane == 0) {
+      reinterpret_cast<double*>(smraw + L.msum)[pw] = msum;
+      mbar_arrive(prod_done);
+    }
   } else {
     // ============================ io lane: TMA row loads ============================
     if (lane == 0) {
-      long long iw = 0, it0 = clock64();
-      const bool itim = (A.dbg & 256) && b == 0;
-      for (int f = 0; f < len; ++f) {
+      const long long stepf = (DIR == 0 ? 1LL : -1LL) * (long long)B * V;
+      long long i0 = ((long long)frame_t(0) * B + b) * V;
+      for (int f = 0; f < len; ++f, i0 += stepf) {
         const int rs = f % NRAW;
-        {
-          long long c0 = itim ? clock64() : 0;
-          if (f >= NRAW) mbar_wait(raw_empty(rs), ((f / NRAW) - 1) & 1);
-          if (itim) iw += clock64() - c0;
-        }
-        const RowGeo gq = row_geo(frame_t(f), b, B, V, A.total);
+        if (f >= NRAW) mbar_wait(raw_empty(rs), ((f / NRAW) - 1) & 1);
+        const int r = (int)(i0 & 3);
+        const long long w0 = i0 - r;
+        const long long room = (A.total - w0) & ~3LL;
+        const int nfl = pad4(r + V);
+        const int nbulk = (int)(room < (long long)nfl ? room : (long long)nfl);
         const unsigned dst = raw_a + rs * rowf * 4;
         // <= 3 floats at the very end of the tensor do not fill a 16-byte chunk: plain stores, made
         // visible to the producers by the release of the arrive below
-        for (int idx = gq.nbulk; idx < gq.r + V; ++idx) sts(dst + idx * 4, A.x[gq.w0 + idx]);
+        for (int idx = nbulk; idx < r + V; ++idx) sts(dst + idx * 4, A.x[w0 + idx]);
         if (A.dbg & 32) {
           mbar_arrive(raw_full(rs));
           continue;
         }
         fence_async_smem();
-        mbar_expect_tx(raw_full(rs), gq.nbulk * 4);
-        bulk_g2s(dst, A.x + gq.w0, gq.nbulk * 4, raw_full(rs));
+        mbar_expect_tx(raw_full(rs), nbulk * 4);
+        bulk_g2s(dst, A.x + w0, nbulk * 4, raw_full(rs));
       }
-      if (itim) printf("sweep dir %d io: total %lld  wait_raw_empty %lld\n", DIR, clock64() - it0, iw);
     }
   }
 }
@@ -601,16 +618,17 @@ BisweepPlan bisweep_plan(int T, int B, int V, int S) {
   BisweepPlan p{};
   p.ok = 0;
   if (S < 4 || S > 64 || V != S * S || T < 1 || B < 1) return p;
-  p.nmain = (S + 3) / 4;
+  p.nmain = (S + 7) / 8;
   p.threads = (p.nmain + 1 + NPROD + 1) * 32;
   p.rowf = pad4(V + 3);
   p.prowf = pad4(S + 3);
   const int PF = S | 1;
-  p.estride = pad4(S * PF) + 4;
+  p.estride = pad4(S * PF);
+  p.epad = 16 * PF + 64;  // zeros behind the last stage: states o >= S read up to 15 rows past a stage
   p.K = KSEG;
   p.nck = (T + p.K - 1) / p.K + 1;
-  p.smem_bytes = sweep_smem(p.rowf, p.estride).bytes;
-  if (p.smem_bytes > 227 * 1024 || p.threads > 704) return p;
+  p.smem_bytes = sweep_smem(p.rowf, p.estride, p.epad).bytes;
+  if (p.smem_bytes > 227 * 1024 || p.threads > 448) return p;
   p.spill_bytes = (size_t)B * T * p.prowf * 4;
   p.ckpt_bytes = (size_t)B * p.nck * V * 4;
   p.ok = 1;
@@ -637,10 +655,10 @@ cudaError_t launch_bisweep(const BisweepArgs& a_in, const BisweepPlan& p, cudaSt
     if (e != cudaSuccess) return e;                                                                      \
     bisweep_kernel<SCT, MAXT><<<grid, p.threads, p.smem_bytes, st>>>(a);                                \
   } while (0)
-#define MAXT_OF(S_) ((((S_) + 3) / 4 + 1 + NPROD + 1) * 32)
+#define MAXT_OF(S_) ((((S_) + 7) / 8 + 1 + NPROD + 1) * 32)
     if (a.S == 49) CTCG_SWEEP(49, MAXT_OF(49));       // the WSJ character set (egs/wsj/vocabulary.txt)
     else if (a.S == 36) CTCG_SWEEP(36, MAXT_OF(36));  // BASELINE.json's nominal V = 1296
-    else CTCG_SWEEP(0, 704);
+    else CTCG_SWEEP(0, 448);
 #undef MAXT_OF
 #undef CTCG_SWEEP
     ++g_launches;
