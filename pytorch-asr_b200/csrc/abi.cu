@@ -31,7 +31,7 @@ struct Plan {
   int nlp = 0;       // compact row pitch (floats), multiple of 4
   int arow_num = 0;  // alpha row pitch of the numerator
   int arow_den = 0;
-  size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
+  size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, beta_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
   size_t pspill = 0, ckpt = 0;
   size_t spill2 = 0, ckpt2 = 0, fin = 0;
   BicharPlan bi{};   // bi.ok: the denominator runs on the factorised bi-char kernels
@@ -71,6 +71,7 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
     p.xg = take(TB * p.nlp * 4);
     p.gg = take(TB * p.nlp * 4);
     p.alpha_num = take(TB * p.arow_num * 4);
+    p.beta_num = take(TB * p.arow_num * 4);
     p.cost_num = take((size_t)B * 8);
   }
   p.rowlse = take(TB * 4);
@@ -447,7 +448,13 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     a.g_sign = 1.f;
     a.g_scale = nullptr;
     a.write_grad = grad != nullptr;
-    if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
+    static const bool num_legacy = [] {
+      const char* e = std::getenv("CTCG_NUM_LEGACY");
+      return e && e[0] == '1';
+    }();
+    a.beta_ws = reinterpret_cast<float*>(ws + p.beta_num);
+    if (!num_legacy && num_split_supported(a)) CTCG_CUDA(launch_num_split(a, st));
+    else if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
     else CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
     return CTCG_OK;
   }();

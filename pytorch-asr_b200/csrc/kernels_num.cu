@@ -761,6 +761,350 @@ __global__ void __launch_bounds__(NTH) num_log_kernel(const PathArgs a, const in
   }
 }
 
+
+// =====================================================================================
+// Split numerator: the alpha and the beta recursion run AT THE SAME TIME on separate CTAs
+// (grid (B, 2)), each spilling its normalised rows; the posteriors are then formed by a
+// time-parallel combine kernel.  Halves the serial chain of the fused kernel above (T frames
+// instead of 2T) and takes the posterior work off it altogether.
+//
+//   num_sweep_kernel    DIR 0: alpha_hat_t rows (+ fp64 offset c_t) and the cost, arcs by destination
+//                       DIR 1: beta_hat_{t+1} rows (+ offset d_t), arcs by source, frames descending
+//   num_combine_kernel  one warp per frame: gamma_t[j] = sum_{arcs e labelled j}
+//                       2^(alpha_hat_t[src] + beta_hat_{t+1}[dst] + x_t[j] + w_e + c_t + d_t - cost),
+//                       fixed summation order (arcs grouped by label on the host), row normalised to one
+// =====================================================================================
+constexpr int SW_TH = NS + 32;  // state warps + io warp
+
+struct SweepPlan {
+  int pk, w, a0, a1, fin, red, xring, bytes;
+};
+__host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp, bool unit) {
+  SweepPlan p;
+  int o = 0;
+  auto take = [&](int bytes) {
+    const int at = o;
+    o += (bytes + 15) & ~15;
+    return at;
+  };
+  p.pk = take(maxN * DEG * 4);
+  p.w = unit ? 0 : take(maxN * DEG * 4);
+  p.a0 = take((maxN + 1) * 4);
+  p.a1 = take((maxN + 1) * 4);
+  p.fin = take(maxN * 4);
+  p.red = take((16 + 2 * (SW_TH / 32)) * 4);
+  p.xring = take(XR * nlp * 4);
+  p.bytes = o;
+  return p;
+}
+
+template <bool UNIT, int SPT>
+__global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, const int maxN) {
+  extern __shared__ __align__(16) unsigned char sm[];
+  const GraphDev& g = a.g;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int DIR = blockIdx.y;
+  const int gi = (g.num_graphs == 1) ? 0 : b;
+  const int so = g.state_off[gi];
+  const int n = g.state_off[gi + 1] - so;
+  const int ro = so + gi;
+  const int len = min(a.lens[b], a.T);
+  const int nlp = (int)a.x_stride_t, arow = a.alpha_row;
+  const SweepPlan P = sweep_plan(maxN, nlp, UNIT);
+  uint4* pkv = reinterpret_cast<uint4*>(sm + P.pk);
+  float4* wv = reinterpret_cast<float4*>(sm + P.w);
+  float* abuf0 = reinterpret_cast<float*>(sm + P.a0);
+  float* abuf1 = reinterpret_cast<float*>(sm + P.a1);
+  float* fin = reinterpret_cast<float*>(sm + P.fin);
+  int* wmax = reinterpret_cast<int*>(sm + P.red);
+  float* scr = reinterpret_cast<float*>(wmax + 16);
+  float* xring = reinterpret_cast<float*>(sm + P.xring);
+  constexpr int NW = SW_TH / 32;
+
+  const int32_t* ptr = DIR ? g.out_ptr : g.in_ptr;
+  const int32_t* oth = DIR ? g.out_dst : g.in_src;
+  const int32_t* clab = DIR ? g.out_clab : g.in_clab;
+  const float* wgt = DIR ? g.out_w : g.in_w;
+  for (int s = tid; s < n; s += SW_TH) {
+    unsigned pi[DEG];
+    float wi[DEG];
+#pragma unroll
+    for (int k = 0; k < DEG; ++k) {
+      const int e = ptr[ro + s] + k;
+      const bool v = e < ptr[ro + s + 1];
+      pi[k] = v ? ((unsigned)oth[e] | ((unsigned)clab[e] << 16)) : NOARC;
+      wi[k] = (v && !UNIT) ? wgt[e] * kLog2e : 0.f;
+    }
+    pkv[s] = make_uint4(pi[0], pi[1], pi[2], pi[3]);
+    if (!UNIT) wv[s] = make_float4(wi[0], wi[1], wi[2], wi[3]);
+    const float f = g.final_w[so + s];
+    fin[s] = (f > kDeadWeight) ? f * kLog2e : neg_inf();
+    abuf0[s] = DIR ? fin[s] : ((s == 0) ? 0.f : neg_inf());
+  }
+  if (tid < 3) wmax[tid] = (tid == 0) ? 0 : IMIN;  // the vector entering the first frame is not normalised
+  if (tid == 0) abuf0[maxN] = abuf1[maxN] = neg_inf();
+  const float* xb = a.x + (long long)b * a.x_stride_b;
+  float* rows = (DIR ? a.beta_ws : a.alpha_ws) + (long long)b * a.T * arow;
+  const int xchunks = nlp / 4;
+  __syncthreads();
+  auto frame_t = [&](int i) { return DIR ? len - 1 - i : i; };
+  const long long rstep = DIR ? -(long long)arow : (long long)arow;
+
+  float* a_cur = abuf0;
+  float* a_nxt = abuf1;
+  double c = 0.0;  // io warp: vector = normalised vector + c (log2 units)
+  if (SPT > 0 && warp < W_LAB) {
+    constexpr int NSP = SPT > 0 ? SPT : 1;
+    unsigned so4[NSP][DEG], lo4[NSP][DEG];
+    float wi[NSP][DEG];
+    float* arp[NSP];
+#pragma unroll
+    for (int i = 0; i < NSP; ++i) {
+      const int s = tid + i * NS;
+      const uint4 pk = (s < n) ? pkv[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
+      const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
+      const float4 w = (!UNIT && s < n) ? wv[s] : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float ww[DEG] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int k = 0; k < DEG; ++k) {
+        so4[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 4u : (pkk[k] & 0xffffu) * 4u;
+        lo4[i][k] = (pkk[k] == NOARC) ? 0u : (pkk[k] >> 16) * 4u;
+        wi[i][k] = ww[k];
+      }
+      arp[i] = rows + (long long)frame_t(0) * arow + (s < n ? s : 0);
+    }
+    unsigned ac = sm_u32(a_cur), an = sm_u32(a_nxt);
+    const unsigned xr0 = sm_u32(xring), wm_a = sm_u32(wmax);
+    int r = 0, slot = 0;
+    for (int t = 0; t < len; ++t) {
+      __syncthreads();
+      int wmi;
+      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(wmi) : "r"(wm_a + r * 4));
+      const float mx = norm_of(wmi);
+      r = next3(r);
+      const unsigned xa = xr0 + slot * nlp * 4;
+      slot = (slot + 1 == XR) ? 0 : slot + 1;
+      float lm = neg_inf();
+#pragma unroll
+      for (int i = 0; i < NSP; ++i) {
+        const int s = tid + i * NS;
+        float v[DEG];
+#pragma unroll
+        for (int k = 0; k < DEG; ++k) {
+          v[k] = fmaf(lds_f(xa + lo4[i][k]), kLog2e, lds_f(ac + so4[i][k]) - mx);
+          if (!UNIT) v[k] += wi[i][k];
+        }
+        const float res = lse4(v);
+        if (s < n) {
+          *arp[i] = lds_f(ac + s * 4) - mx;
+          sts_f(an + s * 4, res);
+        }
+        arp[i] += rstep;
+        lm = fmaxf(lm, res);
+      }
+      const int wm = warp_floor_max(lm);
+      if (lane == 0) atomicMax(&wmax[r], wm);
+      const unsigned tmp = ac;
+      ac = an;
+      an = tmp;
+    }
+  } else if (warp < W_LAB) {
+    int r = 0;
+    for (int t = 0; t < len; ++t) {
+      __syncthreads();
+      const float mx = norm_of(wmax[r]);
+      r = next3(r);
+      const float* xrow = xring + (t % XR) * nlp;
+      float* ar = rows + (long long)frame_t(t) * arow;
+      float lm = neg_inf();
+      for (int s = tid; s < n; s += NS) {
+        ar[s] = a_cur[s] - mx;
+        const uint4 pk = pkv[s];
+        const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
+        float v[DEG];
+#pragma unroll
+        for (int k = 0; k < DEG; ++k) {
+          const unsigned q = (pkk[k] == NOARC) ? 0u : pkk[k];
+          const float val = fmaf(xrow[q >> 16], kLog2e, a_cur[q & 0xffffu] - mx);
+          v[k] = (pkk[k] == NOARC) ? neg_inf() : val;
+        }
+        if (!UNIT) {
+          const float4 w = wv[s];
+          v[0] += w.x;
+          v[1] += w.y;
+          v[2] += w.z;
+          v[3] += w.w;
+        }
+        const float res = lse4(v);
+        a_nxt[s] = res;
+        lm = fmaxf(lm, res);
+      }
+      const int wm = warp_floor_max(lm);
+      if (lane == 0) atomicMax(&wmax[r], wm);
+      float* tmp = a_cur;
+      a_cur = a_nxt;
+      a_nxt = tmp;
+    }
+  } else {  // io warp
+    auto issue_x = [&](int i, int slot) {
+      if (i >= 0 && i < len) {
+        const float* src = xb + (long long)frame_t(i) * nlp;
+        float* dst = xring + slot * nlp;
+        for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
+      }
+      cp_async_commit();
+    };
+    for (int i = 0; i < XR - 1; ++i) issue_x(i, i);
+    cp_async_wait<XR - 2>();
+    int r = 0;
+    for (int t = 0; t < len; ++t) {
+      __syncthreads();
+      issue_x(t + XR - 1, (t + XR - 1) % XR);
+      c += (double)norm_of(wmax[r]);
+      r = next3(r);
+      if (lane == 0) {
+        float* ar = rows + (long long)frame_t(t) * arow;
+        const float hi = (float)c;
+        ar[arow - 2] = hi;
+        ar[arow - 1] = (float)(c - (double)hi);
+        wmax[next3(r)] = IMIN;  // the slot the state warps fill during the next frame
+      }
+      cp_async_wait<XR - 2>();
+    }
+    cp_async_wait<0>();
+  }
+  if (DIR) return;
+  a_cur = (len & 1) ? abuf1 : abuf0;  // alpha_len (the register path swapped addresses, not these pointers)
+  __syncthreads();
+  // terminal: cost = c_len + LSE_n(alpha_hat_len[n] + final[n])
+  float tm = neg_inf();
+  for (int s = tid; s < n; s += SW_TH) tm = fmaxf(tm, a_cur[s] + fin[s]);
+  tm = warp_max(tm);
+  if (lane == 0) scr[warp] = tm;
+  __syncthreads();
+  float TM = scr[0];
+#pragma unroll
+  for (int w = 1; w < NW; ++w) TM = fmaxf(TM, scr[w]);
+  float ts = 0.f;
+  if (TM > neg_inf())
+    for (int s = tid; s < n; s += SW_TH) ts += ex2(a_cur[s] + fin[s] - TM);
+  ts = warp_sum(ts);
+  if (lane == 0) scr[NW + warp] = ts;
+  __syncthreads();
+  float TS = 0.f;
+#pragma unroll
+  for (int w = 0; w < NW; ++w) TS += scr[NW + w];
+  const bool feasible = TM > neg_inf() && TS > 0.f;
+  if (warp == W_LAB && lane == 0) {  // the io warp holds c
+    const double cost2 = c + (double)TM + (double)lg2(TS);
+    a.cost[b] = feasible ? cost2 * kLn2 : -1e20;
+  }
+}
+
+constexpr int CB_FR = 8;            // frames per combine CTA (one per warp)
+constexpr int CB_TH = CB_FR * 32;
+
+template <bool UNIT>
+__global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
+  extern __shared__ __align__(16) unsigned char sm[];
+  const GraphDev& g = a.g;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.y;
+  const int t = blockIdx.x * CB_FR + warp;
+  const int len = min(a.lens[b], a.T);
+  if (blockIdx.x * CB_FR >= len) return;
+  const int gi = (g.num_graphs == 1) ? 0 : b;
+  const int ro = g.state_off[gi] + gi;
+  const int n = g.state_off[gi + 1] - g.state_off[gi];
+  const int lo = g.lab_off[gi];
+  const int nl = g.lab_off[gi + 1] - lo;
+  const int nlp = (int)a.x_stride_t, arow = a.alpha_row;
+  int o = 0;
+  auto take = [&](int bytes) {
+    const int at = o;
+    o += (bytes + 15) & ~15;
+    return at;
+  };
+  int* lab_ptr = reinterpret_cast<int*>(sm + take((maxL + 1) * 4));
+  unsigned* lab_pk = reinterpret_cast<unsigned*>(sm + take(maxA * 4));
+  float* lab_w = reinterpret_cast<float*>(sm + (UNIT ? 0 : take(maxA * 4)));
+  float* rows_s = reinterpret_cast<float*>(sm + take(CB_FR * (2 * arow + 2 * nlp) * 4));
+  const int arc0 = g.in_ptr[ro];
+  const int narcs = g.in_ptr[ro + n] - arc0;
+  for (int j = tid; j <= nl; j += CB_TH) lab_ptr[j] = g.lab_ptr[lo + gi + j] - arc0;
+  for (int e = tid; e < narcs; e += CB_TH) {
+    lab_pk[e] = (unsigned)g.lab_src[arc0 + e] | ((unsigned)g.lab_dst[arc0 + e] << 16);
+    if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
+  }
+  float* at = rows_s + warp * (2 * arow + 2 * nlp);
+  float* bt = at + arow;
+  float* xt = bt + arow;
+  float* gt = xt + nlp;
+  const bool live = t < len;
+  if (live) {
+    const float4* as = reinterpret_cast<const float4*>(a.alpha_ws + ((long long)b * a.T + t) * arow);
+    const float4* bs = reinterpret_cast<const float4*>(a.beta_ws + ((long long)b * a.T + t) * arow);
+    const float4* xs = reinterpret_cast<const float4*>(a.x + (long long)b * a.x_stride_b + (long long)t * nlp);
+    for (int i = lane; i < arow / 4; i += 32) {
+      reinterpret_cast<float4*>(at)[i] = as[i];
+      reinterpret_cast<float4*>(bt)[i] = bs[i];
+    }
+    for (int i = lane; i < nlp / 4; i += 32) reinterpret_cast<float4*>(xt)[i] = xs[i];
+  }
+  __syncthreads();
+  if (!live) return;
+  float* dst = a.gout + (long long)b * a.g_stride_b + (long long)t * a.g_stride_t;
+  const double costn = a.cost[b];
+  if (!(costn > -1e19)) {  // no accepting path: zero posterior
+    for (int j = lane; j < nl; j += 32) dst[j] = 0.f;
+    return;
+  }
+  const double ct = (double)at[arow - 2] + (double)at[arow - 1];
+  const double dt = (double)bt[arow - 2] + (double)bt[arow - 1];
+  const float Kt = (float)(ct + dt - costn / kLn2);
+  const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
+  float ls = 0.f;
+  for (int base = 0; base < nl; base += 32) {
+    const int j = base + lane;
+    int e0 = 0, e1 = 0;
+    if (j < nl) {
+      e0 = lab_ptr[j];
+      e1 = lab_ptr[j + 1];
+    }
+    const bool heavy = (e1 - e0) > HEAVY;
+    float acc = 0.f;
+    if (j < nl && !heavy) {
+      const float kx = fmaf(xt[j], kLog2e, Kt);
+      for (int e = e0; e < e1; ++e) {
+        const unsigned pk = lab_pk[e];
+        acc += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+      }
+    }
+    unsigned hm = __ballot_sync(0xffffffffu, heavy);
+    while (hm) {  // labels with many arcs (the blank): the whole warp strides over the arcs
+      const int src_lane = __ffs(hm) - 1;
+      hm &= hm - 1;
+      const int jh = base + src_lane;
+      const int h0 = __shfl_sync(0xffffffffu, e0, src_lane), h1 = __shfl_sync(0xffffffffu, e1, src_lane);
+      const float kx = fmaf(xt[jh], kLog2e, Kt);
+      float part = 0.f;
+      for (int e = h0 + lane; e < h1; e += 32) {
+        const unsigned pk = lab_pk[e];
+        part += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+      }
+      part = warp_sum(part);
+      if (lane == src_lane) acc = part;
+    }
+    if (j < nl) gt[j] = acc;
+    ls += acc;
+  }
+  const float tot = warp_sum(ls);
+  const float sc = tot > 0.f ? gmul / tot : 0.f;
+  __syncwarp();
+  for (int j = lane; j < nl; j += 32) dst[j] = gt[j] * sc;
+}
+
 }  // namespace
 
 bool num_lin_supported(const PathArgs& a) {
@@ -777,6 +1121,55 @@ static cudaError_t launch_one(const PathArgs& a, int bytes, cudaStream_t st) {
   if (e != cudaSuccess) return e;
   num_log_kernel<UNIT, SPT><<<a.B, NTH, bytes, st>>>(a, a.g.max_states, a.g.max_arcs, a.g.max_labels);
   return cudaGetLastError();
+}
+
+template <bool UNIT, int SPT>
+static cudaError_t launch_sweep(const PathArgs& a, int bytes, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  num_sweep_kernel<UNIT, SPT><<<dim3(a.B, a.write_grad ? 2 : 1), SW_TH, bytes, st>>>(a, a.g.max_states);
+  return cudaGetLastError();
+}
+
+bool num_split_supported(const PathArgs& a) {
+  if (!a.beta_ws || !num_lin_supported(a)) return false;
+  const int cb = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * 2 +
+                 CB_FR * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
+  return cb <= 200 * 1024;
+}
+
+cudaError_t launch_num_split(const PathArgs& a, cudaStream_t st) {
+  const bool unit = a.g.unit_weights != 0;
+  cudaError_t e;
+  {
+    ProfScope prof("num_sweep", st);
+    const SweepPlan P = sweep_plan(a.g.max_states, (int)a.x_stride_t, unit);
+    const int spt = (a.g.max_states + NS - 1) / NS;
+    if (spt <= 1) e = unit ? launch_sweep<true, 1>(a, P.bytes, st) : launch_sweep<false, 1>(a, P.bytes, st);
+    else if (spt == 2) e = unit ? launch_sweep<true, 2>(a, P.bytes, st) : launch_sweep<false, 2>(a, P.bytes, st);
+    else e = unit ? launch_sweep<true, 0>(a, P.bytes, st) : launch_sweep<false, 0>(a, P.bytes, st);
+    ++g_launches;
+    if (e != cudaSuccess) return e;
+  }
+  if (!a.write_grad) return e;
+  {
+    ProfScope prof("num_combine", st);
+    const int bytes = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
+                      CB_FR * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
+    const dim3 grid((a.T + CB_FR - 1) / CB_FR, a.B);
+    if (unit) {
+      e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+      if (e != cudaSuccess) return e;
+      num_combine_kernel<true><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
+    } else {
+      e = cudaFuncSetAttribute(num_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+      if (e != cudaSuccess) return e;
+      num_combine_kernel<false><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
+    }
+    ++g_launches;
+    e = cudaGetLastError();
+  }
+  return e;
 }
 
 cudaError_t launch_num_lin(const PathArgs& a_in, cudaStream_t st) {
