@@ -32,6 +32,7 @@ NVCC_FLAGS = [
 # (profiles/trace_roles.py); off in the product build, they cost ~3 % of its instructions.
 if os.environ.get("CTCG_TRACE_BUILD") == "1":
     NVCC_FLAGS.append("-DCTCG_BICHAR_TRACE_BUILD")
+    NVCC_FLAGS.append("-DCTCG_SWEEP_TIMERS")  # per-role cycle counters of bisweep_kernel (CTCG_SWEEP_DEBUG=256)
 
 
 def _nvcc():

@@ -234,14 +234,20 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       ed = lds(ed_a + es * RBW * 4 + edo);
       if (++es == NE) { es = 0; epar ^= 1; }
     };
+#ifdef CTCG_SWEEP_TIMERS
     long long mseg[5] = {0, 0, 0, 0, 0}, mprev = clock64();
     const bool mtim = (A.dbg & 256) && b == 0 && lane == 0 && warp == 0;
+#endif
+#ifdef CTCG_SWEEP_TIMERS
 #define MSEG(i)                          \
   if (mtim) {                            \
     const long long now_ = clock64();    \
     mseg[i] += now_ - mprev;             \
     mprev = now_;                        \
   }
+#else
+#define MSEG(i)
+#endif
     auto step = [&](int f, const float (&ev)[16], const float ed, float (&evn)[16], float& edn) {
       const unsigned rb = rb_a + (f & 1) * RBW * 4 + rc;
       const float4 r0 = lds4(rb), r1 = lds4(rb + 16), r2 = lds4(rb + 128), r3 = lds4(rb + 144);
@@ -292,7 +298,9 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       named_sync(1, NB);
       MSEG(4)
     };
+#ifdef CTCG_SWEEP_TIMERS
     const long long mt0 = clock64();
+#endif
     if (!(A.dbg & 1)) {
       if (len > 0) prefetch(evA, edA);
       int f = 0;
@@ -309,7 +317,9 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         named_sync(1, NB);
       }
     }
+#ifdef CTCG_SWEEP_TIMERS
     if (mtim) printf("sweep dir %d main: total %lld (len %d)  Rloads %lld  prefetch %lld  math %lld  store+arrive %lld  barrier %lld\n", DIR, clock64() - mt0, len, mseg[0], mseg[1], mseg[2], mseg[3], mseg[4]);
+#endif
 #undef MSEG
   } else if (warp == nmain) {
     // ============================ scale / spill warp ============================
@@ -372,14 +382,20 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     const int B3 = B & 3, b3 = b & 3, V3 = V & 3;
     double msum = 0.0;
     const bool skip_ld = (A.dbg & 16) != 0, skip_ex = (A.dbg & 2) != 0;
+#ifdef CTCG_SWEEP_TIMERS
     long long seg[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
     const bool ptim = (A.dbg & 256) && b == 0 && pw == 0 && lane == 0;
+#endif
+#ifdef CTCG_SWEEP_TIMERS
 #define PSEG(i)                          \
   if (ptim) {                            \
     const long long now_ = clock64();    \
     seg[i] += now_ - tprev;              \
     tprev = now_;                        \
   }
+#else
+#define PSEG(i)
+#endif
     for (int f = pw; f < len; f += NPROD) {
       const int t = frame_t(f);
       const int rs = f % NRAW, es = f % NE;
@@ -466,7 +482,9 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       if (lane == 0) mbar_arrive(e_full(es));
       PSEG(5)
     }
+#ifdef CTCG_SWEEP_TIMERS
     if (ptim) printf("sweep dir %d producer 0: loop-top %lld  wait_raw_full %lld  load+max %lld  wait_e_empty %lld  exp+store %lld  fixup+arrive %lld\n", DIR, seg[0], seg[1], seg[2], seg[3], seg[4], seg[5]);
+#endif
 #undef PSEG
     if (lane == 0) {
       reinterpret_cast<double*>(smraw + L.msum)[pw] = msum;
