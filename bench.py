@@ -326,16 +326,39 @@ def run_ours(args):
     # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
     # (profiles/r01_ncu_full_summary.md); only captured for the default workload
     traffic = NCU_TRAFFIC.get((args.workload, dom))
+    # every kernel against the bytes it must move itself (fp32): the sweeps read the logits once per
+    # direction, the combine reads them once and writes the gradient once, the row kernels of plain CTC
+    # read + write once; the compact-column kernels of the numerator move far less than 8*V per frame
+    own_bytes = {"bisweep": 8.0 * V * frames, "bicombine": 8.0 * V * frames, "bichar_den": 8.0 * V * frames,
+                 "rows": 8.0 * V * frames, "rows_ctx": 8.0 * V * frames}
+    per_kernel = {}
+    for k, v in kern.items():
+        ent = {"ms": round(v, 4)}
+        if k in own_bytes and v > 0:
+            ent["own_algorithmic_bytes"] = own_bytes[k]
+            ent["own_gbs"] = own_bytes[k] / (v * 1e-3) / 1e9
+            ent["own_frac"] = ent["own_gbs"] / peak
+        tr = NCU_TRAFFIC.get((args.workload, k))
+        if tr:
+            ent["ncu_dram_bytes"] = tr
+        per_kernel[k] = ent
+    if "bisweep" in kern:
+        conc = ("denominator (bisweep -> bicombine) on a side stream, concurrent with the numerator "
+                "(gather -> num_sweep -> num_combine) on the caller's stream; joined before scatter_sub")
+    elif "bichar_den" in kern:
+        conc = "bichar_den runs on a side stream concurrently with gather+num_log"
+    else:
+        conc = "single stream"
     roof = {"bound": "hbm", "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak,
             "traffic": traffic, "peak_source": peak_src,
             "kernel": dom, "algorithmic_bytes_per_launch": alg_bytes,
             "scope": "dominant kernel: algorithmic bytes of one launch (8*V*sum(len)) / its mean CUDA-event "
                      "duration over %d steps run right after the timed region" % nprof_steps,
             "kernel_ms": {k: round(v, 4) for k, v in kern.items()},
+            "per_kernel": per_kernel,
             "dominant_kernel_share": (kern[dom] / sum(kern.values())) if kern else None,
             "step_achieved": step_gbs, "step_frac": step_gbs / peak,
-            "concurrency": "bichar_den runs on a side stream concurrently with gather+num_log"
-                           if "bichar_den" in kern else "single stream"}
+            "concurrency": conc}
     line = {
         "metric": "CTC(-G) loss+grad utterance-frames/sec", "value": value, "unit": "utterance-frames/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,

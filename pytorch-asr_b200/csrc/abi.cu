@@ -424,6 +424,8 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     (void)join();
     return st_;
   }
+  PathArgs num_args{};
+  bool split_num = false, scatter_num = false;
   st_ = [&]() -> int {
     // 1. compact the label columns each utterance touches
     CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp,
@@ -453,8 +455,19 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
       return e && e[0] == '1';
     }();
     a.beta_ws = reinterpret_cast<float*>(ws + p.beta_num);
-    if (!num_legacy && num_split_supported(a)) CTCG_CUDA(launch_num_split(a, st));
-    else if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
+    if (!num_legacy && num_split_supported(a)) {
+      CTCG_CUDA(launch_num_sweeps(a, st));
+      num_args = a;
+      split_num = true;
+      // with the factorised denominator the posterior combine runs after the join and subtracts
+      // from the dense rows in place (no compact round trip, no scatter_sub launch)
+      static const bool fuse_scatter = [] {
+        const char* e = std::getenv("CTCG_NUM_SCATTER");
+        return !(e && e[0] == '0');
+      }();
+      scatter_num = fused_den && grad && fuse_scatter;
+      if (!scatter_num) CTCG_CUDA(launch_num_combine(a, st));
+    } else if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
     else CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
     return CTCG_OK;
   }();
@@ -466,7 +479,14 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
 
   if (fused_den) {
     // 3a'. gamma_den - gamma_num
-    if (grad) CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
+    if (grad && split_num && scatter_num) {
+      num_args.scatter_grad = grad;
+      num_args.scatter_V = V;
+      num_args.g_scale = grad_scale;
+      CTCG_CUDA(launch_num_combine(num_args, st));
+    } else if (grad) {
+      CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
+    }
   } else if (den) {
     // 3a. denominator path sum over the shared decoding graph, writes +gamma_den rows
     PathArgs d{};

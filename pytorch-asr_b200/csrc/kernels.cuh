@@ -18,6 +18,8 @@ struct PathArgs {
   int32_t T, B;
   float* alpha_ws;        // [B][T][row] normalised alpha_t in log2 units, + frame offset (2 floats)
   int32_t alpha_row;      // floats per row: pad4(max_states + 2)
+  float* scatter_grad;    // nullable: dense (T, B, scatter_V) gradient the split numerator subtracts its posteriors from
+  int32_t scatter_V;
   float* beta_ws;         // nullable; same shape as alpha_ws: beta rows of the split numerator (kernels_num.cu)
   double* cost;           // [B] natural-log path sum
   float* gout;            // posterior rows; element (t, b, l) at gout[t*g_stride_t + b*g_stride_b + l]
@@ -40,7 +42,9 @@ bool num_lin_supported(const PathArgs& a);
 cudaError_t launch_num_lin(const PathArgs& a, cudaStream_t st);
 // Split variant: alpha and beta sweeps on separate CTAs at the same time, then a time-parallel combine.
 bool num_split_supported(const PathArgs& a);
-cudaError_t launch_num_split(const PathArgs& a, cudaStream_t st);
+cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st);
+// Posteriors from the spilled rows; with a.scatter_grad set they are subtracted from the dense gradient directly.
+cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st);
 
 // xg[b][t][j] = logits[t][b][lab_list_b[j]] * log2(e) for t < lens[b]
 cudaError_t launch_gather(const float* logits, int T, int B, int V, const int32_t* lens,

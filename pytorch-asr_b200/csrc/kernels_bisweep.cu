@@ -527,8 +527,15 @@ __global__ void __launch_bounds__(MAXT, 1) bisweep_kernel(const BisweepArgs A) {
 }
 
 // ---- combine: posterior rows of one K-frame segment of one utterance -----------------------
+// Per class v = (c, l) the K frames of the segment are two scalar recurrences (forward for a, backward
+// for f) driven by the spilled vectors; every class reads P[pi] and Q[qi] with
+//   l >= 1           pi = c, qi = l, explicit loop iff l != c
+//   l == 0, ctx      pi = c, qi = c           (blank state of context c, class c*S)
+//   l == 0, global   class 0: pi -> 1, qi -> sum_c P[c] Q[c];  classes c*S, c >= 1: pi -> 0 (never emitted)
+// so the inner loops are branch free.  KW = floats per staged vector row.
+constexpr int KW = 72;
 template <int SCT, int KMAX>
-__global__ void __launch_bounds__(CTHREADS) bicombine_kernel(const BisweepArgs A) {
+__global__ void __launch_bounds__(CTHREADS, 3) bicombine_kernel(const BisweepArgs A) {
   const int S = SCT > 0 ? SCT : A.S;
   const int V = S * S;
   const int b = blockIdx.y, j = blockIdx.x, K = A.K, B = A.B, T = A.T, prowf = A.prowf;
@@ -547,8 +554,8 @@ __global__ void __launch_bounds__(CTHREADS) bicombine_kernel(const BisweepArgs A
   }
   if (n == 0) return;
 
-  __shared__ float Ps[KMAX][RBW], Qs[KMAX][RBW];
-  __shared__ float nmL_s[KMAX], scF_s[KMAX], scB_s[KMAX], cB_s[KMAX], D_s[KMAX];
+  __shared__ float Ps[KMAX][KW], Qs[KMAX][KW];
+  __shared__ float nmL_s[KMAX], scF_s[KMAX], scB_s[KMAX], cB_s[KMAX];
   const float* spF = A.spill[0] + ((long long)b * T + t0) * prowf;
   const float* spB = A.spill[1] + ((long long)b * T + t0) * prowf;
   const float gsc = A.g_scale ? A.g_scale[b] : 1.f;
@@ -556,75 +563,130 @@ __global__ void __launch_bounds__(CTHREADS) bicombine_kernel(const BisweepArgs A
   // cA = gscale / mass * 2^E1 (about 2^-TARGET, rides on the a recurrence) and cB_t = 2^(E_t - E1)
   const int E1 = max(-120, min(120, -TARGET - exponent_of(fin.inv_mass)));
   const float cA = fin.inv_mass * pow2i(E1) * gsc;
-  for (int i = tid; i < n * RBW; i += CTHREADS) {
-    const int f = i / RBW, c = i - f * RBW;
-    Ps[f][c] = (c < S) ? spF[f * prowf + c] * cA : 0.f;
-    Qs[f][c] = (c < S) ? spB[f * prowf + c] : 0.f;
+  for (int i = tid; i < KMAX * KW; i += CTHREADS) {
+    const int f = i / KW, c = i - f * KW;
+    float pv = 0.f, qv = 0.f;
+    if (f < n && c < S) {
+      pv = spF[f * prowf + c] * cA;
+      qv = spB[f * prowf + c];
+    }
+    if (c == 64) pv = 1.f;
+    Ps[f][c] = pv;
+    Qs[f][c] = qv;
   }
-  if (tid < n) {
-    const float* rf = spF + tid * prowf;
-    const float* rq = spB + tid * prowf;
-    nmL_s[tid] = -rf[S] * kLog2e;
-    scF_s[tid] = pow2i((int)rf[S + 1]);
-    scB_s[tid] = pow2i((int)rq[S + 1]);
-    const int Et = fin.kfinal - ((int)rf[S + 2] + (int)rf[S + 1]) - (int)rq[S + 2];
-    cB_s[tid] = pow2i(max(-126, min(126, Et - E1)));
+  if (tid < KMAX) {
+    float nm = 0.f, sF = 0.f, sB = 0.f, cb = 0.f;
+    if (tid < n) {
+      const float* rf = spF + tid * prowf;
+      const float* rq = spB + tid * prowf;
+      nm = -rf[S] * kLog2e;
+      sF = pow2i((int)rf[S + 1]);
+      sB = pow2i((int)rq[S + 1]);
+      const int Et = fin.kfinal - ((int)rf[S + 2] + (int)rf[S + 1]) - (int)rq[S + 2];
+      cb = pow2i(max(-126, min(126, Et - E1)));
+    }
+    nmL_s[tid] = nm;
+    scF_s[tid] = sF;
+    scB_s[tid] = sB;
+    cB_s[tid] = cb;
   }
   __syncthreads();
   const bool loops = A.loops != 0, ctx = A.ctx != 0;
-  if (!ctx) {  // one global blank: its posterior is the sum over the S blank states
+  if (!ctx) {  // one global blank: sum over the S blank states, read by class 0 through Qs[f][64]
     for (int f = warp; f < n; f += CTHREADS / 32) {
-      const float cb = cB_s[f];
-      float d = Ps[f][lane] * (Qs[f][lane] * cb) + Ps[f][lane + 32] * (Qs[f][lane + 32] * cb);
+      float d = Ps[f][lane] * Qs[f][lane] + Ps[f][lane + 32] * Qs[f][lane + 32];
       d = warp_sum(d);
-      if (lane == 0) D_s[f] = d;
+      if (lane == 0) Qs[f][64] = d;
     }
     __syncthreads();
+  }
+  float nmL[KMAX], scF[KMAX], scB[KMAX], cB[KMAX];
+#pragma unroll
+  for (int f = 0; f < KMAX; ++f) {
+    nmL[f] = nmL_s[f];
+    scF[f] = scF_s[f];
+    scB[f] = scB_s[f];
+    cB[f] = cB_s[f];
   }
   const float* x0 = A.x + ((long long)t0 * B + b) * V;
   float* g0 = A.grad + ((long long)t0 * B + b) * V;
   const long long rstride = (long long)B * V;
   const float* ckA = A.ck[0] + ((long long)b * A.nck + j) * V;
   const float* ckF = A.ck[1] + ((long long)b * A.nck + j) * V;
-  for (int v = tid; v < V; v += CTHREADS) {
-    const int c = v / S, l = v - c * S;
-    float e[KMAX], ah[KMAX];
+  const bool haveA = j > 0, haveF = t1 < len;
+  float en[KMAX];
 #pragma unroll
-    for (int f = 0; f < KMAX; ++f)
-      if (f < n) e[f] = __ldg(x0 + f * rstride + v);
+  for (int f = 0; f < KMAX; ++f) en[f] = 0.f;
+  int c = tid / S, l = tid - c * S;
+  const int dc = CTHREADS / S, dl = CTHREADS - dc * S;
+  for (int v = tid; v < V; v += CTHREADS) {
+    int pi = c, qi = l;
+    bool m = loops && l != c;
     if (l == 0) {
+      m = false;
+      qi = c;
+      if (!ctx) {
+        qi = 64;
+        pi = (v == 0) ? 64 : 65;
+      }
+    }
+    const float mf = m ? 1.f : 0.f;
+    // the checkpoints hold the sweeps' scaled values; cA rides on the forward recurrence (Ps has it too)
+    float a = (m && haveA) ? ckA[v] * cA : 0.f;
+    float fv = (m && haveF) ? ckF[v] : 0.f;
+    const float* xp = x0 + v;
+    float* gp = g0 + v;
+    float e[KMAX], ah[KMAX];
+    if (n == KMAX) {
+      // software pipeline: this class's logits were requested one iteration ago, the next class's go out now
+      if (v == tid) {
+#pragma unroll
+        for (int f = 0; f < KMAX; ++f) en[f] = ld_stream(xp + f * rstride);
+      }
+#pragma unroll
+      for (int f = 0; f < KMAX; ++f) e[f] = en[f];
+      if (v + CTHREADS < V) {
+#pragma unroll
+        for (int f = 0; f < KMAX; ++f) en[f] = ld_stream(xp + CTHREADS + f * rstride);
+      }
+#pragma unroll
+      for (int f = 0; f < KMAX; ++f) {
+        e[f] = ex2(fmaf(e[f], kLog2e, nmL[f]));
+        ah[f] = (e[f] * scF[f]) * fmaf(mf, a, Ps[f][pi]);   // a_{t+1}[c][l] * cA
+        a = ah[f];
+      }
+#pragma unroll
+      for (int f = KMAX - 1; f >= 0; --f) {
+        const float bh = fmaf(mf, fv, Qs[f][qi]);            // b_{t+1}[c][l]
+        st_stream(gp + f * rstride, ah[f] * (bh * cB[f]));
+        fv = (e[f] * scB[f]) * bh;                           // f_t[c][l]
+      }
+    } else {
+#pragma unroll
+      for (int f = 0; f < KMAX; ++f)
+        if (f < n) e[f] = __ldg(xp + f * rstride);
 #pragma unroll
       for (int f = 0; f < KMAX; ++f) {
         if (f < n) {
-          const float ef = ex2(fmaf(e[f], kLog2e, nmL_s[f])) * scF_s[f];
-          float gm;
-          if (ctx) gm = ef * Ps[f][c] * (Qs[f][c] * cB_s[f]);
-          else gm = (v == 0) ? ef * D_s[f] : 0.f;
-          g0[f * rstride + v] = gm;
+          e[f] = ex2(fmaf(e[f], kLog2e, nmL[f]));
+          ah[f] = (e[f] * scF[f]) * fmaf(mf, a, Ps[f][pi]);
+          a = ah[f];
         }
       }
-      continue;
-    }
-    const bool m = loops && l != c;
-    const float mf = m ? 1.f : 0.f;
-    // the checkpoints hold the sweeps' scaled values; cA rides on the forward recurrence (Ps has it too)
-    float a = (m && j > 0) ? ckA[v] * cA : 0.f;
-    float fv = (m && t1 < len) ? ckF[v] : 0.f;
 #pragma unroll
-    for (int f = 0; f < KMAX; ++f) {
-      if (f < n) {
-        e[f] = ex2(fmaf(e[f], kLog2e, nmL_s[f]));
-        ah[f] = e[f] * scF_s[f] * fmaf(mf, a, Ps[f][c]);  // a_{t+1}[c][l] * cA
-        a = ah[f];
+      for (int f = KMAX - 1; f >= 0; --f) {
+        if (f < n) {
+          const float bh = fmaf(mf, fv, Qs[f][qi]);
+          gp[f * rstride] = ah[f] * (bh * cB[f]);
+          fv = (e[f] * scB[f]) * bh;
+        }
       }
     }
-#pragma unroll
-    for (int f = KMAX - 1; f >= 0; --f) {
-      if (f < n) {
-        const float bh = fmaf(mf, fv, Qs[f][l]);          // b_{t+1}[c][l]
-        g0[f * rstride + v] = ah[f] * (bh * cB_s[f]);
-        fv = e[f] * scB_s[f] * bh;                        // f_t[c][l]
-      }
+    c += dc;
+    l += dl;
+    if (l >= S) {
+      l -= S;
+      ++c;
     }
   }
 }

@@ -798,7 +798,20 @@ __host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp, bool unit) {
   return p;
 }
 
-template <bool UNIT, int SPT>
+// DK: arcs per state that exist anywhere in the batch (3 for the CTC training graphs, fst_utils.py:592-605).
+template <int DK>
+__device__ __forceinline__ float lseK(const float (&v)[DK]) {
+  float M = v[0];
+#pragma unroll
+  for (int k = 1; k < DK; ++k) M = fmaxf(M, v[k]);
+  const float Ms = (M > neg_inf()) ? M : 0.f;
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < DK; ++k) s += ex2(v[k] - Ms);
+  return Ms + lg2(s);  // lg2(0) = -inf
+}
+
+template <bool UNIT, int SPT, int DK>
 __global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, const int maxN) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
@@ -856,8 +869,8 @@ __global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, cons
   double c = 0.0;  // io warp: vector = normalised vector + c (log2 units)
   if (SPT > 0 && warp < W_LAB) {
     constexpr int NSP = SPT > 0 ? SPT : 1;
-    unsigned so4[NSP][DEG], lo4[NSP][DEG];
-    float wi[NSP][DEG];
+    unsigned so4[NSP][DK], lo4[NSP][DK];
+    float wi[NSP][DK];
     float* arp[NSP];
 #pragma unroll
     for (int i = 0; i < NSP; ++i) {
@@ -867,7 +880,7 @@ __global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, cons
       const float4 w = (!UNIT && s < n) ? wv[s] : make_float4(0.f, 0.f, 0.f, 0.f);
       const float ww[DEG] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-      for (int k = 0; k < DEG; ++k) {
+      for (int k = 0; k < DK; ++k) {
         so4[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 4u : (pkk[k] & 0xffffu) * 4u;
         lo4[i][k] = (pkk[k] == NOARC) ? 0u : (pkk[k] >> 16) * 4u;
         wi[i][k] = ww[k];
@@ -889,13 +902,13 @@ __global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, cons
 #pragma unroll
       for (int i = 0; i < NSP; ++i) {
         const int s = tid + i * NS;
-        float v[DEG];
+        float v[DK];
 #pragma unroll
-        for (int k = 0; k < DEG; ++k) {
+        for (int k = 0; k < DK; ++k) {
           v[k] = fmaf(lds_f(xa + lo4[i][k]), kLog2e, lds_f(ac + so4[i][k]) - mx);
           if (!UNIT) v[k] += wi[i][k];
         }
-        const float res = lse4(v);
+        const float res = lseK<DK>(v);
         if (s < n) {
           *arp[i] = lds_f(ac + s * 4) - mx;
           sts_f(an + s * 4, res);
@@ -1002,16 +1015,21 @@ __global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, cons
   }
 }
 
-constexpr int CB_FR = 8;            // frames per combine CTA (one per warp)
-constexpr int CB_TH = CB_FR * 32;
+constexpr int CB_W = 8;             // warps per combine CTA, one frame at a time each
+constexpr int CB_FPW = 4;           // frames per warp: the graph tables are staged once per CB_W * CB_FPW frames
+constexpr int CB_FR = CB_W * CB_FPW;
+constexpr int CB_TH = CB_W * 32;
 
+// With a.scatter_grad set the normalised posteriors are subtracted from the dense gradient rows the
+// denominator wrote (grad[t][b][lab_list[j]] -= scale_b * gamma_t[j], the scatter_sub step fused in:
+// every (t, b, label) is touched by exactly one lane, no atomics); otherwise the compact rows
+// gout[b][t][j] are written for the row kernels of plain CTC.
 template <bool UNIT>
 __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
-  const int t = blockIdx.x * CB_FR + warp;
   const int len = min(a.lens[b], a.T);
   if (blockIdx.x * CB_FR >= len) return;
   const int gi = (g.num_graphs == 1) ? 0 : b;
@@ -1029,7 +1047,7 @@ __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, co
   int* lab_ptr = reinterpret_cast<int*>(sm + take((maxL + 1) * 4));
   unsigned* lab_pk = reinterpret_cast<unsigned*>(sm + take(maxA * 4));
   float* lab_w = reinterpret_cast<float*>(sm + (UNIT ? 0 : take(maxA * 4)));
-  float* rows_s = reinterpret_cast<float*>(sm + take(CB_FR * (2 * arow + 2 * nlp) * 4));
+  float* rows_s = reinterpret_cast<float*>(sm + take(CB_W * (2 * arow + 2 * nlp) * 4));
   const int arc0 = g.in_ptr[ro];
   const int narcs = g.in_ptr[ro + n] - arc0;
   for (int j = tid; j <= nl; j += CB_TH) lab_ptr[j] = g.lab_ptr[lo + gi + j] - arc0;
@@ -1037,12 +1055,25 @@ __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, co
     lab_pk[e] = (unsigned)g.lab_src[arc0 + e] | ((unsigned)g.lab_dst[arc0 + e] << 16);
     if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
   }
+  __syncthreads();
   float* at = rows_s + warp * (2 * arow + 2 * nlp);
   float* bt = at + arow;
   float* xt = bt + arow;
   float* gt = xt + nlp;
-  const bool live = t < len;
-  if (live) {
+  const double costn = a.cost[b];
+  const bool feasible = costn > -1e19;
+  const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
+  const int V = a.scatter_V;
+  for (int q = 0; q < CB_FPW; ++q) {
+    const int t = blockIdx.x * CB_FR + q * CB_W + warp;
+    if (t >= len) break;
+    float* dst = a.gout + (long long)b * a.g_stride_b + (long long)t * a.g_stride_t;
+    if (!feasible) {  // no accepting path: zero posterior
+      if (!a.scatter_grad)
+        for (int j = lane; j < nl; j += 32) dst[j] = 0.f;
+      continue;
+    }
+    __syncwarp();
     const float4* as = reinterpret_cast<const float4*>(a.alpha_ws + ((long long)b * a.T + t) * arow);
     const float4* bs = reinterpret_cast<const float4*>(a.beta_ws + ((long long)b * a.T + t) * arow);
     const float4* xs = reinterpret_cast<const float4*>(a.x + (long long)b * a.x_stride_b + (long long)t * nlp);
@@ -1051,58 +1082,55 @@ __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, co
       reinterpret_cast<float4*>(bt)[i] = bs[i];
     }
     for (int i = lane; i < nlp / 4; i += 32) reinterpret_cast<float4*>(xt)[i] = xs[i];
-  }
-  __syncthreads();
-  if (!live) return;
-  float* dst = a.gout + (long long)b * a.g_stride_b + (long long)t * a.g_stride_t;
-  const double costn = a.cost[b];
-  if (!(costn > -1e19)) {  // no accepting path: zero posterior
-    for (int j = lane; j < nl; j += 32) dst[j] = 0.f;
-    return;
-  }
-  const double ct = (double)at[arow - 2] + (double)at[arow - 1];
-  const double dt = (double)bt[arow - 2] + (double)bt[arow - 1];
-  const float Kt = (float)(ct + dt - costn / kLn2);
-  const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
-  float ls = 0.f;
-  for (int base = 0; base < nl; base += 32) {
-    const int j = base + lane;
-    int e0 = 0, e1 = 0;
-    if (j < nl) {
-      e0 = lab_ptr[j];
-      e1 = lab_ptr[j + 1];
-    }
-    const bool heavy = (e1 - e0) > HEAVY;
-    float acc = 0.f;
-    if (j < nl && !heavy) {
-      const float kx = fmaf(xt[j], kLog2e, Kt);
-      for (int e = e0; e < e1; ++e) {
-        const unsigned pk = lab_pk[e];
-        acc += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+    __syncwarp();
+    const double ct = (double)at[arow - 2] + (double)at[arow - 1];
+    const double dt = (double)bt[arow - 2] + (double)bt[arow - 1];
+    const float Kt = (float)(ct + dt - costn / kLn2);
+    float ls = 0.f;
+    for (int base = 0; base < nl; base += 32) {
+      const int j = base + lane;
+      int e0 = 0, e1 = 0;
+      if (j < nl) {
+        e0 = lab_ptr[j];
+        e1 = lab_ptr[j + 1];
       }
-    }
-    unsigned hm = __ballot_sync(0xffffffffu, heavy);
-    while (hm) {  // labels with many arcs (the blank): the whole warp strides over the arcs
-      const int src_lane = __ffs(hm) - 1;
-      hm &= hm - 1;
-      const int jh = base + src_lane;
-      const int h0 = __shfl_sync(0xffffffffu, e0, src_lane), h1 = __shfl_sync(0xffffffffu, e1, src_lane);
-      const float kx = fmaf(xt[jh], kLog2e, Kt);
-      float part = 0.f;
-      for (int e = h0 + lane; e < h1; e += 32) {
-        const unsigned pk = lab_pk[e];
-        part += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+      const bool heavy = (e1 - e0) > HEAVY;
+      float acc = 0.f;
+      if (j < nl && !heavy) {
+        const float kx = fmaf(xt[j], kLog2e, Kt);
+        for (int e = e0; e < e1; ++e) {
+          const unsigned pk = lab_pk[e];
+          acc += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+        }
       }
-      part = warp_sum(part);
-      if (lane == src_lane) acc = part;
+      unsigned hm = __ballot_sync(0xffffffffu, heavy);
+      while (hm) {  // labels with many arcs (the blank): the whole warp strides over the arcs
+        const int src_lane = __ffs(hm) - 1;
+        hm &= hm - 1;
+        const int jh = base + src_lane;
+        const int h0 = __shfl_sync(0xffffffffu, e0, src_lane), h1 = __shfl_sync(0xffffffffu, e1, src_lane);
+        const float kx = fmaf(xt[jh], kLog2e, Kt);
+        float part = 0.f;
+        for (int e = h0 + lane; e < h1; e += 32) {
+          const unsigned pk = lab_pk[e];
+          part += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+        }
+        part = warp_sum(part);
+        if (lane == src_lane) acc = part;
+      }
+      if (j < nl) gt[j] = acc;
+      ls += acc;
     }
-    if (j < nl) gt[j] = acc;
-    ls += acc;
+    const float tot = warp_sum(ls);
+    const float sc = tot > 0.f ? gmul / tot : 0.f;
+    __syncwarp();
+    if (a.scatter_grad) {
+      float* out = a.scatter_grad + ((long long)t * a.B + b) * V;
+      for (int j = lane; j < nl; j += 32) out[g.lab_list[lo + j]] -= gt[j] * sc;
+    } else {
+      for (int j = lane; j < nl; j += 32) dst[j] = gt[j] * sc;
+    }
   }
-  const float tot = warp_sum(ls);
-  const float sc = tot > 0.f ? gmul / tot : 0.f;
-  __syncwarp();
-  for (int j = lane; j < nl; j += 32) dst[j] = gt[j] * sc;
 }
 
 }  // namespace
@@ -1123,53 +1151,58 @@ static cudaError_t launch_one(const PathArgs& a, int bytes, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+template <bool UNIT, int SPT, int DK>
+static cudaError_t launch_sweep_dk(const PathArgs& a, int bytes, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT, DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  num_sweep_kernel<UNIT, SPT, DK><<<dim3(a.B, a.write_grad ? 2 : 1), SW_TH, bytes, st>>>(a, a.g.max_states);
+  return cudaGetLastError();
+}
 template <bool UNIT, int SPT>
 static cudaError_t launch_sweep(const PathArgs& a, int bytes, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e != cudaSuccess) return e;
-  num_sweep_kernel<UNIT, SPT><<<dim3(a.B, a.write_grad ? 2 : 1), SW_TH, bytes, st>>>(a, a.g.max_states);
-  return cudaGetLastError();
+  if (SPT > 0 && a.g.max_in_degree <= 3 && a.g.max_out_degree <= 3) return launch_sweep_dk<UNIT, SPT, 3>(a, bytes, st);
+  return launch_sweep_dk<UNIT, SPT, DEG>(a, bytes, st);
 }
 
 bool num_split_supported(const PathArgs& a) {
   if (!a.beta_ws || !num_lin_supported(a)) return false;
   const int cb = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * 2 +
-                 CB_FR * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
+                 CB_W * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
   return cb <= 200 * 1024;
 }
 
-cudaError_t launch_num_split(const PathArgs& a, cudaStream_t st) {
+cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st) {
   const bool unit = a.g.unit_weights != 0;
   cudaError_t e;
-  {
-    ProfScope prof("num_sweep", st);
-    const SweepPlan P = sweep_plan(a.g.max_states, (int)a.x_stride_t, unit);
-    const int spt = (a.g.max_states + NS - 1) / NS;
-    if (spt <= 1) e = unit ? launch_sweep<true, 1>(a, P.bytes, st) : launch_sweep<false, 1>(a, P.bytes, st);
-    else if (spt == 2) e = unit ? launch_sweep<true, 2>(a, P.bytes, st) : launch_sweep<false, 2>(a, P.bytes, st);
-    else e = unit ? launch_sweep<true, 0>(a, P.bytes, st) : launch_sweep<false, 0>(a, P.bytes, st);
-    ++g_launches;
-    if (e != cudaSuccess) return e;
-  }
-  if (!a.write_grad) return e;
-  {
-    ProfScope prof("num_combine", st);
-    const int bytes = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
-                      CB_FR * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
-    const dim3 grid((a.T + CB_FR - 1) / CB_FR, a.B);
-    if (unit) {
-      e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-      if (e != cudaSuccess) return e;
-      num_combine_kernel<true><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
-    } else {
-      e = cudaFuncSetAttribute(num_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-      if (e != cudaSuccess) return e;
-      num_combine_kernel<false><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
-    }
-    ++g_launches;
-    e = cudaGetLastError();
-  }
+  ProfScope prof("num_sweep", st);
+  const SweepPlan P = sweep_plan(a.g.max_states, (int)a.x_stride_t, unit);
+  const int spt = (a.g.max_states + NS - 1) / NS;
+  if (spt <= 1) e = unit ? launch_sweep<true, 1>(a, P.bytes, st) : launch_sweep<false, 1>(a, P.bytes, st);
+  else if (spt == 2) e = unit ? launch_sweep<true, 2>(a, P.bytes, st) : launch_sweep<false, 2>(a, P.bytes, st);
+  else e = unit ? launch_sweep<true, 0>(a, P.bytes, st) : launch_sweep<false, 0>(a, P.bytes, st);
+  ++g_launches;
   return e;
+}
+
+cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st) {
+  if (!a.write_grad) return cudaSuccess;
+  const bool unit = a.g.unit_weights != 0;
+  cudaError_t e;
+  ProfScope prof("num_combine", st);
+  const int bytes = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
+                    CB_W * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
+  const dim3 grid((a.T + CB_FR - 1) / CB_FR, a.B);
+  if (unit) {
+    e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    num_combine_kernel<true><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
+  } else {
+    e = cudaFuncSetAttribute(num_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    num_combine_kernel<false><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
+  }
+  ++g_launches;
+  return cudaGetLastError();
 }
 
 cudaError_t launch_num_lin(const PathArgs& a_in, cudaStream_t st) {
