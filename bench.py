@@ -35,8 +35,10 @@ WORKLOADS = {
     "cfg4": ("CTC-GB contextual blanks", 2, 49, 256, 800, {"use_contextual_blanks": True}, None, True),
     "cfg5": ("CTC-G sweep shard", 2, 49, 256, 800, {}, None, True),
 }
-# dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_ncu_full_summary.md)
-NCU_TRAFFIC = {("cfg3", "bichar_den"): 613843712}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_e_ncu_full_summary.md;
+# bichar_den: the previous generation, profiles/r01_d_ncu_full_summary.md)
+NCU_TRAFFIC = {("cfg3", "bisweep"): 402027264, ("cfg3", "bicombine"): 449876992, ("cfg3", "num_sweep"): 9512448,
+               ("cfg3", "num_combine"): 206980352, ("cfg3", "bichar_den"): 613843712}
 CFG_INDEX = {"cfg1": 1, "cfg2": 2, "cfg2s": 2, "cfg3": 3, "cfg4": 4, "cfg5": 5}
 
 
@@ -324,7 +326,7 @@ def run_ours(args):
     # dominant kernel: one launch processes the whole batch (all `frames` utterance-frames)
     dom_gbs = alg_bytes / (kern[dom] * 1e-3) / 1e9 if dom else step_gbs
     # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-    # (profiles/r01_ncu_full_summary.md); only captured for the default workload
+    # (profiles/r01_e_ncu_full_summary.md); only captured for the default workload
     traffic = NCU_TRAFFIC.get((args.workload, dom))
     # every kernel against the bytes it must move itself (fp32): the sweeps read the logits once per
     # direction, the combine reads them once and writes the gradient once, the row kernels of plain CTC
