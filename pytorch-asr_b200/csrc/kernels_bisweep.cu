@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(MAXT, 1) bisweep_kernel(const BisweepArgs A) {
 // so the inner loops are branch free.  KW = floats per staged vector row.
 constexpr int KW = 72;
 template <int SCT, int KMAX>
-__global__ void __launch_bounds__(CTHREADS, 3) bicombine_kernel(const BisweepArgs A) {
+__global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArgs A) {
   const int S = SCT > 0 ? SCT : A.S;
   const int V = S * S;
   const int b = blockIdx.y, j = blockIdx.x, K = A.K, B = A.B, T = A.T, prowf = A.prowf;
@@ -614,12 +614,10 @@ __global__ void __launch_bounds__(CTHREADS, 3) bicombine_kernel(const BisweepArg
   const float* ckA = A.ck[0] + ((long long)b * A.nck + j) * V;
   const float* ckF = A.ck[1] + ((long long)b * A.nck + j) * V;
   const bool haveA = j > 0, haveF = t1 < len;
-  float en[KMAX];
-#pragma unroll
-  for (int f = 0; f < KMAX; ++f) en[f] = 0.f;
-  int c = tid / S, l = tid - c * S;
-  const int dc = CTHREADS / S, dl = CTHREADS - dc * S;
-  for (int v = tid; v < V; v += CTHREADS) {
+  // One class over the (at most KMAX) frames of the segment: e[] holds the logits on entry, the
+  // posteriors on exit.
+  auto walk = [&](int v, float (&e)[KMAX], const bool full) {
+    const int c = v / S, l = v - c * S;
     int pi = c, qi = l;
     bool m = loops && l != c;
     if (l == 0) {
@@ -634,60 +632,78 @@ __global__ void __launch_bounds__(CTHREADS, 3) bicombine_kernel(const BisweepArg
     // the checkpoints hold the sweeps' scaled values; cA rides on the forward recurrence (Ps has it too)
     float a = (m && haveA) ? ckA[v] * cA : 0.f;
     float fv = (m && haveF) ? ckF[v] : 0.f;
-    const float* xp = x0 + v;
-    float* gp = g0 + v;
-    float e[KMAX], ah[KMAX];
-    if (n == KMAX) {
-      // software pipeline: this class's logits were requested one iteration ago, the next class's go out now
-      if (v == tid) {
+    float ah[KMAX];
 #pragma unroll
-        for (int f = 0; f < KMAX; ++f) en[f] = ld_stream(xp + f * rstride);
-      }
-#pragma unroll
-      for (int f = 0; f < KMAX; ++f) e[f] = en[f];
-      if (v + CTHREADS < V) {
-#pragma unroll
-        for (int f = 0; f < KMAX; ++f) en[f] = ld_stream(xp + CTHREADS + f * rstride);
-      }
-#pragma unroll
-      for (int f = 0; f < KMAX; ++f) {
+    for (int f = 0; f < KMAX; ++f) {
+      if (full || f < n) {
         e[f] = ex2(fmaf(e[f], kLog2e, nmL[f]));
         ah[f] = (e[f] * scF[f]) * fmaf(mf, a, Ps[f][pi]);   // a_{t+1}[c][l] * cA
         a = ah[f];
       }
+    }
 #pragma unroll
-      for (int f = KMAX - 1; f >= 0; --f) {
+    for (int f = KMAX - 1; f >= 0; --f) {
+      if (full || f < n) {
         const float bh = fmaf(mf, fv, Qs[f][qi]);            // b_{t+1}[c][l]
-        st_stream(gp + f * rstride, ah[f] * (bh * cB[f]));
         fv = (e[f] * scB[f]) * bh;                           // f_t[c][l]
-      }
-    } else {
-#pragma unroll
-      for (int f = 0; f < KMAX; ++f)
-        if (f < n) e[f] = __ldg(xp + f * rstride);
-#pragma unroll
-      for (int f = 0; f < KMAX; ++f) {
-        if (f < n) {
-          e[f] = ex2(fmaf(e[f], kLog2e, nmL[f]));
-          ah[f] = (e[f] * scF[f]) * fmaf(mf, a, Ps[f][pi]);
-          a = ah[f];
-        }
-      }
-#pragma unroll
-      for (int f = KMAX - 1; f >= 0; --f) {
-        if (f < n) {
-          const float bh = fmaf(mf, fv, Qs[f][qi]);
-          gp[f * rstride] = ah[f] * (bh * cB[f]);
-          fv = (e[f] * scB[f]) * bh;
-        }
+        e[f] = ah[f] * (bh * cB[f]);
       }
     }
-    c += dc;
-    l += dl;
-    if (l >= S) {
-      l -= S;
-      ++c;
+  };
+  auto scalar_class = [&](int v) {
+    float e[KMAX];
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f)
+      if (f < n) e[f] = __ldg(x0 + v + f * rstride);
+    walk(v, e, false);
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f)
+      if (f < n) g0[v + f * rstride] = e[f];
+  };
+  // Rows start on arbitrary 4-byte boundaries.  When B*V is a multiple of 4 every frame of the
+  // segment has the same offset inside its 16-byte window, so a thread can take the same aligned
+  // 4-class chunk of all KMAX rows with 16-byte accesses; the <= 3 classes before the first and
+  // after the last full chunk (and every partial segment) go through the scalar path.
+  const long long i0 = ((long long)t0 * B + b) * V;
+  const bool vec = (n == KMAX) && ((rstride & 3) == 0);
+  if (!vec) {
+    for (int v = tid; v < V; v += CTHREADS) scalar_class(v);
+    return;
+  }
+  const int v0 = (int)((4 - (i0 & 3)) & 3);
+  const int nch = (V - v0) >> 2;
+  for (int k = tid; k < nch; k += CTHREADS) {
+    const int v = v0 + 4 * k;
+    float4 xv[KMAX];
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f) {
+      const float4* p = reinterpret_cast<const float4*>(x0 + v + f * rstride);
+      asm volatile("ld.global.cs.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(xv[f].x), "=f"(xv[f].y), "=f"(xv[f].z), "=f"(xv[f].w) : "l"(p));
     }
+    float e[KMAX];
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f) e[f] = xv[f].x;
+    walk(v, e, true);
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f) { xv[f].x = e[f]; e[f] = xv[f].y; }
+    walk(v + 1, e, true);
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f) { xv[f].y = e[f]; e[f] = xv[f].z; }
+    walk(v + 2, e, true);
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f) { xv[f].z = e[f]; e[f] = xv[f].w; }
+    walk(v + 3, e, true);
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f) {
+      xv[f].w = e[f];
+      float4* p = reinterpret_cast<float4*>(g0 + v + f * rstride);
+      asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(xv[f].x), "f"(xv[f].y), "f"(xv[f].z), "f"(xv[f].w) : "memory");
+    }
+  }
+  if (tid < v0) scalar_class(tid);
+  {
+    const int vt = v0 + 4 * nch + (tid - 32);
+    if (tid >= 32 && vt < V) scalar_class(vt);
   }
 }
 
