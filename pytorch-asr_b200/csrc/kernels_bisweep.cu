@@ -697,7 +697,7 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
     for (int f = 0; f < KMAX; ++f) {
       xv[f].w = e[f];
       float4* p = reinterpret_cast<float4*>(g0 + v + f * rstride);
-      asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(xv[f].x), "f"(xv[f].y), "f"(xv[f].z), "f"(xv[f].w) : "memory");
+      asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(xv[f].x), "f"(xv[f].y), "f"(xv[f].z), "f"(xv[f].w) : "memory");
     }
   }
   if (tid < v0) scalar_class(tid);

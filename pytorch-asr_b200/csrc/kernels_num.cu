@@ -1029,7 +1029,9 @@ __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, co
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int b = blockIdx.y;
+  // utterances in descending order: with the scatter fused in, the gradient rows written last by the
+  // denominator's combine kernel (the highest b) are the ones most likely to be L2 resident still
+  const int b = a.B - 1 - (int)blockIdx.y;
   const int len = min(a.lens[b], a.T);
   if (blockIdx.x * CB_FR >= len) return;
   const int gi = (g.num_graphs == 1) ? 0 : b;
@@ -1125,8 +1127,23 @@ __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, co
     const float sc = tot > 0.f ? gmul / tot : 0.f;
     __syncwarp();
     if (a.scatter_grad) {
+      // the labels of an utterance are distinct: all loads of a batch of 8 go out before the first store
       float* out = a.scatter_grad + ((long long)t * a.B + b) * V;
-      for (int j = lane; j < nl; j += 32) out[g.lab_list[lo + j]] -= gt[j] * sc;
+      for (int j0 = 0; j0 < nl; j0 += 256) {
+        float* ptr[8];
+        float cur[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int j = j0 + lane + 32 * u;
+          ptr[u] = out + ((j < nl) ? g.lab_list[lo + j] : 0);
+          if (j < nl) cur[u] = *ptr[u];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int j = j0 + lane + 32 * u;
+          if (j < nl) *ptr[u] = cur[u] - gt[j] * sc;
+        }
+      }
     } else {
       for (int j = lane; j < nl; j += 32) dst[j] = gt[j] * sc;
     }
