@@ -103,6 +103,9 @@ __device__ __forceinline__ float4 lds4(unsigned a) {
   asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
   return v;
 }
+__device__ __forceinline__ void sts4(unsigned a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ void sts(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
 __device__ __forceinline__ void stsi(unsigned a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 
@@ -207,6 +210,11 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
   }
   __syncthreads();
   auto frame_t = [&](int f) { return DIR == 0 ? f : len - 1 - f; };
+  // Odd S: the e row keeps the layout of the landed 16-byte aligned window (class v at float r + v,
+  // r = ((t*B + b) * V) mod 4), so the producers move it with 16-byte accesses; the pitch is S itself.
+  constexpr bool WIN = (SCT > 0) && ((SCT & 1) != 0);
+  const int B3_ = B & 3, b3_ = b & 3, V3_ = V & 3;
+  auto row_r = [&](int t) { return ((((t & 3) * B3_ + b3_) & 3) * V3_) & 3; };
 
   if (warp < nmain) {
     // ============================ main warps: the recursion ============================
@@ -226,9 +234,11 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     int es = 0;          // e stage of the frame being prefetched
     unsigned epar = 0;
     int ckc = !loops ? 0x7fffffff : (DIR == 0 ? KSEG : (len & (KSEG - 1)));  // frames until the next checkpoint
+    int fpre = 0;        // frame being prefetched
     auto prefetch = [&](float (&ev)[16], float& ed) {
       mbar_wait(e_full(es), epar);
-      const unsigned eb = eb_a + es * estride * 4 + ebase;
+      const unsigned eb = eb_a + es * estride * 4 + ebase + (WIN ? row_r(frame_t(fpre)) * 4 : 0);
+      ++fpre;
 #pragma unroll
       for (int s = 0; s < 16; ++s) ev[s] = lds(eb + soff(s));
       ed = lds(ed_a + es * RBW * 4 + edo);
@@ -403,10 +413,49 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       const int r = ((((t & 3) * B3 + b3) & 3) * V3) & 3;  // ((t*B + b) * V) mod 4
       const unsigned src = raw_a + (rs * rowf + r) * 4;
       const unsigned dst = eb_a + es * estride * 4;
+      const int roff = WIN ? r : 0;
       mbar_wait(raw_full(rs), (f / NRAW) & 1);
       PSEG(1)
       float mx = neg_inf();
-      if (SCT > 0) {
+      if (WIN) {
+        // 16-byte chunks of the window; floats that belong to the neighbouring rows become -inf (e = 0)
+        constexpr int NQ4 = SCT > 0 ? ((SCT * SCT + 3 + 3) / 4 + 31) / 32 : 1;
+        const unsigned srcw = raw_a + rs * rowf * 4;
+        const int hi = r + V, nchw = (hi + 3) >> 2;
+        float4 xq[NQ4];
+#pragma unroll
+        for (int q = 0; q < NQ4; ++q) {
+          const int ch = q * 32 + lane;
+          const float ninf = neg_inf();
+          xq[q] = make_float4(ninf, ninf, ninf, ninf);
+          if (!skip_ld && ch < nchw) xq[q] = lds4(srcw + ch * 16);
+          if (q == 0 || q == NQ4 - 1) {
+            const int w = 4 * ch;
+            if (w < r || w >= hi) xq[q].x = ninf;
+            if (w + 1 < r || w + 1 >= hi) xq[q].y = ninf;
+            if (w + 2 < r || w + 2 >= hi) xq[q].z = ninf;
+            if (w + 3 < r || w + 3 >= hi) xq[q].w = ninf;
+          }
+          mx = fmaxf(mx, fmaxf(fmaxf(xq[q].x, xq[q].y), fmaxf(xq[q].z, xq[q].w)));
+        }
+        mx = warp_max(mx);  // every lane's loads have landed in registers here
+        if (lane == 0) mbar_arrive(raw_empty(rs));
+        if (!(mx > neg_inf())) mx = 0.f;
+        const float nmL = -mx * kLog2e;
+        PSEG(2)
+        if (f >= NE) mbar_wait(e_empty(es), ((f / NE) - 1) & 1);
+        PSEG(3)
+        if (!skip_ex) {
+          const float2 l2 = splat2(kLog2e), n2 = splat2(nmL);
+#pragma unroll
+          for (int q = 0; q < NQ4; ++q) {
+            const int ch = q * 32 + lane;
+            const float2 y0 = ffma2(make_float2(xq[q].x, xq[q].y), l2, n2);
+            const float2 y1 = ffma2(make_float2(xq[q].z, xq[q].w), l2, n2);
+            if (ch < nchw) sts4(dst + ch * 16, make_float4(ex2(y0.x), ex2(y0.y), ex2(y1.x), ex2(y1.y)));
+          }
+        }
+      } else if (SCT > 0) {
         float xr[NQ];
         if (!skip_ld) {
 #pragma unroll
@@ -460,8 +509,8 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         const int c = lane + 32 * h;
         e0c[h] = egg[h] = 0.f;
         if (c < S) {
-          e0c[h] = lds(dst + (ctx ? c * PF : 0) * 4);
-          if (c >= 1) egg[h] = lds(dst + (c * PF + c) * 4);
+          e0c[h] = lds(dst + (roff + (ctx ? c * PF : 0)) * 4);
+          if (c >= 1) egg[h] = lds(dst + (roff + c * PF + c) * 4);
         }
       }
       __syncwarp();
@@ -470,8 +519,8 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         const int c = lane + 32 * h;
         if (c < S) {
           sts(ed_a + (es * RBW + c) * 4, e0c[h] + egg[h]);
-          sts(dst + (c * PF) * 4, 0.f);
-          sts(dst + (c * PF + c) * 4, 0.f);
+          sts(dst + (roff + c * PF) * 4, 0.f);
+          sts(dst + (roff + c * PF + c) * 4, 0.f);
         }
       }
       if (lane == 0) {
@@ -719,7 +768,7 @@ BisweepPlan bisweep_plan(int T, int B, int V, int S) {
   p.rowf = pad4(V + 3);
   p.prowf = pad4(S + 3);
   const int PF = S | 1;
-  p.estride = pad4(S * PF);
+  p.estride = pad4(S * PF + 3);
   p.epad = 16 * PF + 64;  // zeros behind the last stage: states o >= S read up to 15 rows past a stage
   p.K = KSEG;
   p.nck = (T + p.K - 1) / p.K + 1;
