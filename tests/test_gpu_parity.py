@@ -178,6 +178,20 @@ def test_full_vocabulary_slice_matches_fp64_oracle(P, variant):
     assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
 
 
+def test_all_row_alignments_and_vector_paths_match_fp64_oracle(P):
+    """B = 4 with V = 2401: the logits rows of the four utterances start at the four possible
+    offsets inside a 16-byte window (the sweeps' producers work on the aligned window) and
+    B*V is a multiple of 4, which is the condition for the 16-byte path of the combine kernel;
+    T = 43 leaves a partial last segment (scalar path) next to full ones."""
+    T, B = 43, 4
+    logits, lens, seqs = _random_case(2, 49, {}, T, B, seed=4242)
+    want_loss, want_grad = _oracle(2, 49, {}, logits, lens, seqs, True, None)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=49)
+    loss, grad = _run_fused(P, logits, lens, gen.get_training_graphs(seqs), gen.get_decoding_graph(), None, 49)
+    assert _rel(loss, want_loss.numpy()) < LOSS_RTOL
+    assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
+
+
 @pytest.mark.parametrize("S,args", [(49, {}), (49, {"use_contextual_blanks": True}), (36, {}),
                                     (11, {"allow_nonblank_selfloops": False})])
 def test_fused_bichar_kernel_equals_generic_csr_kernel(P, S, args):
