@@ -130,7 +130,7 @@ __host__ __device__ inline SwSmem sweep_smem(int rowf, int estride, int epad) {
   s.msum = o;   o += NPROD * 8;  // per-producer sums of the frame maxima (fp64)
   s.kflag = o;  o += 4 * 4;
   o = (o + 15) & ~15;
-  s.mbar = o;   o += (2 * NRAW + 2 * NE + 1) * 8;
+  s.mbar = o;   o += (2 * NRAW + 2 * NE + 2) * 8;
   s.bytes = o;
   return s;
 }
@@ -179,6 +179,10 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
   auto e_full = [&](int s) { return bar_a + (2 * NRAW + s) * 8; };
   auto e_empty = [&](int s) { return bar_a + (2 * NRAW + NE + s) * 8; };
   const unsigned prod_done = bar_a + (2 * NRAW + 2 * NE) * 8;
+  // Frame barrier of the recursion (main warps + scale warp) as an mbarrier, so that a warp can
+  // ARRIVE as soon as its part of the new vector is stored and only WAIT after it has issued the
+  // next frame's e loads: the prefetch leaves the per-frame chain.
+  const unsigned frame_bar = bar_a + (2 * NRAW + 2 * NE + 1) * 8;
   const int NB = (nmain + 1) * 32;  // threads of the per-frame barrier: main warps + scale warp
   float* spill = A.spill[DIR] + (long long)b * A.T * prowf;
   float* ck = A.ck[DIR] + (long long)b * A.nck * V;
@@ -205,6 +209,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         mbar_init(e_empty(s), nmain);
       }
       mbar_init(prod_done, NPROD);
+      mbar_init(frame_bar, nmain + 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
   }
@@ -259,12 +264,12 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
 #define MSEG(i)
 #endif
     auto step = [&](int f, const float (&ev)[16], const float ed, float (&evn)[16], float& edn) {
+      if (f > 0) mbar_wait(frame_bar, (f - 1) & 1);  // every group's entry of the vector entering frame f is stored
+      MSEG(4)
       const unsigned rb = rb_a + (f & 1) * RBW * 4 + rc;
       const float4 r0 = lds4(rb), r1 = lds4(rb + 16), r2 = lds4(rb + 128), r3 = lds4(rb + 144);
       const int kk = ldsi(kf_a + (f & 3) * 4);
       MSEG(0)
-      if (f + 1 < len) prefetch(evn, edn);  // next frame's e values: ready several frames ahead
-      MSEG(1)
       if (ckc == 0) {  // checkpoint of the per-state values entering this frame (explicit self-loops only)
         const int t = frame_t(f);
         float* cp = ck + (long long)(t / KSEG) * V;
@@ -303,10 +308,14 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       Rown = Rn;
       MSEG(2)
       if (k4 == 0 && gv) sts(rb_a + ((f + 1) & 1) * RBW * 4 + g * 4, Rn);
-      if (lane == 0) mbar_arrive(e_empty(f % NE));
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(frame_bar);
+        mbar_arrive(e_empty(f % NE));
+      }
       MSEG(3)
-      named_sync(1, NB);
-      MSEG(4)
+      if (f + 1 < len) prefetch(evn, edn);  // next frame's e values, behind the arrive: off the chain
+      MSEG(1)
     };
 #ifdef CTCG_SWEEP_TIMERS
     const long long mt0 = clock64();
@@ -323,8 +332,11 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       for (int f = 0; f < len; ++f) {
         mbar_wait(e_full(es), epar);
         if (++es == NE) { es = 0; epar ^= 1; }
-        if (lane == 0) mbar_arrive(e_empty(f % NE));
-        named_sync(1, NB);
+        if (lane == 0) {
+          mbar_arrive(e_empty(f % NE));
+          mbar_arrive(frame_bar);
+        }
+        mbar_wait(frame_bar, f & 1);
       }
     }
 #ifdef CTCG_SWEEP_TIMERS
@@ -340,6 +352,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     const float inf = __int_as_float(0x7f800000);
     bool dead = false;
     for (int f = 0; f < len; ++f) {
+      if (f > 0) mbar_wait(frame_bar, (f - 1) & 1);
       if (!(A.dbg & 8)) {
         const int t = frame_t(f);
         const unsigned rb = rb_a + (f & 1) * RBW * 4;
@@ -364,8 +377,10 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         kcur = knext;
         knext = knext2;
       }
-      named_sync(1, NB);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(frame_bar);
     }
+    if (len > 0) mbar_wait(frame_bar, (len - 1) & 1);
     if (DIR == 0) {  // total mass = sum_c P_len[c]; cost = log(mass) - K ln2 + sum of the frame maxima
       const unsigned rb = rb_a + (len & 1) * RBW * 4;
       const float v0 = lds(rb + lane * 4), v1 = lds(rb + (lane + 32) * 4);
