@@ -32,6 +32,7 @@
 // HBM traffic per valid frame (fp32 words): sweeps 2V (+ 2(S+3) + 2V/K), combine 2V (+ 2V/K).
 #include <cstdio>
 #include <cstdlib>
+#include <type_traits>
 
 #include "device_utils.cuh"
 #include "kernels.cuh"
@@ -263,10 +264,13 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
 #else
 #define MSEG(i)
 #endif
-    auto step = [&](int f, const float (&ev)[16], const float ed, float (&evn)[16], float& edn) {
-      if (f > 0) mbar_wait(frame_bar, (f - 1) & 1);  // every group's entry of the vector entering frame f is stored
+    const unsigned rb_ld = rb_a + rc, rb_st = rb_a + g * 4;
+    // PAR = f & 1 at compile time (the loop below is unrolled by two): buffer offsets become immediates
+    auto step = [&](auto par_tag, int f, const float (&ev)[16], const float ed, float (&evn)[16], float& edn) {
+      constexpr int PAR = decltype(par_tag)::value;
+      if (f > 0) mbar_wait(frame_bar, PAR ^ 1);  // every group's entry of the vector entering frame f is stored
       MSEG(4)
-      const unsigned rb = rb_a + (f & 1) * RBW * 4 + rc;
+      const unsigned rb = rb_ld + PAR * RBW * 4;
       const float4 r0 = lds4(rb), r1 = lds4(rb + 16), r2 = lds4(rb + 128), r3 = lds4(rb + 144);
       const int kk = ldsi(kf_a + (f & 3) * 4);
       MSEG(0)
@@ -307,7 +311,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       }
       Rown = Rn;
       MSEG(2)
-      if (k4 == 0 && gv) sts(rb_a + ((f + 1) & 1) * RBW * 4 + g * 4, Rn);
+      if (k4 == 0 && gv) sts(rb_st + (PAR ^ 1) * RBW * 4, Rn);
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(frame_bar);
@@ -324,10 +328,10 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       if (len > 0) prefetch(evA, edA);
       int f = 0;
       for (; f + 1 < len; f += 2) {
-        step(f, evA, edA, evB, edB);
-        step(f + 1, evB, edB, evA, edA);
+        step(std::integral_constant<int, 0>{}, f, evA, edA, evB, edB);
+        step(std::integral_constant<int, 1>{}, f + 1, evB, edB, evA, edA);
       }
-      if (f < len) step(f, evA, edA, evB, edB);
+      if (f < len) step(std::integral_constant<int, 0>{}, f, evA, edA, evB, edB);
     } else {  // timing experiment: hand-shakes and barriers only
       for (int f = 0; f < len; ++f) {
         mbar_wait(e_full(es), epar);
@@ -366,6 +370,8 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
           dead = true;
         }
         if (lane == 0) stsi(kf_a + ((f + 2) & 3) * 4, knext2);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(frame_bar);  // the vector is in registers: the spill below is off the chain
         float* sp = spill + (long long)t * prowf;
         if (lane < S) sp[lane] = v0;
         if (lane + 32 < S) sp[lane + 32] = v1;
@@ -376,9 +382,10 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
         Kcum += kcur;
         kcur = knext;
         knext = knext2;
+      } else {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(frame_bar);
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(frame_bar);
     }
     if (len > 0) mbar_wait(frame_bar, (len - 1) & 1);
     if (DIR == 0) {  // total mass = sum_c P_len[c]; cost = log(mass) - K ln2 + sum of the frame maxima
