@@ -37,8 +37,8 @@ WORKLOADS = {
 }
 # dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_e_ncu_full_summary.md;
 # bichar_den: the previous generation, profiles/r01_d_ncu_full_summary.md)
-NCU_TRAFFIC = {("cfg3", "bisweep"): 402286592, ("cfg3", "bicombine"): 448932352, ("cfg3", "num_sweep"): 9510400,
-               ("cfg3", "num_combine"): 205947136, ("cfg3", "bichar_den"): 613843712}
+NCU_TRAFFIC = {("cfg3", "bisweep"): 407014656, ("cfg3", "bicombine"): 448727808, ("cfg3", "num_sweep"): 9512960,
+               ("cfg3", "num_combine"): 205858304, ("cfg3", "bichar_den"): 613843712}
 CFG_INDEX = {"cfg1": 1, "cfg2": 2, "cfg2s": 2, "cfg3": 3, "cfg4": 4, "cfg5": 5}
 
 
