@@ -239,7 +239,10 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
     float evA[16], evB[16], edA = 0.f, edB = 0.f;
     int es = 0;          // e stage of the frame being prefetched
     unsigned epar = 0;
-    int ckc = !loops ? 0x7fffffff : (DIR == 0 ? KSEG : (len & (KSEG - 1)));  // frames until the next checkpoint
+    // steps until the values leaving a step are the checkpoint of the next frame (forward: frames 8j;
+    // backward: frames with t = 8j + 7, the all-zero one at the sweep's first frame is never read)
+    int ckc = !loops ? 0x7fffffff : (DIR == 0 ? KSEG : ((len & (KSEG - 1)) ? (len & (KSEG - 1)) : KSEG));
+    int esc = 0;  // e stage of the frame being consumed
     int fpre = 0;        // frame being prefetched
     auto prefetch = [&](float (&ev)[16], float& ed) {
       mbar_wait(e_full(es), epar);
@@ -274,20 +277,6 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       const float4 r0 = lds4(rb), r1 = lds4(rb + 16), r2 = lds4(rb + 128), r3 = lds4(rb + 144);
       const int kk = ldsi(kf_a + (f & 3) * 4);
       MSEG(0)
-      if (ckc == 0) {  // checkpoint of the per-state values entering this frame (explicit self-loops only)
-        const int t = frame_t(f);
-        float* cp = ck + (long long)(t / KSEG) * V;
-#pragma unroll
-        for (int s = 0; s < 16; ++s) {
-          const int o = 32 * (s >> 3) + 8 * k4 + (s & 7);
-          const bool valid = gv && o < S && (DIR == 0 ? g >= 1 : o >= 1);
-          const int cls = DIR == 0 ? o * S + g : g * S + o;
-          const float v = (s & 1) ? val[s >> 1].y : val[s >> 1].x;
-          if (valid) cp[cls] = v;
-        }
-        ckc = KSEG;
-      }
-      --ckc;
       val[0] = fmul2(make_float2(ev[0], ev[1]), ffma2(lf2, val[0], make_float2(r0.x, r0.y)));
       val[1] = fmul2(make_float2(ev[2], ev[3]), ffma2(lf2, val[1], make_float2(r0.z, r0.w)));
       val[2] = fmul2(make_float2(ev[4], ev[5]), ffma2(lf2, val[2], make_float2(r1.x, r1.y)));
@@ -301,24 +290,40 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
       float tot = s2.x + s2.y;
       tot += __shfl_xor_sync(0xffffffffu, tot, 8);
       tot += __shfl_xor_sync(0xffffffffu, tot, 16);
-      float Rn = fmaf(ed, Rown, tot);
-      if (kk != 0) {  // rare: power-of-two rescale decided two frames ago
-        const float sc = pow2i(kk);
-        const float2 sc2 = splat2(sc);
-#pragma unroll
-        for (int h = 0; h < 8; ++h) val[h] = fmul2(val[h], sc2);
-        Rn *= sc;
-      }
+      const float sc = pow2i(kk);  // power-of-two rescale decided two frames ago (1 almost always)
+      const float Rn = fmaf(ed, Rown, tot) * sc;
       Rown = Rn;
       MSEG(2)
       if (k4 == 0 && gv) sts(rb_st + (PAR ^ 1) * RBW * 4, Rn);
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(frame_bar);
-        mbar_arrive(e_empty(f % NE));
+        mbar_arrive(e_empty(esc));
       }
       MSEG(3)
-      if (f + 1 < len) prefetch(evn, edn);  // next frame's e values, behind the arrive: off the chain
+      // ---- everything below is off the per-frame chain ----
+      if (++esc == NE) esc = 0;
+      if (kk != 0) {
+        const float2 sc2 = splat2(sc);
+#pragma unroll
+        for (int h = 0; h < 8; ++h) val[h] = fmul2(val[h], sc2);
+      }
+      if (--ckc == 0) {  // the values entering frame f + 1 are a checkpoint (explicit self-loops only)
+        ckc = KSEG;
+        if (f + 1 < len) {
+          const int t = frame_t(f + 1);
+          float* cp = ck + (long long)(t / KSEG) * V;
+#pragma unroll
+          for (int s = 0; s < 16; ++s) {
+            const int o = 32 * (s >> 3) + 8 * k4 + (s & 7);
+            const bool valid = gv && o < S && (DIR == 0 ? g >= 1 : o >= 1);
+            const int cls = DIR == 0 ? o * S + g : g * S + o;
+            const float v = (s & 1) ? val[s >> 1].y : val[s >> 1].x;
+            if (valid) cp[cls] = v;
+          }
+        }
+      }
+      if (f + 1 < len) prefetch(evn, edn);  // next frame's e values
       MSEG(1)
     };
 #ifdef CTCG_SWEEP_TIMERS
