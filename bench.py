@@ -35,10 +35,9 @@ WORKLOADS = {
     "cfg4": ("CTC-GB contextual blanks", 2, 49, 256, 800, {"use_contextual_blanks": True}, None, True),
     "cfg5": ("CTC-G sweep shard", 2, 49, 256, 800, {}, None, True),
 }
-# dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_e_ncu_full_summary.md;
-# bichar_den: the previous generation, profiles/r01_d_ncu_full_summary.md)
+# dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_e_ncu_full_summary.md)
 NCU_TRAFFIC = {("cfg3", "bisweep"): 407014656, ("cfg3", "bicombine"): 448727808, ("cfg3", "num_sweep"): 9512960,
-               ("cfg3", "num_combine"): 205858304, ("cfg3", "bichar_den"): 613843712}
+               ("cfg3", "num_combine"): 205858304}
 CFG_INDEX = {"cfg1": 1, "cfg2": 2, "cfg2s": 2, "cfg3": 3, "cfg4": 4, "cfg5": 5}
 
 
@@ -331,7 +330,7 @@ def run_ours(args):
     # every kernel against the bytes it must move itself (fp32): the sweeps read the logits once per
     # direction, the combine reads them once and writes the gradient once, the row kernels of plain CTC
     # read + write once; the compact-column kernels of the numerator move far less than 8*V per frame
-    own_bytes = {"bisweep": 8.0 * V * frames, "bicombine": 8.0 * V * frames, "bichar_den": 8.0 * V * frames,
+    own_bytes = {"bisweep": 8.0 * V * frames, "bicombine": 8.0 * V * frames,
                  "rows": 8.0 * V * frames, "rows_ctx": 8.0 * V * frames}
     per_kernel = {}
     for k, v in kern.items():
@@ -347,8 +346,6 @@ def run_ours(args):
     if "bisweep" in kern:
         conc = ("denominator (bisweep -> bicombine) on a side stream, concurrent with the numerator "
                 "(gather -> num_sweep -> num_combine) on the caller's stream; joined before scatter_sub")
-    elif "bichar_den" in kern:
-        conc = "bichar_den runs on a side stream concurrently with gather+num_log"
     else:
         conc = "single stream"
     roof = {"bound": "hbm", "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak,

@@ -18,7 +18,7 @@ LIB = os.path.join(HERE, "libctcg_b200.so")
 STAMP = os.path.join(HERE, "build", "sources.sha256")
 
 SOURCES = ["graph.cpp", "graph_abi.cpp", "abi.cu", "kernels_path.cu", "kernels_rows.cu",
-           "kernels_aux.cu", "kernels_bichar.cu", "kernels_bisweep.cu", "kernels_num.cu", "kernels_post.cu"]
+           "kernels_aux.cu", "kernels_bisweep.cu", "kernels_num.cu", "kernels_post.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -28,10 +28,9 @@ NVCC_FLAGS = [
 ]
 
 
-# CTCG_TRACE_BUILD=1: compile the in-kernel clock stamps of the bi-char kernel in
-# (profiles/trace_roles.py); off in the product build, they cost ~3 % of its instructions.
+# CTCG_TRACE_BUILD=1: compile the per-role cycle counters of bisweep_kernel in
+# (profiles/micro/run_tim.sh, CTCG_SWEEP_DEBUG=256); off in the product build.
 if os.environ.get("CTCG_TRACE_BUILD") == "1":
-    NVCC_FLAGS.append("-DCTCG_BICHAR_TRACE_BUILD")
     NVCC_FLAGS.append("-DCTCG_SWEEP_TIMERS")  # per-role cycle counters of bisweep_kernel (CTCG_SWEEP_DEBUG=256)
 
 

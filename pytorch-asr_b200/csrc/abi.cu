@@ -34,25 +34,16 @@ struct Plan {
   size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, beta_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
   size_t pspill = 0, ckpt = 0;
   size_t spill2 = 0, ckpt2 = 0, fin = 0;
-  BicharPlan bi{};   // bi.ok: the denominator runs on the factorised bi-char kernels
-  BisweepPlan sw{};  // split-sweep kernels (default); bi describes the single-CTA kernel (CTCG_BICHAR_LEGACY=1)
+  BisweepPlan sw{};  // sw.ok: the denominator runs on the factorised bi-char kernels (kernels_bisweep.cu)
   size_t total = 0;
 };
 
-bool legacy_bichar() {
-  static const bool on = [] {
-    const char* e = std::getenv("CTCG_BICHAR_LEGACY");
-    return e && e[0] == '1';
-  }();
-  return on;
-}
-
 // The factorised kernels cover the bi-char decoding graph of ctcg_decoding_graph (shared by the batch).
-BicharPlan structured_plan(int T, int B, int V, const ctcg_graph* den) {
-  BicharPlan none{};
+BisweepPlan structured_plan(int T, int B, int V, const ctcg_graph* den) {
+  BisweepPlan none{};
   if (!den || den->structured.kind != 2 || den->num_graphs != 1) return none;
   if (den->structured.S * den->structured.S != V) return none;
-  return bichar_plan(T, B, V, den->structured.S);
+  return bisweep_plan(T, B, V, den->structured.S);
 }
 
 Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den) {
@@ -76,13 +67,11 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
   }
   p.rowlse = take(TB * 4);
   if (den) {
-    p.bi = structured_plan(T, B, V, den);
+    p.sw = structured_plan(T, B, V, den);
     p.cost_den = take((size_t)B * 8);
-    if (p.bi.ok) p.sw = bisweep_plan(T, B, V, den->structured.S);
-    if (p.bi.ok && !p.sw.ok) p.bi.ok = 0;
-    if (p.bi.ok) {
-      p.pspill = take(std::max(p.bi.pspill_bytes, p.sw.spill_bytes));
-      p.ckpt = take(std::max(p.bi.ckpt_bytes, p.sw.ckpt_bytes));
+    if (p.sw.ok) {
+      p.pspill = take(p.sw.spill_bytes);
+      p.ckpt = take(p.sw.ckpt_bytes);
       p.spill2 = take(p.sw.spill_bytes);
       p.ckpt2 = take(p.sw.ckpt_bytes);
       p.fin = take((size_t)B * sizeof(BiFin));
@@ -266,58 +255,32 @@ namespace {
 
 int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, int V, const int32_t* lens,
                const ctcg_graph* den, double* cost, float* grad, const float* grad_scale, cudaStream_t st) {
-  if (!legacy_bichar()) {
-    BisweepArgs s{};
-    s.x = x;
-    s.total = (long long)T * B * V;
-    s.T = T;
-    s.B = B;
-    s.V = V;
-    s.S = den->structured.S;
-    s.lens = lens;
-    s.loops = den->structured.allow_nonblank_selfloops;
-    s.ctx = den->structured.use_contextual_blanks;
-    s.spill[0] = reinterpret_cast<float*>(ws + p.pspill);
-    s.spill[1] = reinterpret_cast<float*>(ws + p.spill2);
-    s.ck[0] = reinterpret_cast<float*>(ws + p.ckpt);
-    s.ck[1] = reinterpret_cast<float*>(ws + p.ckpt2);
-    s.prowf = p.sw.prowf;
-    s.nck = p.sw.nck;
-    s.K = p.sw.K;
-    s.cost = cost;
-    s.fin = reinterpret_cast<BiFin*>(ws + p.fin);
-    s.grad = grad;
-    s.g_scale = grad_scale;
-    s.nmain = p.sw.nmain;
-    s.rowf = p.sw.rowf;
-    s.estride = p.sw.estride;
-    s.epad = p.sw.epad;
-    CTCG_CUDA(launch_bisweep(s, p.sw, st));
-    return CTCG_OK;
-  }
-  BicharArgs a{};
-  a.x = x;
-  a.total = (long long)T * B * V;
-  a.T = T;
-  a.B = B;
-  a.V = V;
-  a.S = den->structured.S;
-  a.lens = lens;
-  a.loops = den->structured.allow_nonblank_selfloops;
-  a.ctx = den->structured.use_contextual_blanks;
-  a.pspill = reinterpret_cast<float*>(ws + p.pspill);
-  a.prowf = p.bi.prowf;
-  a.ckpt = reinterpret_cast<float*>(ws + p.ckpt);
-  a.nck = p.bi.nck;
-  a.cost = cost;
-  a.grad = grad;
-  a.g_scale = grad_scale;
-  a.K = p.bi.K;
-  a.DB = p.bi.DB;
-  a.NR = p.bi.NR;
-  a.rowf = p.bi.rowf;
-  a.nmain = p.bi.nmain;
-  CTCG_CUDA(launch_bichar_den(a, p.bi, st));
+  BisweepArgs s{};
+  s.x = x;
+  s.total = (long long)T * B * V;
+  s.T = T;
+  s.B = B;
+  s.V = V;
+  s.S = den->structured.S;
+  s.lens = lens;
+  s.loops = den->structured.allow_nonblank_selfloops;
+  s.ctx = den->structured.use_contextual_blanks;
+  s.spill[0] = reinterpret_cast<float*>(ws + p.pspill);
+  s.spill[1] = reinterpret_cast<float*>(ws + p.spill2);
+  s.ck[0] = reinterpret_cast<float*>(ws + p.ckpt);
+  s.ck[1] = reinterpret_cast<float*>(ws + p.ckpt2);
+  s.prowf = p.sw.prowf;
+  s.nck = p.sw.nck;
+  s.K = p.sw.K;
+  s.cost = cost;
+  s.fin = reinterpret_cast<BiFin*>(ws + p.fin);
+  s.grad = grad;
+  s.g_scale = grad_scale;
+  s.nmain = p.sw.nmain;
+  s.rowf = p.sw.rowf;
+  s.estride = p.sw.estride;
+  s.epad = p.sw.epad;
+  CTCG_CUDA(launch_bisweep(s, p.sw, st));
   return CTCG_OK;
 }
 
@@ -400,11 +363,11 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
 
   // A per-frame softmax normaliser cancels between numerator and denominator.
   const bool softmax = (normalize == CTCG_NORM_SOFTMAX) && !den;
-  const bool fused_den = den && p.bi.ok && aligned16(logits) && aligned16(grad);
-  if (den && p.bi.ok && !fused_den) return CTCG_EUNSUPPORTED;  // misaligned tensors: the workspace was planned for the fused kernel
+  const bool fused_den = den && p.sw.ok && aligned16(logits) && aligned16(grad);
+  if (den && p.sw.ok && !fused_den) return CTCG_EUNSUPPORTED;  // misaligned tensors: the workspace was planned for the fused kernel
   SideStream* side = fused_den ? side_stream() : nullptr;
   if (fused_den) {
-    // 1'. factorised bi-char denominator (kernels_bichar.cu), writes +gamma_den rows; concurrent with 1-2
+    // 1'. factorised bi-char denominator (kernels_bisweep.cu), writes +gamma_den rows; concurrent with 1-2
     cudaStream_t ds = st;
     if (side) {
       CTCG_CUDA(cudaEventRecord(side->fork, st));
@@ -450,12 +413,8 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     a.g_sign = 1.f;
     a.g_scale = nullptr;
     a.write_grad = grad != nullptr;
-    static const bool num_legacy = [] {
-      const char* e = std::getenv("CTCG_NUM_LEGACY");
-      return e && e[0] == '1';
-    }();
     a.beta_ws = reinterpret_cast<float*>(ws + p.beta_num);
-    if (!num_legacy && num_split_supported(a)) {
+    if (num_split_supported(a)) {
       CTCG_CUDA(launch_num_sweeps(a, st));
       num_args = a;
       split_num = true;
@@ -467,8 +426,9 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
       }();
       scatter_num = fused_den && grad && fuse_scatter;
       if (!scatter_num) CTCG_CUDA(launch_num_combine(a, st));
-    } else if (num_lin_supported(a)) CTCG_CUDA(launch_num_lin(a, st));
-    else CTCG_CUDA(launch_path_fwd_bwd(a, true, st));
+    } else {
+      CTCG_CUDA(launch_path_fwd_bwd(a, true, st));  // graphs the split kernels do not take: generic CSR kernel
+    }
     return CTCG_OK;
   }();
   {
@@ -571,7 +531,7 @@ int ctcg_path_sum(const float* log_probs, int32_t T, int32_t B, int32_t V, const
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   int32_t* lens = nullptr;
   const Plan ps = make_plan(T, B, V, nullptr, graph);
-  if (ps.bi.ok && aligned16(log_probs) && aligned16(grad)) {
+  if (ps.sw.ok && aligned16(log_probs) && aligned16(grad)) {
     if (workspace_bytes < ps.total) return CTCG_EWORKSPACE;
     if ((st_ = upload_lens(ps, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
     double* c64 = reinterpret_cast<double*>(ws + ps.cost_den);

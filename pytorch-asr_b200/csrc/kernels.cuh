@@ -29,18 +29,15 @@ struct PathArgs {
   float g_sign;
   const float* g_scale;   // nullable, per-utterance multiplier
   int32_t write_grad;
-  int32_t dbg;            // timing experiments only (CTCG_NUM_DEBUG bit mask: roles skip their work); 0 in production
+  int32_t dbg;            // reserved for timing experiments; 0 in production
 };
 
 // compact = 1: x / gout are the per-utterance compact label columns produced by
 // launch_gather (16-byte aligned rows, prescaled), staged through a cp.async ring.
 cudaError_t launch_path_fwd_bwd(const PathArgs& a, bool compact, cudaStream_t st);
 
-// Warp-per-utterance linear-domain variant for small graphs (kernels_num.cu); same arguments
-// as the compact mode above.
-bool num_lin_supported(const PathArgs& a);
-cudaError_t launch_num_lin(const PathArgs& a, cudaStream_t st);
-// Split variant: alpha and beta sweeps on separate CTAs at the same time, then a time-parallel combine.
+// Numerator on the compact columns (kernels_num.cu): alpha and beta sweeps on separate CTAs at the same
+// time, then a time-parallel combine; same arguments as the compact mode above.
 bool num_split_supported(const PathArgs& a);
 cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st);
 // Posteriors from the spilled rows; with a.scatter_grad set they are subtracted from the dense gradient directly.
@@ -78,33 +75,6 @@ cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* l
 
 cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uint64_t* counts,
                               cudaStream_t st);
-
-// Arguments of the fused bi-char denominator kernel (kernels_bichar.cu).
-struct BicharArgs {
-  const float* x;          // logits (T, B, V), raw
-  long long total;         // T*B*V
-  int32_t T, B, V, S;
-  const int32_t* lens;     // device [B]
-  int32_t loops, ctx;      // allow_nonblank_selfloops, use_contextual_blanks (after loop_using_symbol_repetitions)
-  float* pspill;           // [B][T][prowf]: P_t[0..S), frame max, k_t, K_{t+1}
-  int32_t prowf;
-  float* ckpt;             // [B][nck][V]: scaled alpha at frames K, 2K, ...
-  int32_t nck;
-  double* cost;            // [B] natural-log path sum over the decoding graph
-  float* grad;             // (T, B, V) nullable: receives g_scale[b] * gamma_den
-  const float* g_scale;    // nullable
-  int32_t K, DB, NR, rowf, nmain;
-  long long* trace;        // diagnostics only (CTCG_BICHAR_TRACE): [warps][trace_steps][2] clocks of CTA 0
-  int32_t trace_steps;
-  int32_t dbg;             // timing experiments only (CTCG_BICHAR_DEBUG bit mask: roles skip their work)
-};
-// Workspace floats needed per batch (pspill + ckpt); smem plan and launch.
-struct BicharPlan {
-  int32_t ok, K, DB, NR, rowf, nmain, prowf, nck, threads, ru;
-  size_t smem_bytes, pspill_bytes, ckpt_bytes;
-};
-BicharPlan bichar_plan(int T, int B, int V, int S);
-cudaError_t launch_bichar_den(const BicharArgs& a, const BicharPlan& p, cudaStream_t st);
 
 // Split-sweep bi-char denominator (kernels_bisweep.cu): forward and backward recursions on
 // separate CTAs at the same time, then an elementwise combine over the whole GPU.
