@@ -178,6 +178,21 @@ def test_full_vocabulary_slice_matches_fp64_oracle(P, variant):
     assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
 
 
+@pytest.mark.parametrize("S,args", [(12, {}), (49, {"use_contextual_blanks": True})])
+def test_wide_logit_spread_exercises_the_power_of_two_rescale(P, S, args):
+    """Logits ~ 12 * N(0,1): the scaled-linear sweeps of the bi-char denominator leave their
+    exponent band every few frames, so the lagged power-of-two rescale (sweeps) and its replay in
+    the combine kernel are on the path (oracle/bichar_model.py shows it firing at this spread)."""
+    T, B = 96, 3
+    logits, lens, seqs = _random_case(2, S, args, T, B, seed=977 + S)
+    logits = (logits * 4).astype(np.float32)
+    want_loss, want_grad = _oracle(2, S, args, logits, lens, seqs, True, None)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
+    loss, grad = _run_fused(P, logits, lens, gen.get_training_graphs(seqs), gen.get_decoding_graph(), None, S)
+    assert _rel(loss, want_loss.numpy()) < LOSS_RTOL
+    assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
+
+
 def test_all_row_alignments_and_vector_paths_match_fp64_oracle(P):
     """B = 4 with V = 2401: the logits rows of the four utterances start at the four possible
     offsets inside a 16-byte window (the sweeps' producers work on the aligned window) and
