@@ -253,3 +253,21 @@ class GraphGen(object):
                                     nc_weight=self.nc_weight)
             self._dec = [m[None] for m in mats]
         return self._dec
+
+
+def collapse_by_arc_table(g, frame_labels):
+    """Emitted symbols of the (unique) path that reads ``frame_labels`` in the input-deterministic
+    graph ``g``: what ``shortestpath(compose(chain, dec_fst))`` + the olabel read-out of
+    advanced_decoder.py:556-571 returns.  Walks the arc table; ``None`` if the sequence is no path."""
+    out_arcs = g.out_lists()
+    state, out = 0, []
+    for v in frame_labels:
+        nxt = [a for a in out_arcs[state] if a[2] == int(v)]
+        if len(nxt) != 1:
+            return None
+        a = nxt[0]
+        if a[3] > 0:
+            out.append(a[3])
+        state = a[1]
+    return out
+

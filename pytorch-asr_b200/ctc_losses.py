@@ -182,6 +182,38 @@ class FSTLossMixin(object):
         return {"fst_loss": fst_loss_, "loss": fst_loss_}
 
 
+    def decode(self, encoded, encoded_lens, texts=None, text_lens=None,
+               return_texts_and_generated_loss=False, return_logits_text_diff=False, spkids=None,
+               **other_data_in_batch):
+        """``FSTDecoder.decode`` (advanced_decoder.py:536-593): best path through the decoding graph
+        (tropical reduction on the device), then the collapse of its frame labels to symbols by
+        walking the topology rule (:556-571 does it with OpenFst compose + shortestpath)."""
+        from . import _lib
+        logits = self.logits(encoded, encoded_lens)
+        gg = self.graph_generator
+        lens = _check_lens(encoded_lens)
+        _, frame_labels = _lib.viterbi(logits.detach(), lens, gg.get_decoding_graph())
+        frame_labels = frame_labels.cpu()
+        decoded_texts = [gg.collapse(frame_labels[:lens[i], i]) for i in range(logits.size(1))]
+        ret = {"decoded": decoded_texts, "logits": logits}
+        if texts is not None and text_lens is not None:
+            fst_text_losses = self.get_fst_loss(logits, encoded_lens, texts, text_lens, other_data_in_batch)
+            fst_text_loss = fst_text_losses.sum()
+            ret["loss"] = dict(fst_loss=fst_text_loss, loss=fst_text_loss)
+        if return_texts_and_generated_loss:
+            decoded_lens = torch.IntTensor([len(x) for x in decoded_texts])
+            width = max(1, int(decoded_lens.max())) if len(decoded_texts) else 1
+            padded = torch.zeros((len(decoded_texts), width), dtype=torch.int64)
+            for i, x in enumerate(decoded_texts):
+                padded[i, :len(x)] = torch.as_tensor(x, dtype=torch.int64)
+            fst_generated_losses = self.get_fst_loss(logits, encoded_lens, padded, decoded_lens, None)
+            ret["text_loss"] = fst_text_losses.tolist()
+            ret["generated_loss"] = fst_generated_losses.tolist()
+        if return_logits_text_diff:
+            ret["logits_text_diff"] = (torch.as_tensor(encoded_lens) - torch.as_tensor(text_lens)).tolist()
+        return ret
+
+
 class FSTLoss(FSTLossMixin, torch.nn.Module):
     """Stand-alone loss head with ``FSTDecoder``'s constructor arguments that
     matter for the loss (advanced_decoder.py:395-411); ``fc`` defaults to identity

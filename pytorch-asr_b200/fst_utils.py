@@ -160,6 +160,54 @@ def path_reduction(log_probs, act_lens, graph_matrices, red_kind="logsumexp", ne
     return _PathViterbi.apply(log_probs, lens, graph)
 
 
+def collapse_frame_labels(frame_labels, context_order, num_symbols, allow_nonblank_selfloops=True,
+                          use_contextual_blanks=False, loop_using_symbol_repetitions=False):
+    """Frame-level class ids of a best path -> emitted symbols.
+
+    Replaces ``shortestpath(compose(chain(idx), dec_fst))`` followed by the read-out of the
+    non-zero olabels in ``FSTDecoder.decode`` (advanced_decoder.py:556-571): the decoding graphs
+    of fst_utils.py:694-712 / 765-817 are input-deterministic, so the path of a class sequence is
+    unique and can be walked with the topology rule itself -- no OpenFst, no arc table.
+    Raises ``ValueError`` when the sequence is not a path of the graph (the composition would be
+    empty)."""
+    S = int(num_symbols)
+    labels = [int(v) for v in (frame_labels.tolist() if hasattr(frame_labels, "tolist") else frame_labels)]
+    out = []
+    if context_order == 1:
+        state = 0
+        for v in labels:
+            if not 0 <= v < S:
+                raise ValueError("class %d is not a label of the mono-char decoding graph" % v)
+            if v != state:
+                if v != 0:
+                    out.append(v)
+                state = v
+        return out
+    assert context_order == 2
+    loops, ctx = bool(allow_nonblank_selfloops), bool(use_contextual_blanks)
+    rep = bool(loop_using_symbol_repetitions)
+    if rep:
+        loops, ctx = False, True
+    c1, l1 = 0, 0
+    for v in labels:
+        if not 0 <= v < S * S:
+            raise ValueError("class %d is not a label of the bi-char decoding graph" % v)
+        cls1 = c1 * S + l1 if (l1 != 0 or ctx) else 0
+        if loops and l1 != 0 and c1 != l1 and v == cls1:
+            continue                                  # explicit self-loop, emits nothing
+        c2 = c1 if l1 == 0 else l1
+        if v == 0 and not ctx:
+            l2 = 0
+        else:
+            cv, l2 = divmod(v, S)
+            if cv != c2 or (l2 == 0 and not ctx):
+                raise ValueError("class %d cannot follow state (%d, %d)" % (v, c1, l1))
+        if not (l2 == 0 or (c1, l1) == (c2, l2) or (rep and l1 == l2)):
+            out.append(l2)
+        c1, l1 = c2, l2
+    return out
+
+
 def setattr_matched(obj, var, val):
     val_orig = getattr(obj, var)
     if val_orig is not None:
@@ -243,6 +291,10 @@ class BaseGraphGen(object):
 
     def get_decoding_graph(self):
         return self.decoding_fst
+
+    def collapse(self, frame_labels):
+        """Emitted symbols of the path that reads ``frame_labels`` (class ids) in the decoding graph."""
+        return collapse_frame_labels(frame_labels, self.context_order, self.num_symbols, **self._build_args())
 
 
 class CTCGraphGen(BaseGraphGen):

@@ -359,3 +359,45 @@ def test_ctc_forward_postprocessing(P, flags):
     assert np.abs(got - want).max() < 1e-5
     ref32 = pp.postprocess(lp.numpy(), dtype=np.float32, **flags)        # what the reference would write
     assert np.abs(got - ref32).max() < 2e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("order", [1, 2])
+def test_decode_returns_the_transcript_on_peaked_logits(P, order):
+    """FSTDecoder.decode (advanced_decoder.py:536-593) through the stand-alone head: Viterbi frame
+    labels on the device, collapse by the topology rule; logits peaked on an alignment of the
+    transcript (symbol held one extra frame where the graph has a self-loop, blank in between)."""
+    S, B = 9, 3
+    rng = np.random.default_rng(31 + order)
+    seqs = [rng.integers(1, S, size=n).tolist() for n in (7, 5, 4)]
+    aligns = []
+    for seq in seqs:
+        frames, ctx_sym = [], 0
+        for cur in seq:
+            cls = cur if order == 1 else ctx_sym * S + cur
+            frames.append(cls)
+            if order == 1 or ctx_sym != cur:
+                frames.append(cls)          # hold: explicit self-loop
+            frames.append(0)                # blank (global)
+            ctx_sym = cur
+        aligns.append(frames)
+    lens = sorted((len(a) for a in aligns), reverse=True)
+    order_idx = sorted(range(B), key=lambda i: -len(aligns[i]))
+    aligns = [aligns[i] for i in order_idx]
+    seqs = [seqs[i] for i in order_idx]
+    T, V = lens[0], S ** order
+    logits = (rng.standard_normal((T, B, V)) * 0.5).astype(np.float32)
+    for b, a in enumerate(aligns):
+        for t, c in enumerate(a):
+            logits[t, b, c] += 12
+    gen = P.CTCGraphGen(context_order=order, graph_build_args={}, num_symbols=S)
+    head = P.FSTLoss(gen, normalize_by_dim=None)
+    U = max(len(q) for q in seqs)
+    texts = torch.zeros((B, U), dtype=torch.int64)
+    for i, q in enumerate(seqs):
+        texts[i, :len(q)] = torch.tensor(q)
+    ret = head.decode(torch.from_numpy(logits).cuda(), torch.tensor(lens), texts,
+                      torch.tensor([len(q) for q in seqs]))
+    assert ret["decoded"] == seqs
+    assert torch.isfinite(ret["loss"]["loss"]).item()
+
