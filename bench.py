@@ -345,7 +345,7 @@ def run_ours(args):
         per_kernel[k] = ent
     if "bisweep" in kern:
         conc = ("denominator (bisweep -> bicombine) on a side stream, concurrent with the numerator "
-                "(gather -> num_sweep -> num_combine) on the caller's stream; joined before scatter_sub")
+                "(gather -> num_sweep -> num_combine) on the caller's stream; joined before the numerator subtracts its posteriors (num_combine) and final")
     else:
         conc = "single stream"
     roof = {"bound": "hbm", "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak,
