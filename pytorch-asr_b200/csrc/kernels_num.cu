@@ -324,7 +324,7 @@ constexpr int CB_TH = CB_W * 32;
 // every (t, b, label) is touched by exactly one lane, no atomics); otherwise the compact rows
 // gout[b][t][j] are written for the row kernels of plain CTC.
 template <bool UNIT>
-__global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
+__global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -387,6 +387,20 @@ __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, co
     const double ct = (double)at[arow - 2] + (double)at[arow - 1];
     const double dt = (double)bt[arow - 2] + (double)bt[arow - 1];
     const float Kt = (float)(ct + dt - costn / kLn2);
+    // scatter mode: the gradient entries this frame will touch are requested now, so that their DRAM
+    // latency runs behind the posterior sums (first 256 labels; the labels of an utterance are distinct)
+    float* out = a.scatter_grad ? a.scatter_grad + ((long long)t * a.B + b) * V : nullptr;
+    float* ptr[8];
+    float cur[8];
+    if (out) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int j = lane + 32 * u;
+        ptr[u] = out + ((j < nl) ? g.lab_list[lo + j] : 0);
+        cur[u] = 0.f;
+        if (j < nl) cur[u] = __ldcg(ptr[u]);
+      }
+    }
     float ls = 0.f;
     for (int base = 0; base < nl; base += 32) {
       const int j = base + lane;
@@ -426,21 +440,24 @@ __global__ void __launch_bounds__(CB_TH) num_combine_kernel(const PathArgs a, co
     const float sc = tot > 0.f ? gmul / tot : 0.f;
     __syncwarp();
     if (a.scatter_grad) {
-      // the labels of an utterance are distinct: all loads of a batch of 8 go out before the first store
-      float* out = a.scatter_grad + ((long long)t * a.B + b) * V;
-      for (int j0 = 0; j0 < nl; j0 += 256) {
-        float* ptr[8];
-        float cur[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int j = lane + 32 * u;
+        if (j < nl) *ptr[u] = cur[u] - gt[j] * sc;
+      }
+      for (int j0 = 256; j0 < nl; j0 += 256) {  // more than 256 distinct labels: batches of 8 loads, then 8 stores
+        float* p2[8];
+        float c2[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const int j = j0 + lane + 32 * u;
-          ptr[u] = out + ((j < nl) ? g.lab_list[lo + j] : 0);
-          if (j < nl) cur[u] = *ptr[u];
+          p2[u] = out + ((j < nl) ? g.lab_list[lo + j] : 0);
+          if (j < nl) c2[u] = *p2[u];
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const int j = j0 + lane + 32 * u;
-          if (j < nl) *ptr[u] = cur[u] - gt[j] * sc;
+          if (j < nl) *p2[u] = c2[u] - gt[j] * sc;
         }
       }
     } else {
