@@ -348,7 +348,10 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
   int* lab_ptr = reinterpret_cast<int*>(sm + take((maxL + 1) * 4));
   unsigned* lab_pk = reinterpret_cast<unsigned*>(sm + take(maxA * 4));
   float* lab_w = reinterpret_cast<float*>(sm + (UNIT ? 0 : take(maxA * 4)));
-  float* rows_s = reinterpret_cast<float*>(sm + take(CB_W * (2 * arow + 2 * nlp) * 4));
+  // per warp: two staging buffers {alpha row, beta row, x row} (the next frame's rows are copied in with
+  // cp.async while this frame's posteriors are summed) and one posterior row
+  const int stg = 2 * arow + nlp;
+  float* rows_s = reinterpret_cast<float*>(sm + take(CB_W * (2 * stg + nlp) * 4));
   const int arc0 = g.in_ptr[ro];
   const int narcs = g.in_ptr[ro + n] - arc0;
   for (int j = tid; j <= nl; j += CB_TH) lab_ptr[j] = g.lab_ptr[lo + gi + j] - arc0;
@@ -357,14 +360,28 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
     if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
   }
   __syncthreads();
-  float* at = rows_s + warp * (2 * arow + 2 * nlp);
-  float* bt = at + arow;
-  float* xt = bt + arow;
-  float* gt = xt + nlp;
+  float* wbase = rows_s + warp * (2 * stg + nlp);
+  float* gt = wbase + 2 * stg;
   const double costn = a.cost[b];
   const bool feasible = costn > -1e19;
   const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
   const int V = a.scatter_V;
+  auto stage = [&](int q) {  // always commits a group (possibly empty), so that the wait counts stay uniform
+    const int t = blockIdx.x * CB_FR + q * CB_W + warp;
+    if (q < CB_FPW && t < len && feasible) {
+      float* d = wbase + (q & 1) * stg;
+      const float* as = a.alpha_ws + ((long long)b * a.T + t) * arow;
+      const float* bs = a.beta_ws + ((long long)b * a.T + t) * arow;
+      const float* xs = a.x + (long long)b * a.x_stride_b + (long long)t * nlp;
+      for (int i = lane; i < arow / 4; i += 32) {
+        cp_async16(d + 4 * i, as + 4 * i);
+        cp_async16(d + arow + 4 * i, bs + 4 * i);
+      }
+      for (int i = lane; i < nlp / 4; i += 32) cp_async16(d + 2 * arow + 4 * i, xs + 4 * i);
+    }
+    cp_async_commit();
+  };
+  stage(0);
   for (int q = 0; q < CB_FPW; ++q) {
     const int t = blockIdx.x * CB_FR + q * CB_W + warp;
     if (t >= len) break;
@@ -374,16 +391,13 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
         for (int j = lane; j < nl; j += 32) dst[j] = 0.f;
       continue;
     }
+    __syncwarp();       // the previous frame's reads of the buffer about to be refilled are done
+    stage(q + 1);
+    cp_async_wait<1>();
     __syncwarp();
-    const float4* as = reinterpret_cast<const float4*>(a.alpha_ws + ((long long)b * a.T + t) * arow);
-    const float4* bs = reinterpret_cast<const float4*>(a.beta_ws + ((long long)b * a.T + t) * arow);
-    const float4* xs = reinterpret_cast<const float4*>(a.x + (long long)b * a.x_stride_b + (long long)t * nlp);
-    for (int i = lane; i < arow / 4; i += 32) {
-      reinterpret_cast<float4*>(at)[i] = as[i];
-      reinterpret_cast<float4*>(bt)[i] = bs[i];
-    }
-    for (int i = lane; i < nlp / 4; i += 32) reinterpret_cast<float4*>(xt)[i] = xs[i];
-    __syncwarp();
+    const float* at = wbase + (q & 1) * stg;
+    const float* bt = at + arow;
+    const float* xt = bt + arow;
     const double ct = (double)at[arow - 2] + (double)at[arow - 1];
     const double dt = (double)bt[arow - 2] + (double)bt[arow - 1];
     const float Kt = (float)(ct + dt - costn / kLn2);
@@ -487,7 +501,7 @@ bool num_split_supported(const PathArgs& a) {
   if (a.g.max_in_degree > DEG || a.g.max_out_degree > DEG) return false;
   if (sweep_plan(a.g.max_states, (int)a.x_stride_t, a.g.unit_weights != 0).bytes > 200 * 1024) return false;
   const int cb = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * 2 +
-                 CB_W * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
+                 CB_W * (2 * (2 * a.alpha_row + (int)a.x_stride_t) + (int)a.x_stride_t) * 4 + 64;
   return cb <= 200 * 1024;
 }
 
@@ -510,7 +524,7 @@ cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st) {
   cudaError_t e;
   ProfScope prof("num_combine", st);
   const int bytes = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
-                    CB_W * (2 * a.alpha_row + 2 * (int)a.x_stride_t) * 4 + 64;
+                    CB_W * (2 * (2 * a.alpha_row + (int)a.x_stride_t) + (int)a.x_stride_t) * 4 + 64;
   const dim3 grid((a.T + CB_FR - 1) / CB_FR, a.B);
   if (unit) {
     e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
