@@ -36,8 +36,8 @@ WORKLOADS = {
     "cfg5": ("CTC-G sweep shard", 2, 49, 256, 800, {}, None, True),
 }
 # dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_e_ncu_full_summary.md)
-NCU_TRAFFIC = {("cfg3", "bisweep"): 407014656, ("cfg3", "bicombine"): 448727808, ("cfg3", "num_sweep"): 9512960,
-               ("cfg3", "num_combine"): 205858304}
+NCU_TRAFFIC = {("cfg3", "bisweep"): 402519296, ("cfg3", "bicombine"): 448670208, ("cfg3", "num_sweep"): 9504512,
+               ("cfg3", "num_combine"): 203017216}
 CFG_INDEX = {"cfg1": 1, "cfg2": 2, "cfg2s": 2, "cfg3": 3, "cfg4": 4, "cfg5": 5}
 
 
