@@ -16,11 +16,15 @@ struct PathArgs {
   float x_scale;          // multiplies x on load (log2(e) for natural-log input, 1 if prescaled)
   const int32_t* lens;    // device, [B]
   int32_t T, B;
-  float* alpha_ws;        // [B][T][row] normalised alpha_t in log2 units, + frame offset (2 floats)
-  int32_t alpha_row;      // floats per row: pad4(max_states + 2)
+  float* alpha_ws;        // [B][T][row]: generic kernel: normalised alpha_t in log2 units + frame offset (2 floats);
+                          // split numerator: (int32 integer part, fp32 fraction) per state
+  int32_t alpha_row;      // floats per row: pad4(2 * max_states + 2)
   float* scatter_grad;    // nullable: dense (T, B, scatter_V) gradient the split numerator subtracts its posteriors from
   int32_t scatter_V;
   float* beta_ws;         // nullable; same shape as alpha_ws: beta rows of the split numerator (kernels_num.cu)
+  const float* dense_x;   // nullable: the (T, B, V) logits; the numerator sweeps gather their label columns
+  long long dense_stride_t;  // from it themselves and the alpha sweep writes the compact rows x[b][t][j]
+  long long dense_stride_b;
   double* cost;           // [B] natural-log path sum
   float* gout;            // posterior rows; element (t, b, l) at gout[t*g_stride_t + b*g_stride_b + l]
   long long g_stride_t;

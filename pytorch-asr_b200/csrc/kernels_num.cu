@@ -1,23 +1,32 @@
-// Numerator (per-utterance training graph) forward-backward on the compact label columns,
-// log2 domain, sm_100a: the alpha and the beta recursion on separate CTAs at the same time
-// (num_sweep_kernel), then a time-parallel posterior kernel (num_combine_kernel).
+// Numerator (per-utterance training graph) forward-backward, sm_100a: one WARP per (utterance,
+// direction) runs the alpha or the beta recursion (num_sweep_kernel), then a time-parallel kernel
+// forms the posteriors (num_combine_kernel).
 //
-// Reference semantics: PathLogSumExp.forward/backward (att_speech/fst_utils.py:400-488)
-// on the graphs of BaseGraphGen.get_training_matrices (fst_utils.py:647-660): N = 2U+1
-// states with at most 3 arcs into / out of a state.
+// Reference semantics: PathLogSumExp.forward/backward (att_speech/fst_utils.py:400-488) on the
+// graphs of BaseGraphGen.get_training_matrices (fst_utils.py:647-660): N = 2U+1 states with at
+// most 3 arcs into / out of a state.
 //
-// Why the log domain here and plain scaled numbers in the denominator kernels: a
-// training graph is a chain, so alpha_t of the states that carry the posterior mass can
-// sit hundreds of binary orders below max_s alpha_t[s] (measured: below 2^-126 at T=400
-// on random logits) -- a per-frame rescale cannot keep alpha * beta representable.
-// In the decoding graph every state reaches every other within two frames, which
-// bounds that ratio by the frame's logit spread.
+// Number domain.  A training graph is a chain, so alpha_t of the states that carry the posterior
+// mass sits hundreds of binary orders below max_s alpha_t[s]: scaled linear numbers underflow
+// (measured at T = 400) and a plain fp32 log value of that magnitude has an ulp of ~1.5e-5, which
+// is where the round-1 kernel lost the gradient tolerance at T >= 800.  Every value is therefore
+// carried as  log2 v = I + f  with an exact int32 integer part I and an fp32 fraction |f| <= 1/2:
+// the integer parts add exactly, only differences of integer parts (small) and fractions ever
+// meet in floating point, so the precision does not depend on the magnitude, no per-frame
+// normaliser is needed and nothing is lagged.  Integer <-> float conversions go through the
+// 1.5 * 2^23 magic constant (FADD / IADD), not through the quarter-rate conversion unit.
 //
-// Input: the compact label columns xg[b][t][j] = logits[t][b][lab_list_b[j]] (natural log;
-// multiplied by log2(e) inside an fma so that the input is rounded once) written by
-// gather_kernel; output: cost[b] (natural log) and either the compact posterior rows
-// gout[b][t][j] (plain CTC: the row kernels fold them into the dense gradient) or the
-// subtraction from the dense gradient rows directly (with a factorised denominator).
+// num_sweep_kernel   4 warps per CTA, each an independent sweep with its own shared-memory slice:
+//                    the vector of the current frame (int2 per state, double buffered), the arcs of
+//                    <= 13 states per lane in registers, a 16-frame cp.async ring of the label
+//                    columns this utterance touches -- gathered straight from the (T, B, V) logits
+//                    (the round-1 gather kernel is gone; the alpha warp writes the compact rows the
+//                    combine reads) -- and the (integer, fraction) split of the next frame's row.
+//                    One __syncwarp per frame, no block barrier, no atomics.
+// num_combine_kernel one warp per frame: gamma_t[j] = sum_{arcs e labelled j}
+//                    2^(alpha_t[src] + x_t[j] + w_e + beta_{t+1}[dst] - cost), fixed summation order
+//                    (arcs grouped by label on the host), row normalised to one; with a factorised
+//                    denominator the result is subtracted from the dense gradient rows directly.
 #include <algorithm>
 #include <cstdlib>
 
@@ -27,56 +36,40 @@
 namespace ctcg {
 namespace {
 
-constexpr int NS = 256;                 // state threads
-constexpr int W_LAB = NS / 32;          // first warp after the state warps (the io warp)
-constexpr int XR = 8;          // cp.async ring depth (frames)
-constexpr int DEG = 4;         // arcs packed per state
-constexpr int HEAVY = 12;      // labels with more arcs are summed by the whole warp
+constexpr int NWPB = 4;         // sweeps (warps) per CTA, fewer when the graphs are large
+constexpr int XR = 16;          // frames of label columns in flight per sweep
+constexpr int DEG = 4;          // arcs packed per state
+constexpr int HEAVY = 12;       // labels with more arcs are summed by the whole warp
 constexpr unsigned NOARC = 0xffffffffu;
-constexpr int IMIN = -2147483647 - 1;
+constexpr int IDEAD = -(1 << 28);          // integer part of "no path"
+constexpr float MAGIC = 12582912.f;        // 1.5 * 2^23: x + MAGIC has rint(x) in its low mantissa bits
+constexpr int MAGIC_BITS = 0x4B400000;
+constexpr float XCLAMP = 1048576.f;        // |x log2 e| is clamped to 2^20 (T * 2^20 stays inside int32 for T < 2048)
 
-// 2^(a + b + k) with the rounding error of a + b carried along (two-sum): a and b sit
-// tens of binary orders below zero where one fp32 ulp is ~1e-5, k brings the sum back
-// to <= 0.
-__device__ __forceinline__ float post_term(float a, float b, float k) {
-  const float s = a + b;
-  const float bb = s - a;
-  float err = (a - (s - bb)) + (b - bb);
-  err = (s > neg_inf()) ? err : 0.f;
-  return ex2((s + k) + err);
-}
-
-
-// floor(max over the warp) as an integer; -inf saturates to IMIN
-__device__ __forceinline__ int warp_floor_max(float v) {
-  return __reduce_max_sync(0xffffffffu, __float2int_rd(v));
-}
-__device__ __forceinline__ float norm_of(int m) { return (m == IMIN) ? 0.f : (float)m; }
-__device__ __forceinline__ int next3(int r) { return r == 2 ? 0 : r + 1; }
-
-__device__ __forceinline__ float lds_f(unsigned a) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+__device__ __forceinline__ int2 lds64(unsigned a) {
+  int2 v;
+  asm volatile("ld.shared.v2.s32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
   return v;
 }
-__device__ __forceinline__ void sts_f(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v)); }
+__device__ __forceinline__ void sts64(unsigned a, int2 v) {
+  asm volatile("st.shared.v2.s32 [%0], {%1,%2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory");
+}
 __device__ __forceinline__ unsigned sm_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void cp_async4(unsigned dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
 
-// =====================================================================================
-// The alpha and the beta recursion run AT THE SAME TIME on separate CTAs (grid (B, 2)), each
-// spilling its normalised rows; the posteriors are then formed by a time-parallel combine
-// kernel: the serial chain is T frames instead of 2T and the posterior work is off it.
-//
-//   num_sweep_kernel    DIR 0: alpha_hat_t rows (+ fp64 offset c_t) and the cost, arcs by destination
-//                       DIR 1: beta_hat_{t+1} rows (+ offset d_t), arcs by source, frames descending
-//   num_combine_kernel  one warp per frame: gamma_t[j] = sum_{arcs e labelled j}
-//                       2^(alpha_hat_t[src] + beta_hat_{t+1}[dst] + x_t[j] + w_e + c_t + d_t - cost),
-//                       fixed summation order (arcs grouped by label on the host), row normalised to one
-// =====================================================================================
-constexpr int SW_TH = NS + 32;  // state warps + io warp
+// x (log2 units) -> (rint(x), x - rint(x)); |x| <= 2^20
+__device__ __forceinline__ int2 split_log2(float xs) {
+  xs = fminf(fmaxf(xs, -XCLAMP), XCLAMP);
+  const float t = xs + MAGIC;
+  return make_int2(__float_as_int(t) - MAGIC_BITS, __float_as_int(xs - (t - MAGIC)));
+}
+// (float)n for |n| < 2^22
+__device__ __forceinline__ float small_int_to_float(int n) { return __int_as_float(n + MAGIC_BITS) - MAGIC; }
 
 struct SweepPlan {
-  int pk, w, a0, a1, fin, red, xring, bytes;
+  int pk, w, a0, a1, fin, lab, land, xt, bytes;  // byte offsets inside one warp's slice
 };
 __host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp, bool unit) {
   SweepPlan p;
@@ -88,63 +81,75 @@ __host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp, bool unit) {
   };
   p.pk = take(maxN * DEG * 4);
   p.w = unit ? 0 : take(maxN * DEG * 4);
-  p.a0 = take((maxN + 1) * 4);
-  p.a1 = take((maxN + 1) * 4);
+  p.a0 = take((maxN + 1) * 8);
+  p.a1 = take((maxN + 1) * 8);
   p.fin = take(maxN * 4);
-  p.red = take((16 + 2 * (SW_TH / 32)) * 4);
-  p.xring = take(XR * nlp * 4);
+  p.lab = take(nlp * 4);
+  p.land = take(XR * nlp * 4);
+  p.xt = take(2 * nlp * 8);
   p.bytes = o;
   return p;
 }
 
-// DK: arcs per state that exist anywhere in the batch (3 for the CTC training graphs, fst_utils.py:592-605).
+// One state: log-sum-exp over its DK arcs in the (integer, fraction) representation.
 template <int DK>
-__device__ __forceinline__ float lseK(const float (&v)[DK]) {
-  float M = v[0];
+__device__ __forceinline__ int2 lse_state(const int (&J)[DK], const float (&g)[DK]) {
+  int Jm = J[0];
 #pragma unroll
-  for (int k = 1; k < DK; ++k) M = fmaxf(M, v[k]);
-  const float Ms = (M > neg_inf()) ? M : 0.f;
+  for (int k = 1; k < DK; ++k) Jm = max(Jm, J[k]);
   float s = 0.f;
 #pragma unroll
-  for (int k = 0; k < DK; ++k) s += ex2(v[k] - Ms);
-  return Ms + lg2(s);  // lg2(0) = -inf
+  for (int k = 0; k < DK; ++k) s += ex2(small_int_to_float(max(J[k] - Jm, -4096)) + g[k]);
+  const float r = lg2(s);  // every live state has a term 2^g with |g| <= ~1: r is O(1)
+  const float t = r + MAGIC;
+  const int2 out = make_int2(Jm + (__float_as_int(t) - MAGIC_BITS), __float_as_int(r - (t - MAGIC)));
+  return (Jm < IDEAD / 2 || !(s > 0.f)) ? make_int2(IDEAD, 0) : out;
 }
 
+// SPT > 0: the arcs of the SPT states of a lane (state = lane + 32 i) live in registers as packed
+// shared-memory byte offsets; SPT == 0: any number of states, arcs re-read from shared memory.
+// DK: arcs per state that exist anywhere in the batch (3 for CTC training graphs, fst_utils.py:592-605).
 template <bool UNIT, int SPT, int DK>
-__global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, const int maxN) {
-  extern __shared__ __align__(16) unsigned char sm[];
+__global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, const int maxN, const int nsweeps) {
+  extern __shared__ __align__(16) unsigned char sm_all[];
   const GraphDev& g = a.g;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int b = blockIdx.x;
-  const int DIR = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int q = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (q >= nsweeps) return;
+  const bool both = a.write_grad != 0;
+  const int b = both ? (q >> 1) : q;
+  const int DIR = both ? (q & 1) : 0;
   const int gi = (g.num_graphs == 1) ? 0 : b;
   const int so = g.state_off[gi];
   const int n = g.state_off[gi + 1] - so;
   const int ro = so + gi;
+  const int lo = g.lab_off[gi];
+  const int nl = g.lab_off[gi + 1] - lo;
   const int len = min(a.lens[b], a.T);
   const int nlp = (int)a.x_stride_t, arow = a.alpha_row;
   const SweepPlan P = sweep_plan(maxN, nlp, UNIT);
+  unsigned char* sm = sm_all + (size_t)warp * P.bytes;
   uint4* pkv = reinterpret_cast<uint4*>(sm + P.pk);
   float4* wv = reinterpret_cast<float4*>(sm + P.w);
-  float* abuf0 = reinterpret_cast<float*>(sm + P.a0);
-  float* abuf1 = reinterpret_cast<float*>(sm + P.a1);
+  int2* abuf0 = reinterpret_cast<int2*>(sm + P.a0);
+  int2* abuf1 = reinterpret_cast<int2*>(sm + P.a1);
   float* fin = reinterpret_cast<float*>(sm + P.fin);
-  int* wmax = reinterpret_cast<int*>(sm + P.red);
-  float* scr = reinterpret_cast<float*>(wmax + 16);
-  float* xring = reinterpret_cast<float*>(sm + P.xring);
-  constexpr int NW = SW_TH / 32;
+  int* labs = reinterpret_cast<int*>(sm + P.lab);
+  float* land = reinterpret_cast<float*>(sm + P.land);
+  int2* xt = reinterpret_cast<int2*>(sm + P.xt);
 
   const int32_t* ptr = DIR ? g.out_ptr : g.in_ptr;
   const int32_t* oth = DIR ? g.out_dst : g.in_src;
   const int32_t* clab = DIR ? g.out_clab : g.in_clab;
   const float* wgt = DIR ? g.out_w : g.in_w;
-  for (int s = tid; s < n; s += SW_TH) {
+  for (int s = lane; s < n; s += 32) {
     unsigned pi[DEG];
     float wi[DEG];
+    const int e0 = ptr[ro + s], e1 = ptr[ro + s + 1];
 #pragma unroll
     for (int k = 0; k < DEG; ++k) {
-      const int e = ptr[ro + s] + k;
-      const bool v = e < ptr[ro + s + 1];
+      const int e = e0 + k;
+      const bool v = e < e1;
       pi[k] = v ? ((unsigned)oth[e] | ((unsigned)clab[e] << 16)) : NOARC;
       wi[k] = (v && !UNIT) ? wgt[e] * kLog2e : 0.f;
     }
@@ -152,187 +157,211 @@ __global__ void __launch_bounds__(SW_TH) num_sweep_kernel(const PathArgs a, cons
     if (!UNIT) wv[s] = make_float4(wi[0], wi[1], wi[2], wi[3]);
     const float f = g.final_w[so + s];
     fin[s] = (f > kDeadWeight) ? f * kLog2e : neg_inf();
-    abuf0[s] = DIR ? fin[s] : ((s == 0) ? 0.f : neg_inf());
+    int2 v0 = make_int2(IDEAD, 0);
+    if (DIR) {
+      if (f > kDeadWeight) v0 = split_log2(f * kLog2e);
+    } else if (s == 0) {
+      v0 = make_int2(0, 0);
+    }
+    abuf0[s] = v0;
   }
-  if (tid < 3) wmax[tid] = (tid == 0) ? 0 : IMIN;  // the vector entering the first frame is not normalised
-  if (tid == 0) abuf0[maxN] = abuf1[maxN] = neg_inf();
-  const float* xb = a.x + (long long)b * a.x_stride_b;
-  float* rows = (DIR ? a.beta_ws : a.alpha_ws) + (long long)b * a.T * arow;
-  const int xchunks = nlp / 4;
-  __syncthreads();
-  auto frame_t = [&](int i) { return DIR ? len - 1 - i : i; };
-  const long long rstep = DIR ? -(long long)arow : (long long)arow;
+  if (lane == 0) abuf0[maxN] = abuf1[maxN] = make_int2(IDEAD, 0);  // the slot absent arcs point at
+  for (int j = lane; j < nlp; j += 32) labs[j] = (j < nl) ? g.lab_list[lo + j] : 0;
+  __syncwarp();
 
-  float* a_cur = abuf0;
-  float* a_nxt = abuf1;
-  double c = 0.0;  // io warp: vector = normalised vector + c (log2 units)
-  if (SPT > 0 && warp < W_LAB) {
-    constexpr int NSP = SPT > 0 ? SPT : 1;
-    unsigned so4[NSP][DK], lo4[NSP][DK];
-    float wi[NSP][DK];
-    float* arp[NSP];
+  auto frame_t = [&](int i) { return DIR ? len - 1 - i : i; };
+  const bool direct = a.dense_x != nullptr;
+  const float* xb = a.x + (long long)b * a.x_stride_b;  // compact rows [t][nlp]: input (gathered by a kernel) or output (direct)
+  float* xout = (direct && DIR == 0 && a.write_grad) ? const_cast<float*>(xb) : nullptr;
+  const float* dense = direct ? a.dense_x + (long long)b * a.dense_stride_b : nullptr;
+  const unsigned land_a = sm_u32(land);
+  auto issue_x = [&](int i) {
+    if (i < len) {
+      const int t = frame_t(i);
+      const int slot = i % XR;
+      if (direct) {
+        const float* src = dense + (long long)t * a.dense_stride_t;
+        for (int j = lane; j < nl; j += 32) cp_async4(land_a + (slot * nlp + j) * 4, src + labs[j]);
+      } else {
+        const float* src = xb + (long long)t * nlp;
+        for (int cc = lane; cc < nlp / 4; cc += 32) cp_async16(land + slot * nlp + 4 * cc, src + 4 * cc);
+      }
+    }
+    cp_async_commit();
+  };
+  // landed row of frame i -> (integer, fraction) of x log2 e; the alpha sweep also writes the compact row
+  auto transform = [&](int i) {
+    if (i >= len) return;
+    const float* src = land + (i % XR) * nlp;
+    int2* dst = xt + (i & 1) * nlp;
+    float* xo = xout ? xout + (long long)frame_t(i) * nlp : nullptr;
+    for (int j = lane; j < nlp; j += 32) {
+      const float x = (j < nl) ? src[j] : 0.f;
+      dst[j] = split_log2(x * kLog2e);
+      if (xo) xo[j] = x;
+    }
+  };
+  int2* rows = reinterpret_cast<int2*>((DIR ? a.beta_ws : a.alpha_ws) + (long long)b * a.T * arow);
+  const bool spill = a.write_grad != 0;
+
+  for (int i = 0; i < XR - 1; ++i) issue_x(i);
+  cp_async_wait<XR - 2>();
+  __syncwarp();
+  transform(0);
+  if (spill && len > 0) {
+    int2* r0 = rows + (long long)frame_t(0) * (arow / 2);
+    for (int s = lane; s < n; s += 32) r0[s] = abuf0[s];
+  }
+  __syncwarp();
+
+  unsigned ac = sm_u32(abuf0), an = sm_u32(abuf1);
+  const unsigned xt_a = sm_u32(xt);
+  constexpr int NSP = SPT > 0 ? SPT : 1;
+  unsigned arcs[NSP][DK];
+  float wreg[NSP][UNIT ? 1 : DK];
+  if (SPT > 0) {
 #pragma unroll
     for (int i = 0; i < NSP; ++i) {
-      const int s = tid + i * NS;
+      const int s = lane + 32 * i;
       const uint4 pk = (s < n) ? pkv[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
       const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
       const float4 w = (!UNIT && s < n) ? wv[s] : make_float4(0.f, 0.f, 0.f, 0.f);
       const float ww[DEG] = {w.x, w.y, w.z, w.w};
 #pragma unroll
       for (int k = 0; k < DK; ++k) {
-        so4[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 4u : (pkk[k] & 0xffffu) * 4u;
-        lo4[i][k] = (pkk[k] == NOARC) ? 0u : (pkk[k] >> 16) * 4u;
-        wi[i][k] = ww[k];
+        arcs[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 8u : ((pkk[k] & 0xffffu) * 8u) | ((pkk[k] >> 16) * 8u << 16);
+        if (!UNIT) wreg[i][k] = ww[k];
       }
-      arp[i] = rows + (long long)frame_t(0) * arow + (s < n ? s : 0);
     }
-    unsigned ac = sm_u32(a_cur), an = sm_u32(a_nxt);
-    const unsigned xr0 = sm_u32(xring), wm_a = sm_u32(wmax);
-    int r = 0, slot = 0;
-    for (int t = 0; t < len; ++t) {
-      __syncthreads();
-      int wmi;
-      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(wmi) : "r"(wm_a + r * 4));
-      const float mx = norm_of(wmi);
-      r = next3(r);
-      const unsigned xa = xr0 + slot * nlp * 4;
-      slot = (slot + 1 == XR) ? 0 : slot + 1;
-      float lm = neg_inf();
+  }
+  for (int i = 0; i < len; ++i) {
+    issue_x(i + XR - 1);
+    cp_async_wait<XR - 2>();  // the row of frame i + 1 has landed
+    __syncwarp();
+    transform(i + 1);
+    const unsigned xa = xt_a + (i & 1) * nlp * 8;
+    int2* rn = (spill && i + 1 < len) ? rows + (long long)frame_t(i + 1) * (arow / 2) : nullptr;
+    if (SPT > 0) {
+      // three phases, so that the loads of all states are in flight before the first log-sum-exp
+      int J[NSP][DK];
+      float gf[NSP][DK];
 #pragma unroll
-      for (int i = 0; i < NSP; ++i) {
-        const int s = tid + i * NS;
-        float v[DK];
+      for (int u = 0; u < NSP; ++u) {
 #pragma unroll
         for (int k = 0; k < DK; ++k) {
-          v[k] = fmaf(lds_f(xa + lo4[i][k]), kLog2e, lds_f(ac + so4[i][k]) - mx);
-          if (!UNIT) v[k] += wi[i][k];
+          const int2 av = lds64(ac + (arcs[u][k] & 0xffffu));
+          const int2 xv = lds64(xa + (arcs[u][k] >> 16));
+          J[u][k] = av.x + xv.x;
+          gf[u][k] = __int_as_float(av.y) + __int_as_float(xv.y);
+          if (!UNIT) {
+            const int2 ws = split_log2(wreg[u][k]);
+            J[u][k] += ws.x;
+            gf[u][k] += __int_as_float(ws.y);
+          }
         }
-        const float res = lseK<DK>(v);
+      }
+      int2 res[NSP];
+#pragma unroll
+      for (int u = 0; u < NSP; ++u) res[u] = lse_state<DK>(J[u], gf[u]);
+#pragma unroll
+      for (int u = 0; u < NSP; ++u) {
+        const int s = lane + 32 * u;
         if (s < n) {
-          *arp[i] = lds_f(ac + s * 4) - mx;
-          sts_f(an + s * 4, res);
+          sts64(an + s * 8, res[u]);
+          if (rn) rn[s] = res[u];
         }
-        arp[i] += rstep;
-        lm = fmaxf(lm, res);
       }
-      const int wm = warp_floor_max(lm);
-      if (lane == 0) atomicMax(&wmax[r], wm);
-      const unsigned tmp = ac;
-      ac = an;
-      an = tmp;
-    }
-  } else if (warp < W_LAB) {
-    int r = 0;
-    for (int t = 0; t < len; ++t) {
-      __syncthreads();
-      const float mx = norm_of(wmax[r]);
-      r = next3(r);
-      const float* xrow = xring + (t % XR) * nlp;
-      float* ar = rows + (long long)frame_t(t) * arow;
-      float lm = neg_inf();
-      for (int s = tid; s < n; s += NS) {
-        ar[s] = a_cur[s] - mx;
-        const uint4 pk = pkv[s];
-        const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
-        float v[DEG];
+    } else {
+      constexpr int CH = 4;  // states of a lane per pass
+      for (int s0 = lane; s0 < n; s0 += 32 * CH) {
+        int J[CH][DEG];
+        float gf[CH][DEG];
 #pragma unroll
-        for (int k = 0; k < DEG; ++k) {
-          const unsigned q = (pkk[k] == NOARC) ? 0u : pkk[k];
-          const float val = fmaf(xrow[q >> 16], kLog2e, a_cur[q & 0xffffu] - mx);
-          v[k] = (pkk[k] == NOARC) ? neg_inf() : val;
+        for (int u = 0; u < CH; ++u) {
+          const int s = s0 + 32 * u;
+          const uint4 pk = (s < n) ? pkv[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
+          const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
+          float ww[DEG] = {0.f, 0.f, 0.f, 0.f};
+          if (!UNIT && s < n) {
+            const float4 w = wv[s];
+            ww[0] = w.x, ww[1] = w.y, ww[2] = w.z, ww[3] = w.w;
+          }
+#pragma unroll
+          for (int k = 0; k < DEG; ++k) {
+            const bool v = pkk[k] != NOARC;
+            const int2 av = lds64(ac + (v ? (pkk[k] & 0xffffu) : (unsigned)maxN) * 8u);
+            const int2 xv = lds64(xa + (v ? (pkk[k] >> 16) : 0u) * 8u);
+            J[u][k] = av.x + xv.x;
+            gf[u][k] = __int_as_float(av.y) + __int_as_float(xv.y);
+            if (!UNIT) {
+              const int2 ws = split_log2(ww[k]);
+              J[u][k] += ws.x;
+              gf[u][k] += __int_as_float(ws.y);
+            }
+          }
         }
-        if (!UNIT) {
-          const float4 w = wv[s];
-          v[0] += w.x;
-          v[1] += w.y;
-          v[2] += w.z;
-          v[3] += w.w;
+#pragma unroll
+        for (int u = 0; u < CH; ++u) {
+          const int s = s0 + 32 * u;
+          const int2 res = lse_state<DEG>(J[u], gf[u]);
+          if (s < n) {
+            sts64(an + s * 8, res);
+            if (rn) rn[s] = res;
+          }
         }
-        const float res = lseK<DEG>(v);
-        a_nxt[s] = res;
-        lm = fmaxf(lm, res);
       }
-      const int wm = warp_floor_max(lm);
-      if (lane == 0) atomicMax(&wmax[r], wm);
-      float* tmp = a_cur;
-      a_cur = a_nxt;
-      a_nxt = tmp;
     }
-  } else {  // io warp
-    auto issue_x = [&](int i, int slot) {
-      if (i >= 0 && i < len) {
-        const float* src = xb + (long long)frame_t(i) * nlp;
-        float* dst = xring + slot * nlp;
-        for (int cc = lane; cc < xchunks; cc += 32) cp_async16(dst + 4 * cc, src + 4 * cc);
-      }
-      cp_async_commit();
-    };
-    for (int i = 0; i < XR - 1; ++i) issue_x(i, i);
-    cp_async_wait<XR - 2>();
-    int r = 0;
-    for (int t = 0; t < len; ++t) {
-      __syncthreads();
-      issue_x(t + XR - 1, (t + XR - 1) % XR);
-      c += (double)norm_of(wmax[r]);
-      r = next3(r);
-      if (lane == 0) {
-        float* ar = rows + (long long)frame_t(t) * arow;
-        const float hi = (float)c;
-        ar[arow - 2] = hi;
-        ar[arow - 1] = (float)(c - (double)hi);
-        wmax[next3(r)] = IMIN;  // the slot the state warps fill during the next frame
-      }
-      cp_async_wait<XR - 2>();
-    }
-    cp_async_wait<0>();
+    __syncwarp();
+    const unsigned tmp = ac;
+    ac = an;
+    an = tmp;
   }
+  cp_async_wait<0>();
   if (DIR) return;
-  a_cur = (len & 1) ? abuf1 : abuf0;  // alpha_len (the register path swapped addresses, not these pointers)
-  __syncthreads();
-  // terminal: cost = c_len + LSE_n(alpha_hat_len[n] + final[n])
-  float tm = neg_inf();
-  for (int s = tid; s < n; s += SW_TH) tm = fmaxf(tm, a_cur[s] + fin[s]);
-  tm = warp_max(tm);
-  if (lane == 0) scr[warp] = tm;
-  __syncthreads();
-  float TM = scr[0];
-#pragma unroll
-  for (int w = 1; w < NW; ++w) TM = fmaxf(TM, scr[w]);
+  // terminal: cost = LSE_n(alpha_len[n] + final[n])
+  const int2* a_end = (len & 1) ? abuf1 : abuf0;
+  int Im = IDEAD;
+  for (int s = lane; s < n; s += 32)
+    if (fin[s] > neg_inf()) Im = max(Im, a_end[s].x);
+  Im = __reduce_max_sync(0xffffffffu, Im);
   float ts = 0.f;
-  if (TM > neg_inf())
-    for (int s = tid; s < n; s += SW_TH) ts += ex2(a_cur[s] + fin[s] - TM);
+  if (Im > IDEAD / 2)
+    for (int s = lane; s < n; s += 32)
+      if (fin[s] > neg_inf())
+        ts += ex2(small_int_to_float(max(a_end[s].x - Im, -4096)) + __int_as_float(a_end[s].y) + fin[s]);
   ts = warp_sum(ts);
-  if (lane == 0) scr[NW + warp] = ts;
-  __syncthreads();
-  float TS = 0.f;
-#pragma unroll
-  for (int w = 0; w < NW; ++w) TS += scr[NW + w];
-  const bool feasible = TM > neg_inf() && TS > 0.f;
-  if (warp == W_LAB && lane == 0) {  // the io warp holds c
-    const double cost2 = c + (double)TM + (double)lg2(TS);
-    a.cost[b] = feasible ? cost2 * kLn2 : -1e20;
+  if (lane == 0) {
+    const bool feasible = Im > IDEAD / 2 && ts > 0.f;
+    a.cost[b] = feasible ? ((double)Im + log2((double)ts)) * kLn2 : -1e20;
   }
 }
 
-constexpr int CB_W = 8;             // warps per combine CTA, one frame at a time each
-constexpr int CB_FPW = 4;           // frames per warp: the graph tables are staged once per CB_W * CB_FPW frames
-constexpr int CB_FR = CB_W * CB_FPW;
+constexpr int CB_W = 8;             // warps per combine CTA (fewer when the rows are long), one frame at a time each
+constexpr int CB_FPW = 4;           // frames per warp: the graph tables are staged once per warps * CB_FPW frames
 constexpr int CB_TH = CB_W * 32;
+
+// 2^(alpha[src] + beta[dst] + k) in the (integer, fraction) representation; kI / kf hold x_t[j] - cost (+ w)
+__device__ __forceinline__ float post_term(int2 av, int2 bv, int kI, float kf) {
+  const int e = av.x + bv.x + kI;  // dead parts are -2^28 each: no wrap-around
+  return ex2(small_int_to_float(min(max(e, -4096), 4096)) + (__int_as_float(av.y) + __int_as_float(bv.y) + kf));
+}
 
 // With a.scatter_grad set the normalised posteriors are subtracted from the dense gradient rows the
 // denominator wrote (grad[t][b][lab_list[j]] -= scale_b * gamma_t[j], the scatter_sub step fused in:
 // every (t, b, label) is touched by exactly one lane, no atomics); otherwise the compact rows
 // gout[b][t][j] are written for the row kernels of plain CTC.
 template <bool UNIT>
-__global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
+__global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // utterances in descending order: with the scatter fused in, the gradient rows written last by the
-  // denominator's combine kernel (the highest b) are the ones most likely to be L2 resident still
+  // denominator (the highest b) are the ones most likely to be L2 resident still
   const int b = a.B - 1 - (int)blockIdx.y;
   const int len = min(a.lens[b], a.T);
-  if (blockIdx.x * CB_FR >= len) return;
+  const int nwarps = blockDim.x >> 5, nthreads = blockDim.x;
+  const int cb_fr = nwarps * CB_FPW;
+  if (blockIdx.x * cb_fr >= len) return;
   const int gi = (g.num_graphs == 1) ? 0 : b;
   const int ro = g.state_off[gi] + gi;
   const int n = g.state_off[gi + 1] - g.state_off[gi];
@@ -351,11 +380,11 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
   // per warp: two staging buffers {alpha row, beta row, x row} (the next frame's rows are copied in with
   // cp.async while this frame's posteriors are summed) and one posterior row
   const int stg = 2 * arow + nlp;
-  float* rows_s = reinterpret_cast<float*>(sm + take(CB_W * (2 * stg + nlp) * 4));
+  float* rows_s = reinterpret_cast<float*>(sm + take(nwarps * (2 * stg + nlp) * 4));
   const int arc0 = g.in_ptr[ro];
   const int narcs = g.in_ptr[ro + n] - arc0;
-  for (int j = tid; j <= nl; j += CB_TH) lab_ptr[j] = g.lab_ptr[lo + gi + j] - arc0;
-  for (int e = tid; e < narcs; e += CB_TH) {
+  for (int j = tid; j <= nl; j += nthreads) lab_ptr[j] = g.lab_ptr[lo + gi + j] - arc0;
+  for (int e = tid; e < narcs; e += nthreads) {
     lab_pk[e] = (unsigned)g.lab_src[arc0 + e] | ((unsigned)g.lab_dst[arc0 + e] << 16);
     if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
   }
@@ -364,16 +393,21 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
   float* gt = wbase + 2 * stg;
   const double costn = a.cost[b];
   const bool feasible = costn > -1e19;
+  // cost in log2 units, split like every other value
+  const double cost2 = costn / kLn2;
+  const double cI_d = rint(cost2);
+  const int cI = (int)cI_d;
+  const float cf = (float)(cost2 - cI_d);
   const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
   const int V = a.scatter_V;
   auto stage = [&](int q) {  // always commits a group (possibly empty), so that the wait counts stay uniform
-    const int t = blockIdx.x * CB_FR + q * CB_W + warp;
+    const int t = blockIdx.x * cb_fr + q * nwarps + warp;
     if (q < CB_FPW && t < len && feasible) {
       float* d = wbase + (q & 1) * stg;
       const float* as = a.alpha_ws + ((long long)b * a.T + t) * arow;
       const float* bs = a.beta_ws + ((long long)b * a.T + t) * arow;
       const float* xs = a.x + (long long)b * a.x_stride_b + (long long)t * nlp;
-      for (int i = lane; i < arow / 4; i += 32) {
+      for (int i = lane; i < (2 * n + 3) / 4; i += 32) {
         cp_async16(d + 4 * i, as + 4 * i);
         cp_async16(d + arow + 4 * i, bs + 4 * i);
       }
@@ -383,7 +417,7 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
   };
   stage(0);
   for (int q = 0; q < CB_FPW; ++q) {
-    const int t = blockIdx.x * CB_FR + q * CB_W + warp;
+    const int t = blockIdx.x * cb_fr + q * nwarps + warp;
     if (t >= len) break;
     float* dst = a.gout + (long long)b * a.g_stride_b + (long long)t * a.g_stride_t;
     if (!feasible) {  // no accepting path: zero posterior
@@ -395,12 +429,9 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
     stage(q + 1);
     cp_async_wait<1>();
     __syncwarp();
-    const float* at = wbase + (q & 1) * stg;
-    const float* bt = at + arow;
-    const float* xt = bt + arow;
-    const double ct = (double)at[arow - 2] + (double)at[arow - 1];
-    const double dt = (double)bt[arow - 2] + (double)bt[arow - 1];
-    const float Kt = (float)(ct + dt - costn / kLn2);
+    const int2* at = reinterpret_cast<const int2*>(wbase + (q & 1) * stg);
+    const int2* bt = reinterpret_cast<const int2*>(wbase + (q & 1) * stg + arow);
+    const float* xt = wbase + (q & 1) * stg + 2 * arow;
     // scatter mode: the gradient entries this frame will touch are requested now, so that their DRAM
     // latency runs behind the posterior sums (first 256 labels; the labels of an utterance are distinct)
     float* out = a.scatter_grad ? a.scatter_grad + ((long long)t * a.B + b) * V : nullptr;
@@ -426,10 +457,13 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
       const bool heavy = (e1 - e0) > HEAVY;
       float acc = 0.f;
       if (j < nl && !heavy) {
-        const float kx = fmaf(xt[j], kLog2e, Kt);
+        const int2 xs = split_log2(xt[j] * kLog2e);
+        const int kI = xs.x - cI;
+        const float kf = __int_as_float(xs.y) - cf;
         for (int e = e0; e < e1; ++e) {
           const unsigned pk = lab_pk[e];
-          acc += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+          const int2 ws = UNIT ? make_int2(0, 0) : split_log2(lab_w[e]);
+          acc += post_term(at[pk & 0xffffu], bt[pk >> 16], kI + ws.x, kf + __int_as_float(ws.y));
         }
       }
       unsigned hm = __ballot_sync(0xffffffffu, heavy);
@@ -438,11 +472,14 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
         hm &= hm - 1;
         const int jh = base + src_lane;
         const int h0 = __shfl_sync(0xffffffffu, e0, src_lane), h1 = __shfl_sync(0xffffffffu, e1, src_lane);
-        const float kx = fmaf(xt[jh], kLog2e, Kt);
+        const int2 xs = split_log2(xt[jh] * kLog2e);
+        const int kI = xs.x - cI;
+        const float kf = __int_as_float(xs.y) - cf;
         float part = 0.f;
         for (int e = h0 + lane; e < h1; e += 32) {
           const unsigned pk = lab_pk[e];
-          part += post_term(at[pk & 0xffffu], bt[pk >> 16], UNIT ? kx : kx + lab_w[e]);
+          const int2 ws = UNIT ? make_int2(0, 0) : split_log2(lab_w[e]);
+          part += post_term(at[pk & 0xffffu], bt[pk >> 16], kI + ws.x, kf + __int_as_float(ws.y));
         }
         part = warp_sum(part);
         if (lane == src_lane) acc = part;
@@ -480,40 +517,59 @@ __global__ void __launch_bounds__(CB_TH, 3) num_combine_kernel(const PathArgs a,
   }
 }
 
+constexpr int kSmemBudget = 200 * 1024;
+int combine_smem_bytes(const PathArgs& a, bool unit, int warps) {
+  return ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
+         warps * (2 * (2 * a.alpha_row + (int)a.x_stride_t) + (int)a.x_stride_t) * 4 + 64;
+}
+// most warps (<= CB_W) whose staging buffers fit; 0: not even one
+int combine_warps(const PathArgs& a, bool unit) {
+  int w = CB_W;
+  while (w > 0 && combine_smem_bytes(a, unit, w) > kSmemBudget) --w;
+  return w;
+}
+int sweep_warps(const PathArgs& a, bool unit) {
+  const int per = sweep_plan(a.g.max_states, (int)a.x_stride_t, unit).bytes;
+  return std::min(NWPB, kSmemBudget / std::max(per, 1));
+}
+
 }  // namespace
 
 template <bool UNIT, int SPT, int DK>
-static cudaError_t launch_sweep_dk(const PathArgs& a, int bytes, cudaStream_t st) {
+static cudaError_t launch_sweep_dk(const PathArgs& a, int warps, int nsweeps, cudaStream_t st) {
+  const int bytes = warps * sweep_plan(a.g.max_states, (int)a.x_stride_t, UNIT).bytes;
   cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT, DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   if (e != cudaSuccess) return e;
-  num_sweep_kernel<UNIT, SPT, DK><<<dim3(a.B, a.write_grad ? 2 : 1), SW_TH, bytes, st>>>(a, a.g.max_states);
+  num_sweep_kernel<UNIT, SPT, DK><<<(nsweeps + warps - 1) / warps, warps * 32, bytes, st>>>(a, a.g.max_states, nsweeps);
   return cudaGetLastError();
 }
-template <bool UNIT, int SPT>
-static cudaError_t launch_sweep(const PathArgs& a, int bytes, cudaStream_t st) {
-  if (SPT > 0 && a.g.max_in_degree <= 3 && a.g.max_out_degree <= 3) return launch_sweep_dk<UNIT, SPT, 3>(a, bytes, st);
-  return launch_sweep_dk<UNIT, SPT, DEG>(a, bytes, st);
+template <bool UNIT>
+static cudaError_t launch_sweep(const PathArgs& a, int warps, int nsweeps, cudaStream_t st) {
+  const int spt = (a.g.max_states + 31) / 32;
+  const bool d3 = a.g.max_in_degree <= 3 && a.g.max_out_degree <= 3;
+  const bool regs = a.g.max_states * 8 <= 65535 && (int)a.x_stride_t * 8 <= 65535;  // packed 16-bit byte offsets
+  if (regs && d3 && spt <= 4) return launch_sweep_dk<UNIT, 4, 3>(a, warps, nsweeps, st);
+  if (regs && d3 && spt <= 7) return launch_sweep_dk<UNIT, 7, 3>(a, warps, nsweeps, st);
+  if (regs && d3 && spt <= 13) return launch_sweep_dk<UNIT, 13, 3>(a, warps, nsweeps, st);
+  if (regs && spt <= 7) return launch_sweep_dk<UNIT, 7, DEG>(a, warps, nsweeps, st);
+  return launch_sweep_dk<UNIT, 0, DEG>(a, warps, nsweeps, st);
 }
 
 bool num_split_supported(const PathArgs& a) {
   if (!a.beta_ws) return false;
   if (a.g.max_states > 65535 || a.g.max_labels > 65535 || a.g.max_arcs < 1) return false;
   if (a.g.max_in_degree > DEG || a.g.max_out_degree > DEG) return false;
-  if (sweep_plan(a.g.max_states, (int)a.x_stride_t, a.g.unit_weights != 0).bytes > 200 * 1024) return false;
-  const int cb = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * 2 +
-                 CB_W * (2 * (2 * a.alpha_row + (int)a.x_stride_t) + (int)a.x_stride_t) * 4 + 64;
-  return cb <= 200 * 1024;
+  if (a.alpha_row < 2 * a.g.max_states) return false;
+  const bool unit = a.g.unit_weights != 0;
+  return sweep_warps(a, unit) >= 1 && combine_warps(a, unit) >= 1;
 }
 
 cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st) {
   const bool unit = a.g.unit_weights != 0;
-  cudaError_t e;
   ProfScope prof("num_sweep", st);
-  const SweepPlan P = sweep_plan(a.g.max_states, (int)a.x_stride_t, unit);
-  const int spt = (a.g.max_states + NS - 1) / NS;
-  if (spt <= 1) e = unit ? launch_sweep<true, 1>(a, P.bytes, st) : launch_sweep<false, 1>(a, P.bytes, st);
-  else if (spt == 2) e = unit ? launch_sweep<true, 2>(a, P.bytes, st) : launch_sweep<false, 2>(a, P.bytes, st);
-  else e = unit ? launch_sweep<true, 0>(a, P.bytes, st) : launch_sweep<false, 0>(a, P.bytes, st);
+  const int warps = sweep_warps(a, unit);
+  const int nsweeps = a.write_grad ? 2 * a.B : a.B;
+  const cudaError_t e = unit ? launch_sweep<true>(a, warps, nsweeps, st) : launch_sweep<false>(a, warps, nsweeps, st);
   ++g_launches;
   return e;
 }
@@ -523,17 +579,18 @@ cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st) {
   const bool unit = a.g.unit_weights != 0;
   cudaError_t e;
   ProfScope prof("num_combine", st);
-  const int bytes = ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
-                    CB_W * (2 * (2 * a.alpha_row + (int)a.x_stride_t) + (int)a.x_stride_t) * 4 + 64;
-  const dim3 grid((a.T + CB_FR - 1) / CB_FR, a.B);
+  const int warps = combine_warps(a, unit);
+  const int bytes = combine_smem_bytes(a, unit, warps);
+  const int cb_fr = warps * CB_FPW;
+  const dim3 grid((a.T + cb_fr - 1) / cb_fr, a.B);
   if (unit) {
     e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return e;
-    num_combine_kernel<true><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
+    num_combine_kernel<true><<<grid, warps * 32, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
   } else {
     e = cudaFuncSetAttribute(num_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return e;
-    num_combine_kernel<false><<<grid, CB_TH, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
+    num_combine_kernel<false><<<grid, warps * 32, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
   }
   ++g_launches;
   return cudaGetLastError();

@@ -178,6 +178,74 @@ def test_full_vocabulary_slice_matches_fp64_oracle(P, variant):
     assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
 
 
+def _record(name, value):
+    """Largest deviations seen by the bench-size parity tests, kept for DESIGN.md (best effort)."""
+    import json
+    import os
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if not os.path.isdir(d):
+        return
+    path = os.path.join(d, "parity_maxerr.json")
+    try:
+        data = json.load(open(path)) if os.path.exists(path) else {}
+        data[name] = value
+        json.dump(data, open(path, "w"), indent=1, sort_keys=True)
+    except (OSError, ValueError):
+        pass
+
+
+@pytest.mark.parametrize("variant,S,B,T,peaky", [
+    ("ctcg", 49, 64, 400, False),     # cfg3, the bench default: CTC-G, V=2401
+    ("ctcg", 49, 64, 400, True),
+    ("ctcgb", 49, 32, 800, False),    # cfg4 / cfg5 shape: CTC-GB, T=800 (an utterance does not depend on B)
+    ("ctcgb", 49, 32, 800, True),
+    ("ctcg", 36, 64, 400, False),     # BASELINE's nominal V=1296
+    ("ctc", 36, 64, 400, False),
+    ("ctc", 49, 64, 400, True),       # cfg2
+])
+def test_bench_configurations_match_fp64_oracle(P, variant, S, B, T, peaky):
+    """The configurations bench.py times (seed-1003 batch at full B and T) against the fp64 oracle:
+    the CUDA path runs the whole batch, the oracle three utterances of it (first, middle, last)."""
+    args = {"use_contextual_blanks": True} if variant == "ctcgb" else {}
+    use_den, nbd = (False, 0) if variant == "ctc" else (True, None)
+    logits, lens, seqs = _random_case(2, S, args, T, B, seed=1003, peaky=peaky)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
+    loss, grad = _run_fused(P, logits, lens, gen.get_training_graphs(seqs),
+                            gen.get_decoding_graph() if use_den else None, nbd, S)
+    sub = [0, B // 2, B - 1]
+    want_loss, want_grad = _oracle(2, S, args, np.ascontiguousarray(logits[:, sub]), [lens[i] for i in sub],
+                                   [seqs[i] for i in sub], use_den, nbd)
+    dl = _rel(loss[sub], want_loss.numpy())
+    dg = float(np.abs(grad[:, sub] - want_grad.numpy()).max())
+    _record("%s_S%d_B%d_T%d%s" % (variant, S, B, T, "_peaky" if peaky else ""), {"loss_rel": dl, "grad_abs": dg})
+    assert dl < LOSS_RTOL
+    assert dg < GRAD_ATOL
+
+
+@pytest.mark.parametrize("S,T,args", [(49, 400, {}), (49, 200, {"use_contextual_blanks": True}), (36, 300, {})])
+def test_viterbi_and_collapse_at_full_vocabulary(P, S, T, args):
+    """Best path over the full bi-char decoding graph (fst_utils.py:366-397, advanced_decoder.py:546-571)
+    at production size: score and per-frame labels against the oracle's tropical recursion, and the
+    collapse of the labels against the oracle's walk over the arc table."""
+    logits, lens, seqs = _random_case(2, S, args, T, 2, seed=515 + S, peaky=True)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
+    ogen = graphs.GraphGen(2, S, args)
+    lp = torch.as_tensor(logits)
+    want_score, want_labels = engine.path_viterbi(lp, lens, ogen.get_decoding_matrices(), dtype=torch.float64)
+    score, labels = P._lib.viterbi(lp.cuda(), lens, gen.get_decoding_graph())
+    assert _rel(score.cpu().numpy(), want_score.numpy()) < LOSS_RTOL
+    labels = labels.cpu().numpy()
+    want_labels = np.asarray(want_labels)
+    for b, n in enumerate(lens):
+        got = P.collapse_frame_labels(labels[:n, b].tolist(), 2, S, **args)
+        assert got == graphs.collapse_by_arc_table(ogen.decoding_graph, labels[:n, b].tolist())
+        if not np.array_equal(labels[:n, b], want_labels[:n, b]):
+            # fp32 recursion vs fp64 oracle: a different path is acceptable only when it is a path of the
+            # graph (checked by the collapse above) whose own fp64 score ties with the optimum
+            mine = float(sum(np.float64(logits[t, b, labels[t, b]]) for t in range(n)))
+            assert abs(mine - float(want_score[b])) < 2e-3
+
+
 @pytest.mark.parametrize("S,args", [(12, {}), (49, {"use_contextual_blanks": True})])
 def test_wide_logit_spread_exercises_the_power_of_two_rescale(P, S, args):
     """Logits ~ 12 * N(0,1): the scaled-linear sweeps of the bi-char denominator leave their
