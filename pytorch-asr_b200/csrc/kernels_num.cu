@@ -7,28 +7,29 @@
 // most 3 arcs into / out of a state.
 //
 // Number domain.  A training graph is a chain, so alpha_t of the states that carry the posterior
-// mass sits hundreds of binary orders below max_s alpha_t[s]: scaled linear numbers underflow
+// mass sits hundreds of binary orders below max_s alpha_t[s]: numbers scaled per frame underflow
 // (measured at T = 400) and a plain fp32 log value of that magnitude has an ulp of ~1.5e-5, which
-// is where the round-1 kernel lost the gradient tolerance at T >= 800.  Every value is therefore
-// carried as  log2 v = I + f  with an exact int32 integer part I and an fp32 fraction |f| <= 1/2:
-// the integer parts add exactly, only differences of integer parts (small) and fractions ever
-// meet in floating point, so the precision does not depend on the magnitude, no per-frame
-// normaliser is needed and nothing is lagged.  Integer <-> float conversions go through the
-// 1.5 * 2^23 magic constant (FADD / IADD), not through the quarter-rate conversion unit.
+// is where the round-1 kernel lost the gradient tolerance at T >= 800.  Every value is therefore a
+// block-floating-point pair  v = f * 2^E  with an fp32 mantissa f in {0} U [1, 2) and an exact
+// int32 exponent E per state: exponents add exactly, mantissas multiply with a relative error of
+// 2^-24 whatever the magnitude, a sum aligns its terms to the largest exponent with a power of two
+// built in the integer pipe.  No per-frame normaliser, nothing lagged, and no transcendental on
+// the recursion at all: the only MUFU work is one ex2 per label and frame for
+// e = 2^frac(x log2 e) (the integer part of x log2 e goes to the exponent).
 //
-// num_sweep_kernel   4 warps per CTA, each an independent sweep with its own shared-memory slice:
-//                    the vector of the current frame (int2 per state, double buffered), the arcs of
-//                    <= 13 states per lane in registers, a 16-frame cp.async ring of the label
-//                    columns this utterance touches -- gathered straight from the (T, B, V) logits
-//                    (the round-1 gather kernel is gone; the alpha warp writes the compact rows the
-//                    combine reads) -- and the (integer, fraction) split of the next frame's row.
-//                    One __syncwarp per frame, no block barrier, no atomics.
+// num_sweep_kernel   one 128-thread CTA per (utterance, direction): the vector of the current frame in
+//                    shared memory (int2 per state, double buffered), the arcs of <= 4 states per thread
+//                    in registers, a 16-frame cp.async ring of the label columns this utterance touches
+//                    -- gathered straight from the (T, B, V) logits (the round-1 gather kernel is gone;
+//                    the alpha CTA writes the compact rows the combine reads) -- and the (exponent,
+//                    mantissa) form of the next frame's row.  One block barrier per frame, no atomics.
 // num_combine_kernel one warp per frame: gamma_t[j] = sum_{arcs e labelled j}
-//                    2^(alpha_t[src] + x_t[j] + w_e + beta_{t+1}[dst] - cost), fixed summation order
-//                    (arcs grouped by label on the host), row normalised to one; with a factorised
-//                    denominator the result is subtracted from the dense gradient rows directly.
+//                    alpha_t[src] e_t[j] w_e beta_{t+1}[dst] / cost, fixed summation order (arcs grouped
+//                    by label on the host), row normalised to one; with a factorised denominator the
+//                    result is subtracted from the dense gradient rows directly.
 #include <algorithm>
 #include <cstdlib>
+#include <type_traits>
 
 #include "device_utils.cuh"
 #include "kernels.cuh"
@@ -36,7 +37,7 @@
 namespace ctcg {
 namespace {
 
-constexpr int NWPB = 4;         // sweeps (warps) per CTA, fewer when the graphs are large
+constexpr int NT = 128;         // threads of a sweep CTA
 constexpr int XR = 16;          // frames of label columns in flight per sweep
 constexpr int DEG = 4;          // arcs packed per state
 constexpr int HEAVY = 12;       // labels with more arcs are summed by the whole warp
@@ -44,7 +45,7 @@ constexpr unsigned NOARC = 0xffffffffu;
 constexpr int IDEAD = -(1 << 28);          // integer part of "no path"
 constexpr float MAGIC = 12582912.f;        // 1.5 * 2^23: x + MAGIC has rint(x) in its low mantissa bits
 constexpr int MAGIC_BITS = 0x4B400000;
-constexpr float XCLAMP = 1048576.f;        // |x log2 e| is clamped to 2^20 (T * 2^20 stays inside int32 for T < 2048)
+constexpr float XCLAMP = 65536.f;          // |x log2 e| is clamped to 2^16: T * 2^16 stays above IDEAD for T <= 2048
 
 __device__ __forceinline__ int2 lds64(unsigned a) {
   int2 v;
@@ -59,14 +60,19 @@ __device__ __forceinline__ void cp_async4(unsigned dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
 
-// x (log2 units) -> (rint(x), x - rint(x)); |x| <= 2^20
-__device__ __forceinline__ int2 split_log2(float xs) {
+// x (log2 units, clamped) -> (E, f): 2^x = f * 2^E with E = rint(x), f = 2^(x - E) in [0.707, 1.415]
+__device__ __forceinline__ int2 split_pow2(float xs) {
   xs = fminf(fmaxf(xs, -XCLAMP), XCLAMP);
   const float t = xs + MAGIC;
-  return make_int2(__float_as_int(t) - MAGIC_BITS, __float_as_int(xs - (t - MAGIC)));
+  return make_int2(__float_as_int(t) - MAGIC_BITS, __float_as_int(ex2(xs - (t - MAGIC))));
 }
-// (float)n for |n| < 2^22
-__device__ __forceinline__ float small_int_to_float(int n) { return __int_as_float(n + MAGIC_BITS) - MAGIC; }
+// 2^d for d <= 127; anything at or below -127 is exactly 0
+__device__ __forceinline__ float pow2c(int d) { return __int_as_float((max(d, -127) + 127) << 23); }
+// v > 0 normal -> (floor(log2 v), mantissa in [1, 2))
+__device__ __forceinline__ int2 renorm(float v, int base) {
+  const int bits = __float_as_int(v);
+  return make_int2(base + ((bits >> 23) - 127), (bits & 0x007fffff) | 0x3f800000);
+}
 
 struct SweepPlan {
   int pk, w, a0, a1, fin, lab, land, xt, bytes;  // byte offsets inside one warp's slice
@@ -91,32 +97,33 @@ __host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp, bool unit) {
   return p;
 }
 
-// One state: log-sum-exp over its DK arcs in the (integer, fraction) representation.
+// One state: sum over its DK arcs, terms aligned to the largest exponent.  An absent / dead arc has
+// mantissa 0 and an exponent near IDEAD, far below any live one.
 template <int DK>
-__device__ __forceinline__ int2 lse_state(const int (&J)[DK], const float (&g)[DK]) {
+__device__ __forceinline__ int2 sum_state(const int (&J)[DK], const float (&p)[DK]) {
   int Jm = J[0];
 #pragma unroll
   for (int k = 1; k < DK; ++k) Jm = max(Jm, J[k]);
-  float s = 0.f;
+  float acc = 0.f;
 #pragma unroll
-  for (int k = 0; k < DK; ++k) s += ex2(small_int_to_float(max(J[k] - Jm, -4096)) + g[k]);
-  const float r = lg2(s);  // every live state has a term 2^g with |g| <= ~1: r is O(1)
-  const float t = r + MAGIC;
-  const int2 out = make_int2(Jm + (__float_as_int(t) - MAGIC_BITS), __float_as_int(r - (t - MAGIC)));
-  return (Jm < IDEAD / 2 || !(s > 0.f)) ? make_int2(IDEAD, 0) : out;
+  for (int k = 0; k < DK; ++k) acc = fmaf(p[k], pow2c(J[k] - Jm), acc);
+  const int2 out = renorm(acc, Jm);
+  return (acc > 0.f) ? out : make_int2(IDEAD, 0);
 }
 
-// SPT > 0: the arcs of the SPT states of a lane (state = lane + 32 i) live in registers as packed
-// shared-memory byte offsets; SPT == 0: any number of states, arcs re-read from shared memory.
-// DK: arcs per state that exist anywhere in the batch (3 for CTC training graphs, fst_utils.py:592-605).
-template <bool UNIT, int SPT, int DK>
-__global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, const int maxN, const int nsweeps) {
-  extern __shared__ __align__(16) unsigned char sm_all[];
+// One CTA of NT threads per sweep.  SPT > 0: the arcs of the SPT states of a thread (state = tid + NT i)
+// live in registers as shared-memory byte offsets; SPT == 0: any number of states, arcs re-read from
+// shared memory.  DK: arcs per state that exist anywhere in the batch (3 for CTC training graphs,
+// fst_utils.py:592-605).  NLJ > 0: at most NT * NLJ distinct labels, their class ids in registers.
+template <bool UNIT, int SPT, int DK, int NLJ>
+__global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const int maxN) {
+  extern __shared__ __align__(16) unsigned char sm[];
+  __shared__ int red_i[NT / 32];
+  __shared__ float red_f[NT / 32];
   const GraphDev& g = a.g;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int q = blockIdx.x * (blockDim.x >> 5) + warp;
-  if (q >= nsweeps) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool both = a.write_grad != 0;
+  const int q = blockIdx.x;
   const int b = both ? (q >> 1) : q;
   const int DIR = both ? (q & 1) : 0;
   const int gi = (g.num_graphs == 1) ? 0 : b;
@@ -128,7 +135,6 @@ __global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, 
   const int len = min(a.lens[b], a.T);
   const int nlp = (int)a.x_stride_t, arow = a.alpha_row;
   const SweepPlan P = sweep_plan(maxN, nlp, UNIT);
-  unsigned char* sm = sm_all + (size_t)warp * P.bytes;
   uint4* pkv = reinterpret_cast<uint4*>(sm + P.pk);
   float4* wv = reinterpret_cast<float4*>(sm + P.w);
   int2* abuf0 = reinterpret_cast<int2*>(sm + P.a0);
@@ -142,7 +148,7 @@ __global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, 
   const int32_t* oth = DIR ? g.out_dst : g.in_src;
   const int32_t* clab = DIR ? g.out_clab : g.in_clab;
   const float* wgt = DIR ? g.out_w : g.in_w;
-  for (int s = lane; s < n; s += 32) {
+  for (int s = tid; s < n; s += NT) {
     unsigned pi[DEG];
     float wi[DEG];
     const int e0 = ptr[ro + s], e1 = ptr[ro + s + 1];
@@ -159,15 +165,15 @@ __global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, 
     fin[s] = (f > kDeadWeight) ? f * kLog2e : neg_inf();
     int2 v0 = make_int2(IDEAD, 0);
     if (DIR) {
-      if (f > kDeadWeight) v0 = split_log2(f * kLog2e);
+      if (f > kDeadWeight) v0 = split_pow2(f * kLog2e);
     } else if (s == 0) {
-      v0 = make_int2(0, 0);
+      v0 = make_int2(0, __float_as_int(1.f));
     }
     abuf0[s] = v0;
   }
-  if (lane == 0) abuf0[maxN] = abuf1[maxN] = make_int2(IDEAD, 0);  // the slot absent arcs point at
-  for (int j = lane; j < nlp; j += 32) labs[j] = (j < nl) ? g.lab_list[lo + j] : 0;
-  __syncwarp();
+  if (tid == 0) abuf0[maxN] = abuf1[maxN] = make_int2(IDEAD, 0);  // the slot absent arcs point at
+  for (int j = tid; j < nlp; j += NT) labs[j] = (j < nl) ? g.lab_list[lo + j] : 0;
+  __syncthreads();
 
   auto frame_t = [&](int i) { return DIR ? len - 1 - i : i; };
   const bool direct = a.dense_x != nullptr;
@@ -175,30 +181,53 @@ __global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, 
   float* xout = (direct && DIR == 0 && a.write_grad) ? const_cast<float*>(xb) : nullptr;
   const float* dense = direct ? a.dense_x + (long long)b * a.dense_stride_b : nullptr;
   const unsigned land_a = sm_u32(land);
+  constexpr int NLR = NLJ > 0 ? NLJ : 1;
+  int labr[NLR];
+#pragma unroll
+  for (int jj = 0; jj < NLR; ++jj) labr[jj] = (tid + NT * jj < nl) ? labs[tid + NT * jj] : -1;
   auto issue_x = [&](int i) {
     if (i < len) {
       const int t = frame_t(i);
       const int slot = i % XR;
       if (direct) {
         const float* src = dense + (long long)t * a.dense_stride_t;
-        for (int j = lane; j < nl; j += 32) cp_async4(land_a + (slot * nlp + j) * 4, src + labs[j]);
+        const unsigned d0 = land_a + (slot * nlp + tid) * 4;
+        if (NLJ > 0) {
+#pragma unroll
+          for (int jj = 0; jj < NLR; ++jj)
+            if (labr[jj] >= 0) cp_async4(d0 + jj * NT * 4, src + labr[jj]);
+        } else {
+          for (int j = tid; j < nl; j += NT) cp_async4(land_a + (slot * nlp + j) * 4, src + labs[j]);
+        }
       } else {
         const float* src = xb + (long long)t * nlp;
-        for (int cc = lane; cc < nlp / 4; cc += 32) cp_async16(land + slot * nlp + 4 * cc, src + 4 * cc);
+        for (int cc = tid; cc < nlp / 4; cc += NT) cp_async16(land + slot * nlp + 4 * cc, src + 4 * cc);
       }
     }
     cp_async_commit();
   };
-  // landed row of frame i -> (integer, fraction) of x log2 e; the alpha sweep also writes the compact row
+  // landed row of frame i -> (exponent, mantissa) of e = 2^(x log2 e); the alpha sweep also writes the compact row
   auto transform = [&](int i) {
     if (i >= len) return;
     const float* src = land + (i % XR) * nlp;
     int2* dst = xt + (i & 1) * nlp;
     float* xo = xout ? xout + (long long)frame_t(i) * nlp : nullptr;
-    for (int j = lane; j < nlp; j += 32) {
-      const float x = (j < nl) ? src[j] : 0.f;
-      dst[j] = split_log2(x * kLog2e);
-      if (xo) xo[j] = x;
+    if (NLJ > 0) {
+#pragma unroll
+      for (int jj = 0; jj < NLR; ++jj) {
+        const int j = tid + NT * jj;
+        if (j < nlp) {
+          const float x = (labr[jj] >= 0) ? src[j] : 0.f;
+          dst[j] = split_pow2(x * kLog2e);
+          if (xo) xo[j] = x;
+        }
+      }
+    } else {
+      for (int j = tid; j < nlp; j += NT) {
+        const float x = (j < nl) ? src[j] : 0.f;
+        dst[j] = split_pow2(x * kLog2e);
+        if (xo) xo[j] = x;
+      }
     }
   };
   int2* rows = reinterpret_cast<int2*>((DIR ? a.beta_ws : a.alpha_ws) + (long long)b * a.T * arow);
@@ -206,79 +235,82 @@ __global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, 
 
   for (int i = 0; i < XR - 1; ++i) issue_x(i);
   cp_async_wait<XR - 2>();
-  __syncwarp();
+  __syncthreads();
   transform(0);
   if (spill && len > 0) {
     int2* r0 = rows + (long long)frame_t(0) * (arow / 2);
-    for (int s = lane; s < n; s += 32) r0[s] = abuf0[s];
+    for (int s = tid; s < n; s += NT) r0[s] = abuf0[s];
   }
-  __syncwarp();
 
   unsigned ac = sm_u32(abuf0), an = sm_u32(abuf1);
   const unsigned xt_a = sm_u32(xt);
   constexpr int NSP = SPT > 0 ? SPT : 1;
-  unsigned arcs[NSP][DK];
+  unsigned asrc[NSP][DK], alab[NSP][DK];  // byte offsets of the source state / the label
   float wreg[NSP][UNIT ? 1 : DK];
   if (SPT > 0) {
 #pragma unroll
     for (int i = 0; i < NSP; ++i) {
-      const int s = lane + 32 * i;
+      const int s = tid + NT * i;
       const uint4 pk = (s < n) ? pkv[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
       const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
       const float4 w = (!UNIT && s < n) ? wv[s] : make_float4(0.f, 0.f, 0.f, 0.f);
       const float ww[DEG] = {w.x, w.y, w.z, w.w};
 #pragma unroll
       for (int k = 0; k < DK; ++k) {
-        arcs[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 8u : ((pkk[k] & 0xffffu) * 8u) | ((pkk[k] >> 16) * 8u << 16);
+        asrc[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 8u : (pkk[k] & 0xffffu) * 8u;
+        alab[i][k] = (pkk[k] == NOARC) ? 0u : (pkk[k] >> 16) * 8u;
         if (!UNIT) wreg[i][k] = ww[k];
       }
     }
   }
+  // ONE block barrier per frame.  It publishes (a) the vector and the split label row written during
+  // the previous frame, (b) the landed label row of the next frame (every thread has waited for its own
+  // copies), and it separates this frame's writes from the previous frame's reads of the same buffers.
   for (int i = 0; i < len; ++i) {
     issue_x(i + XR - 1);
-    cp_async_wait<XR - 2>();  // the row of frame i + 1 has landed
-    __syncwarp();
+    cp_async_wait<XR - 2>();  // this thread's share of the row of frame i + 1 has landed
+    __syncthreads();
     transform(i + 1);
     const unsigned xa = xt_a + (i & 1) * nlp * 8;
     int2* rn = (spill && i + 1 < len) ? rows + (long long)frame_t(i + 1) * (arow / 2) : nullptr;
     if (SPT > 0) {
-      // three phases, so that the loads of all states are in flight before the first log-sum-exp
+      // three phases, so that every load is in flight before the first sum
       int J[NSP][DK];
-      float gf[NSP][DK];
+      float pm[NSP][DK];
 #pragma unroll
       for (int u = 0; u < NSP; ++u) {
 #pragma unroll
         for (int k = 0; k < DK; ++k) {
-          const int2 av = lds64(ac + (arcs[u][k] & 0xffffu));
-          const int2 xv = lds64(xa + (arcs[u][k] >> 16));
+          const int2 av = lds64(ac + asrc[u][k]);
+          const int2 xv = lds64(xa + alab[u][k]);
           J[u][k] = av.x + xv.x;
-          gf[u][k] = __int_as_float(av.y) + __int_as_float(xv.y);
+          pm[u][k] = __int_as_float(av.y) * __int_as_float(xv.y);
           if (!UNIT) {
-            const int2 ws = split_log2(wreg[u][k]);
+            const int2 ws = split_pow2(wreg[u][k]);
             J[u][k] += ws.x;
-            gf[u][k] += __int_as_float(ws.y);
+            pm[u][k] *= __int_as_float(ws.y);
           }
         }
       }
       int2 res[NSP];
 #pragma unroll
-      for (int u = 0; u < NSP; ++u) res[u] = lse_state<DK>(J[u], gf[u]);
+      for (int u = 0; u < NSP; ++u) res[u] = sum_state<DK>(J[u], pm[u]);
 #pragma unroll
       for (int u = 0; u < NSP; ++u) {
-        const int s = lane + 32 * u;
+        const int s = tid + NT * u;
         if (s < n) {
           sts64(an + s * 8, res[u]);
           if (rn) rn[s] = res[u];
         }
       }
     } else {
-      constexpr int CH = 4;  // states of a lane per pass
-      for (int s0 = lane; s0 < n; s0 += 32 * CH) {
+      constexpr int CH = 2;
+      for (int s0 = tid; s0 < n; s0 += NT * CH) {
         int J[CH][DEG];
-        float gf[CH][DEG];
+        float pm[CH][DEG];
 #pragma unroll
         for (int u = 0; u < CH; ++u) {
-          const int s = s0 + 32 * u;
+          const int s = s0 + NT * u;
           const uint4 pk = (s < n) ? pkv[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
           const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
           float ww[DEG] = {0.f, 0.f, 0.f, 0.f};
@@ -292,18 +324,18 @@ __global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, 
             const int2 av = lds64(ac + (v ? (pkk[k] & 0xffffu) : (unsigned)maxN) * 8u);
             const int2 xv = lds64(xa + (v ? (pkk[k] >> 16) : 0u) * 8u);
             J[u][k] = av.x + xv.x;
-            gf[u][k] = __int_as_float(av.y) + __int_as_float(xv.y);
+            pm[u][k] = __int_as_float(av.y) * __int_as_float(xv.y);
             if (!UNIT) {
-              const int2 ws = split_log2(ww[k]);
+              const int2 ws = split_pow2(ww[k]);
               J[u][k] += ws.x;
-              gf[u][k] += __int_as_float(ws.y);
+              pm[u][k] *= __int_as_float(ws.y);
             }
           }
         }
 #pragma unroll
         for (int u = 0; u < CH; ++u) {
-          const int s = s0 + 32 * u;
-          const int2 res = lse_state<DEG>(J[u], gf[u]);
+          const int s = s0 + NT * u;
+          const int2 res = sum_state<DEG>(J[u], pm[u]);
           if (s < n) {
             sts64(an + s * 8, res);
             if (rn) rn[s] = res;
@@ -311,28 +343,36 @@ __global__ void __launch_bounds__(NWPB * 32) num_sweep_kernel(const PathArgs a, 
         }
       }
     }
-    __syncwarp();
     const unsigned tmp = ac;
     ac = an;
     an = tmp;
   }
   cp_async_wait<0>();
   if (DIR) return;
-  // terminal: cost = LSE_n(alpha_len[n] + final[n])
+  __syncthreads();
+  // terminal: cost = log sum_n alpha_len[n] final[n]
   const int2* a_end = (len & 1) ? abuf1 : abuf0;
   int Im = IDEAD;
-  for (int s = lane; s < n; s += 32)
-    if (fin[s] > neg_inf()) Im = max(Im, a_end[s].x);
+  for (int s = tid; s < n; s += NT)
+    if (fin[s] > neg_inf() && a_end[s].x > IDEAD / 2) Im = max(Im, a_end[s].x);
   Im = __reduce_max_sync(0xffffffffu, Im);
+  if (lane == 0) red_i[warp] = Im;
+  __syncthreads();
+#pragma unroll
+  for (int w = 0; w < NT / 32; ++w) Im = max(Im, red_i[w]);
   float ts = 0.f;
   if (Im > IDEAD / 2)
-    for (int s = lane; s < n; s += 32)
-      if (fin[s] > neg_inf())
-        ts += ex2(small_int_to_float(max(a_end[s].x - Im, -4096)) + __int_as_float(a_end[s].y) + fin[s]);
+    for (int s = tid; s < n; s += NT)
+      if (fin[s] > neg_inf()) ts += __int_as_float(a_end[s].y) * pow2c(a_end[s].x - Im) * ex2(fin[s]);
   ts = warp_sum(ts);
-  if (lane == 0) {
-    const bool feasible = Im > IDEAD / 2 && ts > 0.f;
-    a.cost[b] = feasible ? ((double)Im + log2((double)ts)) * kLn2 : -1e20;
+  if (lane == 0) red_f[warp] = ts;
+  __syncthreads();
+  if (tid == 0) {
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < NT / 32; ++w) tot += red_f[w];
+    const bool feasible = Im > IDEAD / 2 && tot > 0.f;
+    a.cost[b] = feasible ? ((double)Im + log2((double)tot)) * kLn2 : -1e20;
   }
 }
 
@@ -340,10 +380,9 @@ constexpr int CB_W = 8;             // warps per combine CTA (fewer when the row
 constexpr int CB_FPW = 4;           // frames per warp: the graph tables are staged once per warps * CB_FPW frames
 constexpr int CB_TH = CB_W * 32;
 
-// 2^(alpha[src] + beta[dst] + k) in the (integer, fraction) representation; kI / kf hold x_t[j] - cost (+ w)
-__device__ __forceinline__ float post_term(int2 av, int2 bv, int kI, float kf) {
-  const int e = av.x + bv.x + kI;  // dead parts are -2^28 each: no wrap-around
-  return ex2(small_int_to_float(min(max(e, -4096), 4096)) + (__int_as_float(av.y) + __int_as_float(bv.y) + kf));
+// alpha[src] * beta[dst] * k * 2^(exponents): kE / km hold e_t[j] (and w) with the cost's exponent taken off
+__device__ __forceinline__ float post_term(int2 av, int2 bv, int kE, float km) {
+  return (__int_as_float(av.y) * __int_as_float(bv.y)) * (km * pow2c(min(av.x + bv.x + kE, 64)));
 }
 
 // With a.scatter_grad set the normalised posteriors are subtracted from the dense gradient rows the
@@ -393,11 +432,8 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
   float* gt = wbase + 2 * stg;
   const double costn = a.cost[b];
   const bool feasible = costn > -1e19;
-  // cost in log2 units, split like every other value
-  const double cost2 = costn / kLn2;
-  const double cI_d = rint(cost2);
-  const int cI = (int)cI_d;
-  const float cf = (float)(cost2 - cI_d);
+  // the cost's exponent keeps the terms in range; its mantissa cancels in the row normalisation
+  const int cE = (int)rint(costn / kLn2);
   const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
   const int V = a.scatter_V;
   auto stage = [&](int q) {  // always commits a group (possibly empty), so that the wait counts stay uniform
@@ -457,13 +493,13 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
       const bool heavy = (e1 - e0) > HEAVY;
       float acc = 0.f;
       if (j < nl && !heavy) {
-        const int2 xs = split_log2(xt[j] * kLog2e);
-        const int kI = xs.x - cI;
-        const float kf = __int_as_float(xs.y) - cf;
+        const int2 xs = split_pow2(xt[j] * kLog2e);
+        const int kE = xs.x - cE;
+        const float km = __int_as_float(xs.y);
         for (int e = e0; e < e1; ++e) {
           const unsigned pk = lab_pk[e];
-          const int2 ws = UNIT ? make_int2(0, 0) : split_log2(lab_w[e]);
-          acc += post_term(at[pk & 0xffffu], bt[pk >> 16], kI + ws.x, kf + __int_as_float(ws.y));
+          const int2 ws = UNIT ? make_int2(0, __float_as_int(1.f)) : split_pow2(lab_w[e]);
+          acc += post_term(at[pk & 0xffffu], bt[pk >> 16], kE + ws.x, UNIT ? km : km * __int_as_float(ws.y));
         }
       }
       unsigned hm = __ballot_sync(0xffffffffu, heavy);
@@ -472,14 +508,14 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
         hm &= hm - 1;
         const int jh = base + src_lane;
         const int h0 = __shfl_sync(0xffffffffu, e0, src_lane), h1 = __shfl_sync(0xffffffffu, e1, src_lane);
-        const int2 xs = split_log2(xt[jh] * kLog2e);
-        const int kI = xs.x - cI;
-        const float kf = __int_as_float(xs.y) - cf;
+        const int2 xs = split_pow2(xt[jh] * kLog2e);
+        const int kE = xs.x - cE;
+        const float km = __int_as_float(xs.y);
         float part = 0.f;
         for (int e = h0 + lane; e < h1; e += 32) {
           const unsigned pk = lab_pk[e];
-          const int2 ws = UNIT ? make_int2(0, 0) : split_log2(lab_w[e]);
-          part += post_term(at[pk & 0xffffu], bt[pk >> 16], kI + ws.x, kf + __int_as_float(ws.y));
+          const int2 ws = UNIT ? make_int2(0, __float_as_int(1.f)) : split_pow2(lab_w[e]);
+          part += post_term(at[pk & 0xffffu], bt[pk >> 16], kE + ws.x, UNIT ? km : km * __int_as_float(ws.y));
         }
         part = warp_sum(part);
         if (lane == src_lane) acc = part;
@@ -528,31 +564,31 @@ int combine_warps(const PathArgs& a, bool unit) {
   while (w > 0 && combine_smem_bytes(a, unit, w) > kSmemBudget) --w;
   return w;
 }
-int sweep_warps(const PathArgs& a, bool unit) {
-  const int per = sweep_plan(a.g.max_states, (int)a.x_stride_t, unit).bytes;
-  return std::min(NWPB, kSmemBudget / std::max(per, 1));
-}
-
+int sweep_smem_bytes(const PathArgs& a, bool unit) { return sweep_plan(a.g.max_states, (int)a.x_stride_t, unit).bytes; }
 }  // namespace
 
-template <bool UNIT, int SPT, int DK>
-static cudaError_t launch_sweep_dk(const PathArgs& a, int warps, int nsweeps, cudaStream_t st) {
-  const int bytes = warps * sweep_plan(a.g.max_states, (int)a.x_stride_t, UNIT).bytes;
-  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT, DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+template <bool UNIT, int SPT, int DK, int NLJ>
+static cudaError_t launch_sweep_nl(const PathArgs& a, int nsweeps, cudaStream_t st) {
+  const int bytes = sweep_smem_bytes(a, UNIT);
+  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT, DK, NLJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   if (e != cudaSuccess) return e;
-  num_sweep_kernel<UNIT, SPT, DK><<<(nsweeps + warps - 1) / warps, warps * 32, bytes, st>>>(a, a.g.max_states, nsweeps);
+  num_sweep_kernel<UNIT, SPT, DK, NLJ><<<nsweeps, NT, bytes, st>>>(a, a.g.max_states);
   return cudaGetLastError();
 }
+template <bool UNIT, int SPT, int DK>
+static cudaError_t launch_sweep_dk(const PathArgs& a, int nsweeps, cudaStream_t st) {
+  if (SPT > 0 && a.x_stride_t <= NT * 2) return launch_sweep_nl<UNIT, SPT, DK, 2>(a, nsweeps, st);
+  return launch_sweep_nl<UNIT, SPT, DK, 0>(a, nsweeps, st);
+}
 template <bool UNIT>
-static cudaError_t launch_sweep(const PathArgs& a, int warps, int nsweeps, cudaStream_t st) {
-  const int spt = (a.g.max_states + 31) / 32;
+static cudaError_t launch_sweep(const PathArgs& a, int nsweeps, cudaStream_t st) {
+  const int spt = (a.g.max_states + NT - 1) / NT;
   const bool d3 = a.g.max_in_degree <= 3 && a.g.max_out_degree <= 3;
-  const bool regs = a.g.max_states * 8 <= 65535 && (int)a.x_stride_t * 8 <= 65535;  // packed 16-bit byte offsets
-  if (regs && d3 && spt <= 4) return launch_sweep_dk<UNIT, 4, 3>(a, warps, nsweeps, st);
-  if (regs && d3 && spt <= 7) return launch_sweep_dk<UNIT, 7, 3>(a, warps, nsweeps, st);
-  if (regs && d3 && spt <= 13) return launch_sweep_dk<UNIT, 13, 3>(a, warps, nsweeps, st);
-  if (regs && spt <= 7) return launch_sweep_dk<UNIT, 7, DEG>(a, warps, nsweeps, st);
-  return launch_sweep_dk<UNIT, 0, DEG>(a, warps, nsweeps, st);
+  if (d3 && spt <= 1) return launch_sweep_dk<UNIT, 1, 3>(a, nsweeps, st);
+  if (d3 && spt <= 2) return launch_sweep_dk<UNIT, 2, 3>(a, nsweeps, st);
+  if (d3 && spt <= 4) return launch_sweep_dk<UNIT, 4, 3>(a, nsweeps, st);
+  if (spt <= 2) return launch_sweep_dk<UNIT, 2, DEG>(a, nsweeps, st);
+  return launch_sweep_dk<UNIT, 0, DEG>(a, nsweeps, st);
 }
 
 bool num_split_supported(const PathArgs& a) {
@@ -561,15 +597,14 @@ bool num_split_supported(const PathArgs& a) {
   if (a.g.max_in_degree > DEG || a.g.max_out_degree > DEG) return false;
   if (a.alpha_row < 2 * a.g.max_states) return false;
   const bool unit = a.g.unit_weights != 0;
-  return sweep_warps(a, unit) >= 1 && combine_warps(a, unit) >= 1;
+  return sweep_smem_bytes(a, unit) <= kSmemBudget && combine_warps(a, unit) >= 1;
 }
 
 cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st) {
   const bool unit = a.g.unit_weights != 0;
   ProfScope prof("num_sweep", st);
-  const int warps = sweep_warps(a, unit);
   const int nsweeps = a.write_grad ? 2 * a.B : a.B;
-  const cudaError_t e = unit ? launch_sweep<true>(a, warps, nsweeps, st) : launch_sweep<false>(a, warps, nsweeps, st);
+  const cudaError_t e = unit ? launch_sweep<true>(a, nsweeps, st) : launch_sweep<false>(a, nsweeps, st);
   ++g_launches;
   return e;
 }
