@@ -41,7 +41,8 @@ typedef enum ctcg_status {
   CTCG_ENOMEM = 6,       /* host allocation failed */
   CTCG_EWORKSPACE = 7,   /* workspace too small: call ctcg_workspace_bytes */
   CTCG_EUNSUPPORTED = 8, /* configuration outside what the kernels cover */
-  CTCG_ENOTUPLOADED = 9  /* graph used on device before ctcg_graph_upload */
+  CTCG_ENOTUPLOADED = 9, /* graph used on device before ctcg_graph_upload */
+  CTCG_ESCRATCH = 10     /* problem larger than the built-in scratch of ctcg_viterbi_static */
 } ctcg_status;
 
 /* Opaque handle: one graph shared by a whole batch (a decoding / denominator
@@ -178,6 +179,28 @@ int ctcg_viterbi(const float* log_probs, int32_t T, int32_t B, int32_t V,
                  const int32_t* lens_host, const ctcg_graph* graph, float* score,
                  int32_t* frame_labels, void* workspace, size_t workspace_bytes,
                  void* stream);
+
+/* ctcg_viterbi without any allocation on the call path.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same outputs as ctcg_viterbi; differences:
+ *  - no workspace argument: the kernel's scratch (lengths + one back-pointer per
+ *    frame and state) is a file-scope device array of CTCG_STATIC_SCRATCH_BYTES
+ *    that every GPU which loads the library holds until exit;
+ *  - lens_dev is a DEVICE pointer to B int32 (clamped to [0, T] on the device),
+ *    so the call makes no host->device copy either;
+ *  - the graph must already be uploaded to the current device
+ *    (ctcg_graph_upload allocates: do it at set-up), else CTCG_ENOTUPLOADED;
+ *  - 256*ceil(4B/256) + 4*B*T*pad4(max_states) bytes must fit the array, else
+ *    CTCG_ESCRATCH (nothing is launched).
+ * Calls no cudaMalloc / cudaFree / allocating library routine; launches two
+ * kernels on `stream`.  All calls share the one array (it keeps the previous
+ * call's contents; nothing in it needs to start at zero): calls that overlap on
+ * the GPU -- other streams or host threads on the same device -- race. */
+#define CTCG_STATIC_SCRATCH_BYTES (32u << 20)
+int ctcg_viterbi_static(const float* log_probs, int32_t T, int32_t B, int32_t V,
+                        const int32_t* lens_dev, const ctcg_graph* graph,
+                        float* score, int32_t* frame_labels, void* stream);
 
 /* Number of accepting paths of length lens[b], modulo 2^64 (the
  * integer counterpart of path_reduction on all-zero log-probs). */

@@ -22,7 +22,7 @@ EXPORTS = (
     "ctcg_decoding_graph", "ctcg_training_graphs", "ctcg_graph_from_padded",
     "ctcg_graph_from_arcs", "ctcg_graph_get_info", "ctcg_graph_padded_dims",
     "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
-    "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi",
+    "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static",
     "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
     "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
@@ -73,6 +73,7 @@ def lib():
                                     C.c_size_t, vp]
     L.ctcg_path_sum.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp, C.c_size_t, vp]
     L.ctcg_viterbi.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp, C.c_size_t, vp]
+    L.ctcg_viterbi_static.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp]
     L.ctcg_path_count.argtypes = [i32, vp, vp, vp, vp, C.c_size_t, vp]
     L.ctcg_loss_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp]
     L.ctcg_logits_post_width.argtypes = [i32, i32]
@@ -340,6 +341,27 @@ def viterbi(log_probs, act_lens, graph):
         labels = torch.empty((T, B), dtype=torch.int32, device=dev)
         check(lib().ctcg_viterbi(x.data_ptr(), T, B, V, _np_ptr(lens), graph.ptr, score.data_ptr(),
                                  labels.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev)))
+    return score, labels
+
+
+STATIC_SCRATCH_BYTES = 32 << 20
+
+
+def viterbi_static(log_probs, lens_dev, graph, score, labels):
+    """``ctcg_viterbi_static``: Viterbi with no allocation on the call path (the scratch is a device
+    array built into the library).  Everything is passed in by the caller: ``lens_dev`` int32 (B,) on
+    the device, ``graph`` already uploaded, ``score`` float32 (B,) and ``labels`` int32 (T, B)
+    outputs.  Calls that overlap on the GPU race on the shared scratch."""
+    _require_cuda(log_probs, "log_probs")
+    T, B, V = log_probs.shape
+    assert log_probs.dtype == torch.float32 and log_probs.is_contiguous()
+    assert lens_dev.is_cuda and lens_dev.dtype == torch.int32 and lens_dev.numel() == B
+    assert score.is_cuda and score.dtype == torch.float32 and score.numel() == B
+    assert labels.is_cuda and labels.dtype == torch.int32 and tuple(labels.shape) == (T, B) and labels.is_contiguous()
+    dev = log_probs.device
+    with torch.cuda.device(dev):
+        check(lib().ctcg_viterbi_static(log_probs.data_ptr(), T, B, V, lens_dev.data_ptr(), graph.ptr,
+                                        score.data_ptr(), labels.data_ptr(), _stream_ptr(dev)))
     return score, labels
 
 

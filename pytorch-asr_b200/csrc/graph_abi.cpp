@@ -267,6 +267,7 @@ const char* ctcg_strerror(int status) {
     case CTCG_EWORKSPACE: return "workspace too small";
     case CTCG_EUNSUPPORTED: return "unsupported configuration";
     case CTCG_ENOTUPLOADED: return "graph not uploaded to the device";
+    case CTCG_ESCRATCH: return "problem exceeds the built-in scratch (CTCG_STATIC_SCRATCH_BYTES) of ctcg_viterbi_static";
     default: return "unknown status";
   }
 }

@@ -10,6 +10,8 @@
 //
 // Path counting is the integer counterpart of path_reduction on all-zero
 // log-probs: exact modulo 2^64.
+#include <mutex>
+
 #include "device_utils.cuh"
 #include "kernels.cuh"
 
@@ -189,3 +191,88 @@ cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uin
 }
 
 }  // namespace ctcg
+
+// ---------------------------------------------------------------------------
+// ctcg_viterbi_static: Viterbi with NO allocation anywhere on the call path (no counterpart in the
+// reference; added for callers that cannot allocate: CUDA graph
+// capture, tight serving loops).  The scratch of viterbi_kernel -- the utterance lengths and one
+// back-pointer per (frame, state) -- lives in a file-scope device array of CTCG_STATIC_SCRATCH_BYTES
+// that every GPU which loads the library holds until exit.  In host code the array's name is only a
+// stand-in: its device address is looked up with cudaGetSymbolAddress, once per device with that
+// device current, and that pointer is what the kernels get.
+//
+// Every call shares the one array, which keeps the previous call's contents.  Nothing in it has to
+// start at zero: the lengths are rewritten by clamp_lens_kernel and viterbi_kernel writes every
+// back-pointer (t < len, s < n) before the back-trace reads it.  Calls that overlap on the GPU
+// (different streams, or several host threads on one device) race on the array: serialise them.
+static __device__ __align__(256) unsigned char ctcg_static_scratch[CTCG_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+__global__ void clamp_lens_kernel(const int32_t* __restrict__ in, int B, int T, int32_t* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) out[b] = min(max(in[b], 0), T);
+}
+
+constexpr int kMaxDevices = 64;
+unsigned char* g_static_ptr[kMaxDevices];  // device address of ctcg_static_scratch, per device
+bool g_static_ok[kMaxDevices];
+std::mutex g_static_mu;
+
+// Device address of the scratch on the current device (set-up on the first call per device).
+int static_scratch(unsigned char** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    (void)cudaGetLastError();
+    return CTCG_ECUDA;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ok[dev]) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, ctcg_static_scratch) != cudaSuccess || !p) {
+      (void)cudaGetLastError();
+      return CTCG_ECUDA;
+    }
+    g_static_ptr[dev] = static_cast<unsigned char*>(p);
+    g_static_ok[dev] = true;
+  }
+  *out = g_static_ptr[dev];
+  return CTCG_OK;
+}
+
+}  // namespace
+
+extern "C" int ctcg_viterbi_static(const float* log_probs, int32_t T, int32_t B, int32_t V, const int32_t* lens_dev,
+                                   const ctcg_graph* graph, float* score, int32_t* frame_labels, void* stream) {
+  using namespace ctcg;
+  if (!log_probs || !lens_dev || !graph || !score || !frame_labels || T < 1 || B < 1 || V < 1) return CTCG_EINVAL;
+  if (graph->num_graphs != 1 && graph->num_graphs != B) return CTCG_EINVAL;
+  if (graph->max_label >= V) return CTCG_EINVAL;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return CTCG_ECUDA;
+  }
+  if (!graph->dev_blob || graph->device != dev) return CTCG_ENOTUPLOADED;  // upload is set-up, done by the caller beforehand
+  const int row = pad4(graph->max_states);
+  const size_t lens_bytes = ((size_t)B * 4 + 255) / 256 * 256;
+  const size_t need = lens_bytes + (size_t)B * (size_t)T * (size_t)row * 4;
+  if (need > (size_t)CTCG_STATIC_SCRATCH_BYTES) return CTCG_ESCRATCH;
+  const size_t smem = (size_t)(2 * pad4(graph->max_states) + 4 * NWARP) * 4;
+  if (smem > 200 * 1024) return CTCG_EUNSUPPORTED;
+  unsigned char* scratch = nullptr;
+  const int st_ = static_scratch(&scratch);
+  if (st_ != CTCG_OK) return st_;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int32_t* lens = reinterpret_cast<int32_t*>(scratch);
+  int32_t* back = reinterpret_cast<int32_t*>(scratch + lens_bytes);
+  clamp_lens_kernel<<<(B + 127) / 128, 128, 0, st>>>(lens_dev, B, T, lens);
+  if (cudaFuncSetAttribute(viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return CTCG_ECUDA;
+  }
+  viterbi_kernel<<<B, NT, smem, st>>>(log_probs, T, B, V, lens, graph->dev, back, row, score, frame_labels);
+  g_launches += 2;
+  if (cudaGetLastError() != cudaSuccess) return CTCG_ECUDA;
+  return CTCG_OK;
+}
