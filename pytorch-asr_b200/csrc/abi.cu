@@ -59,7 +59,7 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
   if (num) {
     p.nlp = pad4(std::max(num->max_labels, 1));
     p.arow_num = pad4(2 * num->max_states + 2);  // split numerator: (integer, fraction) per state
-    p.xg = take(TB * p.nlp * 4);
+    p.xg = take(TB * p.nlp * 8);  // float columns (generic kernel) or (exponent, mantissa) pairs (split sweeps)
     p.gg = take(TB * p.nlp * 4);
     p.alpha_num = take(TB * p.arow_num * 4);
     p.beta_num = take(TB * p.arow_num * 4);
@@ -221,6 +221,7 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   v.lab_w = reinterpret_cast<const float*>(p + o[17]);
   v.max_arcs = g->max_arcs;
   v.unit_weights = g->unit_weights;
+  v.in_label_uniform = g->in_label_uniform;
   g->dev_blob = d;
   g->dev_bytes = blob.size();
   g->device = dev;
@@ -390,7 +391,7 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   PathArgs num_args{};
   bool split_num = false, scatter_num = false;
   st_ = [&]() -> int {
-    // 1.-2. numerator forward-backward on the label columns each utterance touches
+    // 2. numerator forward-backward on the compact columns
     PathArgs a{};
     a.g = num->dev;
     a.x = xg;
@@ -412,17 +413,9 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     a.write_grad = grad != nullptr;
     a.beta_ws = reinterpret_cast<float*>(ws + p.beta_num);
     const bool split = num_split_supported(a);
-    // the split sweeps gather the columns themselves; a per-context softmax (and the generic kernel) go
-    // through the gather kernel, which also normalises
-    const bool direct = split && normalize != CTCG_NORM_CONTEXT;
-    if (direct) {
-      a.dense_x = logits;
-      a.dense_stride_t = (long long)B * V;
-      a.dense_stride_b = V;
-    } else {
-      CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp,
-                              normalize == CTCG_NORM_CONTEXT ? 2 : 0, num_symbols, st));
-    }
+    // 1. compact the label columns each utterance touches (the split sweeps take them as pairs)
+    CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp, normalize == CTCG_NORM_CONTEXT ? 2 : 0,
+                            num_symbols, split, st));
     if (split) {
       CTCG_CUDA(launch_num_sweeps(a, st));
       num_args = a;

@@ -47,6 +47,7 @@ struct GraphDev {
   const float* lab_w;
   int32_t max_arcs;      // most arcs of any one graph
   int32_t unit_weights;  // every arc weight is 0 (semiring One)
+  int32_t in_label_uniform;  // all arcs into a state carry the same label (true for every H o C o transcript graph)
 };
 
 // Factorised description of the bi-char decoding graph (fst_utils.py:765-817):
@@ -76,6 +77,7 @@ struct ctcg_graph {
   std::vector<float> lab_w;
   int32_t max_arcs = 0;
   int32_t unit_weights = 1;
+  int32_t in_label_uniform = 1;
   ctcg::Structured structured{0, 0, 0, 0, 0};
   // device mirror
   int device = -1;

@@ -319,6 +319,7 @@ int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out) {
     int status = CTCG_OK;
     int32_t max_in = 0, max_out = 0;
     bool unit = true;
+    bool in_uniform = true;  // all arcs into a state carry one label
   };
   std::vector<PerGraph> per(G);
   // ---- pass A: validation (fst_utils.py:272-274) + distinct labels ----
@@ -446,6 +447,9 @@ int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out) {
       return std::tie(a.src, a.label, a.weight) < std::tie(b.src, b.label, b.weight);
     }, &idx, &fill);
     for (int32_t s = 0; s <= n; ++s) g->in_ptr[ro + s] = arc_base + ptr[s];
+    for (int32_t s = 0; s < n; ++s)
+      for (int32_t i = ptr[s] + 1; i < ptr[s + 1]; ++i)
+        if (r.arcs[idx[i]].label != r.arcs[idx[ptr[s]]].label) pg.in_uniform = false;
     for (int32_t i = 0; i < na; ++i) {
       const Arc& a = r.arcs[idx[i]];
       g->in_src[arc_base + i] = a.src;
@@ -478,6 +482,7 @@ int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out) {
     g->max_in_degree = std::max(g->max_in_degree, per[gi].max_in);
     g->max_out_degree = std::max(g->max_out_degree, per[gi].max_out);
     if (!per[gi].unit) g->unit_weights = 0;
+    if (!per[gi].in_uniform) g->in_label_uniform = 0;
   }
   *out = g;
   return CTCG_OK;

@@ -11,6 +11,7 @@ namespace ctcg {
 struct PathArgs {
   GraphDev g;
   const float* x;         // scores; element (t, b, l) at x[t*x_stride_t + b*x_stride_b + l]
+                          // (split numerator: int2 pairs written by launch_gather(pairs), strides in entries)
   long long x_stride_t;
   long long x_stride_b;
   float x_scale;          // multiplies x on load (log2(e) for natural-log input, 1 if prescaled)
@@ -22,9 +23,6 @@ struct PathArgs {
   float* scatter_grad;    // nullable: dense (T, B, scatter_V) gradient the split numerator subtracts its posteriors from
   int32_t scatter_V;
   float* beta_ws;         // nullable; same shape as alpha_ws: beta rows of the split numerator (kernels_num.cu)
-  const float* dense_x;   // nullable: the (T, B, V) logits; the numerator sweeps gather their label columns
-  long long dense_stride_t;  // from it themselves and the alpha sweep writes the compact rows x[b][t][j]
-  long long dense_stride_b;
   double* cost;           // [B] natural-log path sum
   float* gout;            // posterior rows; element (t, b, l) at gout[t*g_stride_t + b*g_stride_b + l]
   long long g_stride_t;
@@ -47,9 +45,10 @@ cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st);
 // Posteriors from the spilled rows; with a.scatter_grad set they are subtracted from the dense gradient directly.
 cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st);
 
-// xg[b][t][j] = logits[t][b][lab_list_b[j]] * log2(e) for t < lens[b]
+// xg[b][t][j] = logits[t][b][lab_list_b[j]] for t < lens[b] (minus the context block's LSE when normalize == 2);
+// pairs: as int2 {rint(x log2 e), bits of 2^frac} for the split numerator sweeps (8 bytes per entry)
 cudaError_t launch_gather(const float* logits, int T, int B, int V, const int32_t* lens,
-                          const GraphDev& num, float* xg, int nlp, int normalize, int S,
+                          const GraphDev& num, float* xg, int nlp, int normalize, int S, bool pairs,
                           cudaStream_t st);
 
 // Row pass: mode 1 grad = softmax(x) - scatter(gg), rowlse = logsumexp(x);

@@ -1,10 +1,21 @@
-// Numerator (per-utterance training graph) forward-backward, sm_100a: one WARP per (utterance,
-// direction) runs the alpha or the beta recursion (num_sweep_kernel), then a time-parallel kernel
-// forms the posteriors (num_combine_kernel).
+// Numerator (per-utterance training graph) forward-backward, sm_100a: one CTA per (utterance,
+// direction) runs the alpha-type or the beta-type recursion (num_sweep_kernel), then a time-parallel
+// kernel forms the posteriors (num_combine_kernel).
 //
 // Reference semantics: PathLogSumExp.forward/backward (att_speech/fst_utils.py:400-488) on the
 // graphs of BaseGraphGen.get_training_matrices (fst_utils.py:647-660): N = 2U+1 states with at
 // most 3 arcs into / out of a state.
+//
+// One recursion for both directions.  In a training graph (decoding graph composed with the
+// transcript chain) every arc into a state carries the same label, lab(s) -- the graph compiler
+// checks it (GraphDev::in_label_uniform); other graphs take the generic CSR kernel.  With
+// e_t[j] = exp(x_t[j]):
+//   forward   alpha_{t+1}[s] = e_t[lab(s)]     * sum_{arcs k into s}   w_k alpha_t[src_k]
+//   backward  C_{t-1}[s]     = e_{t-1}[lab(s)] * sum_{arcs k out of s} w_k C_t[dst_k],
+//             C_t[d] = e_t[lab(d)] beta_{t+1}[d],   C_{len-1} = e_{len-1}[lab] * final
+// i.e. v' = e[lab] (.) (M v) with M the in-arc or the out-arc matrix: one label look-up per state
+// instead of one per arc, and the posterior needs no logits any more:
+//   gamma_t[j] = sum_{arcs labelled j} alpha_t[src] w C_t[dst] / Z.
 //
 // Number domain.  A training graph is a chain, so alpha_t of the states that carry the posterior
 // mass sits hundreds of binary orders below max_s alpha_t[s]: numbers scaled per frame underflow
@@ -14,19 +25,19 @@
 // int32 exponent E per state: exponents add exactly, mantissas multiply with a relative error of
 // 2^-24 whatever the magnitude, a sum aligns its terms to the largest exponent with a power of two
 // built in the integer pipe.  No per-frame normaliser, nothing lagged, and no transcendental on
-// the recursion at all: the only MUFU work is one ex2 per label and frame for
-// e = 2^frac(x log2 e) (the integer part of x log2 e goes to the exponent).
+// the recursion: the only MUFU work is one ex2 per label and frame for e = 2^frac(x log2 e) (the
+// integer part of x log2 e goes to the exponent), done by the producer warps off the chain.
 //
-// num_sweep_kernel   one 128-thread CTA per (utterance, direction): the vector of the current frame in
-//                    shared memory (int2 per state, double buffered), the arcs of <= 4 states per thread
-//                    in registers, a 16-frame cp.async ring of the label columns this utterance touches
-//                    -- gathered straight from the (T, B, V) logits (the round-1 gather kernel is gone;
-//                    the alpha CTA writes the compact rows the combine reads) -- and the (exponent,
-//                    mantissa) form of the next frame's row.  One block barrier per frame, no atomics.
-// num_combine_kernel one warp per frame: gamma_t[j] = sum_{arcs e labelled j}
-//                    alpha_t[src] e_t[j] w_e beta_{t+1}[dst] / cost, fixed summation order (arcs grouped
-//                    by label on the host), row normalised to one; with a factorised denominator the
-//                    result is subtracted from the dense gradient rows directly.
+// num_sweep_kernel   256 threads.  7 compute warps own 1..4 states per thread (arcs as shared-memory
+//                    byte offsets in registers); the vector lives in shared memory (int2 per state,
+//                    double buffered).  One producer warp streams the rows of (exponent, mantissa)
+//                    pairs of the label columns this utterance touches -- written once per batch by
+//                    gather_kernel (kernels_rows.cu), which spreads the scattered 4-byte reads of the
+//                    (T, B, V) logits over the whole GPU -- into a 16-row ring with 16-byte cp.async
+//                    copies.  One block barrier per frame, no atomics, no MUFU.
+// num_combine_kernel one warp per frame: the sum above in a fixed order (arcs grouped by label on the
+//                    host), row normalised to one; with a factorised denominator the compact rows go
+//                    to the denominator's combine kernel, which subtracts them while it writes.
 #include <algorithm>
 #include <cstdlib>
 #include <type_traits>
@@ -37,12 +48,16 @@
 namespace ctcg {
 namespace {
 
-constexpr int NT = 128;         // threads of a sweep CTA
-constexpr int XR = 16;          // frames of label columns in flight per sweep
-constexpr int DEG = 4;          // arcs packed per state
-constexpr int HEAVY = 12;       // labels with more arcs are summed by the whole warp
-constexpr unsigned NOARC = 0xffffffffu;
-constexpr int IDEAD = -(1 << 28);          // integer part of "no path"
+constexpr int NCW = 7;           // compute warps of a sweep CTA
+constexpr int NPW = 1;           // producer warp
+constexpr int NCT = NCW * 32;    // compute threads: state s = tid + NCT * u
+constexpr int NPT = NPW * 32;    // producer threads
+constexpr int NT = NCT + NPT;
+constexpr int MAXSPT = 4;        // states per compute thread
+constexpr int ER = 16;           // (exponent, mantissa) rows of the label columns in flight
+constexpr int DEG = 4;           // arcs per state the sweeps take
+constexpr int HEAVY = 12;        // combine: labels with more arcs are summed by the whole warp
+constexpr int IDEAD = -(1 << 28);          // exponent of "no path"
 constexpr float MAGIC = 12582912.f;        // 1.5 * 2^23: x + MAGIC has rint(x) in its low mantissa bits
 constexpr int MAGIC_BITS = 0x4B400000;
 constexpr float XCLAMP = 65536.f;          // |x log2 e| is clamped to 2^16: T * 2^16 stays above IDEAD for T <= 2048
@@ -54,6 +69,11 @@ __device__ __forceinline__ int2 lds64(unsigned a) {
 }
 __device__ __forceinline__ void sts64(unsigned a, int2 v) {
   asm volatile("st.shared.v2.s32 [%0], {%1,%2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ float lds32(unsigned a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
 }
 __device__ __forceinline__ unsigned sm_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void cp_async4(unsigned dst, const void* src) {
@@ -68,16 +88,17 @@ __device__ __forceinline__ int2 split_pow2(float xs) {
 }
 // 2^d for d <= 127; anything at or below -127 is exactly 0
 __device__ __forceinline__ float pow2c(int d) { return __int_as_float((max(d, -127) + 127) << 23); }
-// v > 0 normal -> (floor(log2 v), mantissa in [1, 2))
+// v > 0 normal -> (base + floor(log2 v), mantissa in [1, 2)); v == 0 -> dead
 __device__ __forceinline__ int2 renorm(float v, int base) {
   const int bits = __float_as_int(v);
-  return make_int2(base + ((bits >> 23) - 127), (bits & 0x007fffff) | 0x3f800000);
+  const int2 out = make_int2(base + ((bits >> 23) - 127), (bits & 0x007fffff) | 0x3f800000);
+  return (v > 0.f) ? out : make_int2(IDEAD, 0);
 }
 
 struct SweepPlan {
-  int pk, w, a0, a1, fin, lab, land, xt, bytes;  // byte offsets inside one warp's slice
+  int a0, a1, er, bytes;
 };
-__host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp, bool unit) {
+__host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp) {
   SweepPlan p;
   int o = 0;
   auto take = [&](int bytes) {
@@ -85,41 +106,33 @@ __host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp, bool unit) {
     o += (bytes + 15) & ~15;
     return at;
   };
-  p.pk = take(maxN * DEG * 4);
-  p.w = unit ? 0 : take(maxN * DEG * 4);
   p.a0 = take((maxN + 1) * 8);
   p.a1 = take((maxN + 1) * 8);
-  p.fin = take(maxN * 4);
-  p.lab = take(nlp * 4);
-  p.land = take(XR * nlp * 4);
-  p.xt = take(2 * nlp * 8);
+  p.er = take(ER * nlp * 8);
   p.bytes = o;
   return p;
 }
 
-// One state: sum over its DK arcs, terms aligned to the largest exponent.  An absent / dead arc has
-// mantissa 0 and an exponent near IDEAD, far below any live one.
+// One state: sum over its DK arcs, terms aligned to the largest exponent, times the label factor.
+// An absent / dead arc has mantissa 0 and an exponent near IDEAD, far below any live one.
 template <int DK>
-__device__ __forceinline__ int2 sum_state(const int (&J)[DK], const float (&p)[DK]) {
+__device__ __forceinline__ int2 step_state(const int (&J)[DK], const float (&p)[DK], const int2 ev) {
   int Jm = J[0];
 #pragma unroll
   for (int k = 1; k < DK; ++k) Jm = max(Jm, J[k]);
   float acc = 0.f;
 #pragma unroll
   for (int k = 0; k < DK; ++k) acc = fmaf(p[k], pow2c(J[k] - Jm), acc);
-  const int2 out = renorm(acc, Jm);
-  return (acc > 0.f) ? out : make_int2(IDEAD, 0);
+  return renorm(acc * __int_as_float(ev.y), Jm + ev.x);
 }
 
-// One CTA of NT threads per sweep.  SPT > 0: the arcs of the SPT states of a thread (state = tid + NT i)
-// live in registers as shared-memory byte offsets; SPT == 0: any number of states, arcs re-read from
-// shared memory.  DK: arcs per state that exist anywhere in the batch (3 for CTC training graphs,
-// fst_utils.py:592-605).  NLJ > 0: at most NT * NLJ distinct labels, their class ids in registers.
-template <bool UNIT, int SPT, int DK, int NLJ>
+// SPT: states per compute thread (state s = tid + NCT u).  DK: arcs per state that exist anywhere in
+// the batch (3 for CTC training graphs, fst_utils.py:592-605).
+template <bool UNIT, int SPT, int DK>
 __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const int maxN) {
   extern __shared__ __align__(16) unsigned char sm[];
-  __shared__ int red_i[NT / 32];
-  __shared__ float red_f[NT / 32];
+  __shared__ int red_i[NCW];
+  __shared__ float red_f[NCW];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool both = a.write_grad != 0;
@@ -133,244 +146,171 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
   const int lo = g.lab_off[gi];
   const int nl = g.lab_off[gi + 1] - lo;
   const int len = min(a.lens[b], a.T);
-  const int nlp = (int)a.x_stride_t, arow = a.alpha_row;
-  const SweepPlan P = sweep_plan(maxN, nlp, UNIT);
-  uint4* pkv = reinterpret_cast<uint4*>(sm + P.pk);
-  float4* wv = reinterpret_cast<float4*>(sm + P.w);
-  int2* abuf0 = reinterpret_cast<int2*>(sm + P.a0);
-  int2* abuf1 = reinterpret_cast<int2*>(sm + P.a1);
-  float* fin = reinterpret_cast<float*>(sm + P.fin);
-  int* labs = reinterpret_cast<int*>(sm + P.lab);
-  float* land = reinterpret_cast<float*>(sm + P.land);
-  int2* xt = reinterpret_cast<int2*>(sm + P.xt);
+  const int nlp = (int)a.x_stride_t, arow2 = a.alpha_row / 2;
+  const SweepPlan P = sweep_plan(maxN, nlp);
+  const unsigned a0_a = sm_u32(sm + P.a0), a1_a = sm_u32(sm + P.a1);
+  const unsigned er_a = sm_u32(sm + P.er);
+  const bool spill = a.write_grad != 0;
+  int2* rows = reinterpret_cast<int2*>((DIR ? a.beta_ws : a.alpha_ws) + (long long)b * a.T * a.alpha_row);
+  const bool producer = tid >= NCT;
+  const int i0 = DIR;  // the backward sweep spends frame len-1 in its start vector
 
-  const int32_t* ptr = DIR ? g.out_ptr : g.in_ptr;
-  const int32_t* oth = DIR ? g.out_dst : g.in_src;
-  const int32_t* clab = DIR ? g.out_clab : g.in_clab;
-  const float* wgt = DIR ? g.out_w : g.in_w;
-  for (int s = tid; s < n; s += NT) {
-    unsigned pi[DEG];
-    float wi[DEG];
-    const int e0 = ptr[ro + s], e1 = ptr[ro + s + 1];
+  // ---- compute threads: arcs, label and start value of their states ----
+  unsigned asrc[SPT][DK], lab8[SPT];
+  int wE[SPT][UNIT ? 1 : DK];
+  float wm[SPT][UNIT ? 1 : DK];
+  if (!producer) {
+    const int32_t* ptr = DIR ? g.out_ptr : g.in_ptr;
+    const int32_t* oth = DIR ? g.out_dst : g.in_src;
+    const float* wgt = DIR ? g.out_w : g.in_w;
 #pragma unroll
-    for (int k = 0; k < DEG; ++k) {
-      const int e = e0 + k;
-      const bool v = e < e1;
-      pi[k] = v ? ((unsigned)oth[e] | ((unsigned)clab[e] << 16)) : NOARC;
-      wi[k] = (v && !UNIT) ? wgt[e] * kLog2e : 0.f;
-    }
-    pkv[s] = make_uint4(pi[0], pi[1], pi[2], pi[3]);
-    if (!UNIT) wv[s] = make_float4(wi[0], wi[1], wi[2], wi[3]);
-    const float f = g.final_w[so + s];
-    fin[s] = (f > kDeadWeight) ? f * kLog2e : neg_inf();
-    int2 v0 = make_int2(IDEAD, 0);
-    if (DIR) {
-      if (f > kDeadWeight) v0 = split_pow2(f * kLog2e);
-    } else if (s == 0) {
-      v0 = make_int2(0, __float_as_int(1.f));
-    }
-    abuf0[s] = v0;
-  }
-  if (tid == 0) abuf0[maxN] = abuf1[maxN] = make_int2(IDEAD, 0);  // the slot absent arcs point at
-  for (int j = tid; j < nlp; j += NT) labs[j] = (j < nl) ? g.lab_list[lo + j] : 0;
-  __syncthreads();
-
-  auto frame_t = [&](int i) { return DIR ? len - 1 - i : i; };
-  const bool direct = a.dense_x != nullptr;
-  const float* xb = a.x + (long long)b * a.x_stride_b;  // compact rows [t][nlp]: input (gathered by a kernel) or output (direct)
-  float* xout = (direct && DIR == 0 && a.write_grad) ? const_cast<float*>(xb) : nullptr;
-  const float* dense = direct ? a.dense_x + (long long)b * a.dense_stride_b : nullptr;
-  const unsigned land_a = sm_u32(land);
-  constexpr int NLR = NLJ > 0 ? NLJ : 1;
-  int labr[NLR];
+    for (int u = 0; u < SPT; ++u) {
+      const int s = tid + NCT * u;
+      const bool valid = s < n;
+      const int e0 = valid ? ptr[ro + s] : 0, e1 = valid ? ptr[ro + s + 1] : 0;
 #pragma unroll
-  for (int jj = 0; jj < NLR; ++jj) labr[jj] = (tid + NT * jj < nl) ? labs[tid + NT * jj] : -1;
-  auto issue_x = [&](int i) {
-    if (i < len) {
-      const int t = frame_t(i);
-      const int slot = i % XR;
-      if (direct) {
-        const float* src = dense + (long long)t * a.dense_stride_t;
-        const unsigned d0 = land_a + (slot * nlp + tid) * 4;
-        if (NLJ > 0) {
-#pragma unroll
-          for (int jj = 0; jj < NLR; ++jj)
-            if (labr[jj] >= 0) cp_async4(d0 + jj * NT * 4, src + labr[jj]);
-        } else {
-          for (int j = tid; j < nl; j += NT) cp_async4(land_a + (slot * nlp + j) * 4, src + labs[j]);
+      for (int k = 0; k < DK; ++k) {
+        const bool v = e0 + k < e1;
+        asrc[u][k] = v ? (unsigned)oth[e0 + k] * 8u : (unsigned)maxN * 8u;
+        if (!UNIT) {
+          const int2 ws = split_pow2(v ? wgt[e0 + k] * kLog2e : 0.f);
+          wE[u][k] = ws.x;
+          wm[u][k] = __int_as_float(ws.y);
         }
-      } else {
-        const float* src = xb + (long long)t * nlp;
-        for (int cc = tid; cc < nlp / 4; cc += NT) cp_async16(land + slot * nlp + 4 * cc, src + 4 * cc);
       }
+      int cl = 0;  // the label on the arcs INTO the state, for both directions; none: the value is never read
+      if (valid && g.in_ptr[ro + s] < g.in_ptr[ro + s + 1]) cl = g.in_clab[g.in_ptr[ro + s]];
+      lab8[u] = (unsigned)cl * 8u;
+    }
+    if (tid == 0) {
+      sts64(a0_a + maxN * 8, make_int2(IDEAD, 0));  // the slot absent arcs point at
+      sts64(a1_a + maxN * 8, make_int2(IDEAD, 0));
+    }
+  }
+
+  // ---- producer warp: rows of (exponent, mantissa) pairs written by gather_kernel -> ring, ER - 1 frames ahead ----
+  auto frame_t = [&](int i) { return DIR ? len - 1 - i : i; };
+  const int ptid = tid - NCT;
+  const int2* ebase = reinterpret_cast<const int2*>(a.x) + (long long)b * a.x_stride_b;  // [t][nlp]
+  const int chunks = nlp / 2;  // 16-byte chunks per row (nlp is a multiple of 4)
+  auto issue = [&](int r) {  // copies of row r (frame frame_t(r)); always commits a group
+    if (r < len) {
+      const int2* src = ebase + (long long)frame_t(r) * nlp;
+      unsigned char* dst = sm + P.er + (size_t)(r % ER) * nlp * 8;
+      for (int c = ptid; c < chunks; c += NPT) cp_async16(dst + 16 * c, src + 2 * c);
     }
     cp_async_commit();
   };
-  // landed row of frame i -> (exponent, mantissa) of e = 2^(x log2 e); the alpha sweep also writes the compact row
-  auto transform = [&](int i) {
-    if (i >= len) return;
-    const float* src = land + (i % XR) * nlp;
-    int2* dst = xt + (i & 1) * nlp;
-    float* xo = xout ? xout + (long long)frame_t(i) * nlp : nullptr;
-    if (NLJ > 0) {
-#pragma unroll
-      for (int jj = 0; jj < NLR; ++jj) {
-        const int j = tid + NT * jj;
-        if (j < nlp) {
-          const float x = (labr[jj] >= 0) ? src[j] : 0.f;
-          dst[j] = split_pow2(x * kLog2e);
-          if (xo) xo[j] = x;
-        }
-      }
-    } else {
-      for (int j = tid; j < nlp; j += NT) {
-        const float x = (j < nl) ? src[j] : 0.f;
-        dst[j] = split_pow2(x * kLog2e);
-        if (xo) xo[j] = x;
-      }
-    }
-  };
-  int2* rows = reinterpret_cast<int2*>((DIR ? a.beta_ws : a.alpha_ws) + (long long)b * a.T * arow);
-  const bool spill = a.write_grad != 0;
-
-  for (int i = 0; i < XR - 1; ++i) issue_x(i);
-  cp_async_wait<XR - 2>();
+  if (producer) {
+    for (int r = 0; r < ER - 1 + i0; ++r) issue(r);
+    cp_async_wait<0>();
+  }
   __syncthreads();
-  transform(0);
-  if (spill && len > 0) {
-    int2* r0 = rows + (long long)frame_t(0) * (arow / 2);
-    for (int s = tid; s < n; s += NT) r0[s] = abuf0[s];
-  }
 
-  unsigned ac = sm_u32(abuf0), an = sm_u32(abuf1);
-  const unsigned xt_a = sm_u32(xt);
-  constexpr int NSP = SPT > 0 ? SPT : 1;
-  unsigned asrc[NSP][DK], alab[NSP][DK];  // byte offsets of the source state / the label
-  float wreg[NSP][UNIT ? 1 : DK];
-  if (SPT > 0) {
+  // ---- start vector: alpha_0 = [1, 0, ...];  C_{len-1} = e_{len-1}[lab] * final ----
+  if (!producer) {
 #pragma unroll
-    for (int i = 0; i < NSP; ++i) {
-      const int s = tid + NT * i;
-      const uint4 pk = (s < n) ? pkv[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
-      const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
-      const float4 w = (!UNIT && s < n) ? wv[s] : make_float4(0.f, 0.f, 0.f, 0.f);
-      const float ww[DEG] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-      for (int k = 0; k < DK; ++k) {
-        asrc[i][k] = (pkk[k] == NOARC) ? (unsigned)maxN * 8u : (pkk[k] & 0xffffu) * 8u;
-        alab[i][k] = (pkk[k] == NOARC) ? 0u : (pkk[k] >> 16) * 8u;
-        if (!UNIT) wreg[i][k] = ww[k];
+    for (int u = 0; u < SPT; ++u) {
+      const int s = tid + NCT * u;
+      if (s < n) {
+        int2 v0 = make_int2(IDEAD, 0);
+        if (DIR && len > 0) {
+          const float f = g.final_w[so + s];
+          if (f > kDeadWeight) {
+            const int2 fs = split_pow2(f * kLog2e);
+            const int2 ev = lds64(er_a + lab8[u]);  // row 0 of the backward order = frame len-1 (ring slot 0)
+            v0 = renorm(__int_as_float(fs.y) * __int_as_float(ev.y), fs.x + ev.x);
+          }
+        } else if (!DIR && s == 0) {
+          v0 = make_int2(0, __float_as_int(1.f));
+        }
+        sts64(a0_a + s * 8, v0);
+        if (spill && len > 0) rows[(long long)frame_t(0) * arow2 + s] = v0;
       }
     }
   }
-  // ONE block barrier per frame.  It publishes (a) the vector and the split label row written during
-  // the previous frame, (b) the landed label row of the next frame (every thread has waited for its own
-  // copies), and it separates this frame's writes from the previous frame's reads of the same buffers.
-  for (int i = 0; i < len; ++i) {
-    issue_x(i + XR - 1);
-    cp_async_wait<XR - 2>();  // this thread's share of the row of frame i + 1 has landed
+  unsigned ac = a0_a, an = a1_a;
+  // row of the vector LEAVING step i: alpha_{i+1} -> row i+1; C_{len-1-i} -> row len-1-i
+  long long orow = (DIR ? (long long)(len - 1 - i0) : (long long)(i0 + 1)) * arow2;
+  const long long ostep = DIR ? -(long long)arow2 : (long long)arow2;
+
+  // ONE block barrier per frame.  It publishes the vector written during the previous step and the
+  // label row the producer's copies completed during the previous step, and it separates this step's
+  // writes (vector buffer, ring slot of row i - 1) from the previous step's reads of them.
+  for (int i = i0; i < len; ++i) {
     __syncthreads();
-    transform(i + 1);
-    const unsigned xa = xt_a + (i & 1) * nlp * 8;
-    int2* rn = (spill && i + 1 < len) ? rows + (long long)frame_t(i + 1) * (arow / 2) : nullptr;
-    if (SPT > 0) {
-      // three phases, so that every load is in flight before the first sum
-      int J[NSP][DK];
-      float pm[NSP][DK];
+    if (producer) {
+      issue(i + ER - 1);
+      cp_async_wait<ER - 2>();  // row i + 1 has landed
+    } else {
+      const unsigned ea = er_a + (i & (ER - 1)) * nlp * 8;  // ER is a power of two
+      const bool st = spill && (DIR || i + 1 < len);
+      int J[SPT][DK];
+      float pm[SPT][DK];
+      int2 ev[SPT];
 #pragma unroll
-      for (int u = 0; u < NSP; ++u) {
+      for (int u = 0; u < SPT; ++u) {  // every load in flight before the first sum
+        ev[u] = lds64(ea + lab8[u]);
 #pragma unroll
         for (int k = 0; k < DK; ++k) {
           const int2 av = lds64(ac + asrc[u][k]);
-          const int2 xv = lds64(xa + alab[u][k]);
-          J[u][k] = av.x + xv.x;
-          pm[u][k] = __int_as_float(av.y) * __int_as_float(xv.y);
-          if (!UNIT) {
-            const int2 ws = split_pow2(wreg[u][k]);
-            J[u][k] += ws.x;
-            pm[u][k] *= __int_as_float(ws.y);
-          }
+          J[u][k] = UNIT ? av.x : av.x + wE[u][k];
+          pm[u][k] = UNIT ? __int_as_float(av.y) : __int_as_float(av.y) * wm[u][k];
         }
       }
-      int2 res[NSP];
 #pragma unroll
-      for (int u = 0; u < NSP; ++u) res[u] = sum_state<DK>(J[u], pm[u]);
-#pragma unroll
-      for (int u = 0; u < NSP; ++u) {
-        const int s = tid + NT * u;
+      for (int u = 0; u < SPT; ++u) {
+        const int s = tid + NCT * u;
+        const int2 res = step_state<DK>(J[u], pm[u], ev[u]);
         if (s < n) {
-          sts64(an + s * 8, res[u]);
-          if (rn) rn[s] = res[u];
-        }
-      }
-    } else {
-      constexpr int CH = 2;
-      for (int s0 = tid; s0 < n; s0 += NT * CH) {
-        int J[CH][DEG];
-        float pm[CH][DEG];
-#pragma unroll
-        for (int u = 0; u < CH; ++u) {
-          const int s = s0 + NT * u;
-          const uint4 pk = (s < n) ? pkv[s] : make_uint4(NOARC, NOARC, NOARC, NOARC);
-          const unsigned pkk[DEG] = {pk.x, pk.y, pk.z, pk.w};
-          float ww[DEG] = {0.f, 0.f, 0.f, 0.f};
-          if (!UNIT && s < n) {
-            const float4 w = wv[s];
-            ww[0] = w.x, ww[1] = w.y, ww[2] = w.z, ww[3] = w.w;
-          }
-#pragma unroll
-          for (int k = 0; k < DEG; ++k) {
-            const bool v = pkk[k] != NOARC;
-            const int2 av = lds64(ac + (v ? (pkk[k] & 0xffffu) : (unsigned)maxN) * 8u);
-            const int2 xv = lds64(xa + (v ? (pkk[k] >> 16) : 0u) * 8u);
-            J[u][k] = av.x + xv.x;
-            pm[u][k] = __int_as_float(av.y) * __int_as_float(xv.y);
-            if (!UNIT) {
-              const int2 ws = split_pow2(ww[k]);
-              J[u][k] += ws.x;
-              pm[u][k] *= __int_as_float(ws.y);
-            }
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < CH; ++u) {
-          const int s = s0 + NT * u;
-          const int2 res = sum_state<DEG>(J[u], pm[u]);
-          if (s < n) {
-            sts64(an + s * 8, res);
-            if (rn) rn[s] = res;
-          }
+          sts64(an + s * 8, res);
+          if (st) rows[orow + s] = res;
         }
       }
     }
+    orow += ostep;
     const unsigned tmp = ac;
     ac = an;
     an = tmp;
   }
-  cp_async_wait<0>();
+  if (producer) cp_async_wait<0>();
   if (DIR) return;
   __syncthreads();
   // terminal: cost = log sum_n alpha_len[n] final[n]
-  const int2* a_end = (len & 1) ? abuf1 : abuf0;
   int Im = IDEAD;
-  for (int s = tid; s < n; s += NT)
-    if (fin[s] > neg_inf() && a_end[s].x > IDEAD / 2) Im = max(Im, a_end[s].x);
+  int2 ae[SPT];
+  float fw[SPT];
+#pragma unroll
+  for (int u = 0; u < SPT; ++u) {
+    const int s = tid + NCT * u;
+    ae[u] = make_int2(IDEAD, 0);
+    fw[u] = 0.f;
+    if (!producer && s < n) {
+      const float f = g.final_w[so + s];
+      if (f > kDeadWeight) {
+        ae[u] = lds64(ac + s * 8);
+        fw[u] = ex2(f * kLog2e);
+        if (ae[u].x > IDEAD / 2) Im = max(Im, ae[u].x);
+      }
+    }
+  }
   Im = __reduce_max_sync(0xffffffffu, Im);
-  if (lane == 0) red_i[warp] = Im;
+  if (lane == 0 && !producer) red_i[warp] = Im;
   __syncthreads();
 #pragma unroll
-  for (int w = 0; w < NT / 32; ++w) Im = max(Im, red_i[w]);
+  for (int w = 0; w < NCW; ++w) Im = max(Im, red_i[w]);
   float ts = 0.f;
-  if (Im > IDEAD / 2)
-    for (int s = tid; s < n; s += NT)
-      if (fin[s] > neg_inf()) ts += __int_as_float(a_end[s].y) * pow2c(a_end[s].x - Im) * ex2(fin[s]);
+  if (Im > IDEAD / 2) {
+#pragma unroll
+    for (int u = 0; u < SPT; ++u) ts += __int_as_float(ae[u].y) * pow2c(ae[u].x - Im) * fw[u];
+  }
   ts = warp_sum(ts);
-  if (lane == 0) red_f[warp] = ts;
+  if (lane == 0 && !producer) red_f[warp] = ts;
   __syncthreads();
   if (tid == 0) {
     float tot = 0.f;
 #pragma unroll
-    for (int w = 0; w < NT / 32; ++w) tot += red_f[w];
+    for (int w = 0; w < NCW; ++w) tot += red_f[w];
     const bool feasible = Im > IDEAD / 2 && tot > 0.f;
     a.cost[b] = feasible ? ((double)Im + log2((double)tot)) * kLn2 : -1e20;
   }
@@ -380,7 +320,7 @@ constexpr int CB_W = 8;             // warps per combine CTA (fewer when the row
 constexpr int CB_FPW = 4;           // frames per warp: the graph tables are staged once per warps * CB_FPW frames
 constexpr int CB_TH = CB_W * 32;
 
-// alpha[src] * beta[dst] * k * 2^(exponents): kE / km hold e_t[j] (and w) with the cost's exponent taken off
+// alpha_t[src] * C_t[dst] (* w) * 2^(exponents - cost exponent)
 __device__ __forceinline__ float post_term(int2 av, int2 bv, int kE, float km) {
   return (__int_as_float(av.y) * __int_as_float(bv.y)) * (km * pow2c(min(av.x + bv.x + kE, 64)));
 }
@@ -416,9 +356,9 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
   int* lab_ptr = reinterpret_cast<int*>(sm + take((maxL + 1) * 4));
   unsigned* lab_pk = reinterpret_cast<unsigned*>(sm + take(maxA * 4));
   float* lab_w = reinterpret_cast<float*>(sm + (UNIT ? 0 : take(maxA * 4)));
-  // per warp: two staging buffers {alpha row, beta row, x row} (the next frame's rows are copied in with
-  // cp.async while this frame's posteriors are summed) and one posterior row
-  const int stg = 2 * arow + nlp;
+  // per warp: two staging buffers {alpha row, C row} (the next frame's rows are copied in with cp.async
+  // while this frame's posteriors are summed) and one posterior row
+  const int stg = 2 * arow;
   float* rows_s = reinterpret_cast<float*>(sm + take(nwarps * (2 * stg + nlp) * 4));
   const int arc0 = g.in_ptr[ro];
   const int narcs = g.in_ptr[ro + n] - arc0;
@@ -442,12 +382,10 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
       float* d = wbase + (q & 1) * stg;
       const float* as = a.alpha_ws + ((long long)b * a.T + t) * arow;
       const float* bs = a.beta_ws + ((long long)b * a.T + t) * arow;
-      const float* xs = a.x + (long long)b * a.x_stride_b + (long long)t * nlp;
       for (int i = lane; i < (2 * n + 3) / 4; i += 32) {
         cp_async16(d + 4 * i, as + 4 * i);
         cp_async16(d + arow + 4 * i, bs + 4 * i);
       }
-      for (int i = lane; i < nlp / 4; i += 32) cp_async16(d + 2 * arow + 4 * i, xs + 4 * i);
     }
     cp_async_commit();
   };
@@ -467,7 +405,6 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
     __syncwarp();
     const int2* at = reinterpret_cast<const int2*>(wbase + (q & 1) * stg);
     const int2* bt = reinterpret_cast<const int2*>(wbase + (q & 1) * stg + arow);
-    const float* xt = wbase + (q & 1) * stg + 2 * arow;
     // scatter mode: the gradient entries this frame will touch are requested now, so that their DRAM
     // latency runs behind the posterior sums (first 256 labels; the labels of an utterance are distinct)
     float* out = a.scatter_grad ? a.scatter_grad + ((long long)t * a.B + b) * V : nullptr;
@@ -493,9 +430,8 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
       const bool heavy = (e1 - e0) > HEAVY;
       float acc = 0.f;
       if (j < nl && !heavy) {
-        const int2 xs = split_pow2(xt[j] * kLog2e);
-        const int kE = xs.x - cE;
-        const float km = __int_as_float(xs.y);
+        const int kE = -cE;
+        const float km = 1.f;
         for (int e = e0; e < e1; ++e) {
           const unsigned pk = lab_pk[e];
           const int2 ws = UNIT ? make_int2(0, __float_as_int(1.f)) : split_pow2(lab_w[e]);
@@ -508,9 +444,8 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
         hm &= hm - 1;
         const int jh = base + src_lane;
         const int h0 = __shfl_sync(0xffffffffu, e0, src_lane), h1 = __shfl_sync(0xffffffffu, e1, src_lane);
-        const int2 xs = split_pow2(xt[jh] * kLog2e);
-        const int kE = xs.x - cE;
-        const float km = __int_as_float(xs.y);
+        const int kE = -cE;
+        const float km = 1.f;
         float part = 0.f;
         for (int e = h0 + lane; e < h1; e += 32) {
           const unsigned pk = lab_pk[e];
@@ -556,7 +491,7 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
 constexpr int kSmemBudget = 200 * 1024;
 int combine_smem_bytes(const PathArgs& a, bool unit, int warps) {
   return ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
-         warps * (2 * (2 * a.alpha_row + (int)a.x_stride_t) + (int)a.x_stride_t) * 4 + 64;
+         warps * (2 * (2 * a.alpha_row) + (int)a.x_stride_t) * 4 + 64;
 }
 // most warps (<= CB_W) whose staging buffers fit; 0: not even one
 int combine_warps(const PathArgs& a, bool unit) {
@@ -564,31 +499,29 @@ int combine_warps(const PathArgs& a, bool unit) {
   while (w > 0 && combine_smem_bytes(a, unit, w) > kSmemBudget) --w;
   return w;
 }
-int sweep_smem_bytes(const PathArgs& a, bool unit) { return sweep_plan(a.g.max_states, (int)a.x_stride_t, unit).bytes; }
+int sweep_smem_bytes(const PathArgs& a) { return sweep_plan(a.g.max_states, (int)a.x_stride_t).bytes; }
+
 }  // namespace
 
-template <bool UNIT, int SPT, int DK, int NLJ>
-static cudaError_t launch_sweep_nl(const PathArgs& a, int nsweeps, cudaStream_t st) {
-  const int bytes = sweep_smem_bytes(a, UNIT);
-  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT, DK, NLJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e != cudaSuccess) return e;
-  num_sweep_kernel<UNIT, SPT, DK, NLJ><<<nsweeps, NT, bytes, st>>>(a, a.g.max_states);
-  return cudaGetLastError();
-}
 template <bool UNIT, int SPT, int DK>
 static cudaError_t launch_sweep_dk(const PathArgs& a, int nsweeps, cudaStream_t st) {
-  if (SPT > 0 && a.x_stride_t <= NT * 2) return launch_sweep_nl<UNIT, SPT, DK, 2>(a, nsweeps, st);
-  return launch_sweep_nl<UNIT, SPT, DK, 0>(a, nsweeps, st);
+  const int bytes = sweep_smem_bytes(a);
+  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT, DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  num_sweep_kernel<UNIT, SPT, DK><<<nsweeps, NT, bytes, st>>>(a, a.g.max_states);
+  return cudaGetLastError();
+}
+template <bool UNIT, int SPT>
+static cudaError_t launch_sweep_spt(const PathArgs& a, int nsweeps, cudaStream_t st) {
+  if (a.g.max_in_degree <= 3 && a.g.max_out_degree <= 3) return launch_sweep_dk<UNIT, SPT, 3>(a, nsweeps, st);
+  return launch_sweep_dk<UNIT, SPT, DEG>(a, nsweeps, st);
 }
 template <bool UNIT>
 static cudaError_t launch_sweep(const PathArgs& a, int nsweeps, cudaStream_t st) {
-  const int spt = (a.g.max_states + NT - 1) / NT;
-  const bool d3 = a.g.max_in_degree <= 3 && a.g.max_out_degree <= 3;
-  if (d3 && spt <= 1) return launch_sweep_dk<UNIT, 1, 3>(a, nsweeps, st);
-  if (d3 && spt <= 2) return launch_sweep_dk<UNIT, 2, 3>(a, nsweeps, st);
-  if (d3 && spt <= 4) return launch_sweep_dk<UNIT, 4, 3>(a, nsweeps, st);
-  if (spt <= 2) return launch_sweep_dk<UNIT, 2, DEG>(a, nsweeps, st);
-  return launch_sweep_dk<UNIT, 0, DEG>(a, nsweeps, st);
+  const int spt = (a.g.max_states + NCT - 1) / NCT;
+  if (spt <= 1) return launch_sweep_spt<UNIT, 1>(a, nsweeps, st);
+  if (spt <= 2) return launch_sweep_spt<UNIT, 2>(a, nsweeps, st);
+  return launch_sweep_spt<UNIT, MAXSPT>(a, nsweeps, st);
 }
 
 bool num_split_supported(const PathArgs& a) {
@@ -596,8 +529,9 @@ bool num_split_supported(const PathArgs& a) {
   if (a.g.max_states > 65535 || a.g.max_labels > 65535 || a.g.max_arcs < 1) return false;
   if (a.g.max_in_degree > DEG || a.g.max_out_degree > DEG) return false;
   if (a.alpha_row < 2 * a.g.max_states) return false;
+  if (!a.g.in_label_uniform || a.g.max_states > NCT * MAXSPT) return false;  // the generic CSR kernel takes these
   const bool unit = a.g.unit_weights != 0;
-  return sweep_smem_bytes(a, unit) <= kSmemBudget && combine_warps(a, unit) >= 1;
+  return sweep_smem_bytes(a) <= kSmemBudget && combine_warps(a, unit) >= 1;
 }
 
 cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st) {

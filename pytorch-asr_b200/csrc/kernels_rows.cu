@@ -21,6 +21,9 @@ constexpr int NWARP = NT / 32;
 // xg[b][t][j] = normalise(logits[t][b][:])[lab_list_b[j]] (natural log); one warp per (t, b) row.
 // normalize: 0/1 -> raw logits (a softmax normaliser is per-frame and is added
 // to the loss by the row pass instead); 2 -> minus the LSE of the label's context block.
+// PAIRS: the split numerator sweeps (kernels_num.cu) take every value as 2^(x log2 e) = f * 2^E, an int32
+// exponent E = rint(x log2 e) and an fp32 mantissa f = 2^(x log2 e - E): xg holds int2 {E, bits of f}.
+template <bool PAIRS>
 __global__ void __launch_bounds__(NT) gather_kernel(const float* __restrict__ logits, int T, int B, int V,
                                                     const int32_t* __restrict__ lens, GraphDev g,
                                                     float* __restrict__ xg, int nlp, int normalize, int S) {
@@ -32,8 +35,12 @@ __global__ void __launch_bounds__(NT) gather_kernel(const float* __restrict__ lo
   const int gi = g.num_graphs == 1 ? 0 : b;
   const int lo = g.lab_off[gi], nl = g.lab_off[gi + 1] - lo;
   const float* x = logits + row * V;
-  float* dst = xg + ((long long)b * T + t) * nlp;
-  for (int j = lane; j < nl; j += 32) {
+  float* dst = xg + ((long long)b * T + t) * nlp * (PAIRS ? 2 : 1);
+  for (int j = lane; j < (PAIRS ? nlp : nl); j += 32) {
+    if (PAIRS && j >= nl) {  // padding labels: 2^0
+      reinterpret_cast<int2*>(dst)[j] = make_int2(0, __float_as_int(1.f));
+      continue;
+    }
     const int lab = g.lab_list[lo + j];
     float v = x[lab];
     if (normalize == 2) {
@@ -44,7 +51,13 @@ __global__ void __launch_bounds__(NT) gather_kernel(const float* __restrict__ lo
       for (int k = 0; k < S; ++k) s += __expf(blk[k] - m);
       v -= m + __logf(s);
     }
-    dst[j] = v;
+    if (PAIRS) {
+      const float xs = fminf(fmaxf(v * kLog2e, -65536.f), 65536.f);  // T * 2^16 stays inside the sweeps' exponent range
+      const float r = xs + 12582912.f;                               // 1.5 * 2^23: rint(xs) in the low mantissa bits
+      reinterpret_cast<int2*>(dst)[j] = make_int2(__float_as_int(r) - 0x4B400000, __float_as_int(ex2(xs - (r - 12582912.f))));
+    } else {
+      dst[j] = v;
+    }
   }
 }
 
@@ -235,11 +248,12 @@ __global__ void cost_to_float_kernel(int B, const double* __restrict__ cost, flo
 }  // namespace
 
 cudaError_t launch_gather(const float* logits, int T, int B, int V, const int32_t* lens, const GraphDev& num,
-                          float* xg, int nlp, int normalize, int S, cudaStream_t st) {
+                          float* xg, int nlp, int normalize, int S, bool pairs, cudaStream_t st) {
   const long long rows = (long long)T * B;
   const unsigned grid = (unsigned)((rows + NWARP - 1) / NWARP);
   ProfScope prof("gather", st);
-  gather_kernel<<<grid, NT, 0, st>>>(logits, T, B, V, lens, num, xg, nlp, normalize, S);
+  if (pairs) gather_kernel<true><<<grid, NT, 0, st>>>(logits, T, B, V, lens, num, xg, nlp, normalize, S);
+  else gather_kernel<false><<<grid, NT, 0, st>>>(logits, T, B, V, lens, num, xg, nlp, normalize, S);
   ++g_launches;
   return cudaGetLastError();
 }
