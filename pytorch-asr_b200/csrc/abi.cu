@@ -33,7 +33,7 @@ struct Plan {
   int arow_den = 0;
   size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, beta_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
   size_t pspill = 0, ckpt = 0;
-  size_t spill2 = 0, ckpt2 = 0, fin = 0;
+  size_t spill2 = 0, ckpt2 = 0, fin = 0, labmap = 0;
   BisweepPlan sw{};  // sw.ok: the denominator runs on the factorised bi-char kernels (kernels_bisweep.cu)
   size_t total = 0;
 };
@@ -61,8 +61,9 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
     p.arow_num = pad4(2 * num->max_states + 2);  // split numerator: (integer, fraction) per state
     p.xg = take(TB * p.nlp * 8);  // float columns (generic kernel) or (exponent, mantissa) pairs (split sweeps)
     p.gg = take(TB * p.nlp * 4);
-    p.alpha_num = take(TB * p.arow_num * 4);
-    p.beta_num = take(TB * p.arow_num * 4);
+    const size_t T1B = (size_t)(std::max(T, 1) + 1) * (size_t)std::max(B, 1);  // the split sweeps spill T + 1 rows
+    p.alpha_num = take(T1B * p.arow_num * 4);
+    p.beta_num = take(T1B * p.arow_num * 4);
     p.cost_num = take((size_t)B * 8);
   }
   p.rowlse = take(TB * 4);
@@ -75,6 +76,7 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
       p.spill2 = take(p.sw.spill_bytes);
       p.ckpt2 = take(p.sw.ckpt_bytes);
       p.fin = take((size_t)B * sizeof(BiFin));
+      if (num) p.labmap = take((size_t)B * V * 2);
     } else {
       p.arow_den = pad4(den->max_states + 2);
       p.alpha_den = take(TB * p.arow_den * 4);
@@ -254,8 +256,8 @@ int ctcg_profile_collect(char* names, size_t names_cap, float* ms, int max_recor
 // ---------------------------------------------------------------------------
 namespace {
 
-int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, int V, const int32_t* lens,
-               const ctcg_graph* den, double* cost, float* grad, const float* grad_scale, cudaStream_t st) {
+BisweepArgs bichar_args(const Plan& p, unsigned char* ws, const float* x, int T, int B, int V, const int32_t* lens,
+                        const ctcg_graph* den, double* cost, float* grad, const float* grad_scale) {
   BisweepArgs s{};
   s.x = x;
   s.total = (long long)T * B * V;
@@ -281,7 +283,14 @@ int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, i
   s.rowf = p.sw.rowf;
   s.estride = p.sw.estride;
   s.epad = p.sw.epad;
+  return s;
+}
+
+int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, int V, const int32_t* lens,
+               const ctcg_graph* den, double* cost, float* grad, const float* grad_scale, cudaStream_t st) {
+  const BisweepArgs s = bichar_args(p, ws, x, T, B, V, lens, den, cost, grad, grad_scale);
   CTCG_CUDA(launch_bisweep(s, p.sw, st));
+  CTCG_CUDA(launch_bicombine(s, p.sw, st));
   return CTCG_OK;
 }
 
@@ -292,7 +301,7 @@ int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, i
 // device; CTCG_SERIAL=1 keeps everything on the caller's stream.
 struct SideStream {
   cudaStream_t stream = nullptr;
-  cudaEvent_t fork = nullptr, join = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr, numdone = nullptr;
   bool ok = false;
 };
 
@@ -310,7 +319,8 @@ SideStream* side_stream() {
   if (!s.ok) {
     if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.numdone, cudaEventDisableTiming) != cudaSuccess) {
       (void)cudaGetLastError();
       return nullptr;
     }
@@ -366,17 +376,45 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   const bool softmax = (normalize == CTCG_NORM_SOFTMAX) && !den;
   const bool fused_den = den && p.sw.ok && aligned16(logits) && aligned16(grad);
   if (den && p.sw.ok && !fused_den) return CTCG_EUNSUPPORTED;  // misaligned tensors: the workspace was planned for the fused kernel
+  // 1. compact the label columns each utterance touches (the split sweeps take them as (exponent, mantissa)
+  // pairs).  Before the fork: next to the denominator sweeps, which hold most of every SM's registers, these
+  // wide streaming kernels get one CTA per SM and take three times as long.
+  const bool split = [&] {
+    PathArgs a{};
+    a.g = num->dev;
+    a.x_stride_t = pad4(std::max(num->max_labels, 1));
+    a.alpha_row = pad4(2 * num->max_states + 2);
+    a.beta_ws = reinterpret_cast<float*>(ws);
+    return num_split_supported(a);
+  }();
+  CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp, normalize == CTCG_NORM_CONTEXT ? 2 : 0,
+                          num_symbols, split, st));
+  if (den && p.sw.ok && aligned16(logits) && aligned16(grad) && grad)
+    CTCG_CUDA(launch_labmap(B, V, num->dev, reinterpret_cast<unsigned short*>(ws + p.labmap), st));
   SideStream* side = fused_den ? side_stream() : nullptr;
+  // With the factorised denominator the numerator's posteriors leave in the denominator's combine kernel
+  // (one store of gamma_den - gamma_num): sweeps || numerator, then the combine.
+  const bool fold = fused_den && grad != nullptr;
+  BisweepArgs den_args{};
+  cudaStream_t ds = st;
   if (fused_den) {
-    // 1'. factorised bi-char denominator (kernels_bisweep.cu), writes +gamma_den rows; concurrent with 1-2
-    cudaStream_t ds = st;
+    // 1'. factorised bi-char denominator sweeps (kernels_bisweep.cu); concurrent with 1-2
     if (side) {
       CTCG_CUDA(cudaEventRecord(side->fork, st));
       CTCG_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
       ds = side->stream;
     }
-    st_ = run_bichar(p, ws, logits, T, B, V, lens, den, cost_den, grad, grad_scale, ds);
-    if (side) CTCG_CUDA(cudaEventRecord(side->join, side->stream));
+    den_args = bichar_args(p, ws, logits, T, B, V, lens, den, cost_den, grad, grad_scale);
+    if (fold) {
+      den_args.num_gg = gg;
+      den_args.num_nlp = p.nlp;
+      den_args.labmap = reinterpret_cast<const unsigned short*>(ws + p.labmap);
+    }
+    if (launch_bisweep(den_args, p.sw, ds) != cudaSuccess) {
+      (void)cudaGetLastError();
+      st_ = CTCG_ECUDA;
+    }
+    if (side && st_ != CTCG_OK) CTCG_CUDA(cudaEventRecord(side->join, side->stream));
   }
   // joins the side stream back (also on failure, so that a capture is never left forked)
   auto join = [&]() -> int {
@@ -388,8 +426,6 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     (void)join();
     return st_;
   }
-  PathArgs num_args{};
-  bool split_num = false, scatter_num = false;
   st_ = [&]() -> int {
     // 2. numerator forward-backward on the compact columns
     PathArgs a{};
@@ -412,43 +448,41 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     a.g_scale = nullptr;
     a.write_grad = grad != nullptr;
     a.beta_ws = reinterpret_cast<float*>(ws + p.beta_num);
-    const bool split = num_split_supported(a);
-    // 1. compact the label columns each utterance touches (the split sweeps take them as pairs)
-    CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp, normalize == CTCG_NORM_CONTEXT ? 2 : 0,
-                            num_symbols, split, st));
     if (split) {
       CTCG_CUDA(launch_num_sweeps(a, st));
-      num_args = a;
-      split_num = true;
-      // with the factorised denominator the posterior combine runs after the join and subtracts
-      // from the dense rows in place (no compact round trip, no scatter_sub launch)
-      static const bool fuse_scatter = [] {
-        const char* e = std::getenv("CTCG_NUM_SCATTER");
-        return !(e && e[0] == '0');
-      }();
-      scatter_num = fused_den && grad && fuse_scatter;
-      if (!scatter_num) CTCG_CUDA(launch_num_combine(a, st));
+      CTCG_CUDA(launch_num_combine(a, st));
     } else {
       CTCG_CUDA(launch_path_fwd_bwd(a, true, st));  // graphs the split kernels do not take: generic CSR kernel
     }
     return CTCG_OK;
   }();
-  {
+  if (fused_den) {
+    // 3a'. combine: gamma_den - gamma_num, after the numerator's compact rows
+    int cs = CTCG_OK;
+    if (st_ == CTCG_OK && side && fold) {
+      if (cudaEventRecord(side->numdone, st) != cudaSuccess || cudaStreamWaitEvent(ds, side->numdone, 0) != cudaSuccess) {
+        (void)cudaGetLastError();
+        cs = CTCG_ECUDA;
+      }
+    }
+    if (st_ == CTCG_OK && cs == CTCG_OK && launch_bicombine(den_args, p.sw, ds) != cudaSuccess) {
+      (void)cudaGetLastError();
+      cs = CTCG_ECUDA;
+    }
+    if (side && cudaEventRecord(side->join, side->stream) != cudaSuccess) {
+      (void)cudaGetLastError();
+      cs = CTCG_ECUDA;
+    }
     const int js = join();
     if (st_ != CTCG_OK) return st_;
+    if (cs != CTCG_OK) return cs;
     if (js != CTCG_OK) return js;
+  } else if (st_ != CTCG_OK) {
+    return st_;
   }
 
   if (fused_den) {
-    // 3a'. gamma_den - gamma_num
-    if (grad && split_num && scatter_num) {
-      num_args.scatter_grad = grad;
-      num_args.scatter_V = V;
-      num_args.g_scale = grad_scale;
-      CTCG_CUDA(launch_num_combine(num_args, st));
-    } else if (grad) {
-      CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
-    }
+    // (nothing left: the combine wrote g_scale * (gamma_den - gamma_num))
   } else if (den) {
     // 3a. denominator path sum over the shared decoding graph, writes +gamma_den rows
     PathArgs d{};

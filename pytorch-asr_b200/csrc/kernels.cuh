@@ -20,8 +20,6 @@ struct PathArgs {
   float* alpha_ws;        // [B][T][row]: generic kernel: normalised alpha_t in log2 units + frame offset (2 floats);
                           // split numerator: (int32 integer part, fp32 fraction) per state
   int32_t alpha_row;      // floats per row: pad4(2 * max_states + 2)
-  float* scatter_grad;    // nullable: dense (T, B, scatter_V) gradient the split numerator subtracts its posteriors from
-  int32_t scatter_V;
   float* beta_ws;         // nullable; same shape as alpha_ws: beta rows of the split numerator (kernels_num.cu)
   double* cost;           // [B] natural-log path sum
   float* gout;            // posterior rows; element (t, b, l) at gout[t*g_stride_t + b*g_stride_b + l]
@@ -102,13 +100,22 @@ struct BisweepArgs {
   const float* g_scale;    // nullable
   int32_t nmain, rowf, estride, epad;
   int32_t dbg;             // timing experiments only (CTCG_SWEEP_DEBUG bit mask); 0 in production
+  // numerator posteriors folded into the combine (nullable): grad = g_scale * (gamma_den - gamma_num) in ONE store.
+  const float* num_gg;            // compact rows gg[b][t][j], j indexes the utterance's distinct labels
+  int32_t num_nlp;                // their pitch
+  const unsigned short* labmap;   // [B][V]: class -> j, 0xffff = not a label of this utterance (launch_labmap)
 };
 struct BisweepPlan {
   int32_t ok, K, nck, nmain, threads, rowf, prowf, estride, epad;
   size_t smem_bytes, spill_bytes, ckpt_bytes;
 };
 BisweepPlan bisweep_plan(int T, int B, int V, int S);
+// The two sweeps (the backward one only when a.grad is set), then the combine as a launch of its own: with
+// a.num_gg set it must be ordered after the numerator's compact rows are complete.
 cudaError_t launch_bisweep(const BisweepArgs& a, const BisweepPlan& p, cudaStream_t st);
+cudaError_t launch_bicombine(const BisweepArgs& a, const BisweepPlan& p, cudaStream_t st);
+// labmap[b][v] = index of class v in utterance b's label list, 0xffff if absent (at most 65535 labels)
+cudaError_t launch_labmap(int B, int V, const GraphDev& num, unsigned short* labmap, cudaStream_t st);
 
 // Incremented by every launch_* above.
 extern unsigned long long g_launches;

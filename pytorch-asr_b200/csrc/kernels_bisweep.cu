@@ -726,12 +726,23 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
       }
     }
   };
+  // numerator posteriors (compact rows, L2 resident) leave in the same store: ~6 % of the classes have one
+  const unsigned short* lmap = (A.labmap && A.num_gg) ? A.labmap + (long long)b * V : nullptr;
+  const float* ngg = lmap ? A.num_gg + ((long long)b * T + t0) * A.num_nlp : nullptr;
+  const int nnlp = A.num_nlp;
+  auto sub_num = [&](unsigned j, float (&e)[KMAX], const bool full) {
+    if (j == 0xffffu) return;
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f)
+      if (full || f < n) e[f] = fmaf(-gsc, __ldg(ngg + f * nnlp + j), e[f]);
+  };
   auto scalar_class = [&](int v) {
     float e[KMAX];
 #pragma unroll
     for (int f = 0; f < KMAX; ++f)
       if (f < n) e[f] = __ldg(x0 + v + f * rstride);
     walk(v, e, false);
+    sub_num(lmap ? lmap[v] : 0xffffu, e, false);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f)
       if (f < n) g0[v + f * rstride] = e[f];
@@ -756,19 +767,26 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
       const float4* p = reinterpret_cast<const float4*>(x0 + v + f * rstride);
       asm volatile("ld.global.cs.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(xv[f].x), "=f"(xv[f].y), "=f"(xv[f].z), "=f"(xv[f].w) : "l"(p));
     }
+    // the four map entries of the chunk in one 8-byte load ((b*V + v) is a multiple of 4 on this path)
+    uint2 jm = make_uint2(0xffffffffu, 0xffffffffu);
+    if (lmap) jm = __ldg(reinterpret_cast<const uint2*>(lmap + v));
     float e[KMAX];
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) e[f] = xv[f].x;
     walk(v, e, true);
+    sub_num(jm.x & 0xffffu, e, true);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) { xv[f].x = e[f]; e[f] = xv[f].y; }
     walk(v + 1, e, true);
+    sub_num(jm.x >> 16, e, true);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) { xv[f].y = e[f]; e[f] = xv[f].z; }
     walk(v + 2, e, true);
+    sub_num(jm.y & 0xffffu, e, true);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) { xv[f].z = e[f]; e[f] = xv[f].w; }
     walk(v + 3, e, true);
+    sub_num(jm.y >> 16, e, true);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) {
       xv[f].w = e[f];
@@ -783,7 +801,27 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
   }
 }
 
+__global__ void __launch_bounds__(256) labmap_kernel(int V, GraphDev g, unsigned short* __restrict__ labmap) {
+  const int b = blockIdx.x;
+  const int gi = g.num_graphs == 1 ? 0 : b;
+  const int lo = g.lab_off[gi], nl = g.lab_off[gi + 1] - lo;
+  unsigned short* row = labmap + (long long)b * V;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) row[v] = 0xffffu;
+  __syncthreads();
+  for (int j = threadIdx.x; j < nl; j += blockDim.x) {
+    const int lab = g.lab_list[lo + j];
+    if (lab < V) row[lab] = (unsigned short)j;
+  }
+}
+
 }  // namespace
+
+cudaError_t launch_labmap(int B, int V, const GraphDev& num, unsigned short* labmap, cudaStream_t st) {
+  ProfScope prof("labmap", st);
+  labmap_kernel<<<B, 256, 0, st>>>(V, num, labmap);
+  ++g_launches;
+  return cudaGetLastError();
+}
 
 // ---- host side ------------------------------------------------------------------
 BisweepPlan bisweep_plan(int T, int B, int V, int S) {
@@ -837,17 +875,19 @@ cudaError_t launch_bisweep(const BisweepArgs& a_in, const BisweepPlan& p, cudaSt
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }
-  if (!a.grad) return e;
-  {
-    ProfScope prof("bicombine", st);
-    const dim3 cgrid((a.T + a.K - 1) / a.K, a.B);
-    if (a.S == 49) bicombine_kernel<49, 8><<<cgrid, CTHREADS, 0, st>>>(a);
-    else if (a.S == 36) bicombine_kernel<36, 8><<<cgrid, CTHREADS, 0, st>>>(a);
-    else bicombine_kernel<0, 8><<<cgrid, CTHREADS, 0, st>>>(a);
-    ++g_launches;
-    e = cudaGetLastError();
-  }
   return e;
+}
+
+cudaError_t launch_bicombine(const BisweepArgs& a, const BisweepPlan& p, cudaStream_t st) {
+  (void)p;
+  if (!a.grad) return cudaSuccess;
+  ProfScope prof("bicombine", st);
+  const dim3 cgrid((a.T + a.K - 1) / a.K, a.B);
+  if (a.S == 49) bicombine_kernel<49, 8><<<cgrid, CTHREADS, 0, st>>>(a);
+  else if (a.S == 36) bicombine_kernel<36, 8><<<cgrid, CTHREADS, 0, st>>>(a);
+  else bicombine_kernel<0, 8><<<cgrid, CTHREADS, 0, st>>>(a);
+  ++g_launches;
+  return cudaGetLastError();
 }
 
 }  // namespace ctcg

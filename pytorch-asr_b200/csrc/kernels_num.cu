@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
   const unsigned a0_a = sm_u32(sm + P.a0), a1_a = sm_u32(sm + P.a1);
   const unsigned er_a = sm_u32(sm + P.er);
   const bool spill = a.write_grad != 0;
-  int2* rows = reinterpret_cast<int2*>((DIR ? a.beta_ws : a.alpha_ws) + (long long)b * a.T * a.alpha_row);
+  int2* rows = reinterpret_cast<int2*>((DIR ? a.beta_ws : a.alpha_ws) + (long long)b * (a.T + 1) * a.alpha_row);  // T + 1 rows: alpha_len has a slot too
   const bool producer = tid >= NCT;
   const int i0 = DIR;  // the backward sweep spends frame len-1 in its start vector
 
@@ -193,11 +193,20 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
   const int ptid = tid - NCT;
   const int2* ebase = reinterpret_cast<const int2*>(a.x) + (long long)b * a.x_stride_b;  // [t][nlp]
   const int chunks = nlp / 2;  // 16-byte chunks per row (nlp is a multiple of 4)
+  // this lane's chunks of a row: ptid, ptid + NPT, ...; the source pointer walks the rows in sweep order
+  const int n_mine = producer ? max(0, (chunks - ptid + NPT - 1) / NPT) : 0;
+  const long long pstep = (DIR ? -8LL : 8LL) * nlp;
+  const char* psrc = reinterpret_cast<const char*>(ebase + (long long)frame_t(0) * nlp) + 16 * ptid;
   auto issue = [&](int r) {  // copies of row r (frame frame_t(r)); always commits a group
     if (r < len) {
-      const int2* src = ebase + (long long)frame_t(r) * nlp;
-      unsigned char* dst = sm + P.er + (size_t)(r % ER) * nlp * 8;
-      for (int c = ptid; c < chunks; c += NPT) cp_async16(dst + 16 * c, src + 2 * c);
+      unsigned d = er_a + (r & (ER - 1)) * nlp * 8 + 16 * ptid;
+      const char* sp = psrc;
+      for (int k = 0; k < n_mine; ++k) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(sp) : "memory");
+        d += 16 * NPT;
+        sp += 16 * NPT;
+      }
+      psrc += pstep;
     }
     cp_async_commit();
   };
@@ -244,7 +253,6 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
       cp_async_wait<ER - 2>();  // row i + 1 has landed
     } else {
       const unsigned ea = er_a + (i & (ER - 1)) * nlp * 8;  // ER is a power of two
-      const bool st = spill && (DIR || i + 1 < len);
       int J[SPT][DK];
       float pm[SPT][DK];
       int2 ev[SPT];
@@ -264,7 +272,7 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
         const int2 res = step_state<DK>(J[u], pm[u], ev[u]);
         if (s < n) {
           sts64(an + s * 8, res);
-          if (st) rows[orow + s] = res;
+          if (spill) rows[orow + s] = res;
         }
       }
     }
@@ -325,18 +333,14 @@ __device__ __forceinline__ float post_term(int2 av, int2 bv, int kE, float km) {
   return (__int_as_float(av.y) * __int_as_float(bv.y)) * (km * pow2c(min(av.x + bv.x + kE, 64)));
 }
 
-// With a.scatter_grad set the normalised posteriors are subtracted from the dense gradient rows the
-// denominator wrote (grad[t][b][lab_list[j]] -= scale_b * gamma_t[j], the scatter_sub step fused in:
-// every (t, b, label) is touched by exactly one lane, no atomics); otherwise the compact rows
-// gout[b][t][j] are written for the row kernels of plain CTC.
+// Writes the compact posterior rows gout[b][t][j], normalised to sum one (times g_sign * g_scale[b]): the
+// row kernels of plain CTC and the denominator's combine kernel (CTC-G) fold them into the dense gradient.
 template <bool UNIT>
 __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  // utterances in descending order: with the scatter fused in, the gradient rows written last by the
-  // denominator (the highest b) are the ones most likely to be L2 resident still
-  const int b = a.B - 1 - (int)blockIdx.y;
+  const int b = blockIdx.y;
   const int len = min(a.lens[b], a.T);
   const int nwarps = blockDim.x >> 5, nthreads = blockDim.x;
   const int cb_fr = nwarps * CB_FPW;
@@ -375,13 +379,12 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
   // the cost's exponent keeps the terms in range; its mantissa cancels in the row normalisation
   const int cE = (int)rint(costn / kLn2);
   const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
-  const int V = a.scatter_V;
   auto stage = [&](int q) {  // always commits a group (possibly empty), so that the wait counts stay uniform
     const int t = blockIdx.x * cb_fr + q * nwarps + warp;
     if (q < CB_FPW && t < len && feasible) {
       float* d = wbase + (q & 1) * stg;
-      const float* as = a.alpha_ws + ((long long)b * a.T + t) * arow;
-      const float* bs = a.beta_ws + ((long long)b * a.T + t) * arow;
+      const float* as = a.alpha_ws + ((long long)b * (a.T + 1) + t) * arow;
+      const float* bs = a.beta_ws + ((long long)b * (a.T + 1) + t) * arow;
       for (int i = lane; i < (2 * n + 3) / 4; i += 32) {
         cp_async16(d + 4 * i, as + 4 * i);
         cp_async16(d + arow + 4 * i, bs + 4 * i);
@@ -395,8 +398,7 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
     if (t >= len) break;
     float* dst = a.gout + (long long)b * a.g_stride_b + (long long)t * a.g_stride_t;
     if (!feasible) {  // no accepting path: zero posterior
-      if (!a.scatter_grad)
-        for (int j = lane; j < nl; j += 32) dst[j] = 0.f;
+      for (int j = lane; j < nl; j += 32) dst[j] = 0.f;
       continue;
     }
     __syncwarp();       // the previous frame's reads of the buffer about to be refilled are done
@@ -405,20 +407,6 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
     __syncwarp();
     const int2* at = reinterpret_cast<const int2*>(wbase + (q & 1) * stg);
     const int2* bt = reinterpret_cast<const int2*>(wbase + (q & 1) * stg + arow);
-    // scatter mode: the gradient entries this frame will touch are requested now, so that their DRAM
-    // latency runs behind the posterior sums (first 256 labels; the labels of an utterance are distinct)
-    float* out = a.scatter_grad ? a.scatter_grad + ((long long)t * a.B + b) * V : nullptr;
-    float* ptr[8];
-    float cur[8];
-    if (out) {
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int j = lane + 32 * u;
-        ptr[u] = out + ((j < nl) ? g.lab_list[lo + j] : 0);
-        cur[u] = 0.f;
-        if (j < nl) cur[u] = __ldcg(ptr[u]);
-      }
-    }
     float ls = 0.f;
     for (int base = 0; base < nl; base += 32) {
       const int j = base + lane;
@@ -461,30 +449,7 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
     const float tot = warp_sum(ls);
     const float sc = tot > 0.f ? gmul / tot : 0.f;
     __syncwarp();
-    if (a.scatter_grad) {
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int j = lane + 32 * u;
-        if (j < nl) *ptr[u] = cur[u] - gt[j] * sc;
-      }
-      for (int j0 = 256; j0 < nl; j0 += 256) {  // more than 256 distinct labels: batches of 8 loads, then 8 stores
-        float* p2[8];
-        float c2[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int j = j0 + lane + 32 * u;
-          p2[u] = out + ((j < nl) ? g.lab_list[lo + j] : 0);
-          if (j < nl) c2[u] = *p2[u];
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int j = j0 + lane + 32 * u;
-          if (j < nl) *p2[u] = c2[u] - gt[j] * sc;
-        }
-      }
-    } else {
-      for (int j = lane; j < nl; j += 32) dst[j] = gt[j] * sc;
-    }
+    for (int j = lane; j < nl; j += 32) dst[j] = gt[j] * sc;
   }
 }
 
