@@ -33,7 +33,7 @@ struct Plan {
   int arow_den = 0;
   size_t lens = 0, xg = 0, gg = 0, alpha_num = 0, beta_num = 0, cost_num = 0, rowlse = 0, alpha_den = 0, cost_den = 0;
   size_t pspill = 0, ckpt = 0;
-  size_t spill2 = 0, ckpt2 = 0, fin = 0, labmap = 0;
+  size_t spill2 = 0, ckpt2 = 0, fin = 0;
   BisweepPlan sw{};  // sw.ok: the denominator runs on the factorised bi-char kernels (kernels_bisweep.cu)
   size_t total = 0;
 };
@@ -60,7 +60,7 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
     p.nlp = pad4(std::max(num->max_labels, 1));
     p.arow_num = pad4(2 * num->max_states + 2);  // split numerator: (integer, fraction) per state
     p.xg = take(TB * p.nlp * 8);  // float columns (generic kernel) or (exponent, mantissa) pairs (split sweeps)
-    p.gg = take(TB * p.nlp * 4);
+    p.gg = take((TB + 16 * (size_t)std::max(B, 1)) * p.nlp * 4);  // segment-major layout: T rounded up to the segment
     const size_t T1B = (size_t)(std::max(T, 1) + 1) * (size_t)std::max(B, 1);  // the split sweeps spill T + 1 rows
     p.alpha_num = take(T1B * p.arow_num * 4);
     p.beta_num = take(T1B * p.arow_num * 4);
@@ -76,7 +76,6 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
       p.spill2 = take(p.sw.spill_bytes);
       p.ckpt2 = take(p.sw.ckpt_bytes);
       p.fin = take((size_t)B * sizeof(BiFin));
-      if (num) p.labmap = take((size_t)B * V * 2);
     } else {
       p.arow_den = pad4(den->max_states + 2);
       p.alpha_den = take(TB * p.arow_den * 4);
@@ -389,12 +388,10 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   }();
   CTCG_CUDA(launch_gather(logits, T, B, V, lens, num->dev, xg, p.nlp, normalize == CTCG_NORM_CONTEXT ? 2 : 0,
                           num_symbols, split, st));
-  if (den && p.sw.ok && aligned16(logits) && aligned16(grad) && grad)
-    CTCG_CUDA(launch_labmap(B, V, num->dev, reinterpret_cast<unsigned short*>(ws + p.labmap), st));
   SideStream* side = fused_den ? side_stream() : nullptr;
   // With the factorised denominator the numerator's posteriors leave in the denominator's combine kernel
   // (one store of gamma_den - gamma_num): sweeps || numerator, then the combine.
-  const bool fold = fused_den && grad != nullptr;
+  const bool fold = fused_den && grad != nullptr && split;
   BisweepArgs den_args{};
   cudaStream_t ds = st;
   if (fused_den) {
@@ -408,7 +405,9 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     if (fold) {
       den_args.num_gg = gg;
       den_args.num_nlp = p.nlp;
-      den_args.labmap = reinterpret_cast<const unsigned short*>(ws + p.labmap);
+      den_args.num_graphs = num->dev.num_graphs;
+      den_args.num_lab_off = num->dev.lab_off;
+      den_args.num_lab_list = num->dev.lab_list;
     }
     if (launch_bisweep(den_args, p.sw, ds) != cudaSuccess) {
       (void)cudaGetLastError();
@@ -448,6 +447,10 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     a.g_scale = nullptr;
     a.write_grad = grad != nullptr;
     a.beta_ws = reinterpret_cast<float*>(ws + p.beta_num);
+    if (split && fold) {  // the denominator's combine reads the posteriors one K-frame segment at a time
+      a.g_seg = p.sw.K;
+      a.g_stride_b = (long long)p.sw.nck * p.nlp * p.sw.K;
+    }
     if (split) {
       CTCG_CUDA(launch_num_sweeps(a, st));
       CTCG_CUDA(launch_num_combine(a, st));
@@ -482,7 +485,8 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   }
 
   if (fused_den) {
-    // (nothing left: the combine wrote g_scale * (gamma_den - gamma_num))
+    // folded: the combine wrote g_scale * (gamma_den - gamma_num); a numerator of the generic kernel is subtracted here
+    if (grad && !fold) CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
   } else if (den) {
     // 3a. denominator path sum over the shared decoding graph, writes +gamma_den rows
     PathArgs d{};

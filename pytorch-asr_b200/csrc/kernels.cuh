@@ -26,6 +26,8 @@ struct PathArgs {
   long long g_stride_t;
   long long g_stride_b;
   int32_t g_width;        // row width written per frame (max_labels or V)
+  int32_t g_seg;          // split numerator only: > 0 = posteriors stored segment-major, gout[b][t / g_seg][j][t % g_seg]
+                          // (g_stride_b = entries per utterance), the layout the denominator's combine reads
   float g_sign;
   const float* g_scale;   // nullable, per-utterance multiplier
   int32_t write_grad;
@@ -101,9 +103,11 @@ struct BisweepArgs {
   int32_t nmain, rowf, estride, epad;
   int32_t dbg;             // timing experiments only (CTCG_SWEEP_DEBUG bit mask); 0 in production
   // numerator posteriors folded into the combine (nullable): grad = g_scale * (gamma_den - gamma_num) in ONE store.
-  const float* num_gg;            // compact rows gg[b][t][j], j indexes the utterance's distinct labels
-  int32_t num_nlp;                // their pitch
-  const unsigned short* labmap;   // [B][V]: class -> j, 0xffff = not a label of this utterance (launch_labmap)
+  const float* num_gg;            // compact posteriors, segment-major: gg[b][t / K][j][t % K], j indexes the utterance's labels
+  int32_t num_nlp;                // labels per row (pitch)
+  int32_t num_graphs;             // 1 (shared numerator graph) or B
+  const int32_t* num_lab_off;     // GraphDev::lab_off / lab_list of the numerator graphs
+  const int32_t* num_lab_list;
 };
 struct BisweepPlan {
   int32_t ok, K, nck, nmain, threads, rowf, prowf, estride, epad;
@@ -114,8 +118,6 @@ BisweepPlan bisweep_plan(int T, int B, int V, int S);
 // a.num_gg set it must be ordered after the numerator's compact rows are complete.
 cudaError_t launch_bisweep(const BisweepArgs& a, const BisweepPlan& p, cudaStream_t st);
 cudaError_t launch_bicombine(const BisweepArgs& a, const BisweepPlan& p, cudaStream_t st);
-// labmap[b][v] = index of class v in utterance b's label list, 0xffff if absent (at most 65535 labels)
-cudaError_t launch_labmap(int B, int V, const GraphDev& num, unsigned short* labmap, cudaStream_t st);
 
 // Incremented by every launch_* above.
 extern unsigned long long g_launches;

@@ -630,6 +630,30 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
   }
   if (n == 0) return;
 
+  // Numerator posteriors of this segment (compact, segment-major: the K frames of a label are one 32-byte
+  // sector): requested first, so that their latency runs behind the staging below; they go to shared memory
+  // with a class -> label-index table and leave in the store of the dense row (NLT labels at most; an
+  // utterance with more takes the read-modify-write pass at the end of the kernel).
+  constexpr int NLT = 256, VMAX = 64 * 64;
+  __shared__ unsigned short dl[VMAX];
+  __shared__ __align__(16) float gtab[NLT][KMAX];
+  int fold_nl = 0, fold_lo = 0;
+  if (A.num_gg) {
+    const int gi = A.num_graphs == 1 ? 0 : b;
+    fold_lo = A.num_lab_off[gi];
+    fold_nl = A.num_lab_off[gi + 1] - fold_lo;
+  }
+  const bool fold_smem = fold_nl > 0 && fold_nl <= NLT && V <= VMAX;
+  int my_lab = -1;
+  float4 my_g0 = make_float4(0.f, 0.f, 0.f, 0.f), my_g1 = my_g0;
+  if (fold_smem && tid < fold_nl) {
+    my_lab = A.num_lab_list[fold_lo + tid];
+    const float4* gp = reinterpret_cast<const float4*>(A.num_gg + (((long long)b * A.nck + j) * A.num_nlp + tid) * KMAX);
+    my_g0 = __ldg(gp);
+    my_g1 = __ldg(gp + 1);
+  }
+  if (fold_smem)
+    for (int v = tid; v < V; v += CTHREADS) dl[v] = 0xffffu;
   __shared__ float Ps[KMAX][KW], Qs[KMAX][KW];
   __shared__ float nmL_s[KMAX], scF_s[KMAX], scB_s[KMAX], cB_s[KMAX];
   const float* spF = A.spill[0] + ((long long)b * T + t0) * prowf;
@@ -667,7 +691,13 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
     cB_s[tid] = cb;
   }
   __syncthreads();
+  if (fold_smem && my_lab >= 0) {  // after the barrier: the table has been cleared
+    dl[my_lab] = (unsigned short)tid;
+    *reinterpret_cast<float4*>(&gtab[tid][0]) = my_g0;
+    *reinterpret_cast<float4*>(&gtab[tid][4]) = my_g1;
+  }
   const bool loops = A.loops != 0, ctx = A.ctx != 0;
+  if (fold_smem && ctx) __syncthreads();  // (the global-blank branch below has a barrier of its own)
   if (!ctx) {  // one global blank: sum over the S blank states, read by class 0 through Qs[f][64]
     for (int f = warp; f < n; f += CTHREADS / 32) {
       float d = Ps[f][lane] * Qs[f][lane] + Ps[f][lane + 32] * Qs[f][lane + 32];
@@ -726,15 +756,15 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
       }
     }
   };
-  // numerator posteriors (compact rows, L2 resident) leave in the same store: ~6 % of the classes have one
-  const unsigned short* lmap = (A.labmap && A.num_gg) ? A.labmap + (long long)b * V : nullptr;
-  const float* ngg = lmap ? A.num_gg + ((long long)b * T + t0) * A.num_nlp : nullptr;
-  const int nnlp = A.num_nlp;
-  auto sub_num = [&](unsigned j, float (&e)[KMAX], const bool full) {
-    if (j == 0xffffu) return;
+  auto sub_num = [&](int v, float (&e)[KMAX]) {
+    if (!fold_smem) return;
+    const unsigned jl = dl[v];
+    if (jl == 0xffffu) return;
+    const float4 q0 = *reinterpret_cast<const float4*>(&gtab[jl][0]);
+    const float4 q1 = *reinterpret_cast<const float4*>(&gtab[jl][4]);
+    const float gv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
-    for (int f = 0; f < KMAX; ++f)
-      if (full || f < n) e[f] = fmaf(-gsc, __ldg(ngg + f * nnlp + j), e[f]);
+    for (int f = 0; f < KMAX; ++f) e[f] = fmaf(-gsc, gv[f], e[f]);  // frames >= n of a partial segment are not stored
   };
   auto scalar_class = [&](int v) {
     float e[KMAX];
@@ -742,7 +772,7 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
     for (int f = 0; f < KMAX; ++f)
       if (f < n) e[f] = __ldg(x0 + v + f * rstride);
     walk(v, e, false);
-    sub_num(lmap ? lmap[v] : 0xffffu, e, false);
+    sub_num(v, e);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f)
       if (f < n) g0[v + f * rstride] = e[f];
@@ -753,12 +783,10 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
   // after the last full chunk (and every partial segment) go through the scalar path.
   const long long i0 = ((long long)t0 * B + b) * V;
   const bool vec = (n == KMAX) && ((rstride & 3) == 0);
-  if (!vec) {
-    for (int v = tid; v < V; v += CTHREADS) scalar_class(v);
-    return;
-  }
   const int v0 = (int)((4 - (i0 & 3)) & 3);
-  const int nch = (V - v0) >> 2;
+  const int nch = vec ? (V - v0) >> 2 : 0;
+  if (!vec)
+    for (int v = tid; v < V; v += CTHREADS) scalar_class(v);
   for (int k = tid; k < nch; k += CTHREADS) {
     const int v = v0 + 4 * k;
     float4 xv[KMAX];
@@ -767,26 +795,23 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
       const float4* p = reinterpret_cast<const float4*>(x0 + v + f * rstride);
       asm volatile("ld.global.cs.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(xv[f].x), "=f"(xv[f].y), "=f"(xv[f].z), "=f"(xv[f].w) : "l"(p));
     }
-    // the four map entries of the chunk in one 8-byte load ((b*V + v) is a multiple of 4 on this path)
-    uint2 jm = make_uint2(0xffffffffu, 0xffffffffu);
-    if (lmap) jm = __ldg(reinterpret_cast<const uint2*>(lmap + v));
     float e[KMAX];
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) e[f] = xv[f].x;
     walk(v, e, true);
-    sub_num(jm.x & 0xffffu, e, true);
+    sub_num(v, e);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) { xv[f].x = e[f]; e[f] = xv[f].y; }
     walk(v + 1, e, true);
-    sub_num(jm.x >> 16, e, true);
+    sub_num(v + 1, e);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) { xv[f].y = e[f]; e[f] = xv[f].z; }
     walk(v + 2, e, true);
-    sub_num(jm.y & 0xffffu, e, true);
+    sub_num(v + 2, e);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) { xv[f].z = e[f]; e[f] = xv[f].w; }
     walk(v + 3, e, true);
-    sub_num(jm.y >> 16, e, true);
+    sub_num(v + 3, e);
 #pragma unroll
     for (int f = 0; f < KMAX; ++f) {
       xv[f].w = e[f];
@@ -794,34 +819,39 @@ __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArg
       asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(xv[f].x), "f"(xv[f].y), "f"(xv[f].z), "f"(xv[f].w) : "memory");
     }
   }
-  if (tid < v0) scalar_class(tid);
-  {
+  if (vec) {
+    if (tid < v0) scalar_class(tid);
     const int vt = v0 + 4 * nch + (tid - 32);
     if (tid >= 32 && vt < V) scalar_class(vt);
   }
-}
-
-__global__ void __launch_bounds__(256) labmap_kernel(int V, GraphDev g, unsigned short* __restrict__ labmap) {
-  const int b = blockIdx.x;
-  const int gi = g.num_graphs == 1 ? 0 : b;
-  const int lo = g.lab_off[gi], nl = g.lab_off[gi + 1] - lo;
-  unsigned short* row = labmap + (long long)b * V;
-  for (int v = threadIdx.x; v < V; v += blockDim.x) row[v] = 0xffffu;
-  __syncthreads();
-  for (int j = threadIdx.x; j < nl; j += blockDim.x) {
-    const int lab = g.lab_list[lo + j];
-    if (lab < V) row[lab] = (unsigned short)j;
+  // Numerator posteriors: grad[t][b][lab_j] -= g_scale * gamma_num[t][j] for the ~140 labels of this utterance,
+  // on the rows this CTA has just written (they are in L2: a read-modify-write that never reaches DRAM, where
+  // the separate scatter kernel of round 1 moved 17 bytes of sectors per useful byte).  Segment-major compact
+  // rows: the K frames of a label are one 32-byte sector.
+  if (A.num_gg == nullptr || fold_smem) return;
+  __syncthreads();  // every dense store of the segment is visible to the CTA
+  const int gi = A.num_graphs == 1 ? 0 : b;
+  const int lo = A.num_lab_off[gi], nl = A.num_lab_off[gi + 1] - lo;
+  const float* ngg = A.num_gg + ((long long)b * A.nck + j) * A.num_nlp * KMAX;
+  for (int jl = tid; jl < nl; jl += CTHREADS) {
+    const int v = A.num_lab_list[lo + jl];
+    const float4* gp = reinterpret_cast<const float4*>(ngg + jl * KMAX);
+    float gv[KMAX], cur[KMAX];
+#pragma unroll
+    for (int h = 0; h < KMAX / 4; ++h) {
+      const float4 q = __ldg(gp + h);
+      gv[4 * h] = q.x, gv[4 * h + 1] = q.y, gv[4 * h + 2] = q.z, gv[4 * h + 3] = q.w;
+    }
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f)
+      if (f < n) cur[f] = __ldcg(g0 + v + f * rstride);
+#pragma unroll
+    for (int f = 0; f < KMAX; ++f)
+      if (f < n) g0[v + f * rstride] = fmaf(-gsc, gv[f], cur[f]);
   }
 }
 
 }  // namespace
-
-cudaError_t launch_labmap(int B, int V, const GraphDev& num, unsigned short* labmap, cudaStream_t st) {
-  ProfScope prof("labmap", st);
-  labmap_kernel<<<B, 256, 0, st>>>(V, num, labmap);
-  ++g_launches;
-  return cudaGetLastError();
-}
 
 // ---- host side ------------------------------------------------------------------
 BisweepPlan bisweep_plan(int T, int B, int V, int S) {

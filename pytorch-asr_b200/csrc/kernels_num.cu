@@ -396,9 +396,13 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
   for (int q = 0; q < CB_FPW; ++q) {
     const int t = blockIdx.x * cb_fr + q * nwarps + warp;
     if (t >= len) break;
-    float* dst = a.gout + (long long)b * a.g_stride_b + (long long)t * a.g_stride_t;
+    // row-major [t][j], or segment-major [t / seg][j][t % seg] for the denominator's combine kernel
+    const int seg = a.g_seg;
+    float* dst = a.gout + (long long)b * a.g_stride_b +
+                 (seg > 0 ? (long long)(t / seg) * nlp * seg + (t % seg) : (long long)t * a.g_stride_t);
+    const int dstep = seg > 0 ? seg : 1;
     if (!feasible) {  // no accepting path: zero posterior
-      for (int j = lane; j < nl; j += 32) dst[j] = 0.f;
+      for (int j = lane; j < nl; j += 32) dst[j * dstep] = 0.f;
       continue;
     }
     __syncwarp();       // the previous frame's reads of the buffer about to be refilled are done
@@ -449,7 +453,7 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
     const float tot = warp_sum(ls);
     const float sc = tot > 0.f ? gmul / tot : 0.f;
     __syncwarp();
-    for (int j = lane; j < nl; j += 32) dst[j] = gt[j] * sc;
+    for (int j = lane; j < nl; j += 32) dst[j * dstep] = gt[j] * sc;
   }
 }
 

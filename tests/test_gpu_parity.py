@@ -202,6 +202,7 @@ def _record(name, value):
     ("ctcg", 36, 64, 400, False),     # BASELINE's nominal V=1296
     ("ctc", 36, 64, 400, False),
     ("ctc", 49, 64, 400, True),       # cfg2
+    ("ctcg", 49, 3, 1400, False),     # > 256 distinct labels per utterance: the combine's read-modify-write tail
 ])
 def test_bench_configurations_match_fp64_oracle(P, variant, S, B, T, peaky):
     """The configurations bench.py times (seed-1003 batch at full B and T) against the fp64 oracle:
