@@ -103,7 +103,9 @@ int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels,
 /* Import the reference's own padded matrices (the 8-tuple FSTDecoder receives
  * in batch['graph_matrices'], advanced_decoder.py:457-459): G graphs of N
  * states, in-degree K_in, out-degree K_out; arcs with weight <= nc_weight/2 are
- * padding and dropped.  Validates start==0 reachability conventions only. */
+ * padding and dropped.  Validates start==0 reachability conventions only.  * A single graph that is arc for arc the bi-char decoding graph of
+ * fst_utils.py:765-817 (what get_decoding_matrices exports) is recognised and
+ * takes the factorised kernels, as a graph from ctcg_decoding_graph does. */
 int ctcg_graph_from_padded(const int64_t* pred, const int64_t* lab_in,
                            const float* w_in, const float* final_w,
                            const int64_t* succ, const int64_t* lab_out,
@@ -179,6 +181,20 @@ int ctcg_viterbi(const float* log_probs, int32_t T, int32_t B, int32_t V,
                  const int32_t* lens_host, const ctcg_graph* graph, float* score,
                  int32_t* frame_labels, void* workspace, size_t workspace_bytes,
                  void* stream);
+
+/* PathLogSumExp.backward (fst_utils.py:482-485): grad[t][b][:] *= scale[b *
+ * scale_stride], scale a DEVICE pointer (scale_stride 0: one scalar for the
+ * batch, the broadcast grad_output of loss.sum().backward()).  Rows whose scale
+ * is exactly 1 are skipped on the device: the common case costs one launch and
+ * no memory traffic, where the reference multiplies the whole (T,B,V) tensor. */
+int ctcg_scale_grad(float* grad, int32_t T, int32_t B, int32_t V, const float* scale,
+                    int32_t scale_stride, void* stream);
+
+/* Drops the topology tag of a graph built by ctcg_decoding_graph (or recognised by
+ * ctcg_graph_from_padded), so that it takes the generic CSR kernels like any
+ * other graph: the cross-check of the factorised bi-char kernels
+ * (fst_utils.py:400-488 on the arcs of fst_utils.py:765-817). */
+void ctcg_graph_set_generic(ctcg_graph* graph);
 
 /* ctcg_viterbi without any allocation on the call path.  NO COUNTERPART IN THE
  * REFERENCE: added for callers that cannot

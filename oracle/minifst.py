@@ -221,6 +221,24 @@ def _connect(f):
     return out
 
 
+def arcmap(ifst, delta=0.0009765625, map_type="identity", power=1.0, weight=None):
+    """``fst.arcmap(f, 0, 'to_standard', 0)`` (advanced_decoder.py:422-424): the same states and arcs
+    re-typed to the tropical semiring (the numeric weight values carry over).  Only the
+    ``to_standard`` / ``to_log`` / ``identity`` maps the reference uses are restated."""
+    arc_type = {"to_standard": "standard", "to_std": "standard", "to_log": "log",
+                "identity": ifst.arc_type()}[map_type]
+    out = Fst(arc_type=arc_type)
+    for s in ifst.states():
+        out.add_state()
+    if ifst.start() != NO_STATE_ID:
+        out.set_start(ifst.start())
+    for s in ifst.states():
+        out._final[s] = ifst._final[s]
+        for a in ifst.arcs(s):
+            out.add_arc(s, Arc(a.ilabel, a.olabel, Weight(out.weight_type(), float(a.weight)), a.nextstate))
+    return out
+
+
 def compose(ifst1, ifst2, connect=True):
     """``fst.compose`` for (A with output epsilons) o (B without input epsilons)."""
     for s in ifst2.states():

@@ -22,7 +22,7 @@ EXPORTS = (
     "ctcg_decoding_graph", "ctcg_training_graphs", "ctcg_graph_from_padded",
     "ctcg_graph_from_arcs", "ctcg_graph_get_info", "ctcg_graph_padded_dims",
     "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
-    "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static",
+    "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
     "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
     "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
@@ -67,6 +67,8 @@ def lib():
     L.ctcg_graph_upload.argtypes = [vp, vp]
     L.ctcg_graph_free.argtypes = [vp]
     L.ctcg_graph_free.restype = None
+    L.ctcg_graph_set_generic.argtypes = [vp]
+    L.ctcg_graph_set_generic.restype = None
     L.ctcg_workspace_bytes.argtypes = [i32, i32, i32, vp, vp]
     L.ctcg_workspace_bytes.restype = C.c_size_t
     L.ctcg_loss_fwd_bwd.argtypes = [f32p, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp, vp, vp,
@@ -75,6 +77,7 @@ def lib():
     L.ctcg_viterbi.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp, C.c_size_t, vp]
     L.ctcg_viterbi_static.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp]
     L.ctcg_path_count.argtypes = [i32, vp, vp, vp, vp, C.c_size_t, vp]
+    L.ctcg_scale_grad.argtypes = [vp, i32, i32, i32, vp, i32, vp]
     L.ctcg_loss_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp]
     L.ctcg_logits_post_width.argtypes = [i32, i32]
     L.ctcg_logits_post_width.restype = i32
@@ -194,6 +197,11 @@ class Graph(object):
                                            None, None, None, G, N, K, 0, float(nc_weight),
                                            C.byref(out)))
         return cls(out)
+
+    def set_generic(self):
+        """Drop the topology tag: the graph takes the generic CSR kernels (cross-checks)."""
+        lib().ctcg_graph_set_generic(self.ptr)
+        return self
 
     @classmethod
     def from_arcs(cls, graphs):
@@ -342,6 +350,21 @@ def viterbi(log_probs, act_lens, graph):
         check(lib().ctcg_viterbi(x.data_ptr(), T, B, V, _np_ptr(lens), graph.ptr, score.data_ptr(),
                                  labels.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev)))
     return score, labels
+
+
+def scale_grad(grad, grad_output):
+    """In place ``grad[t, b, :] *= grad_output[b]`` on the device (``PathLogSumExp.backward``,
+    fst_utils.py:482-485); rows whose factor is exactly 1 cost nothing."""
+    _require_cuda(grad, "grad")
+    T, B, V = grad.shape
+    go = grad_output
+    assert go.numel() == B or go.numel() == 1
+    stride = 0 if (go.numel() == 1 or go.stride() == (0,)) else 1
+    go = go if stride == 0 else go.contiguous()
+    go = go.to(device=grad.device, dtype=torch.float32)
+    with torch.cuda.device(grad.device):
+        check(lib().ctcg_scale_grad(grad.data_ptr(), T, B, V, go.data_ptr(), stride, _stream_ptr(grad.device)))
+    return grad
 
 
 STATIC_SCRATCH_BYTES = 32 << 20

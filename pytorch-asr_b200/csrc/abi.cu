@@ -523,6 +523,13 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   return CTCG_OK;
 }
 
+int ctcg_scale_grad(float* grad, int32_t T, int32_t B, int32_t V, const float* scale, int32_t scale_stride,
+                    void* stream) {
+  if (!grad || !scale || T < 1 || B < 1 || V < 1 || scale_stride < 0) return CTCG_EINVAL;
+  CTCG_CUDA(launch_scale_grad(grad, T, B, V, scale, scale_stride, static_cast<cudaStream_t>(stream)));
+  return CTCG_OK;
+}
+
 int ctcg_logits_post_width(int32_t V, int32_t flags) {
   if (V < 1) return 0;
   if (flags & CTCG_POST_IMITATE_BIPHONES) return (V <= 46340) ? V * V : 0;

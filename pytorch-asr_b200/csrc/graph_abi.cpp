@@ -63,9 +63,53 @@ void mark_structured(const ctcg_topology& t, ctcg_graph* g) {
   g->structured.loop_using_symbol_repetitions = t.loop_using_symbol_repetitions != 0;
 }
 
+// A single graph with S*S states, all final, unit weights, whose arcs are exactly those of the bi-char
+// decoding graph of some flag combination (fst_utils.py:765-817) is that graph: tag it, so that matrices
+// which went through the reference's padded format (get_decoding_matrices -> path_reduction, the route
+// that leaves the reference's FSTDecoder untouched) still take the factorised kernels.  The padded format
+// carries no output labels, so loop_using_symbol_repetitions cannot be told from (no self-loops,
+// contextual blanks) -- and does not matter for a path sum.
+void recognise_bichar(const RawGraph& r, ctcg_graph* g) {
+  if (g->num_graphs != 1 || !g->unit_weights) return;
+  int S = 2;
+  while (S * S < r.n) ++S;
+  if (S * S != r.n || S < 2 || S > 64) return;
+  for (float f : r.final_w)
+    if (f != 0.f) return;
+  auto key = [](const Arc& a) { return std::make_tuple(a.src, a.dst, a.label); };
+  std::vector<std::tuple<int32_t, int32_t, int32_t>> mine;
+  mine.reserve(r.arcs.size());
+  for (const Arc& a : r.arcs) mine.push_back(key(a));
+  std::sort(mine.begin(), mine.end());
+  for (int loops = 1; loops >= 0; --loops)
+    for (int ctx = 0; ctx <= 1; ++ctx) {
+      ctcg_topology t{};
+      t.context_order = 2;
+      t.num_symbols = S;
+      t.allow_nonblank_selfloops = loops;
+      t.use_contextual_blanks = ctx;
+      t.loop_using_symbol_repetitions = 0;
+      int st = CTCG_OK;
+      const auto c = cached_decoding(t, &st);
+      if (st != CTCG_OK || !c || c->g.arcs.size() != r.arcs.size()) continue;
+      std::vector<std::tuple<int32_t, int32_t, int32_t>> want;
+      want.reserve(c->g.arcs.size());
+      for (const Arc& a : c->g.arcs) want.push_back(key(a));
+      std::sort(want.begin(), want.end());
+      if (want == mine) {
+        mark_structured(t, g);
+        return;
+      }
+    }
+}
+
 }  // namespace
 
 extern "C" {
+
+void ctcg_graph_set_generic(ctcg_graph* g) {
+  if (g) g->structured = ctcg::Structured{0, 0, 0, 0, 0};
+}
 
 int ctcg_decoding_graph(const ctcg_topology* topo, ctcg_graph** out) {
   if (!topo || !out) return CTCG_EINVAL;
@@ -162,7 +206,9 @@ int ctcg_graph_from_padded(const int64_t* pred, const int64_t* lab_in, const flo
         }
       }
     }
-    return finalize_graphs(gs, out);
+    const int st = finalize_graphs(gs, out);
+    if (st == CTCG_OK && G == 1) recognise_bichar(gs[0], *out);
+    return st;
   } catch (const std::bad_alloc&) {
     return CTCG_ENOMEM;
   }

@@ -70,6 +70,9 @@ cudaError_t launch_scatter_sub(int T, int B, int V, const int32_t* lens, const G
 cudaError_t launch_final(int T, int B, const int32_t* lens, const double* cost_num,
                          const double* cost_den, const float* rowlse, float* loss, cudaStream_t st);
 
+// grad[t][b][:] *= scale[b * stride] (stride 0: one scalar for the whole batch); rows with scale 1 are skipped
+cudaError_t launch_scale_grad(float* grad, int T, int B, int V, const float* scale, int stride, cudaStream_t st);
+
 cudaError_t launch_cost_to_float(int B, const double* cost, float* out, cudaStream_t st);
 
 cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* lens,

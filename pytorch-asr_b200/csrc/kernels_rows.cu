@@ -240,6 +240,18 @@ __global__ void __launch_bounds__(NT) final_kernel(int T, int B, const int32_t* 
   }
 }
 
+// grad[t][b][:] *= scale[b * stride]; a row whose scale is exactly 1 is left alone, so the usual
+// loss.sum().backward() (grad_output = ones) costs a launch and no memory traffic.
+__global__ void __launch_bounds__(NT) scale_grad_kernel(float* __restrict__ grad, long long rows, int B, int V,
+                                                        const float* __restrict__ scale, int stride) {
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const float sc = scale[(long long)(row % B) * stride];
+    if (sc == 1.f) continue;
+    float* g = grad + row * V;
+    for (int j = threadIdx.x; j < V; j += NT) g[j] *= sc;
+  }
+}
+
 __global__ void cost_to_float_kernel(int B, const double* __restrict__ cost, float* __restrict__ out) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < B) out[b] = (float)cost[b];
@@ -313,6 +325,15 @@ cudaError_t launch_final(int T, int B, const int32_t* lens, const double* cost_n
   const unsigned grid = (unsigned)((B + NWARP - 1) / NWARP);
   ProfScope prof("final", st);
   final_kernel<<<grid, NT, 0, st>>>(T, B, lens, cost_num, cost_den, rowlse, loss);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_scale_grad(float* grad, int T, int B, int V, const float* scale, int stride, cudaStream_t st) {
+  const long long rows = (long long)T * B;
+  const unsigned grid = (unsigned)std::min<long long>(rows, 148LL * 8);
+  ProfScope prof("scale_grad", st);
+  scale_grad_kernel<<<grid, NT, 0, st>>>(grad, rows, B, V, scale, stride);
   ++g_launches;
   return cudaGetLastError();
 }

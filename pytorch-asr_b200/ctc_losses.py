@@ -58,11 +58,8 @@ class _FstLoss(torch.autograd.Function):
     def backward(ctx, grad_output):
         g = ctx.grads
         ctx.grads = None  # single backward, like the reference's ctx.grads (fst_utils.py:473,484)
-        if grad_output.stride() == (0,):  # .sum().backward(): one broadcast scalar
-            g.mul_(grad_output[0])
-        else:
-            g.mul_(grad_output[None, :, None])
-        return g, None, None, None, None, None
+        # grad_output scales the rows on the device; the usual .sum().backward() (all ones) touches nothing
+        return _lib.scale_grad(g, grad_output), None, None, None, None, None
 
 
 def fst_loss(logits, act_lens, numerator, denominator=None, normalize_by_dim=None,
@@ -76,7 +73,21 @@ def fst_loss(logits, act_lens, numerator, denominator=None, normalize_by_dim=Non
     num = _as_graph(numerator)
     den = _as_graph(denominator) if denominator is not None else None
     assert num.num_graphs in (1, logits.size(1))
-    return _FstLoss.apply(logits, lens, num, den, _norm_mode(normalize_by_dim), int(num_symbols or 0))
+    return _fst_loss(logits, lens, num, den, _norm_mode(normalize_by_dim), int(num_symbols or 0))
+
+
+def _fst_loss(logits, lens, num, den, mode, num_symbols):
+    if mode == _lib.NORM_CONTEXT and den is not None:
+        # Per-context softmax together with a denominator (ctc_losses.py:29-43 feeding
+        # advanced_decoder.py:497-500; no shipped configuration combines them): the kernels fuse that
+        # normalisation for the numerator only, so here it is a device-side log_softmax whose backward
+        # autograd chains in front of the un-normalised loss.
+        V = logits.size(2)
+        S = int(num_symbols)
+        assert S > 0 and V % S == 0
+        lp = torch.log_softmax(logits.view(logits.size(0), logits.size(1), V // S, S), -1).view_as(logits)
+        return _FstLoss.apply(lp, lens, num, den, _lib.NORM_NONE, 0)
+    return _FstLoss.apply(logits, lens, num, den, mode, num_symbols)
 
 
 def _labels_to_batch(labels, label_lens):
@@ -155,11 +166,21 @@ class FSTLossMixin(object):
     ``self.num_symbols`` as the reference's ``__init__`` sets them (:403-411).
     """
 
-    def logits(self, encoded, encoded_lens=None, extra_ret=None):
-        # the normalisation of advanced_decoder.py:448-451 is fused into the loss kernel
+    def _raw_logits(self, encoded, extra_ret=None):
         logits = self.fc(encoded)
         if extra_ret is not None:
             extra_ret["unnormed_logits"] = logits
+        return logits
+
+    def logits(self, encoded, encoded_lens=None, extra_ret=None):
+        """advanced_decoder.py:444-452: normalised scores whenever ``normalize_by_dim`` is set (what
+        ctc_forward.py:93 dumps and ``decode`` returns).  The training path does not come through
+        here: ``forward`` hands the raw ``fc`` output to the loss kernel, which fuses the
+        normalisation."""
+        logits = self._raw_logits(encoded, extra_ret)
+        if self.normalize_by_dim is not None:
+            logits = get_normalized_acts(logits, encoded_lens, self.num_symbols, self.context_order,
+                                         self.normalize_by_dim, normalize_logits=True)
         return logits
 
     def get_fst_loss(self, logits, encoded_lens, texts, text_lens, other_data_in_batch):
@@ -173,11 +194,12 @@ class FSTLossMixin(object):
         if self.denominator_red != "none":
             assert self.denominator_red in ("logsumexp", "logsumexp_fwb", "logsumexp_autodiff")
             den = gg.get_decoding_graph()
-        return _FstLoss.apply(logits, _check_lens(encoded_lens), num, den,
-                              _norm_mode(self.normalize_by_dim), int(self.num_symbols or 0))
+        # (the normalisations are idempotent: logits that went through self.logits() give the same loss)
+        return _fst_loss(logits, _check_lens(encoded_lens), num, den,
+                         _norm_mode(self.normalize_by_dim), int(self.num_symbols or 0))
 
     def forward(self, encoded, encoded_lens, texts, text_lens, spkids=None, **other_data_in_batch):
-        logits = self.logits(encoded, encoded_lens)
+        logits = self._raw_logits(encoded)
         fst_loss_ = self.get_fst_loss(logits, encoded_lens, texts, text_lens, other_data_in_batch).sum()
         return {"fst_loss": fst_loss_, "loss": fst_loss_}
 
@@ -189,10 +211,10 @@ class FSTLossMixin(object):
         (tropical reduction on the device), then the collapse of its frame labels to symbols by
         walking the topology rule (:556-571 does it with OpenFst compose + shortestpath)."""
         from . import _lib
-        logits = self.logits(encoded, encoded_lens)
+        logits = self.logits(encoded, encoded_lens)      # normalised, as the reference decodes and returns them
         gg = self.graph_generator
         lens = _check_lens(encoded_lens)
-        _, frame_labels = _lib.viterbi(logits.detach(), lens, gg.get_decoding_graph())
+        _, frame_labels = _lib.viterbi(logits.detach().contiguous(), lens, gg.get_decoding_graph())
         frame_labels = frame_labels.cpu()
         decoded_texts = [gg.collapse(frame_labels[:lens[i], i]) for i in range(logits.size(1))]
         ret = {"decoded": decoded_texts, "logits": logits}

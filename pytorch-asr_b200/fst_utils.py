@@ -15,6 +15,9 @@ runs in its C++ graph compiler (no OpenFst).  No CPU fallback.
 """
 from __future__ import annotations
 
+import collections
+import weakref
+
 import numpy as np
 import torch
 
@@ -41,14 +44,24 @@ class PackedGraphs(list):
         return batch_training_graph_matrices(mats, self.nc_weight, device=device)
 
 
+class TaggedMatrices(list):
+    """The reference's 4/8 padded matrices of a graph, carrying the CSR handle they were exported
+    from: ``path_reduction`` / ``fst_loss`` on them use the handle (no re-import, no upload, and
+    the bi-char decoding graph keeps its factorised kernels)."""
+
+    def __init__(self, mats, graph=None):
+        super(TaggedMatrices, self).__init__(mats)
+        self._ctcg_graph = graph
+
+
 def padded_matrices(graph, index=0, nc_weight=-1e20, for_forward_only=False, device="cpu"):
-    """The reference's 4/8-tuple for one graph (``fst_to_matrices`` encoding)."""
+    """The reference's 4/8 matrices for one graph (``fst_to_matrices`` encoding)."""
     mats = [torch.from_numpy(m) for m in graph.export_padded(index, False, nc_weight)]
     if not for_forward_only:
         mats += [torch.from_numpy(m) for m in graph.export_padded(index, True, nc_weight)]
     if device is not None and str(device) != "cpu":
         mats = [m.to(device) for m in mats]
-    return tuple(mats)
+    return TaggedMatrices(mats, graph if graph.num_graphs == 1 else None)
 
 
 def batch_training_graph_matrices(matrices, nc_weight=-1e20, device="cpu"):
@@ -78,7 +91,17 @@ def make_full_ngram_table(context_order, num_symbols, num_classes):
     return num_symbols, num_classes, ngram_to_class
 
 
+# Shared graphs in the reference's padded format (leading dimension 1: the decoding matrices a graph
+# generator builds once and hands out every step, advanced_decoder.py:497-500) are converted once and
+# found again by the identity of their tensors -- also after the caller's ``[m.to(device) for m in ...]``
+# dropped a TaggedMatrices tag, because ``.to`` returns the same tensor when nothing changes.
+_SHARED_CACHE = collections.OrderedDict()
+_SHARED_CACHE_SIZE = 8
+import_count = 0  # imports of padded matrices into CSR (tests assert that a shared graph is imported once)
+
+
 def _as_graph(graph_matrices, nc_weight=-1e20):
+    global import_count
     if isinstance(graph_matrices, Graph):
         return graph_matrices
     if isinstance(graph_matrices, PackedGraphs):
@@ -88,7 +111,20 @@ def _as_graph(graph_matrices, nc_weight=-1e20):
         return g
     assert len(graph_matrices) in (4, 8)
     assert all(sm.size(0) == graph_matrices[0].size(0) for sm in graph_matrices)
-    return Graph.from_padded(graph_matrices, nc_weight)
+    shared = torch.is_tensor(graph_matrices[0]) and graph_matrices[0].size(0) == 1
+    if shared:
+        key = tuple(id(m) for m in graph_matrices[:4])
+        ent = _SHARED_CACHE.get(key)
+        if ent is not None and all(r() is m for r, m in zip(ent[0], graph_matrices[:4])):
+            _SHARED_CACHE.move_to_end(key)
+            return ent[1]
+    g = Graph.from_padded(graph_matrices, nc_weight)
+    import_count += 1
+    if shared:
+        _SHARED_CACHE[key] = ([weakref.ref(m) for m in graph_matrices[:4]], g)
+        while len(_SHARED_CACHE) > _SHARED_CACHE_SIZE:
+            _SHARED_CACHE.popitem(last=False)
+    return g
 
 
 class _PathLogSumExp(torch.autograd.Function):
@@ -103,7 +139,9 @@ class _PathLogSumExp(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, grad_output):
-        return grad_output[None, :, None] * ctx.grads, None, None
+        g = ctx.grads
+        ctx.grads = None  # single backward, like the reference's ctx.grads (fst_utils.py:473,484)
+        return _lib.scale_grad(g, grad_output), None, None
 
 
 class _PathViterbi(torch.autograd.Function):
@@ -239,11 +277,56 @@ class BaseGraphGen(object):
         self.ngrams = ngram_to_class.tolist()
         self.grammar_fst_path = None
         self.nc_weight = nc_weight
-        self.decoding_fst = self.get_decoding_fst()
+        self._dec = self.get_decoding_fst()    # native CSR handle
+        self._dec_fst = None                   # pywrapfst view of it, built on first use (decoding_fst)
         self.decoding_mats = {}
         self.for_forward_only = for_forward_only
 
     # -- graphs ----------------------------------------------------------
+    @property
+    def decoding_fst(self):
+        """What the reference keeps here is an OpenFst object (``FSTDecoder.__init__`` arc-maps and
+        arc-sorts it, advanced_decoder.py:420-424).  Where ``pywrapfst`` is importable -- any
+        environment the reference itself runs in -- this is a real FST with the same states, arcs
+        (ilabel = class + 1, olabel = emitted symbol, weight One) and arc order as
+        ``build_ctc_*_decoding_fst`` (fst_utils.py:679-835), built from the native graph on first
+        use; without OpenFst it is the native handle.  The loss never looks at it."""
+        if self._dec_fst is None:
+            self._dec_fst = self._to_openfst()
+            if self._dec_fst is None:
+                self._dec_fst = self._dec
+        return self._dec_fst
+
+    def _to_openfst(self, arc_type="log"):
+        try:
+            import pywrapfst as fst
+        except ImportError:
+            return None
+        S, order = self.num_symbols, self.context_order
+        args = self._build_args()
+        rep = bool(args.get("loop_using_symbol_repetitions", False))
+        succ, labels, weights, _ = self._dec.export_padded(0, True, self.nc_weight)
+        f = fst.Fst(arc_type=arc_type)
+        one = fst.Weight.One(f.weight_type())
+        n = succ.shape[0]
+        for st in range(n):
+            assert f.add_state() == st
+            f.set_final(st)
+        f.set_start(0)
+        for src in range(n):
+            for k in range(succ.shape[1]):
+                if not weights[src, k] > 0.5 * self.nc_weight:
+                    continue
+                dst, cls = int(succ[src, k]), int(labels[src, k])
+                if order == 1:
+                    out = 0 if dst == src else dst
+                else:
+                    l1, l2 = src % S, dst % S
+                    out = 0 if (l2 == 0 or dst == src or (rep and l1 == l2)) else l2
+                f.add_arc(src, fst.Arc(cls + 1, out, one, dst))
+        f.arcsort("olabel")
+        return f
+
     def get_decoding_fst(self):
         return self.get_hc_fst()
 
@@ -284,13 +367,13 @@ class BaseGraphGen(object):
         key = str(device)
         ret = self.decoding_mats.get(key)
         if ret is None:
-            ret = [m.unsqueeze(0) for m in padded_matrices(
-                self.decoding_fst, 0, self.nc_weight, self.for_forward_only, device)]
+            ret = TaggedMatrices([m.unsqueeze(0) for m in padded_matrices(
+                self._dec, 0, self.nc_weight, self.for_forward_only, device)], self._dec)
             self.decoding_mats[key] = ret
         return ret
 
     def get_decoding_graph(self):
-        return self.decoding_fst
+        return self._dec
 
     def collapse(self, frame_labels):
         """Emitted symbols of the path that reads ``frame_labels`` (class ids) in the decoding graph."""

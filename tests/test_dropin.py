@@ -1,0 +1,113 @@
+"""The drop-in routes of INTEGRATION.md against the reference's own classes (CPU; needs
+``/root/reference``, skipped where it is absent -- the GPU box).
+
+Route 1: ``class FSTDecoderB200(P.FSTLossMixin, advanced_decoder.FSTDecoder)`` must construct with the
+reference's ``__init__`` (which arc-maps ``graph_generator.decoding_fst`` through pywrapfst), resolve
+``forward / logits / get_fst_loss / decode`` to the mixin, return the reference's normalised
+``logits()`` and fail loudly -- not fall back -- when there is no CUDA device.
+Route 2: padded matrices handed back to ``path_reduction`` keep or regain their native graph.
+"""
+import importlib
+import sys
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import graphs, ref_loader
+
+needs_ref = pytest.mark.skipif(not ref_loader.available(), reason="reference tree not present")
+
+
+def _reference_decoder_module():
+    ref_loader.load()
+    if "tensorboardX" not in sys.modules:      # logger dependency of the decoder module, off-path
+        tb = types.ModuleType("tensorboardX")
+        tb.SummaryWriter = type("SummaryWriter", (), {})
+        sys.modules["tensorboardX"] = tb
+    import builtins
+    if not hasattr(builtins, "unicode"):       # py2-era builtin used by att_speech/utils.py:74
+        builtins.unicode = str
+    return importlib.import_module("att_speech.modules.decoders.advanced_decoder")
+
+
+@needs_ref
+@pytest.mark.parametrize("order,args", [(1, {}), (2, {}), (2, {"use_contextual_blanks": True}),
+                                        (2, {"loop_using_symbol_repetitions": True})])
+def test_decoding_fst_is_the_reference_fst(lib_built, order, args):
+    """``CTCGraphGen.decoding_fst`` rebuilt through pywrapfst (here: the oracle's stand-in) state for
+    state and arc for arc equal to what the reference's builder makes."""
+    P = lib_built
+    fu, _ = ref_loader.load()
+    S = 5
+    gen = P.CTCGraphGen(context_order=order, graph_build_args=args, num_symbols=S)
+    mine = gen.decoding_fst
+    want = (fu.build_ctc_mono_decoding_fst(S) if order == 1 else fu.build_ctc_bigram_decoding_fst(S, **args))
+    assert mine.num_states() == want.num_states() and mine.start() == want.start() == 0
+
+    def arcs(f):
+        return sorted((s, a.ilabel, a.olabel, a.nextstate) for s in f.states() for a in f.arcs(s))
+    assert arcs(mine) == arcs(want)
+
+
+@needs_ref
+def test_mixin_composes_with_the_reference_decoder(lib_built):
+    P = lib_built
+    ad = _reference_decoder_module()
+    fu, _ = ref_loader.load()
+    fu.CTCGraphGenB200 = P.CTCGraphGen          # INTEGRATION.md route 1: the one line added to att_speech/fst_utils.py
+
+    class FSTDecoderB200(P.FSTLossMixin, ad.FSTDecoder):
+        pass
+
+    S, H = 6, 8
+    vocab = [str(i) for i in range(S)]
+    kw = dict(sample_batch={"features": torch.zeros(3, 2, H)}, num_classes=S * S,
+              graph_generator=dict(class_name="CTCGraphGenB200", context_order=2, graph_build_args={}),
+              normalize_by_dim=0, vocabulary=vocab)
+    torch.manual_seed(3)
+    ad.Globals.cuda = False                     # the reference's global device switch (no GPU in this container)
+    dec = FSTDecoderB200(**kw).eval()           # (in training mode the reference's LutLinear writes to its global logger)
+    for name in ("forward", "logits", "get_fst_loss", "decode"):
+        assert getattr(FSTDecoderB200, name) is getattr(P.FSTLossMixin, name)
+    assert isinstance(dec.graph_generator, P.CTCGraphGen) and dec.dec_fst is not None
+    # logits(): the reference's semantics (normalised) with the reference's own fc
+    enc = torch.randn(7, 2, H)
+    extra = {}
+    got = dec.logits(enc, torch.tensor([7, 5]), extra)
+    want = ad.FSTDecoder.logits(dec, enc, torch.tensor([7, 5]))
+    assert torch.allclose(got, want, atol=1e-6)
+    assert torch.allclose(got.exp().sum(-1), torch.ones(7, 2), atol=1e-5)
+    assert torch.equal(extra["unnormed_logits"], dec.fc(enc))
+    # no CPU path: the loss refuses CPU tensors instead of computing something else
+    texts = torch.tensor([[1, 2], [3, 0]])
+    with pytest.raises(RuntimeError):
+        dec.forward(enc, torch.tensor([7, 5]), texts, torch.tensor([2, 1]))
+
+
+def test_padded_matrices_carry_their_graph_and_shared_graphs_are_imported_once(lib_built):
+    P = lib_built
+    fu = P.fst_utils if hasattr(P, "fst_utils") else importlib.import_module(P.CTCGraphGen.__module__)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=7)
+    mats = gen.get_decoding_matrices()
+    assert fu._as_graph(mats) is gen.get_decoding_graph()            # tagged: no import at all
+    before = fu.import_count
+    plain = [m.to("cpu") for m in mats]                              # what FSTDecoder does (:458): the tag is gone
+    g1 = fu._as_graph(plain)
+    g2 = fu._as_graph([m.to("cpu") for m in mats])                   # next step: same tensors, new list
+    assert g1 is g2 and fu.import_count == before + 1
+    assert g1.info().structured == 1                                 # recognised: factorised kernels
+    # a different graph in tensors of the same shape is not confused with it
+    other = [m.clone() for m in P.CTCGraphGen(context_order=2, graph_build_args={"use_contextual_blanks": True},
+                                              num_symbols=7).get_decoding_matrices()]
+    g3 = fu._as_graph(other)
+    assert g3 is not g1 and fu.import_count == before + 2
+    # per-utterance numerator matrices (leading dimension B) are converted every time, never cached
+    num = gen.get_training_matrices_batch(torch.tensor([[1, 2, 3], [4, 4, 0]]), torch.tensor([3, 2]))
+    assert fu._as_graph(num) is not fu._as_graph(num)
+    # a weighted graph is not mistaken for the bi-char topology
+    ogen = graphs.GraphGen(2, 7, {})
+    dm = [np.array(m, copy=True) for m in ogen.get_decoding_matrices()]
+    dm[2][0, 3, 0] = -0.5
+    assert P.Graph.from_padded([torch.as_tensor(m) for m in dm]).info().structured == 0

@@ -280,14 +280,17 @@ def test_all_row_alignments_and_vector_paths_match_fp64_oracle(P):
                                     (11, {"allow_nonblank_selfloops": False})])
 def test_fused_bichar_kernel_equals_generic_csr_kernel(P, S, args):
     """The factorised bi-char denominator kernel against the generic CSR kernel on the same
-    decoding graph (imported arc by arc through the reference's padded matrices, which drops
-    the topology tag and with it the fused route)."""
+    decoding graph (imported arc by arc through the reference's padded matrices; the import recognises
+    the topology, ``set_generic`` drops the tag and with it the fused route)."""
     T, B = 64, 3
     logits, lens, seqs = _random_case(2, S, args, T, B, seed=77 + S)
     gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
     den = gen.get_decoding_graph()
     mats = den.export_padded(0, out_edges=False) + den.export_padded(0, out_edges=True)
     generic = P.Graph.from_padded([torch.as_tensor(m)[None] for m in mats])
+    assert generic.info().structured == 1          # the re-imported decoding graph is recognised ...
+    generic.set_generic()                          # ... and is sent to the generic kernel on request
+    assert generic.info().structured == 0
     x = torch.from_numpy(logits).cuda()
     c_fused, g_fused = P._lib.path_sum(x, lens, den)
     c_gen, g_gen = P._lib.path_sum(x, lens, generic)
@@ -470,3 +473,89 @@ def test_decode_returns_the_transcript_on_peaked_logits(P, order):
     assert ret["decoded"] == seqs
     assert torch.isfinite(ret["loss"]["loss"]).item()
 
+
+
+def test_path_reduction_on_decoding_matrices_takes_the_factorised_kernels_and_imports_once(P):
+    """Boundary route 2: ``path_reduction`` rebound into the reference, fed with
+    ``graph_generator.get_decoding_matrices(device)`` every step (advanced_decoder.py:497-500)."""
+    import importlib
+    fu = importlib.import_module(P.CTCGraphGen.__module__)
+    S, T, B = 12, 40, 3
+    logits, lens, seqs = _random_case(2, S, {}, T, B, seed=61)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S)
+    x = torch.from_numpy(logits).cuda()
+    mats = gen.get_decoding_matrices(x.device)
+    plain = [m.to(x.device) for m in mats]               # the reference's own copy loop (:458): plain list, same tensors
+    before = fu.import_count
+    want, wgrad, _ = engine.path_logsumexp(torch.from_numpy(logits), lens, graphs.GraphGen(2, S, {}).get_decoding_matrices(),
+                                           dtype=torch.float64)
+    for step in range(2):
+        xs = x.clone().requires_grad_(True)
+        P._lib.profile(True)
+        cost = P.path_reduction(xs, torch.tensor(lens), [m.to(x.device) for m in plain])
+        cost.sum().backward()
+        torch.cuda.synchronize()
+        names = [n for n, _ in P._lib.profile_collect()]
+        P._lib.profile(False)
+        assert "bisweep" in names and not any(n.startswith("path_fwd_bwd") for n in names)
+        assert _rel(cost.detach().cpu(), want) < LOSS_RTOL
+        assert (xs.grad.cpu().double() - wgrad).abs().max().item() < GRAD_ATOL
+    assert fu.import_count == before + 1                  # converted once, found again by tensor identity
+    xs = x.clone().requires_grad_(True)                   # the tagged list needs no import at all
+    P.path_reduction(xs, torch.tensor(lens), mats).sum().backward()
+    assert fu.import_count == before + 1
+
+
+@pytest.mark.parametrize("nbd", [None, 0, 1])
+def test_logits_and_decode_follow_the_reference_normalisation(P, nbd):
+    """``FSTDecoder.logits`` returns normalised scores when ``normalize_by_dim`` is set
+    (advanced_decoder.py:444-452) and ``decode`` finds the best path on those (:536-554)."""
+    S, T, B = 8, 30, 2
+    args = {"use_contextual_blanks": True}
+    logits, lens, seqs = _random_case(2, S, args, T, B, seed=88)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
+    head = P.FSTLoss(gen, normalize_by_dim=nbd, denominator_red="none" if nbd is not None else "logsumexp")
+    x = torch.from_numpy(logits).cuda()
+    got = head.logits(x, torch.tensor(lens))
+    want = engine.normalized_acts(torch.from_numpy(logits).double(), S, 2, nbd) if nbd is not None \
+        else torch.from_numpy(logits).double()
+    assert (got.cpu().double() - want).abs().max().item() < 1e-5
+    ret = head.decode(x, torch.tensor(lens))
+    assert (ret["logits"].cpu().double() - want).abs().max().item() < 1e-5
+    ogen = graphs.GraphGen(2, S, args)
+    _, want_labels = engine.path_viterbi(want, lens, ogen.get_decoding_matrices(), dtype=torch.float64)
+    for b, n in enumerate(lens):
+        assert ret["decoded"][b] == graphs.collapse_by_arc_table(ogen.decoding_graph, want_labels[:n, b].tolist())
+
+
+def test_context_normalisation_together_with_a_denominator(P):
+    """normalize_by_dim=1 with denominator_red='logsumexp' (the reference allows any combination:
+    ctc_losses.py:29-43 feeding advanced_decoder.py:497-500)."""
+    S, T, B = 9, 50, 3
+    args = {"use_contextual_blanks": True}
+    logits, lens, seqs = _random_case(2, S, args, T, B, seed=123)
+    want_loss, want_grad = _oracle(2, S, args, logits, lens, seqs, True, 1)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
+    loss, grad = _run_fused(P, logits, lens, gen.get_training_graphs(seqs), gen.get_decoding_graph(), 1, S)
+    assert _rel(loss, want_loss.numpy()) < LOSS_RTOL
+    assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
+
+
+def test_per_utterance_grad_output_scales_rows_on_the_device(P):
+    """``PathLogSumExp.backward`` (fst_utils.py:482-485): grad_output[b] * grads; the all-ones case of
+    ``.sum().backward()`` must not touch the gradient (ctcg_scale_grad skips rows with factor 1)."""
+    S, T, B = 10, 40, 4
+    logits, lens, seqs = _random_case(2, S, {}, T, B, seed=321)
+    wl, wg = _oracle(2, S, {}, logits, lens, seqs, True, None)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S)
+    num, den = gen.get_training_graphs(seqs), gen.get_decoding_graph()
+    w = torch.tensor([1.0, -2.0, 0.25, 1.0])
+    x = torch.from_numpy(logits).cuda().requires_grad_(True)
+    (P.fst_loss(x, lens, num, den) * w.cuda()).sum().backward()
+    assert np.abs(x.grad.cpu().double().numpy() - wg.numpy() * w.numpy()[None, :, None]).max() < 2 * GRAD_ATOL
+    g = torch.from_numpy(wg.numpy()).float().cuda()
+    keep = g.clone()
+    P._lib.scale_grad(g, torch.ones(B, device="cuda").sum().expand(B) / B)      # broadcast scalar 1.0 (stride 0)
+    assert torch.equal(g, keep)
+    P._lib.scale_grad(g, torch.tensor(3.0, device="cuda").expand(B))
+    assert torch.allclose(g, keep * 3)
