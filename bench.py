@@ -1,13 +1,16 @@
 """Benchmark of the CTC / CTC-G loss+grad hot path (BASELINE.json's metric).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3]
-    python bench.py --impl reference ...       # the CPU implementation of the same path
+    python bench.py --workload cfg5 --scaling strong [--T 800]     # B=2048 in total, striped over the ranks
+    python bench.py --impl reference ...                           # the CPU implementation of the same path
 
-One "step" = one fused loss+grad call (``ctcg_loss_fwd_bwd`` through the C ABI)
-over one synthetic WSJ-shaped batch.  ``value`` = utterance-frames/s with the
-inputs resident in HBM; ``e2e`` = the same metric through the public Python API
-with pinned HOST logits (H2D copy of logits, graph compile + upload from
-labels, D2H read of the loss inside the timed region).  Prints ONE JSON line.
+One "step" = one loss+grad over one synthetic WSJ-shaped batch through the public API, exactly what a
+trainer runs: ``P.fst_loss(logits, ...).sum().backward()`` (one ``ctcg_loss_fwd_bwd`` through the C ABI
+plus ``ctcg_scale_grad`` in backward).  ``value`` = utterance-frames/s with the inputs resident in HBM;
+``e2e`` = the same metric with pinned HOST logits (H2D copy of the logits, graph compile + upload from
+the labels, D2H read of the loss inside the timed region); ``e2e_host`` = the C entry point for host
+buffers (``ctcg_loss_host``), gradient copied back too.  ``roofline.frac`` is the WHOLE STEP:
+8*V*sum(len) bytes / ms_per_step / measured HBM peak.  Prints ONE JSON line.
 """
 from __future__ import annotations
 
@@ -26,7 +29,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-# name -> (variant, S, B per GPU, T, graph_build_args, normalize_by_dim, use_den)
+# name -> (variant, order, S, B per GPU, T, graph_build_args, normalize_by_dim, use_den)
 WORKLOADS = {
     "cfg1": ("mono-char CTC", 1, 49, 16, 400, {}, 0, False),
     "cfg2": ("bi-char CTC", 2, 49, 64, 400, {}, 0, False),
@@ -35,24 +38,35 @@ WORKLOADS = {
     "cfg4": ("CTC-GB contextual blanks", 2, 49, 256, 800, {"use_contextual_blanks": True}, None, True),
     "cfg5": ("CTC-G sweep shard", 2, 49, 256, 800, {}, None, True),
 }
-# dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full, profiles/r01_e_ncu_full_summary.md)
-NCU_TRAFFIC = {("cfg3", "bisweep"): 402519296, ("cfg3", "bicombine"): 448670208, ("cfg3", "num_sweep"): 9504512,
-               ("cfg3", "num_combine"): 203017216}
 CFG_INDEX = {"cfg1": 1, "cfg2": 2, "cfg2s": 2, "cfg3": 3, "cfg4": 4, "cfg5": 5}
+STRONG_TOTAL_B = 2048          # BASELINE.json configs[4]: B=2048 in total, T in {400, 800, 1600}
+TRAFFIC_JSON = os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")   # written by profiles/ncu_traffic.py
 
 
-def make_batch(workload, rank=0):
-    """Seeded synthetic batch of SURVEY 8(d): logits ~ 3*N(0,1), lens[0]=T, others
-    uniform in [0.6T, T] sorted descending, U_b = len_b // 4 labels in 1..S-1."""
+def make_batch(workload, rank=0, world=1, scaling="weak", T_override=None):
+    """Seeded synthetic batch of SURVEY 8(d): logits ~ 3*N(0,1), lens[0]=T, others uniform in
+    [0.6T, T] sorted descending, U_b = len_b // 4 labels in 1..S-1.  ``strong``: one batch of
+    STRONG_TOTAL_B utterances for the whole job, utterance i -> rank i mod world."""
     name, order, S, B, T, args, nbd, use_den = WORKLOADS[workload]
-    seed = 1000 + CFG_INDEX[workload] + 7919 * rank
-    rng = np.random.default_rng(seed)
-    lens = sorted([T] + rng.integers(int(0.6 * T), T + 1, size=B - 1).tolist(), reverse=True)
-    seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens]
-    g = torch.Generator().manual_seed(seed)
+    if T_override:
+        T = int(T_override)
     V = S ** order
+    if scaling == "strong":
+        seed = 1000 + CFG_INDEX[workload]
+        rng = np.random.default_rng(seed)
+        total = STRONG_TOTAL_B
+        lens_all = sorted([T] + rng.integers(int(0.6 * T), T + 1, size=total - 1).tolist(), reverse=True)
+        seqs_all = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens_all]
+        lens, seqs = lens_all[rank::world], seqs_all[rank::world]
+        B = len(lens)
+        T = lens[0]                      # this rank's longest utterance
+    else:
+        seed = 1000 + CFG_INDEX[workload] + 7919 * rank
+        rng = np.random.default_rng(seed)
+        lens = sorted([T] + rng.integers(int(0.6 * T), T + 1, size=B - 1).tolist(), reverse=True)
+        seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens]
     return dict(name=name, order=order, S=S, B=B, T=T, V=V, args=args, nbd=nbd, use_den=use_den,
-                lens=lens, seqs=seqs, gen=g, seed=seed)
+                lens=lens, seqs=seqs, seed=seed + 7919 * rank, scaling=scaling)
 
 
 class ClockSampler(object):
@@ -141,9 +155,33 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
 
 
-def cpu_path_time(batch, sample_b, threads, repeats=1):
-    """Time the oracle's torch-CPU restatement of the reference path (fp32) on the
-    first ``sample_b`` utterances of the batch; returns (seconds, frames)."""
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of every kernel of the step, from the ncu
+    --set full capture committed under profiles/ (profiles/ncu_traffic.py writes the file, with the commit
+    it was taken at); None when the workload has no capture."""
+    try:
+        with open(TRAFFIC_JSON) as f:
+            d = json.load(f)
+        ent = d["workloads"].get(workload)
+        if not ent:
+            return None, None
+        return {k: int(v) for k, v in ent.items()}, d.get("commit")
+    except Exception:
+        return None, None
+
+
+def cpu_sample_size(batch):
+    """BASELINE.md section 3: the CTC-G / CTC-GB CPU path is timed on a slice of the batch (B=8 at T=400;
+    fewer utterances for the long ones so that one pass stays near ten seconds) and scaled linearly."""
+    if not batch["use_den"]:
+        return min(batch["B"], 16)
+    return max(1, min(batch["B"], 8 * 400 // max(batch["T"], 400)))
+
+
+def cpu_path_time(batch, sample_b, threads):
+    """One pass of the oracle's torch-CPU restatement of the reference path (fp32: get_normalized_acts,
+    the max-shift / numerator - denominator glue, path_reduction forward and backward) on the first
+    ``sample_b`` utterances of the batch; returns (seconds, frames)."""
     from oracle import engine, graphs
     torch.set_num_threads(threads)
     S, order = batch["S"], batch["order"]
@@ -158,66 +196,72 @@ def cpu_path_time(batch, sample_b, threads, repeats=1):
     dm = ogen.get_decoding_matrices() if batch["use_den"] else None
     g = torch.Generator().manual_seed(batch["seed"])
     logits = torch.randn(lens[0], sample_b, batch["V"], generator=g) * 3
-    best = None
-    for _ in range(repeats):
-        t0 = time.perf_counter()
-        engine.fst_loss(logits, lens, nm, dm, batch["nbd"], S, order, dtype=torch.float32)
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    return best, int(sum(lens))
+    t0 = time.perf_counter()
+    engine.fst_loss(logits, lens, nm, dm, batch["nbd"], S, order, dtype=torch.float32)
+    return time.perf_counter() - t0, int(sum(lens))
+
+
+def cpu_baseline(batch, passes=3, budget_s=150.0):
+    """The ONE protocol both arms report: 1 warm-up pass + best of ``passes``."""
+    threads = os.cpu_count() or 1
+    sample_b = cpu_sample_size(batch)
+    t_start = time.perf_counter()
+    cpu_path_time(batch, sample_b, threads)                 # warm-up (allocator, thread pool, graph build)
+    times, frames = [], 0
+    for _ in range(max(passes, 1)):
+        dt, frames = cpu_path_time(batch, sample_b, threads)
+        times.append(dt)
+        if time.perf_counter() - t_start > budget_s:
+            break
+    best = min(times)
+    return {"value": frames / best, "unit": "utterance-frames/s", "cores": threads, "kind": "port",
+            "sample": "first %d of %d utterances (T=%d, V=%d), fp32 torch-CPU restatement of the reference path, "
+                      "1 warm-up + best of %d passes (%.2f s), per-utterance cost scales linearly to the batch"
+                      % (sample_b, batch["B"], batch["T"], batch["V"], len(times), best),
+            "pass_seconds": [round(t, 3) for t in times]}
+
+
+def workload_config(workload, batch, n_gpus):
+    tb = 2 * batch["T"] * batch["B"] * batch["V"] * 4
+    cfg = {"workload": "%s: %s, B=%d per GPU, T=%d, V=%d (S=%d), U=len/4, lens in [0.6T,T]" % (
+               workload, batch["name"], batch["B"], batch["T"], batch["V"], batch["S"]),
+           "global_batch": batch["B"] * n_gpus if batch["scaling"] == "weak" else STRONG_TOTAL_B,
+           "frames_per_step_per_gpu": int(sum(batch["lens"])),
+           "parallelism": "utterance-sharded dp%d" % n_gpus,
+           "l2": ("logits+grad per step (%.0f MB) exceed the 126 MB L2; input buffers rotated" if tb > 126e6 else
+                  "logits+grad per step (%.0f MB) fit the 126 MB L2 (parity-size workload, not the bench "
+                  "configuration); input buffers rotated") % (tb / 1e6)}
+    if batch["scaling"] == "strong":
+        cfg["workload"] = "%s strong: %s, B=%d in total striped over %d GPU(s) (B=%d on rank 0), T=%d, V=%d" % (
+            workload, batch["name"], STRONG_TOTAL_B, n_gpus, batch["B"], batch["T"], batch["V"])
+    return cfg
 
 
 def run_reference(args):
     """--impl reference: the CPU implementation of the same path on the host cores.
 
-    The reference is pure Python on torch ops (no compiled sources to build into
-    oracle/_ref) and cannot travel to the GPU box, so the timed code is the
-    oracle's restatement of it (same tensor-op sequence, fp32, all host threads).
-    Each step is a bounded sample (the first ``sample_b`` utterances of the batch)."""
+    The reference is pure Python on torch ops (no compiled sources to build into oracle/_ref) and cannot
+    travel to the GPU box, so the timed code is the oracle's restatement of it (same tensor-op sequence,
+    fp32, all host threads); each step is one pass over a bounded sample of the workload.  Same protocol
+    and the same function as the ``cpu_baseline`` of the main line (1 warm-up + best pass)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    batch = make_batch(args.workload)
-    threads = os.cpu_count() or 1
-    sample_b = 2 if batch["use_den"] else min(batch["B"], 16)
-    if batch["use_den"] and batch["T"] > 400:
-        sample_b = 1
-    for _ in range(max(args.warmup, 0) and 1):
-        cpu_path_time(batch, sample_b, threads)
-    times, frames = [], 0
-    budget_s = float(os.environ.get("CTCG_REFERENCE_BUDGET_S", "120"))   # keep the arm within minutes
-    for _ in range(args.steps):
-        dt, frames = cpu_path_time(batch, sample_b, threads)
-        times.append(dt)
-        if sum(times) > budget_s:
-            break
-    total = sum(times)
-    value = frames * len(times) / total
-    sample = "first %d of %d utterances of %s, T=%d, V=%d, fp32" % (
-        sample_b, batch["B"], args.workload, batch["T"], batch["V"])
+    batch = make_batch(args.workload, 0, 1, "weak", args.T)
+    budget_s = float(os.environ.get("CTCG_REFERENCE_BUDGET_S", "150"))     # keep the arm within minutes
+    cb = cpu_baseline(batch, passes=max(1, min(args.steps, 20)), budget_s=budget_s)
+    n = len(cb["pass_seconds"])
+    best = min(cb["pass_seconds"])
     line = {
-        "impl": "reference", "metric": "CTC(-G) loss+grad utterance-frames/sec", "value": value,
-        "unit": "utterance-frames/s", "n_gpus": args.gpus, "steps": len(times), "steps_requested": args.steps,
-        "warmup": min(args.warmup, 1),
-        "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": "CTC(-G) loss+grad utterance-frames/sec", "value": cb["value"],
+        "unit": "utterance-frames/s", "n_gpus": args.gpus, "steps": n, "steps_requested": args.steps, "warmup": 1,
+        "ms_per_step": 1e3 * best, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.workload, batch, args.gpus),
-        "cpu_baseline": {"value": value, "unit": "utterance-frames/s", "cores": threads, "kind": "port",
-                         "sample": sample},
-        "e2e": {"value": value, "unit": "utterance-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": "utterance-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
-
-
-def workload_config(workload, batch, n_gpus):
-    return {"workload": "%s: %s, B=%d per GPU, T=%d, V=%d (S=%d), U=len/4, lens in [0.6T,T]" % (
-                workload, batch["name"], batch["B"], batch["T"], batch["V"], batch["S"]),
-            "global_batch": batch["B"] * n_gpus, "frames_per_step_per_gpu": int(sum(batch["lens"])),
-            "parallelism": "utterance-sharded dp%d" % n_gpus,
-            "l2": ("logits+grad per step (%.0f MB) exceed the 126 MB L2; 3 input buffers rotated"
-                   if 2 * batch["T"] * batch["B"] * batch["V"] * 4 > 126e6 else
-                   "logits+grad per step (%.0f MB) fit the 126 MB L2 (parity-size workload, not the bench "
-                   "configuration); 3 input buffers rotated") % (2 * batch["T"] * batch["B"] * batch["V"] * 4 / 1e6)}
 
 
 def run_ours(args):
@@ -227,7 +271,7 @@ def run_ours(args):
     rank, world, local = parallel.init_from_env()
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    batch = make_batch(args.workload, rank)
+    batch = make_batch(args.workload, rank, world, args.scaling, args.T)
     T, B, V, S = batch["T"], batch["B"], batch["V"], batch["S"]
     gen = P.CTCGraphGen(context_order=batch["order"], graph_build_args=batch["args"], num_symbols=S)
     num = gen.get_training_graphs(batch["seqs"])
@@ -235,17 +279,26 @@ def run_ours(args):
     mode = {None: P.NORM_NONE, 0: P.NORM_SOFTMAX}[batch["nbd"]]
     lens = batch["lens"]
     frames = int(sum(lens))
-    NBUF = 3
-    host = [(torch.randn(T, B, V, generator=batch["gen"]) * 3).pin_memory() for _ in range(NBUF)]
-    xs = [h.to(dev) for h in host]
-    ones = None
-
+    buf_bytes = T * B * V * 4
+    NBUF = 3 if buf_bytes <= (4 << 30) else (2 if buf_bytes <= (12 << 30) else 1)   # one 31 GB buffer is >> L2 too
+    host_ok = buf_bytes <= (2 << 30)          # pinned host copies (for the end-to-end legs) only at sane sizes
+    if host_ok:
+        g = torch.Generator().manual_seed(batch["seed"])
+        host = [(torch.randn(T, B, V, generator=g) * 3).pin_memory() for _ in range(NBUF)]
+        xs = [h.to(dev).requires_grad_(True) for h in host]
+    else:
+        g = torch.Generator(device=dev).manual_seed(batch["seed"])
+        host = None
+        xs = [(torch.randn(T, B, V, generator=g, device=dev) * 3).requires_grad_(True) for _ in range(NBUF)]
     meter = parallel.LossMeter(dev)
 
     def step(i):
-        # utterances are independent: no exchange per step; the logged scalar [sum loss, frames] is
-        # accumulated on the device and all-reduced once, at the end of the timed region
-        loss, grad = P._lib.loss_fwd_bwd(xs[i % NBUF], lens, num, den, mode, S, grad_scale=ones)
+        # What a trainer runs.  Utterances are independent: no exchange per step; the logged scalar
+        # [sum loss, frames] is accumulated on the device and all-reduced once per logging interval.
+        x = xs[i % NBUF]
+        x.grad = None
+        loss = P.fst_loss(x, lens, num, den, normalize_by_dim=batch["nbd"], num_symbols=S)
+        loss.sum().backward()
         if world > 1:
             meter.add(loss, frames)
         return loss
@@ -261,8 +314,8 @@ def run_ours(args):
         sampler.start()
     l0 = P._lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
     meter = parallel.LossMeter(dev)          # restart the running scalar for the timed steps
+    ev0.record()
     for i in range(args.steps):
         out = step(i)
     if world > 1:
@@ -272,45 +325,74 @@ def run_ours(args):
     parallel.barrier()
     launches = P._lib.launch_count() - l0
     if world == 1:
-        out = parallel.reduce_loss(out, frames)
+        out = parallel.reduce_loss(out.detach(), frames)
     else:
         out = total / args.steps
-    ms = ev0.elapsed_time(ev1)
-    ms = parallel.max_over_ranks(ms)
+    ms = parallel.max_over_ranks(ev0.elapsed_time(ev1))
     clocks = sampler.stop() if rank == 0 else None
     total_frames = parallel.sum_over_ranks(frames)
 
-    # ---- end to end through the public API with host buffers -------------------------------
-    def e2e_step(i):
-        x = host[i % NBUF].to(dev, non_blocking=True).requires_grad_(True)
-        g_num = gen.get_training_graphs(batch["seqs"])          # graph compile + upload from labels
-        loss = P.fst_loss(x, lens, g_num, den, normalize_by_dim=batch["nbd"], num_symbols=S)
-        tot = loss.sum()
-        tot.backward()
-        return float(tot.item()), x.grad                         # D2H read of the step's loss
-
+    # ---- the same steps straight through the C ABI (no autograd around the call) ----------------
+    xd = [x.detach() for x in xs]
+    for x in xs:
+        x.grad = None                        # the gradient of the last public-API step (memory at B=2048, T=1600)
     for i in range(min(args.warmup, 3)):
-        e2e_step(i)
-    parallel.barrier()
+        P._lib.loss_fwd_bwd(xd[i % NBUF], lens, num, den, mode, S)
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    e2e_steps = max(3, min(args.steps, 10))
-    for i in range(e2e_steps):
-        e2e_step(i)
+    ev0.record()
+    for i in range(args.steps):
+        P._lib.loss_fwd_bwd(xd[i % NBUF], lens, num, den, mode, S)
+    ev1.record()
     torch.cuda.synchronize()
-    e2e_s = parallel.max_over_ranks(time.perf_counter() - t0)
-    e2e_value = total_frames * e2e_steps / e2e_s
+    ms_cabi = parallel.max_over_ranks(ev0.elapsed_time(ev1))
+
+    # ---- end to end through the public API with host buffers -------------------------------
+    e2e = e2e_host = None
+    if host_ok:
+        def e2e_step(i):
+            x = host[i % NBUF].to(dev, non_blocking=True).requires_grad_(True)
+            g_num = gen.get_training_graphs(batch["seqs"])          # graph compile + upload from labels
+            loss = P.fst_loss(x, lens, g_num, den, normalize_by_dim=batch["nbd"], num_symbols=S)
+            tot = loss.sum()
+            tot.backward()
+            return float(tot.item()), x.grad                         # D2H read of the step's loss
+
+        for i in range(min(args.warmup, 3)):
+            e2e_step(i)
+        parallel.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e2e_steps = max(3, min(args.steps, 10))
+        for i in range(e2e_steps):
+            e2e_step(i)
+        torch.cuda.synchronize()
+        e2e_s = parallel.max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": total_frames * e2e_steps / e2e_s, "unit": "utterance-frames/s",
+               "h2d_bytes_per_step": int(buf_bytes + 4 * B), "d2h_bytes_per_step": 4, "steps": e2e_steps,
+               "includes": "H2D logits from pinned host, numerator graph compile+upload from labels, fused "
+                           "loss+grad (gradient stays on the device for the trainer's backprop), D2H loss"}
+        if rank == 0 and world == 1:
+            # the C entry point for host buffers: logits H2D, loss AND gradient D2H inside the call
+            gh, lh = torch.empty_like(host[0]).pin_memory(), torch.empty(B).pin_memory()
+            P._lib.loss_host(host[0], lens, num, den, mode, S, loss_out=lh, grad_out=gh)
+            t0 = time.perf_counter()
+            hsteps = 3
+            for i in range(hsteps):
+                P._lib.loss_host(host[i % NBUF], lens, num, den, mode, S, loss_out=lh, grad_out=gh)
+            dt = time.perf_counter() - t0
+            e2e_host = {"value": frames * hsteps / dt, "unit": "utterance-frames/s", "entry": "ctcg_loss_host",
+                        "h2d_bytes_per_step": int(buf_bytes + 4 * B), "d2h_bytes_per_step": int(buf_bytes + 4 * B),
+                        "steps": hsteps}
 
     # ---- per-kernel attribution (outside the timed regions) --------------------------------
     kern = {}
     nprof_steps = 10
     if rank == 0:
         P._lib.profile(True)
-        nprof = nprof_steps
-        for i in range(nprof):
-            P._lib.loss_fwd_bwd(xs[i % NBUF], lens, num, den, mode, S)
+        for i in range(nprof_steps):
+            P._lib.loss_fwd_bwd(xd[i % NBUF], lens, num, den, mode, S)
         for name, t in P._lib.profile_collect():
-            kern[name] = kern.get(name, 0.0) + t / nprof
+            kern[name] = kern.get(name, 0.0) + t / nprof_steps
         P._lib.profile(False)
 
     if rank != 0:
@@ -320,13 +402,9 @@ def run_ours(args):
     value = total_frames * args.steps / (ms * 1e-3)
     peak, peak_src = measured_peak()
     alg_bytes = 8.0 * V * frames                     # read V logits + write V gradients per valid frame
-    dom = max(kern, key=kern.get) if kern else None
     step_gbs = alg_bytes / (ms_per_step * 1e-3) / 1e9
-    # dominant kernel: one launch processes the whole batch (all `frames` utterance-frames)
-    dom_gbs = alg_bytes / (kern[dom] * 1e-3) / 1e9 if dom else step_gbs
-    # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-    # (profiles/r01_e_ncu_full_summary.md); only captured for the default workload
-    traffic = NCU_TRAFFIC.get((args.workload, dom))
+    dom = max(kern, key=kern.get) if kern else None
+    traffic_k, traffic_commit = ncu_traffic(args.workload if args.scaling == "weak" and not args.T else "-")
     # every kernel against the bytes it must move itself (fp32): the sweeps read the logits once per
     # direction, the combine reads them once and writes the gradient once, the row kernels of plain CTC
     # read + write once; the compact-column kernels of the numerator move far less than 8*V per frame
@@ -339,47 +417,51 @@ def run_ours(args):
             ent["own_algorithmic_bytes"] = own_bytes[k]
             ent["own_gbs"] = own_bytes[k] / (v * 1e-3) / 1e9
             ent["own_frac"] = ent["own_gbs"] / peak
-        tr = NCU_TRAFFIC.get((args.workload, k))
-        if tr:
-            ent["ncu_dram_bytes"] = tr
+        if traffic_k and k in traffic_k:
+            ent["ncu_dram_bytes"] = traffic_k[k]
         per_kernel[k] = ent
     if "bisweep" in kern:
-        conc = ("denominator (bisweep -> bicombine) on a side stream, concurrent with the numerator "
-                "(gather -> num_sweep -> num_combine) on the caller's stream; joined before the numerator subtracts its posteriors (num_combine) and final")
+        conc = ("gather on the caller's stream; then the denominator sweeps (bisweep) on a side stream next to the "
+                "numerator (num_sweep -> num_combine); the denominator's combine (bicombine) waits for both and "
+                "writes gamma_den - gamma_num in one store; final")
     else:
         conc = "single stream"
-    roof = {"bound": "hbm", "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak,
+    traffic = sum(traffic_k.values()) if traffic_k else None
+    roof = {"bound": "hbm", "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak,
             "traffic": traffic, "peak_source": peak_src,
-            "kernel": dom, "algorithmic_bytes_per_launch": alg_bytes,
-            "scope": "dominant kernel: algorithmic bytes of one launch (8*V*sum(len)) / its mean CUDA-event "
-                     "duration over %d steps run right after the timed region" % nprof_steps,
-            "kernel_ms": {k: round(v, 4) for k, v in kern.items()},
-            "per_kernel": per_kernel,
-            "dominant_kernel_share": (kern[dom] / sum(kern.values())) if kern else None,
-            "step_achieved": step_gbs, "step_frac": step_gbs / peak,
-            "concurrency": conc}
+            "algorithmic_bytes_per_step": alg_bytes,
+            "scope": "whole step: 8*V*sum(len) algorithmic bytes / ms_per_step (CUDA events around the timed steps); "
+                     "no single kernel does the 8*V work, so the step is the unit",
+            "traffic_scope": ("sum over the step's kernels of dram__bytes_read.sum + dram__bytes_write.sum per launch, "
+                              "ncu --set full at commit %s (profiles/r02_ncu_traffic.json)" % traffic_commit)
+            if traffic_k else "no ncu capture for this workload",
+            "traffic_over_algorithmic": (traffic / alg_bytes) if traffic else None,
+            "dominant_kernel": dom, "kernel_ms": {k: round(v, 4) for k, v in kern.items()},
+            "kernel_ms_scope": "mean CUDA-event duration per kernel on its own stream over %d steps run after the "
+                               "timed region (kernels of different streams overlap: they do not add up to the step)"
+                               % nprof_steps,
+            "per_kernel": per_kernel, "concurrency": conc}
     line = {
         "metric": "CTC(-G) loss+grad utterance-frames/sec", "value": value, "unit": "utterance-frames/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(args.workload, batch, world),
         "clocks": clocks, "gpu_launches": int(launches),
-        "e2e": {"value": e2e_value, "unit": "utterance-frames/s",
-                "h2d_bytes_per_step": int(T * B * V * 4 + 4 * B), "d2h_bytes_per_step": 4,
-                "steps": e2e_steps, "includes": "H2D logits from pinned host, numerator graph compile+upload "
-                "from labels, fused loss+grad, D2H loss"},
+        "timed_call": "P.fst_loss(x, lens, num, den).sum().backward() (public API; device-resident inputs)",
+        "c_abi_direct": {"ms_per_step": ms_cabi / args.steps,
+                         "value": total_frames * args.steps / (ms_cabi * 1e-3),
+                         "call": "ctcg_loss_fwd_bwd through ctypes, no autograd"},
+        "e2e": e2e if e2e else {"value": None, "unit": "utterance-frames/s", "h2d_bytes_per_step": 0,
+                                "d2h_bytes_per_step": 0,
+                                "skipped": "logits of this workload (%.1f GB per buffer) are generated on the "
+                                           "device; no pinned host copy" % (buf_bytes / 1e9)},
         "roofline": roof,
         "loss_per_frame": float(out[0]) / max(float(out[1]), 1.0),
     }
+    if e2e_host:
+        line["e2e_host"] = e2e_host
     if not args.no_cpu_baseline and world == 1:       # reported on rank 0 at N=1 only
-        threads = os.cpu_count() or 1
-        sample_b = 2 if batch["use_den"] else min(B, 16)
-        if batch["use_den"] and T > 400:
-            sample_b = 1
-        dt, fr = cpu_path_time(batch, sample_b, threads)
-        line["cpu_baseline"] = {"value": fr / dt, "unit": "utterance-frames/s", "cores": threads, "kind": "port",
-                                "sample": "first %d of %d utterances, one pass, fp32 torch-CPU restatement of "
-                                          "path_reduction (%.1f s)" % (sample_b, B, dt)}
+        line["cpu_baseline"] = cpu_baseline(make_batch(args.workload, 0, 1, "weak", args.T))
     print(json.dumps(line))
     parallel.finalize()
 
@@ -391,6 +473,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="strong: one batch of %d utterances striped over the ranks (BASELINE config 5)" % STRONG_TOTAL_B)
+    ap.add_argument("--T", type=int, default=None, help="override the workload's T (config 5: 400 / 800 / 1600)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

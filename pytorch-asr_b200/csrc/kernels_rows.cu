@@ -244,6 +244,7 @@ __global__ void __launch_bounds__(NT) final_kernel(int T, int B, const int32_t* 
 // loss.sum().backward() (grad_output = ones) costs a launch and no memory traffic.
 __global__ void __launch_bounds__(NT) scale_grad_kernel(float* __restrict__ grad, long long rows, int B, int V,
                                                         const float* __restrict__ scale, int stride) {
+  if (stride == 0 && scale[0] == 1.f) return;  // broadcast ones (.sum().backward()): one load per CTA
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
     const float sc = scale[(long long)(row % B) * stride];
     if (sc == 1.f) continue;

@@ -67,9 +67,9 @@ def reduce_loss(loss_per_utt, n_frames, blocking=True):
     stream: the caller's stream is not held up by the NCCL launch latency, and the
     result must be read after a device (or ``torch.cuda.current_stream().wait_stream``)
     synchronisation."""
-    buf = torch.zeros(2, dtype=torch.float64, device=loss_per_utt.device)
-    buf[0] = loss_per_utt.double().sum()
-    buf[1] = float(n_frames)
+    buf = torch.empty(2, dtype=torch.float64, device=loss_per_utt.device)
+    buf[0].copy_(loss_per_utt.sum(dtype=torch.float64))
+    buf[1].fill_(float(n_frames))       # kernels only: no host <-> device synchronisation
     if _group_active():
         if not blocking and buf.is_cuda:
             dev = buf.device
@@ -108,8 +108,15 @@ class LossMeter(object):
             self.pending = []
 
     def total(self):
+        """``[sum of losses, frames]`` over all ranks, on the device.  Nothing here waits for the GPU: the
+        buffer is filled by kernels (a ``torch.tensor(x, device=...)`` would be a synchronous copy that
+        stalls the host until every queued step has run, and the fold, the NCCL launch and the next step's
+        launches would then sit exposed behind it), so the collective is enqueued while the last steps are
+        still running."""
         self._fold()
-        buf = torch.stack([self.acc, torch.tensor(float(self.frames), dtype=torch.float64, device=self.acc.device)])
+        buf = torch.empty(2, dtype=torch.float64, device=self.acc.device)
+        buf[0].copy_(self.acc)
+        buf[1].fill_(float(self.frames))
         if _group_active():
             dist.all_reduce(buf, op=dist.ReduceOp.SUM)
         return buf
