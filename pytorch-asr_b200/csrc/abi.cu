@@ -157,7 +157,7 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
     g->dev_blob = nullptr;
   }
   std::vector<unsigned char> blob;
-  size_t o[18];
+  size_t o[20];
   append(&blob, g->state_off, &o[0]);
   append(&blob, g->lab_off, &o[1]);
   append(&blob, g->lab_list, &o[2]);
@@ -176,6 +176,8 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   append(&blob, g->lab_src, &o[15]);
   append(&blob, g->lab_dst, &o[16]);
   append(&blob, g->lab_w, &o[17]);
+  append(&blob, g->slab_ptr, &o[18]);
+  append(&blob, g->slab_state, &o[19]);
   // Stream-ordered allocation and a pinned staging ring: nothing here waits for work already
   // queued on the stream (e.g. the H2D copy of the logits), so graph upload overlaps it.
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -220,6 +222,8 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   v.lab_src = reinterpret_cast<const int32_t*>(p + o[15]);
   v.lab_dst = reinterpret_cast<const int32_t*>(p + o[16]);
   v.lab_w = reinterpret_cast<const float*>(p + o[17]);
+  v.slab_ptr = reinterpret_cast<const int32_t*>(p + o[18]);
+  v.slab_state = reinterpret_cast<const int32_t*>(p + o[19]);
   v.max_arcs = g->max_arcs;
   v.unit_weights = g->unit_weights;
   v.in_label_uniform = g->in_label_uniform;

@@ -45,6 +45,11 @@ struct GraphDev {
   const int32_t* lab_src;
   const int32_t* lab_dst;
   const float* lab_w;
+  // states grouped by the compact label on their in-arcs (graphs with in_label_uniform): graph g owns rows
+  // [lab_off[g]+g, lab_off[g+1]+g] of slab_ptr; entries index slab_state, whose values are state ids inside
+  // the graph (ascending within a label).  States without in-arcs are not listed (never occupied after frame 0).
+  const int32_t* slab_ptr;
+  const int32_t* slab_state;
   int32_t max_arcs;      // most arcs of any one graph
   int32_t unit_weights;  // every arc weight is 0 (semiring One)
   int32_t in_label_uniform;  // all arcs into a state carry the same label (true for every H o C o transcript graph)
@@ -74,6 +79,7 @@ struct ctcg_graph {
   std::vector<int32_t> out_ptr, out_dst, out_lab, out_clab;
   std::vector<float> out_w;
   std::vector<int32_t> lab_ptr, lab_src, lab_dst;
+  std::vector<int32_t> slab_ptr, slab_state;
   std::vector<float> lab_w;
   int32_t max_arcs = 0;
   int32_t unit_weights = 1;

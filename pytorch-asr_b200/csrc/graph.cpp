@@ -383,6 +383,8 @@ int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out) {
   g->lab_w.resize(total_arcs);
   g->lab_list.resize(g->lab_off[G]);
   g->lab_ptr.assign(static_cast<size_t>(g->lab_off[G]) + G, 0);
+  g->slab_ptr.assign(static_cast<size_t>(g->lab_off[G]) + G, 0);
+  g->slab_state.assign(static_cast<size_t>(total_states) + 1, 0);
   // ---- pass B: fill this graph's slices ----
   parallel_for(G, [&](int32_t gi) {
     const RawGraph& r = graphs[gi];
@@ -450,6 +452,16 @@ int finalize_graphs(const std::vector<RawGraph>& graphs, ctcg_graph** out) {
     for (int32_t s = 0; s < n; ++s)
       for (int32_t i = ptr[s] + 1; i < ptr[s + 1]; ++i)
         if (r.arcs[idx[i]].label != r.arcs[idx[ptr[s]]].label) pg.in_uniform = false;
+    {  // states by the compact label of their (first) in-arc: counting sort, states ascending within a label
+      std::vector<int32_t> cnt(nl + 1, 0);
+      for (int32_t s = 0; s < n; ++s)
+        if (ptr[s] < ptr[s + 1]) cnt[clab[idx[ptr[s]]] + 1]++;
+      for (int32_t j = 0; j < nl; ++j) cnt[j + 1] += cnt[j];
+      for (int32_t j = 0; j <= nl; ++j) g->slab_ptr[g->lab_off[gi] + gi + j] = so + cnt[j];
+      std::vector<int32_t> pos(cnt.begin(), cnt.end() - 1);
+      for (int32_t s = 0; s < n; ++s)
+        if (ptr[s] < ptr[s + 1]) g->slab_state[so + pos[clab[idx[ptr[s]]]]++] = s;
+    }
     for (int32_t i = 0; i < na; ++i) {
       const Arc& a = r.arcs[idx[i]];
       g->in_src[arc_base + i] = a.src;

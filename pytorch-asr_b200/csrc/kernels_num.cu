@@ -116,13 +116,14 @@ __host__ __device__ inline SweepPlan sweep_plan(int maxN, int nlp) {
 // One state: sum over its DK arcs, terms aligned to the largest exponent, times the label factor.
 // An absent / dead arc has mantissa 0 and an exponent near IDEAD, far below any live one.
 template <int DK>
-__device__ __forceinline__ int2 step_state(const int (&J)[DK], const float (&p)[DK], const int2 ev) {
+__device__ __forceinline__ int2 step_state(const int (&J)[DK], const float (&p)[DK], const int2 ev, int2* pre) {
   int Jm = J[0];
 #pragma unroll
   for (int k = 1; k < DK; ++k) Jm = max(Jm, J[k]);
   float acc = 0.f;
 #pragma unroll
   for (int k = 0; k < DK; ++k) acc = fmaf(p[k], pow2c(J[k] - Jm), acc);
+  *pre = renorm(acc, Jm);  // (M v)[s]: beta_{t+1}[s] in the backward sweep
   return renorm(acc * __int_as_float(ev.y), Jm + ev.x);
 }
 
@@ -234,13 +235,21 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
           v0 = make_int2(0, __float_as_int(1.f));
         }
         sts64(a0_a + s * 8, v0);
-        if (spill && len > 0) rows[(long long)frame_t(0) * arow2 + s] = v0;
+        if (spill) {  // forward: row 0 = alpha_0; backward: row len = beta_len = final
+          int2 r0 = v0;
+          if (DIR) {
+            const float f = g.final_w[so + s];
+            r0 = (f > kDeadWeight) ? split_pow2(f * kLog2e) : make_int2(IDEAD, 0);
+          }
+          rows[(DIR ? (long long)len : 0LL) * arow2 + s] = r0;
+        }
       }
     }
   }
   unsigned ac = a0_a, an = a1_a;
-  // row of the vector LEAVING step i: alpha_{i+1} -> row i+1; C_{len-1-i} -> row len-1-i
-  long long orow = (DIR ? (long long)(len - 1 - i0) : (long long)(i0 + 1)) * arow2;
+  // what a step spills: forward alpha_{i+1} -> row i+1; backward beta_{t+1} = M C_{t+1}, t = len-1-i -> row len-i
+  // (the combine reads the state occupancies alpha_{t+1} beta_{t+1} from rows t+1 of both)
+  long long orow = (DIR ? (long long)(len - i0) : (long long)(i0 + 1)) * arow2;
   const long long ostep = DIR ? -(long long)arow2 : (long long)arow2;
 
   // ONE block barrier per frame.  It publishes the vector written during the previous step and the
@@ -269,10 +278,11 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
 #pragma unroll
       for (int u = 0; u < SPT; ++u) {
         const int s = tid + NCT * u;
-        const int2 res = step_state<DK>(J[u], pm[u], ev[u]);
+        int2 pre;
+        const int2 res = step_state<DK>(J[u], pm[u], ev[u], &pre);
         if (s < n) {
           sts64(an + s * 8, res);
-          if (spill) rows[orow + s] = res;
+          if (spill) rows[orow + s] = DIR ? pre : res;
         }
       }
     }
@@ -328,15 +338,17 @@ constexpr int CB_W = 8;             // warps per combine CTA (fewer when the row
 constexpr int CB_FPW = 4;           // frames per warp: the graph tables are staged once per warps * CB_FPW frames
 constexpr int CB_TH = CB_W * 32;
 
-// alpha_t[src] * C_t[dst] (* w) * 2^(exponents - cost exponent)
-__device__ __forceinline__ float post_term(int2 av, int2 bv, int kE, float km) {
-  return (__int_as_float(av.y) * __int_as_float(bv.y)) * (km * pow2c(min(av.x + bv.x + kE, 64)));
+// alpha_{t+1}[d] * beta_{t+1}[d] * 2^(exponents - cost exponent): the occupancy of state d after frame t
+__device__ __forceinline__ float post_term(int2 av, int2 bv, int kE) {
+  return (__int_as_float(av.y) * __int_as_float(bv.y)) * pow2c(min(av.x + bv.x + kE, 64));
 }
 
-// Writes the compact posterior rows gout[b][t][j], normalised to sum one (times g_sign * g_scale[b]): the
-// row kernels of plain CTC and the denominator's combine kernel (CTC-G) fold them into the dense gradient.
-template <bool UNIT>
-__global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a, const int maxA, const int maxL) {
+// gamma_t[j] = sum_{states d with lab(d) = j} alpha_{t+1}[d] beta_{t+1}[d] / Z: one product per STATE (the arcs,
+// their weights and the logits are already inside alpha_{t+1} and beta_{t+1}), summed in a fixed order (states
+// grouped by label on the host) and normalised so that the row sums to one.  Writes the compact posterior rows
+// gout[b][t][j] (times g_sign * g_scale[b]): the row kernels of plain CTC and the denominator's combine kernel
+// (CTC-G) fold them into the dense gradient.
+__global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a, const int maxN, const int maxL) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -346,8 +358,8 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
   const int cb_fr = nwarps * CB_FPW;
   if (blockIdx.x * cb_fr >= len) return;
   const int gi = (g.num_graphs == 1) ? 0 : b;
-  const int ro = g.state_off[gi] + gi;
-  const int n = g.state_off[gi + 1] - g.state_off[gi];
+  const int so = g.state_off[gi];
+  const int n = g.state_off[gi + 1] - so;
   const int lo = g.lab_off[gi];
   const int nl = g.lab_off[gi + 1] - lo;
   const int nlp = (int)a.x_stride_t, arow = a.alpha_row;
@@ -358,33 +370,27 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
     return at;
   };
   int* lab_ptr = reinterpret_cast<int*>(sm + take((maxL + 1) * 4));
-  unsigned* lab_pk = reinterpret_cast<unsigned*>(sm + take(maxA * 4));
-  float* lab_w = reinterpret_cast<float*>(sm + (UNIT ? 0 : take(maxA * 4)));
-  // per warp: two staging buffers {alpha row, C row} (the next frame's rows are copied in with cp.async
+  int* lab_st = reinterpret_cast<int*>(sm + take(maxN * 4));
+  // per warp: two staging buffers {alpha row, beta row} (the next frame's rows are copied in with cp.async
   // while this frame's posteriors are summed) and one posterior row
   const int stg = 2 * arow;
   float* rows_s = reinterpret_cast<float*>(sm + take(nwarps * (2 * stg + nlp) * 4));
-  const int arc0 = g.in_ptr[ro];
-  const int narcs = g.in_ptr[ro + n] - arc0;
-  for (int j = tid; j <= nl; j += nthreads) lab_ptr[j] = g.lab_ptr[lo + gi + j] - arc0;
-  for (int e = tid; e < narcs; e += nthreads) {
-    lab_pk[e] = (unsigned)g.lab_src[arc0 + e] | ((unsigned)g.lab_dst[arc0 + e] << 16);
-    if (!UNIT) lab_w[e] = g.lab_w[arc0 + e] * kLog2e;
-  }
+  for (int j = tid; j <= nl; j += nthreads) lab_ptr[j] = g.slab_ptr[lo + gi + j] - so;
+  for (int e = tid; e < n; e += nthreads) lab_st[e] = g.slab_state[so + e];
   __syncthreads();
   float* wbase = rows_s + warp * (2 * stg + nlp);
   float* gt = wbase + 2 * stg;
   const double costn = a.cost[b];
   const bool feasible = costn > -1e19;
   // the cost's exponent keeps the terms in range; its mantissa cancels in the row normalisation
-  const int cE = (int)rint(costn / kLn2);
+  const int kE = -(int)rint(costn / kLn2);
   const float gmul = a.g_sign * (a.g_scale ? a.g_scale[b] : 1.f);
   auto stage = [&](int q) {  // always commits a group (possibly empty), so that the wait counts stay uniform
     const int t = blockIdx.x * cb_fr + q * nwarps + warp;
     if (q < CB_FPW && t < len && feasible) {
       float* d = wbase + (q & 1) * stg;
-      const float* as = a.alpha_ws + ((long long)b * (a.T + 1) + t) * arow;
-      const float* bs = a.beta_ws + ((long long)b * (a.T + 1) + t) * arow;
+      const float* as = a.alpha_ws + ((long long)b * (a.T + 1) + t + 1) * arow;   // alpha_{t+1}
+      const float* bs = a.beta_ws + ((long long)b * (a.T + 1) + t + 1) * arow;    // beta_{t+1}
       for (int i = lane; i < (2 * n + 3) / 4; i += 32) {
         cp_async16(d + 4 * i, as + 4 * i);
         cp_async16(d + arow + 4 * i, bs + 4 * i);
@@ -422,27 +428,20 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
       const bool heavy = (e1 - e0) > HEAVY;
       float acc = 0.f;
       if (j < nl && !heavy) {
-        const int kE = -cE;
-        const float km = 1.f;
         for (int e = e0; e < e1; ++e) {
-          const unsigned pk = lab_pk[e];
-          const int2 ws = UNIT ? make_int2(0, __float_as_int(1.f)) : split_pow2(lab_w[e]);
-          acc += post_term(at[pk & 0xffffu], bt[pk >> 16], kE + ws.x, UNIT ? km : km * __int_as_float(ws.y));
+          const int d = lab_st[e];
+          acc += post_term(at[d], bt[d], kE);
         }
       }
       unsigned hm = __ballot_sync(0xffffffffu, heavy);
-      while (hm) {  // labels with many arcs (the blank): the whole warp strides over the arcs
+      while (hm) {  // labels with many states (the blank): the whole warp strides over them
         const int src_lane = __ffs(hm) - 1;
         hm &= hm - 1;
-        const int jh = base + src_lane;
         const int h0 = __shfl_sync(0xffffffffu, e0, src_lane), h1 = __shfl_sync(0xffffffffu, e1, src_lane);
-        const int kE = -cE;
-        const float km = 1.f;
         float part = 0.f;
         for (int e = h0 + lane; e < h1; e += 32) {
-          const unsigned pk = lab_pk[e];
-          const int2 ws = UNIT ? make_int2(0, __float_as_int(1.f)) : split_pow2(lab_w[e]);
-          part += post_term(at[pk & 0xffffu], bt[pk >> 16], kE + ws.x, UNIT ? km : km * __int_as_float(ws.y));
+          const int d = lab_st[e];
+          part += post_term(at[d], bt[d], kE);
         }
         part = warp_sum(part);
         if (lane == src_lane) acc = part;
@@ -458,14 +457,14 @@ __global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a,
 }
 
 constexpr int kSmemBudget = 200 * 1024;
-int combine_smem_bytes(const PathArgs& a, bool unit, int warps) {
-  return ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_arcs * 4 + 16) * (unit ? 1 : 2) +
+int combine_smem_bytes(const PathArgs& a, int warps) {
+  return ((a.g.max_labels + 1) * 4 + 16) + (a.g.max_states * 4 + 16) +
          warps * (2 * (2 * a.alpha_row) + (int)a.x_stride_t) * 4 + 64;
 }
 // most warps (<= CB_W) whose staging buffers fit; 0: not even one
-int combine_warps(const PathArgs& a, bool unit) {
+int combine_warps(const PathArgs& a) {
   int w = CB_W;
-  while (w > 0 && combine_smem_bytes(a, unit, w) > kSmemBudget) --w;
+  while (w > 0 && combine_smem_bytes(a, w) > kSmemBudget) --w;
   return w;
 }
 int sweep_smem_bytes(const PathArgs& a) { return sweep_plan(a.g.max_states, (int)a.x_stride_t).bytes; }
@@ -499,8 +498,7 @@ bool num_split_supported(const PathArgs& a) {
   if (a.g.max_in_degree > DEG || a.g.max_out_degree > DEG) return false;
   if (a.alpha_row < 2 * a.g.max_states) return false;
   if (!a.g.in_label_uniform || a.g.max_states > NCT * MAXSPT) return false;  // the generic CSR kernel takes these
-  const bool unit = a.g.unit_weights != 0;
-  return sweep_smem_bytes(a) <= kSmemBudget && combine_warps(a, unit) >= 1;
+  return sweep_smem_bytes(a) <= kSmemBudget && combine_warps(a) >= 1;
 }
 
 cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st) {
@@ -514,22 +512,14 @@ cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st) {
 
 cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st) {
   if (!a.write_grad) return cudaSuccess;
-  const bool unit = a.g.unit_weights != 0;
-  cudaError_t e;
   ProfScope prof("num_combine", st);
-  const int warps = combine_warps(a, unit);
-  const int bytes = combine_smem_bytes(a, unit, warps);
+  const int warps = combine_warps(a);
+  const int bytes = combine_smem_bytes(a, warps);
   const int cb_fr = warps * CB_FPW;
   const dim3 grid((a.T + cb_fr - 1) / cb_fr, a.B);
-  if (unit) {
-    e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (e != cudaSuccess) return e;
-    num_combine_kernel<true><<<grid, warps * 32, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
-  } else {
-    e = cudaFuncSetAttribute(num_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (e != cudaSuccess) return e;
-    num_combine_kernel<false><<<grid, warps * 32, bytes, st>>>(a, a.g.max_arcs, a.g.max_labels);
-  }
+  cudaError_t e = cudaFuncSetAttribute(num_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  num_combine_kernel<<<grid, warps * 32, bytes, st>>>(a, a.g.max_states, a.g.max_labels);
   ++g_launches;
   return cudaGetLastError();
 }
