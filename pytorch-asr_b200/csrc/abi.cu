@@ -302,9 +302,11 @@ int run_bichar(const Plan& p, unsigned char* ws, const float* x, int T, int B, i
 // denominator runs on a side stream, forked from and joined back into the caller's stream
 // with events (legal inside a stream capture).  One side stream per host thread and
 // device; CTCG_SERIAL=1 keeps everything on the caller's stream.
+constexpr int kGroups = 16;  // most length groups of the denominator (streams of their own)
 struct SideStream {
-  cudaStream_t stream = nullptr;
-  cudaEvent_t fork = nullptr, join = nullptr, numdone = nullptr;
+  cudaStream_t stream[kGroups] = {};
+  cudaEvent_t fork = nullptr, numdone = nullptr;
+  cudaEvent_t join[kGroups] = {};
   bool ok = false;
 };
 
@@ -320,16 +322,50 @@ SideStream* side_stream() {
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return nullptr;
   SideStream& s = table[dev];
   if (!s.ok) {
-    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&s.numdone, cudaEventDisableTiming) != cudaSuccess) {
+    bool good = cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) == cudaSuccess &&
+                cudaEventCreateWithFlags(&s.numdone, cudaEventDisableTiming) == cudaSuccess;
+    for (int g = 0; g < kGroups && good; ++g)
+      good = cudaStreamCreateWithFlags(&s.stream[g], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&s.join[g], cudaEventDisableTiming) == cudaSuccess;
+    if (!good) {
       (void)cudaGetLastError();
       return nullptr;
     }
     s.ok = true;
   }
   return &s;
+}
+
+// Length groups: the caller's batch is sorted by length (the reference asserts it, fst_utils.py:382,432), so
+// contiguous index ranges are length classes.  Each group's sweeps and combine go to a stream of their own:
+// the sweeps of the short utterances end at 0.6-0.7 of the longest one's, and their combine starts right
+// then, on the SMs those sweeps free, instead of after the whole batch's sweeps (cfg3: 0.413 -> 0.378 ms with
+// 4 groups).  Only while every sweep CTA of the batch is resident at once (2 B <= SMs): beyond that the sweeps
+// run in waves, the SMs are never idle and smaller grids only fragment the waves (cfg5, B=256: 2.75 -> 3.05 ms).
+// CTCG_GROUPS=n forces n groups (1 turns it off).
+int group_count(int B, const int32_t* lens_host) {
+  static const int forced = [] {
+    const char* e = std::getenv("CTCG_GROUPS");
+    return e ? std::atoi(e) : 0;
+  }();
+  static const int sms = [] {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+      (void)cudaGetLastError();
+      n = 148;
+    }
+    return n;
+  }();
+  static const int per_group = [] {
+    const char* e = std::getenv("CTCG_GROUP_MIN");
+    return e ? std::max(1, std::atoi(e)) : 8;
+  }();
+  int g = forced > 0 ? std::min(forced, kGroups) : 8;
+  if (forced <= 0 && 2 * B > sms) g = 1;
+  while (g > 1 && B < per_group * g) g /= 2;     // at least 8 utterances per group
+  for (int b = 1; b < B && g > 1; ++b)
+    if (lens_host[b] > lens_host[b - 1]) g = 1;  // not sorted: index ranges are no length classes
+  return g;
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -397,14 +433,18 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   // (one store of gamma_den - gamma_num): sweeps || numerator, then the combine.
   const bool fold = fused_den && grad != nullptr && split;
   BisweepArgs den_args{};
-  cudaStream_t ds = st;
+  const int ngroups = (fused_den && side && fold) ? group_count(B, lens_host) : 1;
+  auto group_args = [&](int g) {  // utterances [g*B/G, (g+1)*B/G)
+    BisweepArgs a = den_args;
+    if (ngroups > 1) {
+      a.b0 = (int)((long long)g * B / ngroups);
+      a.nb = (int)((long long)(g + 1) * B / ngroups) - a.b0;
+    }
+    return a;
+  };
+  auto group_stream = [&](int g) { return side ? side->stream[g] : st; };
   if (fused_den) {
     // 1'. factorised bi-char denominator sweeps (kernels_bisweep.cu); concurrent with 1-2
-    if (side) {
-      CTCG_CUDA(cudaEventRecord(side->fork, st));
-      CTCG_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
-      ds = side->stream;
-    }
     den_args = bichar_args(p, ws, logits, T, B, V, lens, den, cost_den, grad, grad_scale);
     if (fold) {
       den_args.num_gg = gg;
@@ -413,16 +453,21 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
       den_args.num_lab_off = num->dev.lab_off;
       den_args.num_lab_list = num->dev.lab_list;
     }
-    if (launch_bisweep(den_args, p.sw, ds) != cudaSuccess) {
-      (void)cudaGetLastError();
-      st_ = CTCG_ECUDA;
+    if (side) CTCG_CUDA(cudaEventRecord(side->fork, st));
+    for (int g = 0; g < ngroups && st_ == CTCG_OK; ++g) {
+      if (side) CTCG_CUDA(cudaStreamWaitEvent(side->stream[g], side->fork, 0));
+      if (launch_bisweep(group_args(g), p.sw, group_stream(g)) != cudaSuccess) {
+        (void)cudaGetLastError();
+        st_ = CTCG_ECUDA;
+      }
     }
-    if (side && st_ != CTCG_OK) CTCG_CUDA(cudaEventRecord(side->join, side->stream));
+    if (side && st_ != CTCG_OK)
+      for (int g = 0; g < ngroups; ++g) CTCG_CUDA(cudaEventRecord(side->join[g], side->stream[g]));
   }
   // joins the side stream back (also on failure, so that a capture is never left forked)
   auto join = [&]() -> int {
     if (!side) return CTCG_OK;
-    CTCG_CUDA(cudaStreamWaitEvent(st, side->join, 0));
+    for (int g = 0; g < ngroups; ++g) CTCG_CUDA(cudaStreamWaitEvent(st, side->join[g], 0));
     return CTCG_OK;
   };
   if (st_ != CTCG_OK) {
@@ -464,21 +509,26 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     return CTCG_OK;
   }();
   if (fused_den) {
-    // 3a'. combine: gamma_den - gamma_num, after the numerator's compact rows
+    // 3a'. combine: gamma_den - gamma_num, after the numerator's compact rows; shortest group first
     int cs = CTCG_OK;
-    if (st_ == CTCG_OK && side && fold) {
-      if (cudaEventRecord(side->numdone, st) != cudaSuccess || cudaStreamWaitEvent(ds, side->numdone, 0) != cudaSuccess) {
+    if (st_ == CTCG_OK && side && fold && cudaEventRecord(side->numdone, st) != cudaSuccess) {
+      (void)cudaGetLastError();
+      cs = CTCG_ECUDA;
+    }
+    for (int g = ngroups - 1; g >= 0; --g) {
+      cudaStream_t gs = group_stream(g);
+      if (st_ == CTCG_OK && cs == CTCG_OK && side && fold && cudaStreamWaitEvent(gs, side->numdone, 0) != cudaSuccess) {
         (void)cudaGetLastError();
         cs = CTCG_ECUDA;
       }
-    }
-    if (st_ == CTCG_OK && cs == CTCG_OK && launch_bicombine(den_args, p.sw, ds) != cudaSuccess) {
-      (void)cudaGetLastError();
-      cs = CTCG_ECUDA;
-    }
-    if (side && cudaEventRecord(side->join, side->stream) != cudaSuccess) {
-      (void)cudaGetLastError();
-      cs = CTCG_ECUDA;
+      if (st_ == CTCG_OK && cs == CTCG_OK && launch_bicombine(group_args(g), p.sw, gs) != cudaSuccess) {
+        (void)cudaGetLastError();
+        cs = CTCG_ECUDA;
+      }
+      if (side && cudaEventRecord(side->join[g], gs) != cudaSuccess) {
+        (void)cudaGetLastError();
+        cs = CTCG_ECUDA;
+      }
     }
     const int js = join();
     if (st_ != CTCG_OK) return st_;

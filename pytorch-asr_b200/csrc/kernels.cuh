@@ -105,6 +105,9 @@ struct BisweepArgs {
   const float* g_scale;    // nullable
   int32_t nmain, rowf, estride, epad;
   int32_t dbg;             // timing experiments only (CTCG_SWEEP_DEBUG bit mask); 0 in production
+  // a launch may cover the utterances [b0, b0 + nb) only (nb = 0: the whole batch): groups of a length-sorted
+  // batch on streams of their own, so that a group's combine starts when ITS sweeps are done (abi.cu)
+  int32_t b0, nb;
   // numerator posteriors folded into the combine (nullable): grad = g_scale * (gamma_den - gamma_num) in ONE store.
   const float* num_gg;            // compact posteriors, segment-major: gg[b][t / K][j][t % K], j indexes the utterance's labels
   int32_t num_nlp;                // labels per row (pitch)

@@ -161,7 +161,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
   const SDims<SCT> D(A);
   const int S = D.S, V = D.V, PF = D.PF;
   const int tid = threadIdx.x, lane = tid & 31;
-  const int b = blockIdx.x, B = A.B;
+  const int b = blockIdx.x + A.b0, B = A.B;
   const int len = min(A.lens[b], A.T);
   const int nmain = A.nmain;
   // Role order by hardware warp id: producers, io, main, scale.  The warp schedulers favour the
@@ -614,7 +614,7 @@ template <int SCT, int KMAX>
 __global__ void __launch_bounds__(CTHREADS, 2) bicombine_kernel(const BisweepArgs A) {
   const int S = SCT > 0 ? SCT : A.S;
   const int V = S * S;
-  const int b = blockIdx.y, j = blockIdx.x, K = A.K, B = A.B, T = A.T, prowf = A.prowf;
+  const int b = blockIdx.y + A.b0, j = blockIdx.x, K = A.K, B = A.B, T = A.T, prowf = A.prowf;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int t0 = j * K;
   if (t0 >= T) return;
@@ -885,7 +885,7 @@ cudaError_t launch_bisweep(const BisweepArgs& a_in, const BisweepPlan& p, cudaSt
     }();
     a.dbg = dbg;  // timing experiments only: roles skip their work, results invalid
   }
-  const dim3 grid(a.B, (a.grad && !(a.dbg & 4)) ? 2 : 1);
+  const dim3 grid(a.nb > 0 ? a.nb : a.B, (a.grad && !(a.dbg & 4)) ? 2 : 1);
   {
     ProfScope prof("bisweep", st);
 #define CTCG_SWEEP(SCT, MAXT)                                                                               \
@@ -912,7 +912,7 @@ cudaError_t launch_bicombine(const BisweepArgs& a, const BisweepPlan& p, cudaStr
   (void)p;
   if (!a.grad) return cudaSuccess;
   ProfScope prof("bicombine", st);
-  const dim3 cgrid((a.T + a.K - 1) / a.K, a.B);
+  const dim3 cgrid((a.T + a.K - 1) / a.K, a.nb > 0 ? a.nb : a.B);
   if (a.S == 49) bicombine_kernel<49, 8><<<cgrid, CTHREADS, 0, st>>>(a);
   else if (a.S == 36) bicombine_kernel<36, 8><<<cgrid, CTHREADS, 0, st>>>(a);
   else bicombine_kernel<0, 8><<<cgrid, CTHREADS, 0, st>>>(a);

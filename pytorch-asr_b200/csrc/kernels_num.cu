@@ -14,8 +14,10 @@
 //   backward  C_{t-1}[s]     = e_{t-1}[lab(s)] * sum_{arcs k out of s} w_k C_t[dst_k],
 //             C_t[d] = e_t[lab(d)] beta_{t+1}[d],   C_{len-1} = e_{len-1}[lab] * final
 // i.e. v' = e[lab] (.) (M v) with M the in-arc or the out-arc matrix: one label look-up per state
-// instead of one per arc, and the posterior needs no logits any more:
-//   gamma_t[j] = sum_{arcs labelled j} alpha_t[src] w C_t[dst] / Z.
+// instead of one per arc.  The backward sweep spills beta_{t+1} = M C_{t+1} (the sum before the label
+// factor), the forward sweep alpha_{t+1}; the posterior of a label is then the occupancy of its states,
+//   gamma_t[j] = sum_{states d with lab(d) = j} alpha_{t+1}[d] beta_{t+1}[d] / Z,
+// one product per state with no arcs, weights or logits left in it.
 //
 // Number domain.  A training graph is a chain, so alpha_t of the states that carry the posterior
 // mass sits hundreds of binary orders below max_s alpha_t[s]: numbers scaled per frame underflow
@@ -26,7 +28,7 @@
 // 2^-24 whatever the magnitude, a sum aligns its terms to the largest exponent with a power of two
 // built in the integer pipe.  No per-frame normaliser, nothing lagged, and no transcendental on
 // the recursion: the only MUFU work is one ex2 per label and frame for e = 2^frac(x log2 e) (the
-// integer part of x log2 e goes to the exponent), done by the producer warps off the chain.
+// integer part of x log2 e goes to the exponent), done once per batch by gather_kernel.
 //
 // num_sweep_kernel   256 threads.  7 compute warps own 1..4 states per thread (arcs as shared-memory
 //                    byte offsets in registers); the vector lives in shared memory (int2 per state,
@@ -35,7 +37,7 @@
 //                    gather_kernel (kernels_rows.cu), which spreads the scattered 4-byte reads of the
 //                    (T, B, V) logits over the whole GPU -- into a 16-row ring with 16-byte cp.async
 //                    copies.  One block barrier per frame, no atomics, no MUFU.
-// num_combine_kernel one warp per frame: the sum above in a fixed order (arcs grouped by label on the
+// num_combine_kernel one warp per frame: the sum above in a fixed order (states grouped by label on the
 //                    host), row normalised to one; with a factorised denominator the compact rows go
 //                    to the denominator's combine kernel, which subtracts them while it writes.
 #include <algorithm>
@@ -348,7 +350,12 @@ __device__ __forceinline__ float post_term(int2 av, int2 bv, int kE) {
 // grouped by label on the host) and normalised so that the row sums to one.  Writes the compact posterior rows
 // gout[b][t][j] (times g_sign * g_scale[b]): the row kernels of plain CTC and the denominator's combine kernel
 // (CTC-G) fold them into the dense gradient.
-__global__ void __launch_bounds__(CB_TH, 2) num_combine_kernel(const PathArgs a, const int maxN, const int maxL) {
+// SMALL: 128-thread CTAs capped at 80 registers (10 k registers per CTA), the footprint that fits next to a
+// denominator sweep CTA (416 threads x 126 registers = 52 k of the SM's 64 k): with a factorised denominator the
+// kernel then runs DURING the sweeps instead of waiting for their SMs.
+template <bool SMALL>
+__global__ void __launch_bounds__(SMALL ? 128 : CB_TH, SMALL ? 6 : 2)
+    num_combine_kernel(const PathArgs a, const int maxN, const int maxL) {
   extern __shared__ __align__(16) unsigned char sm[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -462,8 +469,8 @@ int combine_smem_bytes(const PathArgs& a, int warps) {
          warps * (2 * (2 * a.alpha_row) + (int)a.x_stride_t) * 4 + 64;
 }
 // most warps (<= CB_W) whose staging buffers fit; 0: not even one
-int combine_warps(const PathArgs& a) {
-  int w = CB_W;
+int combine_warps(const PathArgs& a, int most = CB_W) {
+  int w = most;
   while (w > 0 && combine_smem_bytes(a, w) > kSmemBudget) --w;
   return w;
 }
@@ -513,13 +520,22 @@ cudaError_t launch_num_sweeps(const PathArgs& a, cudaStream_t st) {
 cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st) {
   if (!a.write_grad) return cudaSuccess;
   ProfScope prof("num_combine", st);
-  const int warps = combine_warps(a);
+  // segment-major output = the denominator's combine will read it = the denominator sweeps are running now
+  const bool small = a.g_seg > 0;
+  const int warps = combine_warps(a, small ? 4 : CB_W);
   const int bytes = combine_smem_bytes(a, warps);
   const int cb_fr = warps * CB_FPW;
   const dim3 grid((a.T + cb_fr - 1) / cb_fr, a.B);
-  cudaError_t e = cudaFuncSetAttribute(num_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e != cudaSuccess) return e;
-  num_combine_kernel<<<grid, warps * 32, bytes, st>>>(a, a.g.max_states, a.g.max_labels);
+  cudaError_t e;
+  if (small) {
+    e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    num_combine_kernel<true><<<grid, warps * 32, bytes, st>>>(a, a.g.max_states, a.g.max_labels);
+  } else {
+    e = cudaFuncSetAttribute(num_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    num_combine_kernel<false><<<grid, warps * 32, bytes, st>>>(a, a.g.max_states, a.g.max_labels);
+  }
   ++g_launches;
   return cudaGetLastError();
 }
