@@ -176,7 +176,11 @@ int ctcg_path_sum(const float* log_probs, int32_t T, int32_t B, int32_t V,
 /* path_reduction(..., red_kind='viterbi') + the arg-min-of-gradient read-out of
  * FSTDecoder.decode (fst_utils.py:366-397, advanced_decoder.py:546-554):
  * score[b] = best accepting path weight, frame_labels (T,B) int32 = label
- * consumed at each frame on that path (0 for t >= lens[b]). */
+ * consumed at each frame on that path (0 for t >= lens[b]).  The bi-char
+ * decoding graph of ctcg_decoding_graph (or one recognised by
+ * ctcg_graph_from_padded) takes a factorised kernel, O(V) per frame instead of
+ * the graph's 51 V arcs; ties go to the smallest source state id, the order
+ * torch.max sees in the reference's sorted arc lists (fst_utils.py:285). */
 int ctcg_viterbi(const float* log_probs, int32_t T, int32_t B, int32_t V,
                  const int32_t* lens_host, const ctcg_graph* graph, float* score,
                  int32_t* frame_labels, void* workspace, size_t workspace_bytes,

@@ -684,6 +684,19 @@ int ctcg_viterbi(const float* log_probs, int32_t T, int32_t B, int32_t V, const 
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   int32_t* lens = nullptr;
   if ((st_ = upload_lens(p, workspace, lens_host, B, st, &lens)) != CTCG_OK) return st_;
+  // the bi-char decoding graph takes the factorised kernel (its back-pointers, 2 bytes per state and frame, fit
+  // the generic kernel's 4-byte slots planned above); CTCG_VITERBI_GENERIC=1 keeps the generic one (cross-checks)
+  static const bool force_generic = [] {
+    const char* e = std::getenv("CTCG_VITERBI_GENERIC");
+    return e && e[0] == '1';
+  }();
+  if (!force_generic && graph->structured.kind == 2 && graph->num_graphs == 1 &&
+      graph->structured.S * graph->structured.S == V && graph->structured.S <= 64) {
+    CTCG_CUDA(launch_biviterbi(log_probs, T, B, graph->structured.S, lens, graph->structured.allow_nonblank_selfloops,
+                               graph->structured.use_contextual_blanks,
+                               reinterpret_cast<unsigned short*>(ws + p.alpha_num), score, frame_labels, st));
+    return CTCG_OK;
+  }
   CTCG_CUDA(launch_viterbi(log_probs, T, B, V, lens, graph->dev, reinterpret_cast<int32_t*>(ws + p.alpha_num),
                            p.arow_num, score, frame_labels, st));
   return CTCG_OK;

@@ -79,6 +79,10 @@ cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* l
                            const GraphDev& g, int32_t* back_ws, int row, float* score,
                            int32_t* frame_labels, cudaStream_t st);
 
+// Viterbi on the bi-char decoding graph, factorised (O(V) per frame); back_ws: B*T*V uint16
+cudaError_t launch_biviterbi(const float* x, int T, int B, int S, const int32_t* lens, int loops, int ctx,
+                             unsigned short* back_ws, float* score, int32_t* frame_labels, cudaStream_t st);
+
 cudaError_t launch_path_count(int B, const int32_t* lens, const GraphDev& g, uint64_t* counts,
                               cudaStream_t st);
 

@@ -128,6 +128,167 @@ __global__ void __launch_bounds__(NT) viterbi_kernel(const float* __restrict__ x
   }
 }
 
+// ---------------------------------------------------------------------------
+// Viterbi on the bi-char decoding graph in its factorised form (the tropical counterpart of
+// kernels_bisweep.cu; fst_utils.py:366-397 on the graph of :765-817).  State (c, l) = (context, last
+// letter), id c*S + l.  Every arc into (c, l) carries class cls(c, l) and comes from a state whose next
+// context is c -- (c1, c) for every c1 when c != 0, and the blank state (c, 0) -- or is the explicit
+// self-loop (allow_nonblank_selfloops, l != 0, l != c):
+//     Pmax[c]  = max( max_{c1} v[c1][c]  (c != 0),  v[c][0] )
+//     v'[c][l] = x[cls(c, l)] + max( Pmax[c], loop(c, l) ? v[c][l] : -inf )
+// O(V) per frame instead of the 51 V arcs of the generic kernel.  Ties take the source with the smallest
+// state id, the order torch.max sees in the reference's arc lists (sorted by source state, :285).
+// One CTA per utterance; back[t][s] = source state (16 bits); the row of frame t+1 is requested a frame ahead.
+constexpr int BV_NT = 512;
+constexpr int BV_PER = 8;  // states per thread: V <= 4096
+
+__global__ void __launch_bounds__(BV_NT) biviterbi_kernel(const float* __restrict__ x, int T, int B, int S,
+                                                          const int32_t* __restrict__ lens, int loops, int ctx,
+                                                          unsigned short* __restrict__ back_ws,
+                                                          float* __restrict__ score, int32_t* __restrict__ frame_labels) {
+  extern __shared__ __align__(16) float bsm[];  // v[2][V], pmax[S], parg[S] (ints), red
+  const int V = S * S;
+  float* v0 = bsm;
+  float* v1 = bsm + V;
+  float* pmax = bsm + 2 * V;
+  int* parg = reinterpret_cast<int*>(pmax + 64);
+  float* rval = reinterpret_cast<float*>(parg + 64);
+  int* ridx = reinterpret_cast<int*>(rval + BV_NT / 32);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int len = min(max(lens[b], 0), T);
+  unsigned short* back = back_ws + (long long)b * T * V;
+  for (int s = tid; s < V; s += BV_NT) v0[s] = (s == 0) ? 0.f : neg_inf();
+  for (int t = len + tid; t < T; t += BV_NT) frame_labels[(long long)t * B + b] = 0;
+  float xr[BV_PER];
+  auto load_row = [&](int t) {
+    const float* row = x + ((long long)t * B + b) * V;
+#pragma unroll
+    for (int k = 0; k < BV_PER; ++k) {
+      const int s = tid + k * BV_NT;
+      if (s < V) {
+        const int c = s / S, l = s - c * S;
+        const int cls = (l != 0 || ctx) ? s : 0;  // all (c, 0) share class 0 unless blanks are contextual
+        xr[k] = __ldg(row + cls);
+        (void)c;
+      }
+    }
+  };
+  if (len > 0) load_row(0);
+  float* vc = v0;
+  float* vn = v1;
+  __syncthreads();
+  for (int t = 0; t < len; ++t) {
+    // phase 1: Pmax[c] and its source, smallest state id among the maxima
+    for (int c = warp; c < S; c += BV_NT / 32) {
+      float best = neg_inf();
+      int arg = 0x7fffffff;
+      if (c != 0)
+        for (int c1 = lane; c1 < S; c1 += 32) {
+          const float val = vc[c1 * S + c];
+          if (val > best) {  // ids ascend with c1: strict > keeps the smallest
+            best = val;
+            arg = c1 * S + c;
+          }
+        }
+      if (lane == 0) {  // the blank state (c, 0)
+        const float val = vc[c * S];
+        const int id = c * S;
+        if (val > best || (val == best && id < arg)) {
+          best = val;
+          arg = id;
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, arg, o);
+        if (ov > best || (ov == best && oi < arg)) {
+          best = ov;
+          arg = oi;
+        }
+      }
+      if (lane == 0) {
+        pmax[c] = best;
+        parg[c] = arg;
+      }
+    }
+    __syncthreads();
+    // phase 2: every state from its context's best source or its own self-loop
+    float xcur[BV_PER];
+#pragma unroll
+    for (int k = 0; k < BV_PER; ++k) xcur[k] = xr[k];
+    if (t + 1 < len) load_row(t + 1);
+    unsigned short* bk = back + (long long)t * V;
+#pragma unroll
+    for (int k = 0; k < BV_PER; ++k) {
+      const int s = tid + k * BV_NT;
+      if (s < V) {
+        const int c = s / S, l = s - c * S;
+        float best = pmax[c];
+        int arg = parg[c];
+        if (loops && l != 0 && l != c) {
+          const float sv = vc[s];
+          if (sv > best || (sv == best && s < arg)) {
+            best = sv;
+            arg = s;
+          }
+        }
+        const bool alive = best > neg_inf();
+        vn[s] = alive ? best + xcur[k] : neg_inf();
+        bk[s] = (unsigned short)(alive ? arg : 0);
+      }
+    }
+    __syncthreads();
+    float* tmp = vc;
+    vc = vn;
+    vn = tmp;
+  }
+  // best final state (all states are final), lowest id on ties
+  float bv = neg_inf();
+  int bi = 0x7fffffff;
+  for (int s = tid; s < V; s += BV_NT) {
+    const float val = vc[s];
+    if (val > bv) {
+      bv = val;
+      bi = s;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > bv || (ov == bv && oi < bi)) {
+      bv = ov;
+      bi = oi;
+    }
+  }
+  if (lane == 0) {
+    rval[warp] = bv;
+    ridx[warp] = bi;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    for (int i = 1; i < BV_NT / 32; ++i)
+      if (rval[i] > bv || (rval[i] == bv && ridx[i] < bi)) {
+        bv = rval[i];
+        bi = ridx[i];
+      }
+    if (!(bv > neg_inf())) {
+      score[b] = -1e20f;
+      for (int t = 0; t < len; ++t) frame_labels[(long long)t * B + b] = 0;
+    } else {
+      score[b] = bv;
+      int s = bi;
+      for (int t = len - 1; t >= 0; --t) {
+        const int l = s % S;
+        frame_labels[(long long)t * B + b] = (l != 0 || ctx) ? s : 0;  // the class on every arc into s
+        s = back[(long long)t * V + s];
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(NT) count_kernel(int B, const int32_t* __restrict__ lens, GraphDev g,
                                                    unsigned long long* __restrict__ counts) {
   extern __shared__ __align__(16) unsigned long long cbuf[];  // 2*n + NT
@@ -175,6 +336,18 @@ cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* l
   if (e != cudaSuccess) return e;
   ProfScope prof("viterbi", st);
   viterbi_kernel<<<B, NT, smem, st>>>(x, T, B, V, lens, g, back_ws, row, score, frame_labels);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_biviterbi(const float* x, int T, int B, int S, const int32_t* lens, int loops, int ctx,
+                             unsigned short* back_ws, float* score, int32_t* frame_labels, cudaStream_t st) {
+  if (S < 2 || S > 64) return cudaErrorInvalidConfiguration;
+  const size_t smem = (size_t)(2 * S * S + 128 + 2 * (BV_NT / 32)) * 4;
+  cudaError_t e = cudaFuncSetAttribute(biviterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  ProfScope prof("biviterbi", st);
+  biviterbi_kernel<<<B, BV_NT, smem, st>>>(x, T, B, S, lens, loops, ctx, back_ws, score, frame_labels);
   ++g_launches;
   return cudaGetLastError();
 }

@@ -559,3 +559,29 @@ def test_per_utterance_grad_output_scales_rows_on_the_device(P):
     assert torch.equal(g, keep)
     P._lib.scale_grad(g, torch.tensor(3.0, device="cuda").expand(B))
     assert torch.allclose(g, keep * 3)
+
+
+@pytest.mark.parametrize("S,args,T,B", [(49, {}, 400, 4), (49, {"use_contextual_blanks": True}, 200, 3),
+                                        (36, {"allow_nonblank_selfloops": False}, 150, 3), (7, {}, 60, 5)])
+def test_factorised_viterbi_equals_the_generic_kernel(P, S, args, T, B):
+    """The tropical counterpart of the factorised denominator (biviterbi_kernel) against the generic CSR
+    Viterbi on the same decoding graph (fst_utils.py:366-397 on the arcs of :765-817): same frame labels,
+    same score; the timings of both are kept for DESIGN.md."""
+    import time
+    logits, lens, seqs = _random_case(2, S, args, T, B, seed=900 + S + T, peaky=True)
+    gen = P.CTCGraphGen(context_order=2, graph_build_args=args, num_symbols=S)
+    fact = gen.get_decoding_graph()
+    generic = P.Graph.decoding(2, S, **args).set_generic()
+    assert fact.info().structured == 1 and generic.info().structured == 0
+    x = torch.from_numpy(logits).cuda()
+    out = {}
+    for name, g in (("factorised", fact), ("generic", generic)):
+        P._lib.viterbi(x, lens, g)                      # warm-up (graph upload, workspace)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        score, labels = P._lib.viterbi(x, lens, g)
+        torch.cuda.synchronize()
+        out[name] = (score.cpu().numpy(), labels.cpu().numpy(), (time.perf_counter() - t0) * 1e3)
+    assert np.array_equal(out["factorised"][1], out["generic"][1])
+    assert _rel(out["factorised"][0], out["generic"][0]) < 1e-6
+    _record("viterbi_S%d_T%d_B%d_ms" % (S, T, B), {"factorised": out["factorised"][2], "generic": out["generic"][2]})
