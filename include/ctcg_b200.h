@@ -137,7 +137,12 @@ int ctcg_graph_export_padded(const ctcg_graph* g, int32_t index, int32_t out_edg
                              float nc_weight, int64_t* states, int64_t* labels,
                              float* weights, float* terminal);
 
-/* Copy the CSR arrays to the current CUDA device (idempotent per device). */
+/* Copy the CSR arrays to the current CUDA device (idempotent per device).  * A handle holds ONE device copy: uploading it while another device is current
+ * releases the first copy (stream-ordered on the stream it was uploaded on), so a
+ * graph shared by several GPUs needs one handle per GPU -- what one process per GPU
+ * gives.  The entry points that take lens_host copy them through a pinned staging
+ * slot and may wait for the copy of four calls ago: they are stream-ordered but not
+ * capturable into a CUDA graph (ctcg_viterbi_static is the allocation-free variant). */
 int ctcg_graph_upload(ctcg_graph* g, void* stream);
 
 void ctcg_graph_free(ctcg_graph* g);

@@ -111,12 +111,16 @@ cudaError_t stage_and_copy(void* dst, const void* src, size_t bytes, cudaStream_
     size_t cap = 0;
     cudaEvent_t done = nullptr;
   };
-  constexpr int kSlots = 4;
-  thread_local Slot ring[kSlots];
-  thread_local int next = 0;
-  Slot& s = ring[next];
-  next = (next + 1) % kSlots;
-  cudaError_t e;
+  constexpr int kSlots = 4, kMaxDev = 64;
+  // one ring per host thread AND device: a slot's event belongs to the device it was created on
+  thread_local Slot rings[kMaxDev][kSlots];
+  thread_local int nexts[kMaxDev] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
+  Slot& s = rings[dev][nexts[dev]];
+  nexts[dev] = (nexts[dev] + 1) % kSlots;
   if (!s.done && (e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)) != cudaSuccess) return e;
   if ((e = cudaEventSynchronize(s.done)) != cudaSuccess) return e;  // never-recorded events are complete
   if (s.cap < bytes) {
@@ -399,6 +403,7 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   for (int b = 0; b < B; ++b)
     if (lens_host[b] < 0 || lens_host[b] > T) return CTCG_EINVAL;
   if (num->max_label >= V || (den && den->max_label >= V)) return CTCG_EINVAL;
+  if (B > 65535) return CTCG_EUNSUPPORTED;  // the combine kernels index the utterance with blockIdx.y
   const Plan p = make_plan(T, B, V, num, den);
   if (workspace_bytes < p.total) return CTCG_EWORKSPACE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
