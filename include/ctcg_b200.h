@@ -100,6 +100,31 @@ int ctcg_decoding_graph(const ctcg_topology* topo, ctcg_graph** out);
 int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels,
                          const int64_t* offsets, int32_t B, ctcg_graph** out);
 
+/* Decoding graphs the caller builds arc by arc WITH output labels -- the
+ * tri-char topologies (build_ctc_trigram_decoding_fst_v2, fst_utils.py:926-1050)
+ * and anything else that is not one of the two built-in topologies.  Arcs in the
+ * caller's insertion order (src, dst, class label, emitted symbol or 0, weight);
+ * connect != 0 applies OpenFst's Connect first (what Fst.rmepsilon() does to a
+ * graph without eps:eps arcs, :1025), then the arcs are stably sorted by output
+ * label (:1030).  State 0 is the start state. */
+typedef struct ctcg_decoder ctcg_decoder;
+int ctcg_decoder_from_arcs(int32_t n_states, int64_t n_arcs, const int32_t* src,
+                           const int32_t* dst, const int32_t* label,
+                           const int32_t* olabel, const float* weight,
+                           const float* final_w, int32_t connect, ctcg_decoder** out);
+int32_t ctcg_decoder_num_states(const ctcg_decoder* dec);
+/* Its decoding (denominator) graph; CTCG_ENONDET when it is not input-deterministic
+ * (the reference raises there too, fst_utils.py:250-252 -- the default tri-char
+ * graph with a shared blank class is such a graph: numerator only). */
+int ctcg_decoder_graph(const ctcg_decoder* dec, ctcg_graph** out);
+/* compose(decoder, chain(labels_b)) for B transcripts, like ctcg_training_graphs
+ * (BaseGraphGen.get_training_fst, fst_utils.py:592-605); labels above `modulo`
+ * are reduced modulo it when modulo > 0 (:595-596). */
+int ctcg_decoder_training_graphs(const ctcg_decoder* dec, const int32_t* labels,
+                                 const int64_t* offsets, int32_t B, int32_t modulo,
+                                 ctcg_graph** out);
+void ctcg_decoder_free(ctcg_decoder* dec);
+
 /* Import the reference's own padded matrices (the 8-tuple FSTDecoder receives
  * in batch['graph_matrices'], advanced_decoder.py:457-459): G graphs of N
  * states, in-degree K_in, out-degree K_out; arcs with weight <= nc_weight/2 are

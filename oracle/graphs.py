@@ -20,6 +20,7 @@ would hold after ``arcsort('olabel')`` (stable sort of insertion order).
 """
 from __future__ import annotations
 
+import itertools
 from collections import deque
 
 import numpy as np
@@ -94,6 +95,72 @@ def bigram_decoding_graph(S, allow_nonblank_selfloops=True,
                 out_s = l2
             arcs.append((s1, s2, in_class(c2, l2), out_s, 0.0))
     return Graph(S * S, _sorted_by_olabel(S * S, arcs), np.zeros(S * S))
+
+
+def _connected(n, arcs, final):
+    """OpenFst Connect: states accessible from 0 and co-accessible, renumbered in order (what
+    ``Fst.rmepsilon()`` leaves of itself on a graph without eps:eps arcs, fst_utils.py:1025)."""
+    out = [[] for _ in range(n)]
+    rev = [[] for _ in range(n)]
+    for a in arcs:
+        out[a[0]].append(a[1])
+        rev[a[1]].append(a[0])
+    acc = [False] * n
+    acc[0] = True
+    dq = deque([0])
+    while dq:
+        s = dq.popleft()
+        for d in out[s]:
+            if not acc[d]:
+                acc[d] = True
+                dq.append(d)
+    co = [bool(np.isfinite(final[s])) for s in range(n)]
+    dq = deque([s for s in range(n) if co[s]])
+    while dq:
+        s = dq.popleft()
+        for p in rev[s]:
+            if not co[p]:
+                co[p] = True
+                dq.append(p)
+    keep = [s for s in range(n) if acc[s] and co[s]]
+    remap = {s: i for i, s in enumerate(keep)}
+    arcs = [(remap[a[0]], remap[a[1]], a[2], a[3], a[4]) for a in arcs if a[0] in remap and a[1] in remap]
+    return len(keep), arcs, np.asarray([final[s] for s in keep])
+
+
+def trigram_decoding_graph(S, use_context_blanks=False):
+    """build_ctc_trigram_decoding_fst_v2 on the full table of S^3 trigrams (fst_utils.py:926-1050,
+    ``prevent_epsilons=True``, ``determinize=False``): state = sorted trigram (c0, c1, c2), final when
+    c2 is the blank; a self loop on every state but (0,0,0); from s1 to every s2 that continues it --
+    (b0, b1, x) with (b0, b1) = (s1[0], s1[2]) if the middle of s1 is a blank else (s1[1], s1[2]), plus
+    (s1[1], 0, s1[2]) -- unless s2 is s1 or (0,0,0), s1 ends in a blank and s2 does not, or s2 starts
+    with a blank and s1 does not; class = index of the target trigram (of (0,0,0) when its middle is a
+    blank and blanks are not contextual), emitted symbol = the target's middle letter."""
+    tgs = [(a, b, c) for a in range(S) for b in range(S) for c in range(S)]
+    idx = {tg: i for i, tg in enumerate(tgs)}
+
+    def cls(tg):
+        return idx[(0, 0, 0)] if (tg[1] == 0 and not use_context_blanks) else idx[tg]
+
+    arcs = []
+    for i1, s1 in enumerate(tgs):
+        if s1 != (0, 0, 0):
+            arcs.append((i1, i1, cls(s1), 0, 0.0))
+        base = (s1[0], s1[2]) if s1[1] == 0 else (s1[1], s1[2])
+        # the reference's own iteration (:994): a set of tuples, whose order decides how compose numbers the
+        # states of a training graph (same interpreter => same order => bit-equal matrices)
+        for s2 in set(itertools.chain([base + (x,) for x in range(S)], [(s1[1], 0, s1[2])])):
+            if s2 == s1 or s2 == (0, 0, 0):
+                continue
+            if s1 != (0, 0, 0):
+                if s1[2] == 0 and s2[2] != 0:
+                    continue
+                if s2[0] == 0 and s1[0] != 0:
+                    continue
+            arcs.append((i1, idx[s2], cls(s2), s2[1], 0.0))
+    final = np.array([0.0 if tg[2] == 0 else -np.inf for tg in tgs])
+    n, arcs, final = _connected(len(tgs), arcs, final)
+    return Graph(n, _sorted_by_olabel(n, arcs), final)
 
 
 def compose_with_chain(dec, labels):
@@ -205,11 +272,11 @@ def batch_matrices(matrices, nc_weight=NC_WEIGHT):
 
 
 class GraphGen(object):
-    """Restated ``CTCGraphGen`` (fst_utils.py:546-676, :1053-1068), orders 1-2."""
+    """Restated ``CTCGraphGen`` (fst_utils.py:546-676, :1053-1068), orders 1-3."""
 
     def __init__(self, context_order, num_symbols, graph_build_args=None,
                  nc_weight=NC_WEIGHT, for_forward_only=False):
-        assert context_order in (1, 2)
+        assert context_order in (1, 2, 3)
         self.context_order = context_order
         self.num_symbols = num_symbols
         self.num_classes = num_symbols ** context_order
@@ -218,9 +285,12 @@ class GraphGen(object):
         self.graph_build_args = dict(graph_build_args or {})
         if context_order == 1:
             self.decoding_graph = mono_decoding_graph(num_symbols)
-        else:
+        elif context_order == 2:
             self.decoding_graph = bigram_decoding_graph(
                 num_symbols, **self.graph_build_args)
+        else:
+            self.decoding_graph = trigram_decoding_graph(
+                num_symbols, bool(self.graph_build_args.get("use_context_blanks", False)))
         self._dec = None
 
     def transcript(self, labels):

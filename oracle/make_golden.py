@@ -47,7 +47,15 @@ CASES = [
      [[1, 1, 2], [3, 2]]),
     ("bi_ctc_context_norm", 2, 5, {"use_contextual_blanks": True}, 1, False, 18, [18, 14],
      [[1, 2, 3], [4, 4]]),
+    # tri-char (build_ctc_trigram_decoding_fst_v2); contextual blanks: the variant whose decoding graph is
+    # input-deterministic, i.e. the one the reference can also use as a denominator
+    ("tri_ctc", 3, 4, {"use_context_blanks": True}, 0, False, 16, [16, 13],
+     [[1, 2, 2, 3], [3, 1]]),
+    ("tri_ctcg", 3, 4, {"use_context_blanks": True}, None, True, 16, [16, 12],
+     [[2, 1, 3], [1, 1, 2]]),
 ]
+
+ONLY = None  # set to a list of case names to (re)generate just those
 
 
 def _bigram_ids(labels, S):
@@ -162,7 +170,11 @@ def make_case(fu, cl, name, order, S, args, normalize_by_dim, use_den, T, lens, 
 def main():
     fu, cl = ref_loader.load()
     os.makedirs(OUT, exist_ok=True)
+    import sys
+    only = sys.argv[1:] or ONLY
     for i, case in enumerate(CASES):
+        if only and case[0] not in only:
+            continue
         out = make_case(fu, cl, *case, seed=1000 + i)
         print(case[0], "loss_f64", np.round(out["loss_f64"], 4),
               "f32-f64 grad diff %.2e" % np.abs(out["grad_f32"] - out["grad_f64"]).max(),

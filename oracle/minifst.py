@@ -157,6 +157,20 @@ class Fst(object):
     def final(self, s):
         return Weight(self.weight_type(), self._final[s])
 
+    def rmepsilon(self, connect=True):
+        """``Fst.rmepsilon()`` (in place, returns self) for the one case the reference reaches
+        (fst_utils.py:1025, ``prevent_epsilons=True``): no arc with an epsilon input AND output, so
+        nothing is removed and what remains of OpenFst's RmEpsilon is its default ``connect``
+        (inaccessible / non-coaccessible states dropped, the others renumbered in order)."""
+        for arcs in self._arcs:
+            for a in arcs:
+                if a.ilabel == 0 and a.olabel == 0:
+                    raise NotImplementedError("rmepsilon with eps:eps arcs is not restated")
+        if connect:
+            t = _connect(self)
+            self._arcs, self._final, self._start = t._arcs, t._final, t._start
+        return self
+
     def properties(self, mask, test):
         props = 0
         if mask & I_DETERMINISTIC:

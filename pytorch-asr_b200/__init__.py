@@ -17,11 +17,11 @@ from .fst_utils import (CTCGraphGen, PackedGraphs, batch_training_graph_matrices
                         collapse_frame_labels, make_full_ngram_table, padded_matrices, path_logsumexp, path_reduction)
 from .ctc_forward import postprocess_logprobs  # noqa: F401
 from .ctc_losses import (FSTLoss, FSTLossMixin, ctc_fst_global_loss, ctc_fst_loss,  # noqa: F401
-                         fst_loss, get_normalized_acts)
+                         ctc_raw_loss, ctc_raw_loss_batch, fst_loss, get_normalized_acts)
 
 __all__ = [
     "Graph", "CTCGraphGen", "PackedGraphs", "path_reduction", "path_logsumexp",
     "batch_training_graph_matrices", "padded_matrices", "make_full_ngram_table", "collapse_frame_labels",
-    "fst_loss", "ctc_fst_loss", "ctc_fst_global_loss", "get_normalized_acts",
+    "fst_loss", "ctc_fst_loss", "ctc_fst_global_loss", "ctc_raw_loss", "ctc_raw_loss_batch", "get_normalized_acts",
     "FSTLoss", "FSTLossMixin", "NORM_NONE", "NORM_SOFTMAX", "NORM_CONTEXT", "postprocess_logprobs",
 ]

@@ -23,6 +23,8 @@ EXPORTS = (
     "ctcg_graph_from_arcs", "ctcg_graph_get_info", "ctcg_graph_padded_dims",
     "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
     "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
+    "ctcg_decoder_from_arcs", "ctcg_decoder_num_states", "ctcg_decoder_graph", "ctcg_decoder_training_graphs",
+    "ctcg_decoder_free",
     "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
     "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
@@ -78,6 +80,13 @@ def lib():
     L.ctcg_viterbi_static.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp]
     L.ctcg_path_count.argtypes = [i32, vp, vp, vp, vp, C.c_size_t, vp]
     L.ctcg_scale_grad.argtypes = [vp, i32, i32, i32, vp, i32, vp]
+    L.ctcg_decoder_from_arcs.argtypes = [i32, i64, vp, vp, vp, vp, vp, vp, i32, C.POINTER(vp)]
+    L.ctcg_decoder_num_states.argtypes = [vp]
+    L.ctcg_decoder_num_states.restype = i32
+    L.ctcg_decoder_graph.argtypes = [vp, C.POINTER(vp)]
+    L.ctcg_decoder_training_graphs.argtypes = [vp, vp, vp, i32, i32, C.POINTER(vp)]
+    L.ctcg_decoder_free.argtypes = [vp]
+    L.ctcg_decoder_free.restype = None
     L.ctcg_loss_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp]
     L.ctcg_logits_post_width.argtypes = [i32, i32]
     L.ctcg_logits_post_width.restype = i32
@@ -267,6 +276,59 @@ class Graph(object):
 
 # ---------------------------------------------------------------------------
 _workspaces = {}
+
+
+class Decoder(object):
+    """A decoding graph given arc by arc with output labels (``ctcg_decoder_*``): the tri-char
+    topologies and anything else the two built-in topologies do not cover."""
+
+    def __init__(self, n_states, arcs, final, connect=True):
+        """``arcs``: (n, 5) integers ``src, dst, class label, emitted symbol (0 = none), 0`` in insertion
+        order, or a tuple of five arrays (the fifth, weights, may be None); ``final``: n floats."""
+        if isinstance(arcs, tuple):
+            src, dst, lab, olab, w = arcs
+        else:
+            a = np.asarray(arcs, dtype=np.int64).reshape(-1, 5)
+            src, dst, lab, olab, w = a[:, 0], a[:, 1], a[:, 2], a[:, 3], None
+        a32 = lambda x: np.ascontiguousarray(np.asarray(x, dtype=np.int32))  # noqa: E731
+        src, dst, lab, olab = a32(src), a32(dst), a32(lab), a32(olab)
+        w = None if w is None else np.ascontiguousarray(np.asarray(w, dtype=np.float32))
+        fin = np.ascontiguousarray(np.asarray(final, dtype=np.float32))
+        assert fin.shape[0] == n_states
+        out = C.c_void_p()
+        check(lib().ctcg_decoder_from_arcs(int(n_states), int(src.shape[0]), _np_ptr(src), _np_ptr(dst), _np_ptr(lab),
+                                           _np_ptr(olab), _np_ptr(w) if w is not None else None, _np_ptr(fin),
+                                           int(bool(connect)), C.byref(out)))
+        self._ptr = out
+
+    @property
+    def num_states(self):
+        return int(lib().ctcg_decoder_num_states(self._ptr))
+
+    def graph(self):
+        """The decoding (denominator) graph; ``ValueError`` when it is not input-deterministic."""
+        out = C.c_void_p()
+        check(lib().ctcg_decoder_graph(self._ptr, C.byref(out)))
+        return Graph(out)
+
+    def training(self, label_seqs, modulo=0):
+        seqs = [np.asarray(s, dtype=np.int64).reshape(-1) for s in label_seqs]
+        offsets = np.zeros(len(seqs) + 1, dtype=np.int64)
+        for i, s in enumerate(seqs):
+            offsets[i + 1] = offsets[i] + len(s)
+        flat = np.ascontiguousarray((np.concatenate(seqs) if seqs else np.zeros(0, np.int64)).astype(np.int32))
+        out = C.c_void_p()
+        check(lib().ctcg_decoder_training_graphs(self._ptr, _np_ptr(flat), _np_ptr(offsets), len(seqs), int(modulo),
+                                                 C.byref(out)))
+        return Graph(out)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_ptr", None):
+                lib().ctcg_decoder_free(self._ptr)
+                self._ptr = None
+        except Exception:
+            pass
 
 
 def _workspace(device, nbytes):

@@ -176,6 +176,155 @@ int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels, const
   }
 }
 
+// ---- decoding graphs given as arcs WITH output labels (tri-char and other topologies built by the caller) ----
+}  // extern "C"
+
+struct ctcg_decoder {
+  RawGraph g;
+  std::vector<std::vector<int32_t>> out;
+  OlabelIndex oi;
+};
+
+extern "C" {
+
+int ctcg_decoder_from_arcs(int32_t n_states, int64_t n_arcs, const int32_t* src, const int32_t* dst,
+                           const int32_t* label, const int32_t* olabel, const float* weight,
+                           const float* final_w, int32_t connect, ctcg_decoder** out) {
+  if (n_states < 1 || n_arcs < 0 || !final_w || !out || (n_arcs > 0 && (!src || !dst || !label || !olabel))) return CTCG_EINVAL;
+  try {
+    std::unique_ptr<ctcg_decoder> d(new ctcg_decoder());
+    RawGraph& r = d->g;
+    r.n = n_states;
+    r.final_w.resize(n_states);
+    for (int32_t s = 0; s < n_states; ++s) r.final_w[s] = (final_w[s] > kDeadWeight) ? final_w[s] : kNegInf;
+    r.arcs.reserve(static_cast<size_t>(n_arcs));
+    for (int64_t i = 0; i < n_arcs; ++i) {
+      if (src[i] < 0 || src[i] >= n_states || dst[i] < 0 || dst[i] >= n_states || olabel[i] < 0) return CTCG_EINVAL;
+      if (label[i] < 0) return CTCG_EEPS;
+      r.arcs.push_back({src[i], dst[i], label[i], weight ? weight[i] : 0.f, olabel[i]});
+    }
+    if (connect) {
+      // OpenFst Connect (what Fst.rmepsilon() leaves of itself on a graph without eps:eps arcs,
+      // fst_utils.py:1025): keep the states that are accessible from state 0 AND can reach a final
+      // state, renumber them in increasing order, keep the arcs in their order
+      const int32_t n = r.n;
+      std::vector<int32_t> ptr(n + 1, 0), rptr(n + 1, 0);
+      for (const Arc& a : r.arcs) {
+        ptr[a.src + 1]++;
+        rptr[a.dst + 1]++;
+      }
+      for (int32_t s = 0; s < n; ++s) {
+        ptr[s + 1] += ptr[s];
+        rptr[s + 1] += rptr[s];
+      }
+      std::vector<int32_t> fwd(r.arcs.size()), bwd(r.arcs.size()), fc(ptr.begin(), ptr.end() - 1), bc(rptr.begin(), rptr.end() - 1);
+      for (const Arc& a : r.arcs) {
+        fwd[fc[a.src]++] = a.dst;
+        bwd[bc[a.dst]++] = a.src;
+      }
+      std::vector<char> acc(n, 0), co(n, 0);
+      std::vector<int32_t> stack{0};
+      acc[0] = 1;
+      while (!stack.empty()) {
+        const int32_t s = stack.back();
+        stack.pop_back();
+        for (int32_t i = ptr[s]; i < ptr[s + 1]; ++i)
+          if (!acc[fwd[i]]) {
+            acc[fwd[i]] = 1;
+            stack.push_back(fwd[i]);
+          }
+      }
+      for (int32_t s = 0; s < n; ++s)
+        if (r.final_w[s] > kDeadWeight) {
+          co[s] = 1;
+          stack.push_back(s);
+        }
+      while (!stack.empty()) {
+        const int32_t s = stack.back();
+        stack.pop_back();
+        for (int32_t i = rptr[s]; i < rptr[s + 1]; ++i)
+          if (!co[bwd[i]]) {
+            co[bwd[i]] = 1;
+            stack.push_back(bwd[i]);
+          }
+      }
+      std::vector<int32_t> remap(n, -1);
+      int32_t m = 0;
+      for (int32_t s = 0; s < n; ++s)
+        if (acc[s] && co[s]) remap[s] = m++;
+      if (m == 0 || remap[0] != 0) return CTCG_ESTART;
+      RawGraph t;
+      t.n = m;
+      t.final_w.resize(m);
+      for (int32_t s = 0; s < n; ++s)
+        if (remap[s] >= 0) t.final_w[remap[s]] = r.final_w[s];
+      for (const Arc& a : r.arcs)
+        if (remap[a.src] >= 0 && remap[a.dst] >= 0) t.arcs.push_back({remap[a.src], remap[a.dst], a.label, a.weight, a.olabel});
+      r = std::move(t);
+    }
+    // arcsort('olabel'), stable: the order compose visits the arcs in, hence the state numbering of the
+    // training graphs (fst_utils.py:1030, :603-605)
+    std::stable_sort(r.arcs.begin(), r.arcs.end(), [](const Arc& a, const Arc& b) {
+      if (a.src != b.src) return a.src < b.src;
+      return a.olabel < b.olabel;
+    });
+    index_out_arcs(r, &d->out);
+    index_olabels(r, d->out, &d->oi);
+    *out = d.release();
+    return CTCG_OK;
+  } catch (const std::bad_alloc&) {
+    return CTCG_ENOMEM;
+  }
+}
+
+int32_t ctcg_decoder_num_states(const ctcg_decoder* d) { return d ? d->g.n : 0; }
+
+int ctcg_decoder_graph(const ctcg_decoder* d, ctcg_graph** out) {
+  if (!d || !out) return CTCG_EINVAL;
+  try {
+    std::vector<RawGraph> gs(1, d->g);
+    return finalize_graphs(gs, out);  // CTCG_ENONDET when two arcs of a state share a class (fst_utils.py:250-252)
+  } catch (const std::bad_alloc&) {
+    return CTCG_ENOMEM;
+  }
+}
+
+int ctcg_decoder_training_graphs(const ctcg_decoder* d, const int32_t* labels, const int64_t* offsets, int32_t B,
+                                 int32_t modulo, ctcg_graph** out) {
+  if (!d || !offsets || !out || B < 0) return CTCG_EINVAL;
+  try {
+    std::vector<RawGraph> gs(B);
+    std::vector<int> status(B, CTCG_OK);
+    for (int32_t b = 0; b < B; ++b)
+      if (offsets[b + 1] < offsets[b]) return CTCG_EINVAL;
+    parallel_for(B, [&](int32_t b) {
+      try {
+        std::vector<int32_t> lab(labels + offsets[b], labels + offsets[b + 1]);
+        bool any_big = false;  // fst_utils.py:595-596: a transcript holding any id above S is taken modulo S
+        for (int32_t v : lab) {
+          if (v < 0) {
+            status[b] = CTCG_EINVAL;
+            return;
+          }
+          any_big |= modulo > 0 && v > modulo;
+        }
+        if (any_big)
+          for (int32_t& v : lab) v %= modulo;
+        status[b] = compose_with_chain(d->g, d->out, lab.data(), static_cast<int64_t>(lab.size()), &gs[b], &d->oi);
+      } catch (const std::bad_alloc&) {
+        status[b] = CTCG_ENOMEM;
+      }
+    });
+    for (int32_t b = 0; b < B; ++b)
+      if (status[b] != CTCG_OK) return status[b];
+    return finalize_graphs(gs, out);
+  } catch (const std::bad_alloc&) {
+    return CTCG_ENOMEM;
+  }
+}
+
+void ctcg_decoder_free(ctcg_decoder* d) { delete d; }
+
 int ctcg_graph_from_padded(const int64_t* pred, const int64_t* lab_in, const float* w_in,
                            const float* final_w, const int64_t* succ, const int64_t* lab_out,
                            const float* w_out, int32_t G, int32_t N, int32_t K_in, int32_t K_out,

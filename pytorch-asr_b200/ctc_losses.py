@@ -153,6 +153,93 @@ def ctc_fst_global_loss(acts, labels, act_lens, label_lens, num_symbols=0, conte
     return _FstLoss.apply(acts, _check_lens(act_lens), num, den, _lib.NORM_NONE, 0)
 
 
+def dense_ctc_graph(labels, S, context_order, allow_nonblank_selfloops=True, eval_repeats_in_context=False):
+    """The state machine of ``get_CTC_matrices_mono`` / ``get_CTC_matrices_bicontext`` (ctc_losses.py:67-94,
+    :111-166) run by ``RawGenericCTC`` (:268-324) as an arc graph for the path-sum kernels: dense states
+    [blank_0, tok_0, blank_1, ..., tok_{U-1}, blank_U] emit on the STATE, so state j becomes node j+1 and
+    every transition i -> j an arc labelled with j's emission; node 0 is a start node with arcs to the
+    two entry states (``enter_first_num=2``), the last two states are final (``terminal_last_num=2``).
+    Returns ``(n_nodes, arcs [(src, dst, label, 0.0)], final)``.  This is NOT the FST topology for
+    bi-char transcripts with a repeated letter (the dense definition forbids tok -> tok there)."""
+    L = [int(v) % S for v in labels]
+    U = len(L)
+    N = 2 * U + 1
+    emit = [0] * N
+    trans = []
+    if context_order == 1:
+        trans += [(0, 0), (0, 1)] if U else [(0, 0)]
+        for i, l in enumerate(L):
+            tok = 2 * i + 1
+            emit[tok] = l
+            trans += [(tok, tok), (tok, tok + 1), (tok + 1, tok + 1)]
+            if tok + 2 < N:
+                trans.append((tok + 1, tok + 2))
+                if L[i + 1] != l:
+                    trans.append((tok, tok + 2))
+    else:
+        context = 0
+        for i, li in enumerate(L):
+            blank, tok = 2 * i, 2 * i + 1
+            emit[blank] = context * S
+            emit[tok] = context * S + li
+            trans += [(blank, blank), (blank, tok)]
+            if allow_nonblank_selfloops:
+                trans.append((tok, tok))
+            trans.append((tok, tok + 1))
+            if tok + 2 < N:
+                rep = ((context * S + li) == (li * S + L[i + 1])) if eval_repeats_in_context else (li == L[i + 1])
+                if not rep:
+                    trans.append((tok, tok + 2))
+            context = li
+        emit[N - 1] = context * S
+        trans.append((N - 1, N - 1))
+    arcs = [(0, j + 1, emit[j], 0.0) for j in range(min(2, N))]
+    arcs += [(i + 1, j + 1, emit[j], 0.0) for (i, j) in trans]
+    final = np.full(N + 1, -np.inf, dtype=np.float32)
+    final[max(1, N - 1):] = 0.0
+    return N + 1, arcs, final
+
+
+def ctc_raw_loss(acts, labels, act_lens, label_lens, num_symbols=0, context_order=1, normalize_by_dim=None,
+                 allow_nonblank_selfloops=True, loop_using_symbol_repetitions=False,
+                 eval_repeats_in_context=False, other_data_in_batch=None, **kwargs):
+    """ctc_losses.py:521-560, the plugin driver of the dense route: ``get_normalized_acts``, then per
+    utterance ``RawGenericCTC`` on the matrices of ``get_CTC_matrices_mono`` / ``_bicontext`` -- whose
+    mean over frames of ``-logsum(lPB + alpha + beta)`` is the negative log-likelihood of that state
+    machine.  Same signature and assertions; the state machines are compiled to arc graphs on the host
+    (:func:`dense_ctc_graph`) and summed by the fused kernels instead of O(T N^2) numpy in fp64."""
+    assert not other_data_in_batch
+    S = acts.size(2)
+    if context_order == 1:
+        assert allow_nonblank_selfloops and not loop_using_symbol_repetitions and not eval_repeats_in_context
+        mode, ns = (_lib.NORM_SOFTMAX, 0) if not normalize_by_dim else (_lib.NORM_CONTEXT, int(num_symbols or S))
+    else:
+        assert context_order == 2
+        assert normalize_by_dim == 1
+        assert num_symbols > 0
+        S = int(round(np.sqrt(S)))
+        mode, ns = _lib.NORM_CONTEXT, int(num_symbols)
+        if loop_using_symbol_repetitions:
+            raise NotImplementedError("get_CTC_matrices_bicontext_looprepeats (ctc_losses.py:169-226) is not restated")
+    seqs = _labels_to_batch(labels, label_lens)
+    graphs = [dense_ctc_graph(q, S, context_order, allow_nonblank_selfloops, eval_repeats_in_context) for q in seqs]
+    num = _lib.Graph.from_arcs(graphs)
+    return _FstLoss.apply(acts, _check_lens(act_lens), num, None, mode, ns)
+
+
+def ctc_raw_loss_batch(acts, labels, act_lens, label_lens, num_symbols=0, context_order=1,
+                       normalize_by_dim=None, allow_nonblank_selfloops=True,
+                       loop_using_symbol_repetitions=False, eval_repeats_in_context=False,
+                       other_data_in_batch=None, **kwargs):
+    """ctc_losses.py:563-609 (``RawGenericCTCBatch``): the batched form of :func:`ctc_raw_loss`."""
+    assert not (eval_repeats_in_context and loop_using_symbol_repetitions)
+    if context_order == 1:
+        assert not loop_using_symbol_repetitions
+    return ctc_raw_loss(acts, labels, act_lens, label_lens, num_symbols, context_order, normalize_by_dim,
+                        allow_nonblank_selfloops, loop_using_symbol_repetitions, eval_repeats_in_context,
+                        other_data_in_batch, **kwargs)
+
+
 class FSTLossMixin(object):
     """Drop-in replacement of ``FSTDecoder.get_fst_loss`` / ``forward`` / ``logits``.
 

@@ -15,14 +15,16 @@ runs in its C++ graph compiler (no OpenFst).  No CPU fallback.
 """
 from __future__ import annotations
 
+import bisect
 import collections
+import itertools
 import weakref
 
 import numpy as np
 import torch
 
 from . import _lib
-from ._lib import Graph
+from ._lib import Decoder, Graph
 
 
 class PackedGraphs(list):
@@ -254,6 +256,50 @@ def setattr_matched(obj, var, val):
         setattr(obj, var, val)
 
 
+def trigram_decoding_arcs(trigrams, use_context_blanks=False, prevent_epsilons=True):
+    """The arcs of ``build_ctc_trigram_decoding_fst_v2`` (fst_utils.py:926-1050) before its ``rmepsilon``
+    and ``arcsort``: states are the sorted trigrams (c0, c1, c2), final when c2 is the blank, class of a
+    trigram = its state index (the shared blank class of (0,0,0) for every trigram with a blank in the
+    middle unless ``use_context_blanks``), emitted symbol = the middle letter of the target.
+    Returns ``(n_states, arcs (m, 5) int64 [src, dst, class, olabel, 0], final (n,) float32)``.
+
+    The arc ORDER decides how ``compose`` numbers the states of a training graph; the reference adds the
+    successors of a state by iterating a Python ``set`` of tuples (:994), so the same construct is used here
+    -- in one interpreter the two orders are the same, which is what makes the exported matrices bit-exact."""
+    trigrams = sorted(tuple(int(c) for c in tg) for tg in trigrams)
+    assert trigrams[0] == (0, 0, 0)
+    tg2state = {tg: i for i, tg in enumerate(trigrams)}
+
+    def in_class(tg):
+        if not use_context_blanks and tg[1] == 0:
+            return tg2state[(0, 0, 0)]
+        return tg2state[tg]
+
+    inf = float("inf")
+    arcs = []
+    for i1, s1 in enumerate(trigrams):
+        if s1 != (0, 0, 0):
+            arcs.append((i1, i1, in_class(s1), 0, 0))          # self loop, emits nothing
+        base = (s1[0], s1[2]) if s1[1] == 0 else (s1[1], s1[2])
+        lo = bisect.bisect_left(trigrams, base + (0,))
+        hi = bisect.bisect_left(trigrams, base + (inf,))
+        for s2 in set(itertools.chain(trigrams[lo:hi], [(s1[1], 0, s1[2])])):
+            if s1 == s2 or s2 == (0, 0, 0):
+                continue
+            if s1 != (0, 0, 0):
+                if s1[-1] == 0 and s2[-1] != 0:                 # after the final blank: terminate
+                    continue
+                if s2[0] == 0 and s1[0] != 0:                   # no starting blank except at the start
+                    continue
+            if s2 not in tg2state:
+                continue
+            if s1 == (0, 0, 0) and not prevent_epsilons:
+                raise NotImplementedError("prevent_epsilons=False needs OpenFst's rmepsilon")
+            arcs.append((i1, tg2state[s2], in_class(s2), int(s2[1]), 0))
+    final = np.array([0.0 if tg[-1] == 0 else -np.inf for tg in trigrams], dtype=np.float32)
+    return len(trigrams), np.asarray(arcs, dtype=np.int64).reshape(-1, 5), final
+
+
 class BaseGraphGen(object):
     """fst_utils.py:546-676 without OpenFst; ``grammar_fst`` is not supported
     (it needs an OpenFst binary-file reader: SURVEY 8f #4)."""
@@ -294,7 +340,7 @@ class BaseGraphGen(object):
         if self._dec_fst is None:
             self._dec_fst = self._to_openfst()
             if self._dec_fst is None:
-                self._dec_fst = self._dec
+                self._dec_fst = self.get_decoding_graph()
         return self._dec_fst
 
     def _to_openfst(self, arc_type="log"):
@@ -381,17 +427,68 @@ class BaseGraphGen(object):
 
 
 class CTCGraphGen(BaseGraphGen):
-    """fst_utils.py:1053-1068 (context orders 1 and 2)."""
+    """fst_utils.py:1053-1068: mono-char, bi-char and tri-char CTC topologies."""
 
     def __init__(self, context_order=None, graph_build_args=None, **kwargs):
         assert context_order in (1, 2, 3)
-        if context_order == 3:
-            raise NotImplementedError("tri-char topologies enter through Graph.from_arcs")
         self.graph_build_args = graph_build_args or {}
+        self._decoder = None
         super(CTCGraphGen, self).__init__(context_order=context_order, **kwargs)
 
     def _build_args(self):
         return self.graph_build_args if self.context_order == 2 else {}
 
     def get_hc_fst(self):
-        return Graph.decoding(self.context_order, self.num_symbols, **self._build_args())
+        if self.context_order < 3:
+            return Graph.decoding(self.context_order, self.num_symbols, **self._build_args())
+        # build_ctc_trigram_decoding_fst_v2(S, self.ngrams, **graph_build_args), :926-1050
+        args = dict(self.graph_build_args)
+        if args.pop("determinize", False):
+            raise NotImplementedError("determinize=True needs OpenFst's determinize")
+        args.pop("add_syms", None)
+        n, arcs, final = trigram_decoding_arcs(self.ngrams, **args)
+        self._tri = (arcs, final)
+        self._decoder = Decoder(n, arcs, final, connect=True)   # rmepsilon() on a graph without eps:eps arcs
+        return None                                              # the decoding graph is made on demand (may not exist)
+
+    def get_decoding_graph(self):
+        if self.context_order == 3 and self._dec is None:
+            # ValueError("FST is not deterministic") for the shared-blank-class variant, where the reference's
+            # get_decoding_matrices raises too (fst_utils.py:250-252): that topology is numerator-only
+            self._dec = self._decoder.graph()
+        return self._dec
+
+    def get_training_graphs(self, label_seqs):
+        if self.context_order < 3:
+            return super(CTCGraphGen, self).get_training_graphs(label_seqs)
+        return self._decoder.training(label_seqs, modulo=self.num_symbols)
+
+    def get_decoding_matrices(self, device="cpu", out_edges=False):
+        self.get_decoding_graph()
+        return super(CTCGraphGen, self).get_decoding_matrices(device, out_edges)
+
+    def collapse(self, frame_labels):
+        if self.context_order < 3:
+            return super(CTCGraphGen, self).collapse(frame_labels)
+        raise NotImplementedError("collapse of tri-char frame labels: walk decoding_fst (needs pywrapfst)")
+
+    def _to_openfst(self, arc_type="log"):
+        if self.context_order < 3:
+            return super(CTCGraphGen, self)._to_openfst(arc_type)
+        try:
+            import pywrapfst as fst
+        except ImportError:
+            return None
+        arcs, final = self._tri
+        f = fst.Fst(arc_type=arc_type)
+        one = fst.Weight.One(f.weight_type())
+        for st in range(final.shape[0]):
+            assert f.add_state() == st
+            if final[st] == 0:
+                f.set_final(st)
+        f.set_start(0)
+        for src, dst, cls, out, _ in arcs.tolist():
+            f.add_arc(src, fst.Arc(cls + 1, out, one, dst))
+        f = f.rmepsilon()
+        f.arcsort("olabel")
+        return f

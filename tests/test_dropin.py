@@ -111,3 +111,42 @@ def test_padded_matrices_carry_their_graph_and_shared_graphs_are_imported_once(l
     dm = [np.array(m, copy=True) for m in ogen.get_decoding_matrices()]
     dm[2][0, 3, 0] = -0.5
     assert P.Graph.from_padded([torch.as_tensor(m) for m in dm]).info().structured == 0
+
+
+@needs_ref
+@pytest.mark.parametrize("S,args", [(4, {}), (5, {"use_context_blanks": True}), (6, {})])
+def test_trichar_graphs_equal_the_reference(lib_built, S, args):
+    """``CTCGraphGen(context_order=3)`` (build_ctc_trigram_decoding_fst_v2, fst_utils.py:926-1050): decoding FST,
+    training matrices and -- where the graph is input-deterministic -- decoding matrices, bit-exact against the
+    reference's own generator run on the oracle's OpenFst stand-in."""
+    import contextlib
+    import io
+    P = lib_built
+    fu, _ = ref_loader.load()
+    with contextlib.redirect_stdout(io.StringIO()):          # the reference prints its progress
+        rgen = fu.CTCGraphGen(context_order=3, graph_build_args=dict(args), num_symbols=S)
+    gen = P.CTCGraphGen(context_order=3, graph_build_args=dict(args), num_symbols=S)
+    assert gen.num_classes == rgen.num_classes == S ** 3
+
+    def arcs(f):
+        return [(s, a.ilabel, a.olabel, a.nextstate) for s in f.states() for a in f.arcs(s)]
+    mine, want = gen.decoding_fst, rgen.decoding_fst
+    assert mine.num_states() == want.num_states()
+    assert arcs(mine) == arcs(want)                          # same arcs in the same order
+    assert [mine.final(s) == want.final(s) for s in mine.states()]
+    rng = np.random.default_rng(S)
+    for _ in range(4):
+        labels = rng.integers(1, S, size=int(rng.integers(1, 7)))
+        want_m = rgen.get_training_matrices(torch.as_tensor(labels))
+        got_m = gen.get_training_matrices(torch.as_tensor(labels))
+        assert len(got_m) == len(want_m) == 8
+        for a, b in zip(got_m, want_m):
+            assert a.dtype == b.dtype and torch.equal(a, b)
+    if args.get("use_context_blanks"):
+        for a, b in zip(gen.get_decoding_matrices(), rgen.get_decoding_matrices("cpu")):
+            assert torch.equal(a, b)
+    else:                                                    # shared blank class: numerator only, in both
+        with pytest.raises(ValueError):
+            rgen.get_decoding_matrices("cpu")
+        with pytest.raises(ValueError):
+            gen.get_decoding_matrices()

@@ -585,3 +585,28 @@ def test_factorised_viterbi_equals_the_generic_kernel(P, S, args, T, B):
     assert np.array_equal(out["factorised"][1], out["generic"][1])
     assert _rel(out["factorised"][0], out["generic"][0]) < 1e-6
     _record("viterbi_S%d_T%d_B%d_ms" % (S, T, B), {"factorised": out["factorised"][2], "generic": out["generic"][2]})
+
+
+@pytest.mark.parametrize("name,fn", [("mono_ctc", "ctc_raw_loss"), ("mono_ctc", "ctc_raw_loss_batch"),
+                                     ("bi_ctc_context_norm", "ctc_raw_loss"), ("bi_ctc_context_norm", "ctc_raw_loss_batch")])
+def test_dense_route_plugin_drivers_match_raw_generic_ctc(P, name, fn):
+    """``ctc_loss_fn: ctc_raw_loss`` / ``ctc_raw_loss_batch`` (ctc_losses.py:521-609, resolved by name at
+    advanced_decoder.py:238): same signature, and the values the reference's own ``RawGenericCTC`` (numpy
+    fp64, :268-324) returned on these inputs (fixture key ``raw_generic_ctc``)."""
+    d = load_golden(name)
+    x = torch.as_tensor(d["logits"]).cuda().requires_grad_(True)
+    labels_cat = torch.as_tensor(np.concatenate([np.asarray(s) for s in d["label_seqs"]]))
+    loss = getattr(P, fn)(x, labels_cat, torch.tensor(d["lens"]), torch.tensor(d["text_lens"]),
+                          d["S"], d["order"], d["normalize_by_dim"], True, False)
+    loss.sum().backward()
+    assert _rel(loss.detach().cpu(), d["raw_generic_ctc"]) < LOSS_RTOL
+    # gradient: the fp64 oracle on the same state machines (the dense bi-context topology is not the FST one
+    # when a letter repeats, so the FST-route fixture gradient does not apply)
+    import importlib
+    cl = importlib.import_module(P.FSTLoss.__module__)
+    g = P.Graph.from_arcs([cl.dense_ctc_graph(q, d["S"], d["order"]) for q in d["label_seqs"]])
+    nm = P.batch_training_graph_matrices([P.padded_matrices(g, i) for i in range(g.num_graphs)])
+    want_loss, want_grad = engine.fst_loss(d["logits"], d["lens"].tolist(), [m.numpy() for m in nm], None,
+                                           d["normalize_by_dim"], d["S"], d["order"], dtype=torch.float64)
+    assert _rel(want_loss.numpy(), d["raw_generic_ctc"]) < 1e-6      # the reference returns it rounded to fp32
+    assert np.abs(x.grad.cpu().double().numpy() - want_grad.numpy()).max() < GRAD_ATOL

@@ -15,7 +15,7 @@ from oracle import graphs
 def test_library_exports_every_declared_symbol(lib_built):
     P = lib_built
     header = open(os.path.join(ROOT, "include", "ctcg_b200.h")).read()
-    declared = set(re.findall(r"^(?:int|void|size_t|uint64_t|const char\*)\s+(ctcg_[a-z_0-9]+)\s*\(", header, re.M))
+    declared = set(re.findall(r"^(?:int|int32_t|void|size_t|uint64_t|const char\*)\s+(ctcg_[a-z_0-9]+)\s*\(", header, re.M))
     assert declared == set(P._lib.EXPORTS)
     L = P._lib.lib()
     for name in declared:
