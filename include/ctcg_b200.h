@@ -100,6 +100,13 @@ int ctcg_decoding_graph(const ctcg_topology* topo, ctcg_graph** out);
 int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels,
                          const int64_t* offsets, int32_t B, ctcg_graph** out);
 
+/* ctcg_training_graphs keeps the composed graph of every (topology, transcript) it
+ * has built (bounded, first in first out; CTCG_GRAPH_CACHE=<entries>, default
+ * 16384, 0 = off): the reference recomputes a transcript's matrices every epoch
+ * (data/kaldi_dataset.py:63-66, 230-232).  Counters since the last clear. */
+void ctcg_graph_cache_info(uint64_t* hits, uint64_t* misses, uint64_t* entries);
+void ctcg_graph_cache_clear(void);
+
 /* Decoding graphs the caller builds arc by arc WITH output labels -- the
  * tri-char topologies (build_ctc_trigram_decoding_fst_v2, fst_utils.py:926-1050)
  * and anything else that is not one of the two built-in topologies.  Arcs in the

@@ -24,7 +24,7 @@ EXPORTS = (
     "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
     "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
     "ctcg_decoder_from_arcs", "ctcg_decoder_num_states", "ctcg_decoder_graph", "ctcg_decoder_training_graphs",
-    "ctcg_decoder_free",
+    "ctcg_decoder_free", "ctcg_graph_cache_info", "ctcg_graph_cache_clear",
     "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
     "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
@@ -87,6 +87,10 @@ def lib():
     L.ctcg_decoder_training_graphs.argtypes = [vp, vp, vp, i32, i32, C.POINTER(vp)]
     L.ctcg_decoder_free.argtypes = [vp]
     L.ctcg_decoder_free.restype = None
+    L.ctcg_graph_cache_info.argtypes = [C.POINTER(C.c_uint64)] * 3
+    L.ctcg_graph_cache_info.restype = None
+    L.ctcg_graph_cache_clear.argtypes = []
+    L.ctcg_graph_cache_clear.restype = None
     L.ctcg_loss_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp]
     L.ctcg_logits_post_width.argtypes = [i32, i32]
     L.ctcg_logits_post_width.restype = i32
@@ -276,6 +280,17 @@ class Graph(object):
 
 # ---------------------------------------------------------------------------
 _workspaces = {}
+
+
+def graph_cache_info():
+    """``(hits, misses, entries)`` of the per-transcript cache of composed training graphs."""
+    h, m, n = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    lib().ctcg_graph_cache_info(C.byref(h), C.byref(m), C.byref(n))
+    return int(h.value), int(m.value), int(n.value)
+
+
+def graph_cache_clear():
+    lib().ctcg_graph_cache_clear()
 
 
 class Decoder(object):

@@ -6,6 +6,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <map>
+#include <deque>
+#include <unordered_map>
+#include <string>
 #include <memory>
 #include <mutex>
 #include <new>
@@ -47,6 +50,32 @@ std::shared_ptr<const CachedDecoding> cached_decoding(const ctcg_topology& t, in
   index_olabels(c->g, c->out, &c->oi);
   cache[key] = c;
   return c;
+}
+
+// Composed training graphs, per (topology, transcript): the same transcripts come back every epoch
+// (kaldi_dataset.py:63-66, 230-232 recomputes them per item per epoch), so the product construction is
+// done once.  Bounded, first-in first-out; CTCG_GRAPH_CACHE=<entries> (default 16384, about 12 KB each at
+// U = 100; 0 turns it off).
+struct TrainingCache {
+  std::mutex mu;
+  std::unordered_map<std::string, std::shared_ptr<const RawGraph>> map;
+  std::deque<std::string> order;
+  uint64_t hits = 0, misses = 0;
+  size_t capacity = [] {
+    const char* e = std::getenv("CTCG_GRAPH_CACHE");
+    return e ? static_cast<size_t>(std::max(0L, std::atol(e))) : size_t{16384};
+  }();
+};
+TrainingCache& training_cache() {
+  static TrainingCache c;
+  return c;
+}
+std::string cache_key(const ctcg_topology& t, const std::vector<int32_t>& lab) {
+  const int32_t head[5] = {t.context_order, t.num_symbols, t.allow_nonblank_selfloops != 0,
+                           t.use_contextual_blanks != 0, t.loop_using_symbol_repetitions != 0};
+  std::string k(reinterpret_cast<const char*>(head), sizeof(head));
+  k.append(reinterpret_cast<const char*>(lab.data()), lab.size() * sizeof(int32_t));
+  return k;
 }
 
 void mark_structured(const ctcg_topology& t, ctcg_graph* g) {
@@ -107,6 +136,22 @@ void recognise_bichar(const RawGraph& r, ctcg_graph* g) {
 
 extern "C" {
 
+void ctcg_graph_cache_info(uint64_t* hits, uint64_t* misses, uint64_t* entries) {
+  TrainingCache& tc = training_cache();
+  std::lock_guard<std::mutex> lock(tc.mu);
+  if (hits) *hits = tc.hits;
+  if (misses) *misses = tc.misses;
+  if (entries) *entries = tc.map.size();
+}
+
+void ctcg_graph_cache_clear(void) {
+  TrainingCache& tc = training_cache();
+  std::lock_guard<std::mutex> lock(tc.mu);
+  tc.map.clear();
+  tc.order.clear();
+  tc.hits = tc.misses = 0;
+}
+
 void ctcg_graph_set_generic(ctcg_graph* g) {
   if (g) g->structured = ctcg::Structured{0, 0, 0, 0, 0};
 }
@@ -155,7 +200,38 @@ int ctcg_training_graphs(const ctcg_topology* topo, const int32_t* labels, const
         }
         if (any_big)
           for (int32_t& v : lab) v %= S;
+        TrainingCache& tc = training_cache();
+        std::string key;
+        if (tc.capacity > 0) {
+          key = cache_key(*topo, lab);
+          std::shared_ptr<const RawGraph> hit;
+          {
+            std::lock_guard<std::mutex> lock(tc.mu);
+            auto it = tc.map.find(key);
+            if (it != tc.map.end()) {
+              hit = it->second;
+              ++tc.hits;
+            } else {
+              ++tc.misses;
+            }
+          }
+          if (hit) {
+            gs[b] = *hit;
+            return;
+          }
+        }
         status[b] = compose_with_chain(dec, dec_out, lab.data(), static_cast<int64_t>(lab.size()), &gs[b], &cached->oi);
+        if (status[b] == CTCG_OK && tc.capacity > 0) {
+          auto copy = std::make_shared<const RawGraph>(gs[b]);
+          std::lock_guard<std::mutex> lock(tc.mu);
+          if (tc.map.emplace(key, std::move(copy)).second) {
+            tc.order.push_back(key);
+            while (tc.order.size() > tc.capacity) {
+              tc.map.erase(tc.order.front());
+              tc.order.pop_front();
+            }
+          }
+        }
       } catch (const std::bad_alloc&) {
         status[b] = CTCG_ENOMEM;
       }

@@ -55,6 +55,11 @@ class TaggedMatrices(list):
         super(TaggedMatrices, self).__init__(mats)
         self._ctcg_graph = graph
 
+    def __reduce__(self):
+        # DataLoader workers are processes (num_workers=4, ctc.yaml:62): the matrices travel, the native
+        # handle does not -- the receiving side converts them like any of the reference's own matrices
+        return (list, (list(self),))
+
 
 def padded_matrices(graph, index=0, nc_weight=-1e20, for_forward_only=False, device="cpu"):
     """The reference's 4/8 matrices for one graph (``fst_to_matrices`` encoding)."""

@@ -105,3 +105,28 @@ def test_unsorted_lengths_are_rejected_like_the_reference(lib_built):
     num = gen.get_training_graphs([[1], [2]])
     with pytest.raises(AssertionError):                 # fst_utils.py:382,432
         P.path_reduction(torch.randn(6, 2, 5), torch.tensor([4, 6]), num)
+
+
+def test_training_graph_cache_and_pickling_of_tagged_matrices(lib_built):
+    """Rest of SURVEY f1: transcripts seen before are not composed again (the reference recomputes them every
+    epoch, kaldi_dataset.py:63-66, 230-232), and matrices made in a DataLoader worker survive the trip."""
+    import pickle
+    P = lib_built
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=9)
+    rng = np.random.default_rng(4)
+    seqs = [rng.integers(1, 9, size=n).tolist() for n in (7, 5, 5, 3)]
+    P._lib.graph_cache_clear()
+    g1 = gen.get_training_graphs(seqs)
+    h, m, n = P._lib.graph_cache_info()
+    assert (h, m, n) == (0, 4, 4)
+    g2 = gen.get_training_graphs(seqs[::-1])                       # another epoch, another order
+    assert P._lib.graph_cache_info()[:2] == (4, 4)
+    for i in range(4):                                             # the cached graphs are the same graphs
+        for a, b in zip(g1.export_padded(i), g2.export_padded(3 - i)):
+            assert np.array_equal(a, b)
+    other = P.CTCGraphGen(context_order=2, graph_build_args={"use_contextual_blanks": True}, num_symbols=9)
+    other.get_training_graphs(seqs[:1])                            # same transcript, other topology: a miss
+    assert P._lib.graph_cache_info()[:2] == (4, 5)
+    mats = gen.get_training_matrices(seqs[0])
+    back = pickle.loads(pickle.dumps(mats))
+    assert type(back) is list and all(torch.equal(a, b) for a, b in zip(mats, back))
