@@ -610,3 +610,54 @@ def test_dense_route_plugin_drivers_match_raw_generic_ctc(P, name, fn):
                                            d["normalize_by_dim"], d["S"], d["order"], dtype=torch.float64)
     assert _rel(want_loss.numpy(), d["raw_generic_ctc"]) < 1e-6      # the reference returns it rounded to fp32
     assert np.abs(x.grad.cpu().double().numpy() - want_grad.numpy()).max() < GRAD_ATOL
+
+
+@pytest.mark.parametrize("order,S,args,use_den,nbd,T,B", [
+    (2, 12, {}, True, None, 37, 5),                                  # CTC-G: sweeps, combine with the fold, groups off (B < 64)
+    (2, 49, {"use_contextual_blanks": True}, True, None, 45, 64),    # CTC-GB at B=64: 8 length groups
+    (2, 12, {}, False, 0, 37, 5),                                    # plain CTC: rows kernel
+    (2, 9, {"use_contextual_blanks": True}, False, 1, 30, 4),        # per-context softmax
+    (3, 4, {"use_context_blanks": True}, True, None, 33, 3),         # tri-char: generic CSR denominator
+    (1, 7, {}, True, None, 29, 4),                                   # mono-char CTC-G: generic denominator
+])
+def test_workspace_and_outputs_stay_inside_their_bounds(P, order, S, args, use_den, nbd, T, B):
+    """compute-sanitizer is closed on this pool, so the bounds are checked directly: the workspace
+    (exactly ``ctcg_workspace_bytes``), the loss and the gradient sit between guard bands of a known
+    pattern, the C entry point is called on them, and no guard byte may change; the results must equal
+    those of the normal path."""
+    rng = np.random.default_rng(T * 31 + B)
+    V = S ** order
+    lens = sorted([T] + rng.integers(int(0.6 * T), T + 1, size=B - 1).tolist(), reverse=True)
+    seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens]
+    x = torch.from_numpy((rng.standard_normal((T, B, V)) * 3).astype(np.float32)).cuda()
+    gen = P.CTCGraphGen(context_order=order, graph_build_args=args, num_symbols=S)
+    num = gen.get_training_graphs(seqs)
+    den = gen.get_decoding_graph() if use_den else None
+    mode = {None: P.NORM_NONE, 0: P.NORM_SOFTMAX, 1: P.NORM_CONTEXT}[nbd]
+    want_loss, want_grad = P._lib.loss_fwd_bwd(x, lens, num, den, mode, S)      # uploads the graphs too
+    L = P._lib.lib()
+    need = L.ctcg_workspace_bytes(T, B, V, num.ptr, den.ptr if den is not None else None)
+    G = 1 << 16                                                                  # guard bytes (keeps 16-byte alignment)
+    ws_all = torch.full((need + 2 * G,), 0xA5, dtype=torch.uint8, device="cuda")
+    out_all = torch.full((2 * G // 4 + T * B * V,), 12345.0, dtype=torch.float32, device="cuda")
+    loss_all = torch.full((2 * 64 + B,), 12345.0, dtype=torch.float32, device="cuda")
+    ws, grad, loss = ws_all[G:G + need], out_all[G // 4:G // 4 + T * B * V], loss_all[64:64 + B]
+    lens_np = np.ascontiguousarray(np.asarray(lens, dtype=np.int32))
+    for _ in range(2):                                                           # twice: stale workspace contents
+        st = L.ctcg_loss_fwd_bwd(x.data_ptr(), T, B, V, lens_np.ctypes.data, num.ptr, den.ptr if den is not None else None,
+                                 int(mode), int(S), None, loss.data_ptr(), grad.data_ptr(), ws.data_ptr(), need, None)
+        assert st == 0
+        torch.cuda.synchronize()
+        assert bool((ws_all[:G] == 0xA5).all()) and bool((ws_all[G + need:] == 0xA5).all())
+        assert bool((out_all[:G // 4] == 12345.0).all()) and bool((out_all[G // 4 + T * B * V:] == 12345.0).all())
+        assert bool((loss_all[:64] == 12345.0).all()) and bool((loss_all[64 + B:] == 12345.0).all())
+        assert torch.equal(loss, want_loss)
+        if order == 2:                                                           # factorised / rows kernels: run-to-run bit-identical
+            assert torch.equal(grad.view(T, B, V), want_grad)
+        else:                                                                    # generic denominator sums arcs with atomics
+            assert torch.allclose(grad.view(T, B, V), want_grad, rtol=0, atol=2e-6)
+    # one byte less of workspace is refused, nothing is launched
+    launches = P._lib.launch_count()
+    st = L.ctcg_loss_fwd_bwd(x.data_ptr(), T, B, V, lens_np.ctypes.data, num.ptr, den.ptr if den is not None else None,
+                             int(mode), int(S), None, loss.data_ptr(), grad.data_ptr(), ws.data_ptr(), need - 1, None)
+    assert st == 7 and P._lib.launch_count() == launches                         # CTCG_EWORKSPACE
