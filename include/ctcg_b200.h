@@ -276,6 +276,18 @@ int ctcg_loss_host(const float* logits_host, int32_t T, int32_t B, int32_t V,
                    int32_t normalize, int32_t num_symbols, float* loss_host,
                    float* grad_host);
 
+/* Host -> device copy of a (T, B, V) logits tensor that moves only the frames
+ * t < lens_host[b] (the others are never read): for a batch sorted by
+ * descending length -- the order the reference asserts, fst_utils.py:382,432 --
+ * one strided copy per run of frames with the same number of live utterances,
+ * sum(lens) * V * 4 bytes over the bus instead of T * B * V * 4; the padding of
+ * `logits_dev` is zero-filled on the device.  An unsorted batch is copied
+ * whole.  Asynchronous on `stream`; `logits_host` should be pinned.  Replaces
+ * the `.to(device)` of a host-side producer (advanced_decoder.py:458 does the
+ * same for the graph matrices); used by ctcg_loss_host. */
+int ctcg_upload_logits(const float* logits_host, int32_t T, int32_t B, int32_t V,
+                       const int32_t* lens_host, float* logits_dev, void* stream);
+
 /* ---- logits post-processing of ctc_forward.py ------------------------------ */
 
 #define CTCG_POST_TRANSFER_HASH 1   /* --transfer-hash-prob   (ctc_forward.py:96-103) */

@@ -12,7 +12,7 @@ this package).  Layout:
 * ``parallel.py``    utterance-sharded multi-GPU driver (one process per GPU)
 """
 from . import _lib  # noqa: F401
-from ._lib import Graph, NORM_CONTEXT, NORM_NONE, NORM_SOFTMAX  # noqa: F401
+from ._lib import Graph, NORM_CONTEXT, NORM_NONE, NORM_SOFTMAX, upload_logits  # noqa: F401
 from .fst_utils import (CTCGraphGen, PackedGraphs, batch_training_graph_matrices,  # noqa: F401
                         collapse_frame_labels, make_full_ngram_table, padded_matrices, path_logsumexp, path_reduction)
 from .ctc_forward import postprocess_logprobs  # noqa: F401
@@ -20,7 +20,7 @@ from .ctc_losses import (FSTLoss, FSTLossMixin, ctc_fst_global_loss, ctc_fst_los
                          ctc_raw_loss, ctc_raw_loss_batch, fst_loss, get_normalized_acts)
 
 __all__ = [
-    "Graph", "CTCGraphGen", "PackedGraphs", "path_reduction", "path_logsumexp",
+    "Graph", "upload_logits", "CTCGraphGen", "PackedGraphs", "path_reduction", "path_logsumexp",
     "batch_training_graph_matrices", "padded_matrices", "make_full_ngram_table", "collapse_frame_labels",
     "fst_loss", "ctc_fst_loss", "ctc_fst_global_loss", "ctc_raw_loss", "ctc_raw_loss_batch", "get_normalized_acts",
     "FSTLoss", "FSTLossMixin", "NORM_NONE", "NORM_SOFTMAX", "NORM_CONTEXT", "postprocess_logprobs",

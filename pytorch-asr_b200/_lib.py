@@ -25,7 +25,7 @@ EXPORTS = (
     "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
     "ctcg_decoder_from_arcs", "ctcg_decoder_num_states", "ctcg_decoder_graph", "ctcg_decoder_training_graphs",
     "ctcg_decoder_free", "ctcg_graph_cache_info", "ctcg_graph_cache_clear",
-    "ctcg_path_count", "ctcg_loss_host", "ctcg_strerror", "ctcg_launch_count",
+    "ctcg_path_count", "ctcg_loss_host", "ctcg_upload_logits", "ctcg_strerror", "ctcg_launch_count",
     "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
 
@@ -92,6 +92,7 @@ def lib():
     L.ctcg_graph_cache_clear.argtypes = []
     L.ctcg_graph_cache_clear.restype = None
     L.ctcg_loss_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp]
+    L.ctcg_upload_logits.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     L.ctcg_logits_post_width.argtypes = [i32, i32]
     L.ctcg_logits_post_width.restype = i32
     L.ctcg_logits_post.argtypes = [f32p, i32, i32, i32, i32, vp, vp]
@@ -493,6 +494,25 @@ def logits_post(log_probs, flags):
     out = torch.empty((T, B, W), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
         check(lib().ctcg_logits_post(x.data_ptr(), T, B, V, int(flags), out.data_ptr(), _stream_ptr(x.device)))
+    return out
+
+
+def upload_logits(logits_host, act_lens, device=None, out=None):
+    """``ctcg_upload_logits``: (T, B, V) host logits -> device, moving only the frames t < act_lens[b] of a
+    length-sorted batch (the padding of the result is zeros).  Asynchronous on the current stream; pass a pinned
+    tensor.  Returns the device tensor."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("ctcg: no CUDA device -- this engine has no CPU path")
+    x = logits_host
+    assert torch.is_tensor(x) and not x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 3
+    T, B, V = x.shape
+    lens = _lens_array(act_lens, B)
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if out is None:
+        out = torch.empty((T, B, V), dtype=torch.float32, device=dev)
+    assert out.is_cuda and out.is_contiguous() and out.shape == x.shape and out.dtype == torch.float32
+    with torch.cuda.device(out.device):
+        check(lib().ctcg_upload_logits(x.data_ptr(), T, B, V, _np_ptr(lens), out.data_ptr(), _stream_ptr(out.device)))
     return out
 
 

@@ -27,6 +27,7 @@ NVCC_FLAGS = [
     "-Xptxas", "-v",
 ]
 
+NVCC_FLAGS += os.environ.get("CTCG_EXTRA_NVCC", "").split()   # experiments (profiles/micro): -D overrides of kernel constants
 
 # CTCG_TRACE_BUILD=1: compile the per-role cycle counters of bisweep_kernel in
 # (profiles/micro/run_tim.sh, CTCG_SWEEP_DEBUG=256); off in the product build.

@@ -752,6 +752,40 @@ int ensure(void** p, size_t* have, size_t need) {
 
 }  // namespace
 
+// Frames t >= lens[b] carry nothing (no kernel reads them, the gradient rows are zeros): a length-sorted batch
+// is copied as one strided block per run of frames with the same number of live utterances -- frame t holds
+// its live utterances as a prefix of the (B, V) row -- so the bus moves sum(lens) * V floats instead of
+// T * B * V (20 % less at lens in [0.6 T, T]).  The padding of the device buffer is zero-filled on the device.
+extern "C" int ctcg_upload_logits(const float* logits_host, int32_t T, int32_t B, int32_t V,
+                                  const int32_t* lens_host, float* logits_dev, void* stream) {
+  if (!logits_host || !lens_host || !logits_dev || T < 1 || B < 1 || V < 1) return CTCG_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t row = (size_t)B * V * 4;
+  bool sorted = true;
+  long long live = 0;
+  for (int b = 0; b < B; ++b) {
+    if (lens_host[b] < 0 || lens_host[b] > T) return CTCG_EINVAL;
+    if (b > 0 && lens_host[b] > lens_host[b - 1]) sorted = false;
+    live += lens_host[b];
+  }
+  if (!sorted || live == (long long)T * B) {  // no prefix structure / nothing to skip: one flat copy
+    CTCG_CUDA(cudaMemcpyAsync(logits_dev, logits_host, row * T, cudaMemcpyHostToDevice, st));
+    return CTCG_OK;
+  }
+  CTCG_CUDA(cudaMemsetAsync(logits_dev, 0, row * T, st));
+  // runs of frames [t0, t1) during which exactly n utterances are alive: n = B for t < lens[B-1], then one
+  // utterance less after every distinct length
+  int t0 = 0;
+  for (int n = B; n >= 1 && t0 < T; --n) {
+    const int t1 = std::min<int>(lens_host[n - 1], T);  // utterance n-1 (the shortest of the first n) ends here
+    if (t1 <= t0) continue;
+    CTCG_CUDA(cudaMemcpy2DAsync(logits_dev + (size_t)t0 * B * V, row, logits_host + (size_t)t0 * B * V, row,
+                                (size_t)n * V * 4, (size_t)(t1 - t0), cudaMemcpyHostToDevice, st));
+    t0 = t1;
+  }
+  return CTCG_OK;
+}
+
 extern "C" int ctcg_loss_host(const float* logits_host, int32_t T, int32_t B, int32_t V,
                               const int32_t* lens_host, ctcg_graph* num, ctcg_graph* den, int32_t normalize,
                               int32_t num_symbols, float* loss_host, float* grad_host) {
@@ -779,7 +813,8 @@ extern "C" int ctcg_loss_host(const float* logits_host, int32_t T, int32_t B, in
   const size_t wsb = ctcg_workspace_bytes(T, B, V, num, den);
   if ((st_ = ensure(&g_cache.ws, &g_cache.ws_bytes, wsb)) != CTCG_OK) return st_;
   cudaStream_t st = nullptr;
-  CTCG_CUDA(cudaMemcpyAsync(g_cache.logits, logits_host, n, cudaMemcpyHostToDevice, st));
+  if ((st_ = ctcg_upload_logits(logits_host, T, B, V, lens_host, static_cast<float*>(g_cache.logits), st)) != CTCG_OK)
+    return st_;
   st_ = ctcg_loss_fwd_bwd(static_cast<const float*>(g_cache.logits), T, B, V, lens_host, num, den, normalize,
                           num_symbols, nullptr, static_cast<float*>(g_cache.loss),
                           grad_host ? static_cast<float*>(g_cache.grad) : nullptr, g_cache.ws, g_cache.ws_bytes,

@@ -41,8 +41,17 @@ namespace ctcg {
 namespace {
 
 constexpr int NPROD = 4;     // producer warps
-constexpr int NRAW = 10;     // TMA landing rows in flight
-constexpr int NE = 6;        // e rows ahead of the recursion
+#ifndef CTCG_NRAW
+#define CTCG_NRAW 10
+#endif
+#ifndef CTCG_NE
+#define CTCG_NE 6
+#endif
+#ifndef CTCG_SWEEP_MINB
+#define CTCG_SWEEP_MINB 1
+#endif
+constexpr int NRAW = CTCG_NRAW;  // TMA landing rows in flight
+constexpr int NE = CTCG_NE;      // e rows ahead of the recursion
 constexpr int TARGET = 60;   // the spilled vectors are kept near 2^TARGET
 constexpr int BAND = 20;
 constexpr int RBW = 64;      // floats per vector buffer (S <= 64)
@@ -596,7 +605,7 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
 }
 
 template <int SCT, int MAXT>
-__global__ void __launch_bounds__(MAXT, 1) bisweep_kernel(const BisweepArgs A) {
+__global__ void __launch_bounds__(MAXT, CTCG_SWEEP_MINB) bisweep_kernel(const BisweepArgs A) {
   extern __shared__ __align__(128) unsigned char smraw[];
   if (blockIdx.y == 0) sweep_body<SCT, 0>(A, smraw);
   else sweep_body<SCT, 1>(A, smraw);

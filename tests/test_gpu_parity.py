@@ -661,3 +661,38 @@ def test_workspace_and_outputs_stay_inside_their_bounds(P, order, S, args, use_d
     st = L.ctcg_loss_fwd_bwd(x.data_ptr(), T, B, V, lens_np.ctypes.data, num.ptr, den.ptr if den is not None else None,
                              int(mode), int(S), None, loss.data_ptr(), grad.data_ptr(), ws.data_ptr(), need - 1, None)
     assert st == 7 and P._lib.launch_count() == launches                         # CTCG_EWORKSPACE
+
+
+def test_upload_logits_moves_the_live_frames_only(P):
+    """``ctcg_upload_logits``: the device copy equals the host tensor on every frame t < len_b and is zero
+    elsewhere; an unsorted batch and a batch without padding are copied whole; the loss computed on the trimmed
+    copy is bit-identical to the loss on the full copy (no kernel reads the padding)."""
+    rng = np.random.default_rng(5)
+    T, B, S = 41, 9, 7
+    V = S * S
+    host = torch.from_numpy(rng.standard_normal((T, B, V)).astype(np.float32)).pin_memory()
+    lens = [41, 41, 40, 33, 33, 33, 20, 7, 0]
+    dev = P.upload_logits(host, lens)
+    torch.cuda.synchronize()
+    want = host.clone()
+    for b, ln in enumerate(lens):
+        want[ln:, b] = 0
+    assert torch.equal(dev.cpu(), want)
+    # out= re-uses a buffer (stale contents must not survive in the padding)
+    buf = torch.full((T, B, V), 7.0, device="cuda")
+    assert P.upload_logits(host, lens, out=buf) is buf and torch.equal(buf.cpu(), want)
+    # not sorted: whole copy;  no padding: whole copy
+    assert torch.equal(P.upload_logits(host, lens[::-1]).cpu(), host)
+    assert torch.equal(P.upload_logits(host, [T] * B).cpu(), host)
+    with pytest.raises(Exception):
+        P.upload_logits(host, [T + 1] + [T] * (B - 1))
+    # the loss does not see the difference
+    lens2 = [41, 40, 33, 33, 29, 25, 20, 18, 15]
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S)
+    seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens2]
+    num, den = gen.get_training_graphs(seqs), gen.get_decoding_graph()
+    la, ga = P._lib.loss_fwd_bwd(host.cuda(), lens2, num, den, P.NORM_NONE, S)
+    lb, gb = P._lib.loss_fwd_bwd(P.upload_logits(host, lens2), lens2, num, den, P.NORM_NONE, S)
+    assert torch.equal(la, lb) and torch.equal(ga, gb)
+    lh, gh = P._lib.loss_host(host, lens2, num, den, P.NORM_NONE, S)       # the host entry point goes through it
+    assert torch.equal(lh, la.cpu()) and torch.equal(gh, ga.cpu())
