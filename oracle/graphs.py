@@ -341,3 +341,23 @@ def collapse_by_arc_table(g, frame_labels):
         state = a[1]
     return out
 
+
+
+def collapse_all_paths(g, frame_labels, limit=10000):
+    """Every symbol sequence an accepting path of ``g`` emits while reading ``frame_labels`` -- the candidates
+    ``shortestpath(compose(chain, dec_fst))`` (advanced_decoder.py:556-571) chooses from when all weights are
+    One and the graph is not input-deterministic (tri-char with a shared blank class).  Exhaustive walk;
+    a set of tuples (empty when the composition is empty)."""
+    out_arcs = g.out_lists()
+    final = g.final
+    layer = {(0, ()): True}
+    for v in frame_labels:
+        nxt = {}
+        for (st, emitted) in layer:
+            for a in out_arcs[st]:
+                if a[2] == int(v):
+                    nxt[(a[1], emitted + ((a[3],) if a[3] > 0 else ()))] = True
+        if len(nxt) > limit:
+            raise RuntimeError("too many partial paths")
+        layer = nxt
+    return {emitted for (st, emitted) in layer if final[st] == 0}

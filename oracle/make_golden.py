@@ -167,11 +167,42 @@ def make_case(fu, cl, name, order, S, args, normalize_by_dim, use_den, T, lens, 
     return out
 
 
+DENSE_VARIANTS = {          # keyword arguments of bi_CTC_loss (ctc_losses.py:492-502) -> fixture key
+    "plain": {},
+    "noloops": {"allow_nonblank_selfloops": False},
+    "repctx": {"eval_repeats_in_context": True},
+    "looprepeats": {"loop_using_symbol_repetitions": True},
+}
+
+
+def make_dense_variants(cl, name="dense_variants", seed=2024):
+    """The dense route's bi-context state machines (get_CTC_matrices_bicontext with its flags, and
+    _bicontext_looprepeats, ctc_losses.py:111-226) run by the reference's own RawGenericCTC (numpy fp64,
+    :268-324, through bi_CTC_loss :492-502) on per-context-normalised scores: loss values per variant."""
+    g = torch.Generator().manual_seed(seed)
+    S, T, B = 5, 40, 4
+    lens = [40, 36, 31, 22]
+    labels = [[1, 1, 3, 2, 2, 2, 4], [4, 3, 3, 1], [2, 4, 4, 4, 1, 3], [3]]
+    logits = torch.randn(T, B, S * S, generator=g) * 2
+    lp = cl.get_normalized_acts(logits.double(), None, S, 2, 1)
+    out = dict(logits=logits.numpy(), lens=np.array(lens), S=S, order=2, normalize_by_dim=1,
+               labels_cat=np.array([v for l in labels for v in l]), text_lens=np.array([len(l) for l in labels]))
+    for key, kw in DENSE_VARIANTS.items():
+        out["raw_" + key] = np.array([float(cl.bi_CTC_loss(lp[:lens[b], b], torch.tensor(labels[b]), **kw))
+                                      for b in range(B)])
+    os.makedirs(os.path.join(OUT, "dense"), exist_ok=True)     # a directory of its own: not one of the FST-route cases
+    np.savez_compressed(os.path.join(OUT, "dense", name + ".npz"), **out)
+    return out
+
+
 def main():
     fu, cl = ref_loader.load()
     os.makedirs(OUT, exist_ok=True)
     import sys
     only = sys.argv[1:] or ONLY
+    if not only or "dense_variants" in only:
+        out = make_dense_variants(cl)
+        print("dense_variants", {k: np.round(v, 4) for k, v in out.items() if k.startswith("raw_")})
     for i, case in enumerate(CASES):
         if only and case[0] not in only:
             continue

@@ -153,20 +153,45 @@ def ctc_fst_global_loss(acts, labels, act_lens, label_lens, num_symbols=0, conte
     return _FstLoss.apply(acts, _check_lens(act_lens), num, den, _lib.NORM_NONE, 0)
 
 
-def dense_ctc_graph(labels, S, context_order, allow_nonblank_selfloops=True, eval_repeats_in_context=False):
-    """The state machine of ``get_CTC_matrices_mono`` / ``get_CTC_matrices_bicontext`` (ctc_losses.py:67-94,
-    :111-166) run by ``RawGenericCTC`` (:268-324) as an arc graph for the path-sum kernels: dense states
-    [blank_0, tok_0, blank_1, ..., tok_{U-1}, blank_U] emit on the STATE, so state j becomes node j+1 and
-    every transition i -> j an arc labelled with j's emission; node 0 is a start node with arcs to the
-    two entry states (``enter_first_num=2``), the last two states are final (``terminal_last_num=2``).
+def dense_ctc_graph(labels, S, context_order, allow_nonblank_selfloops=True, eval_repeats_in_context=False,
+                    loop_using_symbol_repetitions=False):
+    """The state machine of ``get_CTC_matrices_mono`` / ``get_CTC_matrices_bicontext`` /
+    ``get_CTC_matrices_bicontext_looprepeats`` (ctc_losses.py:67-94, :111-166, :169-226) run by ``RawGenericCTC``
+    (:268-324) as an arc graph for the path-sum kernels.  The dense states emit on the STATE, so state j becomes
+    node j+1 and every transition i -> j an arc labelled with j's emission; node 0 is a start node with arcs to the
+    two entry states (``enter_first_num=2``); the last two states are final (``terminal_last_num=2``; three for
+    the loop-repeats machine, :498-501).  States: [blank_0, tok_0, blank_1, ..., tok_{U-1}, blank_U], or for
+    loop-repeats [blank, (entry_i, looping_i, blank_i) ...] where a symbol is entered in the old context, held
+    as the class (l, l) and followed by the blank of its own context.
     Returns ``(n_nodes, arcs [(src, dst, label, 0.0)], final)``.  This is NOT the FST topology for
     bi-char transcripts with a repeated letter (the dense definition forbids tok -> tok there)."""
     L = [int(v) % S for v in labels]
     U = len(L)
-    N = 2 * U + 1
-    emit = [0] * N
     trans = []
-    if context_order == 1:
+    n_final = 2
+    if context_order == 2 and loop_using_symbol_repetitions:
+        assert not eval_repeats_in_context                      # :123
+        N = 3 * U + 1
+        emit = [0] * N
+        n_final = 3
+        trans += [(0, 0), (0, 1)] if U else [(0, 0)]
+        context = 0
+        for i, label in enumerate(L):
+            entry = 3 * i + 1
+            looping, blank, nxt = entry + 1, entry + 2, entry + 3
+            emit[entry] = context * S + label
+            context = label
+            emit[looping] = context * S + label
+            emit[blank] = context * S
+            can_next = i + 1 < U and label != L[i + 1]
+            trans += [(entry, looping), (entry, blank)] + ([(entry, nxt)] if can_next else [])
+            trans += [(looping, looping), (looping, blank)] + ([(looping, nxt)] if can_next else [])
+            trans.append((blank, blank))
+            if i + 1 < U:
+                trans.append((blank, nxt))
+    elif context_order == 1:
+        N = 2 * U + 1
+        emit = [0] * N
         trans += [(0, 0), (0, 1)] if U else [(0, 0)]
         for i, l in enumerate(L):
             tok = 2 * i + 1
@@ -177,6 +202,8 @@ def dense_ctc_graph(labels, S, context_order, allow_nonblank_selfloops=True, eva
                 if L[i + 1] != l:
                     trans.append((tok, tok + 2))
     else:
+        N = 2 * U + 1
+        emit = [0] * N
         context = 0
         for i, li in enumerate(L):
             blank, tok = 2 * i, 2 * i + 1
@@ -196,7 +223,7 @@ def dense_ctc_graph(labels, S, context_order, allow_nonblank_selfloops=True, eva
     arcs = [(0, j + 1, emit[j], 0.0) for j in range(min(2, N))]
     arcs += [(i + 1, j + 1, emit[j], 0.0) for (i, j) in trans]
     final = np.full(N + 1, -np.inf, dtype=np.float32)
-    final[max(1, N - 1):] = 0.0
+    final[max(1, N + 1 - n_final):] = 0.0
     return N + 1, arcs, final
 
 
@@ -219,10 +246,9 @@ def ctc_raw_loss(acts, labels, act_lens, label_lens, num_symbols=0, context_orde
         assert num_symbols > 0
         S = int(round(np.sqrt(S)))
         mode, ns = _lib.NORM_CONTEXT, int(num_symbols)
-        if loop_using_symbol_repetitions:
-            raise NotImplementedError("get_CTC_matrices_bicontext_looprepeats (ctc_losses.py:169-226) is not restated")
     seqs = _labels_to_batch(labels, label_lens)
-    graphs = [dense_ctc_graph(q, S, context_order, allow_nonblank_selfloops, eval_repeats_in_context) for q in seqs]
+    graphs = [dense_ctc_graph(q, S, context_order, allow_nonblank_selfloops, eval_repeats_in_context,
+                              loop_using_symbol_repetitions) for q in seqs]
     num = _lib.Graph.from_arcs(graphs)
     return _FstLoss.apply(acts, _check_lens(act_lens), num, None, mode, ns)
 

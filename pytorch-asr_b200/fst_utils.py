@@ -253,6 +253,44 @@ def collapse_frame_labels(frame_labels, context_order, num_symbols, allow_nonbla
     return out
 
 
+def collapse_by_arcs(frame_labels, arcs, final):
+    """Frame-level class ids -> emitted symbols by walking an arc table (``arcs``: rows ``src, dst, class,
+    emitted symbol, _``; ``final``: 0 for final states, -inf otherwise; start state 0): the read-out of
+    ``shortestpath(compose(chain(idx), dec_fst))`` in ``FSTDecoder.decode`` (advanced_decoder.py:556-571) for
+    graphs without a closed-form rule (tri-char).  The graph need not be input-deterministic (the shared blank
+    class of the tri-char topology is read by several arcs of a state): the walk keeps every state the prefix can
+    be in, with one back-pointer each, and reads the symbols back from a final state -- all weights are One, so
+    every accepting path is a shortest path; among several the one through the smallest state ids is taken.
+    ``ValueError`` when no accepting path reads the sequence (the composition would be empty)."""
+    labels = [int(v) for v in (frame_labels.tolist() if hasattr(frame_labels, "tolist") else frame_labels)]
+    table = getattr(arcs, "_ctcg_table", None) if not isinstance(arcs, np.ndarray) else None
+    if table is None:
+        table = {}
+        for src, dst, cls, out, _ in np.asarray(arcs).tolist():
+            table.setdefault((src, cls), []).append((dst, out))
+    frontier = {0: None}
+    back = []
+    for v in labels:
+        nxt = {}
+        for st in sorted(frontier):
+            for dst, out in table.get((st, v), ()):
+                if dst not in nxt:
+                    nxt[dst] = (st, out)
+        if not nxt:
+            raise ValueError("class %d cannot follow the frames before it" % v)
+        back.append(nxt)
+        frontier = nxt
+    ends = [st for st in sorted(frontier) if final[st] == 0]
+    if not ends:
+        raise ValueError("the frame labels do not end in a final state")
+    st, out = ends[0], []
+    for nxt in reversed(back):
+        st, o = nxt[st]
+        if o > 0:
+            out.append(o)
+    return out[::-1]
+
+
 def setattr_matched(obj, var, val):
     val_orig = getattr(obj, var)
     if val_orig is not None:
@@ -475,7 +513,8 @@ class CTCGraphGen(BaseGraphGen):
     def collapse(self, frame_labels):
         if self.context_order < 3:
             return super(CTCGraphGen, self).collapse(frame_labels)
-        raise NotImplementedError("collapse of tri-char frame labels: walk decoding_fst (needs pywrapfst)")
+        arcs, final = self._tri                  # the arcs as built (dead ends never reach a final state)
+        return collapse_by_arcs(frame_labels, arcs, final)
 
     def _to_openfst(self, arc_type="log"):
         if self.context_order < 3:

@@ -74,3 +74,44 @@ def test_collapse_rejects_exactly_what_the_graph_rejects(lib_built, order, S, ar
 def test_plain_ctc_collapse_is_the_textbook_rule(lib_built):
     gen = lib_built.CTCGraphGen(context_order=1, graph_build_args={}, num_symbols=5)
     assert gen.collapse([0, 1, 1, 0, 1, 2, 2, 2, 0, 0, 3]) == [1, 1, 2, 3]
+
+
+@pytest.mark.parametrize("S,args", [(4, {}), (4, {"use_context_blanks": True}), (5, {})])
+def test_trichar_collapse_walks_the_arc_table(lib_built, S, args):
+    """Tri-char graphs (fst_utils.py:926-1050) have no closed-form rule and, with the shared blank class, are
+    not input-deterministic: the product keeps every state a prefix can be in.  Checked against the oracle's
+    exhaustive walk of its own restatement of the graph: the transducer is functional on accepted sequences (one
+    emitted string whatever path is taken), and that string is what the product returns; sequences that end in a
+    non-final state or leave the graph are rejected by both."""
+    P = lib_built
+    g = graphs.trigram_decoding_graph(S, **args)
+    gen = P.CTCGraphGen(context_order=3, graph_build_args=dict(args), num_symbols=S)
+    out_arcs = g.out_lists()
+    rng = np.random.default_rng(S + len(args))
+    accepted = rejected = 0
+    for n in (1, 2, 3, 8, 25, 60):
+        for _ in range(25):
+            state, labels, emitted = 0, [], []
+            for _ in range(n):
+                arcs = out_arcs[state]
+                stay = [a for a in arcs if a[1] == state]
+                a = stay[0] if (stay and rng.random() < 0.4) else arcs[int(rng.integers(len(arcs)))]
+                labels.append(a[2])
+                if a[3] > 0:
+                    emitted.append(a[3])
+                state = a[1]
+            want = graphs.collapse_all_paths(g, labels)
+            assert len(want) <= 1                                  # functional
+            if g.final[state] == 0:
+                assert want == {tuple(emitted)}
+            if want:
+                accepted += 1
+                assert gen.collapse(labels) == list(next(iter(want)))
+                assert gen.collapse(torch.tensor(labels, dtype=torch.int32)) == list(next(iter(want)))
+            else:
+                rejected += 1
+                with pytest.raises(ValueError):
+                    gen.collapse(labels)
+    assert accepted > 20 and rejected > 20
+    with pytest.raises(ValueError):
+        gen.collapse([S ** 3 - 1, 1])                              # not a path at all

@@ -150,3 +150,38 @@ def test_trichar_graphs_equal_the_reference(lib_built, S, args):
             rgen.get_decoding_matrices("cpu")
         with pytest.raises(ValueError):
             gen.get_decoding_matrices()
+
+
+@needs_ref
+@pytest.mark.parametrize("order,kw", [(1, {}), (2, {}), (2, {"allow_nonblank_selfloops": False}),
+                                      (2, {"eval_repeats_in_context": True}),
+                                      (2, {"loop_using_symbol_repetitions": True})])
+def test_dense_state_machines_equal_the_reference_matrices(lib_built, order, kw):
+    """``dense_ctc_graph`` against ``get_CTC_matrices_mono`` / ``_bicontext`` / ``_bicontext_looprepeats``
+    (ctc_losses.py:67-94, :111-226) of the live reference: transition i -> j exactly where A[i, j] = 1, labelled
+    with the one class B makes state j emit; entry and terminal states as ``mono_CTC_loss`` / ``bi_CTC_loss``
+    pass them to ``RawGenericCTC`` (:486-502)."""
+    P = lib_built
+    _, cl = ref_loader.load()
+    dense = importlib.import_module(P.FSTLoss.__module__).dense_ctc_graph
+    S = 5
+    rng = np.random.default_rng(order * 10 + len(kw))
+    for U in (1, 2, 3, 7):
+        for _ in range(6):
+            lab = rng.integers(1, S, size=U)
+            if U >= 3:
+                lab[1] = lab[0]                                   # a repeated letter
+            if order == 1:
+                A, Bm = cl.get_CTC_matrices_mono(torch.as_tensor(lab), S)
+            else:
+                A, Bm = cl.get_CTC_matrices_bicontext(torch.as_tensor(lab), S, **kw)
+            n_term = 3 if kw.get("loop_using_symbol_repetitions") else 2
+            n, arcs, final = dense(lab.tolist(), S, order, **kw)
+            N = A.shape[0]
+            assert n == N + 1
+            emit = Bm.argmax(0).tolist()
+            assert (Bm.sum(0) == 1).all()
+            want = {(0, j + 1, emit[j]) for j in range(min(2, N))}
+            want |= {(i + 1, j + 1, emit[j]) for i in range(N) for j in range(N) if A[i, j] != 0}
+            assert {(a, b, c) for a, b, c, _ in arcs} == want and len(arcs) == len(want)
+            assert [i for i in range(n) if final[i] == 0] == list(range(N + 1 - n_term, N + 1))

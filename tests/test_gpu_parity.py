@@ -696,3 +696,78 @@ def test_upload_logits_moves_the_live_frames_only(P):
     assert torch.equal(la, lb) and torch.equal(ga, gb)
     lh, gh = P._lib.loss_host(host, lens2, num, den, P.NORM_NONE, S)       # the host entry point goes through it
     assert torch.equal(lh, la.cpu()) and torch.equal(gh, ga.cpu())
+
+
+@pytest.mark.gpu
+def test_trichar_decode_follows_a_peaked_alignment(P):
+    """FSTDecoder.decode on the tri-char graph with contextual blanks (the input-deterministic tri-char
+    topology, fst_utils.py:926-1050): Viterbi on the generic kernel, collapse by the arc-table walk.  The logits
+    are peaked on random accepted paths of the oracle's restatement of the graph; the decoded symbols must be
+    what those paths emit."""
+    from oracle import graphs
+    S, B = 4, 3
+    V = S ** 3
+    g = graphs.trigram_decoding_graph(S, use_context_blanks=True)
+    out_arcs = g.out_lists()
+    rng = np.random.default_rng(77)
+    aligns, emitted = [], []
+    for n in (34, 27, 19):
+        while True:
+            state, labels, out = 0, [], []
+            for _ in range(n):
+                arcs = out_arcs[state]
+                stay = [a for a in arcs if a[1] == state]
+                a = stay[0] if (stay and rng.random() < 0.4) else arcs[int(rng.integers(len(arcs)))]
+                labels.append(a[2])
+                if a[3] > 0:
+                    out.append(a[3])
+                state = a[1]
+            if g.final[state] == 0:
+                break
+        aligns.append(labels)
+        emitted.append(out)
+    lens = [len(a) for a in aligns]
+    T = lens[0]
+    logits = (rng.standard_normal((T, B, V)) * 0.5).astype(np.float32)
+    for b, a in enumerate(aligns):
+        for t, c in enumerate(a):
+            logits[t, b, c] += 12
+    gen = P.CTCGraphGen(context_order=3, graph_build_args={"use_context_blanks": True}, num_symbols=S)
+    head = P.FSTLoss(gen, normalize_by_dim=None)
+    ret = head.decode(torch.from_numpy(logits).cuda(), torch.tensor(lens))
+    assert ret["decoded"] == emitted
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("variant,kw", [("plain", {}), ("noloops", {"allow_nonblank_selfloops": False}),
+                                        ("repctx", {"eval_repeats_in_context": True}),
+                                        ("looprepeats", {"loop_using_symbol_repetitions": True})])
+def test_dense_route_bicontext_variants_match_the_reference_values(P, variant, kw):
+    """``ctc_raw_loss`` with the flags of ``get_CTC_matrices_bicontext`` and the loop-repeats machine
+    (ctc_losses.py:111-226): the values the reference's RawGenericCTC returned (``tests/golden/dense/dense_variants.npz``,
+    made by oracle/make_golden.py from the reference's own bi_CTC_loss), transcripts with doubled and tripled
+    letters; gradient against the fp64 oracle on the same state machines."""
+    import importlib
+    import os
+    d = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "dense", "dense_variants.npz")))
+    S = int(d["S"])
+    x = torch.as_tensor(d["logits"]).cuda().requires_grad_(True)
+    labels_cat = torch.as_tensor(d["labels_cat"].astype(np.int64))
+    ends = np.concatenate([[0], np.cumsum(d["text_lens"])])
+    d["label_seqs"] = [d["labels_cat"][ends[i]:ends[i + 1]].tolist() for i in range(len(d["text_lens"]))]
+    args = dict(allow_nonblank_selfloops=True, loop_using_symbol_repetitions=False, eval_repeats_in_context=False)
+    args.update(kw)
+    loss = P.ctc_raw_loss(x, labels_cat, torch.tensor(d["lens"]), torch.tensor(d["text_lens"]), S, 2, 1, **args)
+    loss.sum().backward()
+    assert _rel(loss.detach().cpu(), d["raw_" + variant]) < LOSS_RTOL
+    cl = importlib.import_module(P.FSTLoss.__module__)
+    g = P.Graph.from_arcs([cl.dense_ctc_graph(q, S, 2, args["allow_nonblank_selfloops"], args["eval_repeats_in_context"],
+                                              args["loop_using_symbol_repetitions"]) for q in d["label_seqs"]])
+    nm = P.batch_training_graph_matrices([P.padded_matrices(g, i) for i in range(g.num_graphs)])
+    want_loss, want_grad = engine.fst_loss(d["logits"], d["lens"].tolist(), [m.numpy() for m in nm], None, 1, S, 2,
+                                           dtype=torch.float64)
+    assert _rel(want_loss.numpy(), d["raw_" + variant]) < 1e-6
+    assert np.abs(x.grad.cpu().double().numpy() - want_grad.numpy()).max() < GRAD_ATOL
+    got_b = P.ctc_raw_loss_batch(x.detach(), labels_cat, torch.tensor(d["lens"]), torch.tensor(d["text_lens"]), S, 2, 1,
+                                 **args)
+    assert torch.equal(got_b, loss.detach())
