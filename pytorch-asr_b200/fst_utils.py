@@ -24,6 +24,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from . import grammar
 from ._lib import Decoder, Graph
 
 
@@ -255,7 +256,7 @@ def collapse_frame_labels(frame_labels, context_order, num_symbols, allow_nonbla
 
 def collapse_by_arcs(frame_labels, arcs, final):
     """Frame-level class ids -> emitted symbols by walking an arc table (``arcs``: rows ``src, dst, class,
-    emitted symbol, _``; ``final``: 0 for final states, -inf otherwise; start state 0): the read-out of
+    emitted symbol, _``; ``final``: log-weights, -inf for non-final states; start state 0): the read-out of
     ``shortestpath(compose(chain(idx), dec_fst))`` in ``FSTDecoder.decode`` (advanced_decoder.py:556-571) for
     graphs without a closed-form rule (tri-char).  The graph need not be input-deterministic (the shared blank
     class of the tri-char topology is read by several arcs of a state): the walk keeps every state the prefix can
@@ -280,7 +281,7 @@ def collapse_by_arcs(frame_labels, arcs, final):
             raise ValueError("class %d cannot follow the frames before it" % v)
         back.append(nxt)
         frontier = nxt
-    ends = [st for st in sorted(frontier) if final[st] == 0]
+    ends = [st for st in sorted(frontier) if final[st] > -1e30]      # final log-weight: 0, or the grammar's
     if not ends:
         raise ValueError("the frame labels do not end in a final state")
     st, out = ends[0], []
@@ -344,17 +345,17 @@ def trigram_decoding_arcs(trigrams, use_context_blanks=False, prevent_epsilons=T
 
 
 class BaseGraphGen(object):
-    """fst_utils.py:546-676 without OpenFst; ``grammar_fst`` is not supported
-    (it needs an OpenFst binary-file reader: SURVEY 8f #4)."""
+    """fst_utils.py:546-676 without OpenFst; ``grammar_fst`` (an OpenFst binary file) is read and composed by
+    :mod:`grammar`."""
+
+    _decoder = None
 
     def __init__(self, num_symbols=None, num_classes=None, ngram_to_class_file=None,
                  context_order=None, nc_weight=-1e20, for_forward_only=False,
                  grammar_fst=None, vocabulary=None, **kwargs):
         super(BaseGraphGen, self).__init__(**kwargs)
-        if grammar_fst is not None or ngram_to_class_file is not None:
-            raise NotImplementedError(
-                "grammar_fst / ngram_to_class_file need OpenFst files; build the graph "
-                "elsewhere and pass it through Graph.from_arcs")
+        if ngram_to_class_file is not None:
+            raise NotImplementedError("ngram_to_class_file (a pruned n-gram table) is not supported")
         self.num_classes = num_classes
         self.num_symbols = num_symbols
         self.context_order = 1 if context_order is None else context_order
@@ -364,8 +365,10 @@ class BaseGraphGen(object):
         setattr_matched(self, "num_classes", num_classes)
         self.ngram_to_class = ngram_to_class
         self.ngrams = ngram_to_class.tolist()
-        self.grammar_fst_path = None
+        self.grammar_fst_path = grammar_fst     # fst_utils.py:580-584
+        self.vocabulary = None if grammar_fst is None else grammar.read_vocabulary(vocabulary)
         self.nc_weight = nc_weight
+        self._grammar = None                    # (arcs, final) of HC o G when a grammar is given
         self._dec = self.get_decoding_fst()    # native CSR handle
         self._dec_fst = None                   # pywrapfst view of it, built on first use (decoding_fst)
         self.decoding_mats = {}
@@ -391,6 +394,8 @@ class BaseGraphGen(object):
             import pywrapfst as fst
         except ImportError:
             return None
+        if self._grammar is not None:
+            return self._grammar_to_openfst(fst, arc_type)
         S, order = self.num_symbols, self.context_order
         args = self._build_args()
         rep = bool(args.get("loop_using_symbol_repetitions", False))
@@ -416,8 +421,58 @@ class BaseGraphGen(object):
         f.arcsort("olabel")
         return f
 
+    def _grammar_to_openfst(self, fst, arc_type):
+        arcs, final, w = self._grammar
+        f = fst.Fst(arc_type=arc_type)
+        for st in range(final.shape[0]):
+            assert f.add_state() == st
+            if np.isfinite(final[st]):
+                f.set_final(st, fst.Weight(f.weight_type(), -float(final[st])))
+        f.set_start(0)
+        for (src, dst, cls, out, _), wt in zip(arcs.tolist(), w.tolist()):
+            f.add_arc(src, fst.Arc(cls + 1, out, fst.Weight(f.weight_type(), -wt), dst))
+        if hasattr(f, "connect"):
+            f.connect()
+        return f
+
     def get_decoding_fst(self):
-        return self.get_hc_fst()
+        """fst_utils.py:634-641: H o C, composed with the grammar when there is one.  The reference's
+        ``rmepsilon(determinize(compose(hc, G)))`` is built as ``compose(hc, rmepsilon(G))`` (same weighted
+        relation, see grammar.py); the result lives in a native decoder that serves the denominator graph and
+        the transcripts' numerator graphs, LM weights included."""
+        hc = self.get_hc_fst()
+        if not self.grammar_fst_path:
+            return hc
+        n, arcs, final = self._hc_arcs(hc)
+        g = grammar.remove_epsilons(*self.get_grammar_fst())
+        m, (src, dst, cls, emit, w), fin = grammar.compose(n, arcs, final, *g)
+        self._grammar = (np.stack([src, dst, cls, emit, np.zeros_like(src)], 1).astype(np.int64), fin, w)
+        self._decoder = Decoder(m, (src, dst, cls, emit, w), fin, connect=True)
+        return None                              # made on demand: ValueError if it is not input-deterministic
+
+    def get_grammar_fst(self):
+        """fst_utils.py:615-632 -> ``(n_states, start, arcs, final)`` in the vocabulary's symbol ids."""
+        return grammar.grammar_acceptor(self.grammar_fst_path, self.vocabulary)
+
+    def _hc_arcs(self, hc):
+        """H o C as ``(n_states, rows (src, dst, class, emitted symbol), final)``: the built-in topologies emit
+        the target's letter unless the arc is a loop or enters a blank (fst_utils.py:694-712, :765-817)."""
+        S, order = self.num_symbols, self.context_order
+        rep = bool(self._build_args().get("loop_using_symbol_repetitions", False))
+        succ, labels, weights, _ = hc.export_padded(0, True, self.nc_weight)
+        rows = []
+        for src in range(succ.shape[0]):
+            for k in range(succ.shape[1]):
+                if not weights[src, k] > 0.5 * self.nc_weight:
+                    continue
+                dst, cls = int(succ[src, k]), int(labels[src, k])
+                if order == 1:
+                    out = 0 if dst == src else dst
+                else:
+                    l1, l2 = src % S, dst % S
+                    out = 0 if (l2 == 0 or dst == src or (rep and l1 == l2)) else l2
+                rows.append((src, dst, cls, out))
+        return succ.shape[0], np.asarray(rows, dtype=np.int64), np.zeros(succ.shape[0], dtype=np.float32)
 
     def get_hc_fst(self):
         raise NotImplementedError()
@@ -427,6 +482,8 @@ class BaseGraphGen(object):
 
     def get_training_graphs(self, label_seqs):
         """Native batch of numerator graphs (CSR), one per transcript."""
+        if self._grammar is not None:
+            return self._decoder.training(label_seqs, modulo=self.num_symbols)
         return Graph.training(self.context_order, self.num_symbols, label_seqs, **self._build_args())
 
     def get_training_fst(self, labels):
@@ -456,16 +513,23 @@ class BaseGraphGen(object):
         key = str(device)
         ret = self.decoding_mats.get(key)
         if ret is None:
+            dec = self.get_decoding_graph()
             ret = TaggedMatrices([m.unsqueeze(0) for m in padded_matrices(
-                self._dec, 0, self.nc_weight, self.for_forward_only, device)], self._dec)
+                dec, 0, self.nc_weight, self.for_forward_only, device)], dec)
             self.decoding_mats[key] = ret
         return ret
 
     def get_decoding_graph(self):
+        if self._dec is None and self._decoder is not None:
+            # ValueError("FST is not deterministic") where the reference's get_decoding_matrices raises it
+            # (fst_utils.py:250-252): the shared-blank tri-char graph, a trigram grammar with double back-off
+            self._dec = self._decoder.graph()
         return self._dec
 
     def collapse(self, frame_labels):
         """Emitted symbols of the path that reads ``frame_labels`` (class ids) in the decoding graph."""
+        if self._grammar is not None:
+            return collapse_by_arcs(frame_labels, self._grammar[0], self._grammar[1])
         return collapse_frame_labels(frame_labels, self.context_order, self.num_symbols, **self._build_args())
 
 
@@ -476,6 +540,7 @@ class CTCGraphGen(BaseGraphGen):
         assert context_order in (1, 2, 3)
         self.graph_build_args = graph_build_args or {}
         self._decoder = None
+        self._tri = None
         super(CTCGraphGen, self).__init__(context_order=context_order, **kwargs)
 
     def _build_args(self):
@@ -494,30 +559,25 @@ class CTCGraphGen(BaseGraphGen):
         self._decoder = Decoder(n, arcs, final, connect=True)   # rmepsilon() on a graph without eps:eps arcs
         return None                                              # the decoding graph is made on demand (may not exist)
 
-    def get_decoding_graph(self):
-        if self.context_order == 3 and self._dec is None:
-            # ValueError("FST is not deterministic") for the shared-blank-class variant, where the reference's
-            # get_decoding_matrices raises too (fst_utils.py:250-252): that topology is numerator-only
-            self._dec = self._decoder.graph()
-        return self._dec
+    def _hc_arcs(self, hc):
+        if self.context_order < 3:
+            return super(CTCGraphGen, self)._hc_arcs(hc)
+        arcs, final = self._tri
+        return final.shape[0], arcs[:, :4], final
 
     def get_training_graphs(self, label_seqs):
-        if self.context_order < 3:
+        if self.context_order < 3 or self._grammar is not None:
             return super(CTCGraphGen, self).get_training_graphs(label_seqs)
         return self._decoder.training(label_seqs, modulo=self.num_symbols)
 
-    def get_decoding_matrices(self, device="cpu", out_edges=False):
-        self.get_decoding_graph()
-        return super(CTCGraphGen, self).get_decoding_matrices(device, out_edges)
-
     def collapse(self, frame_labels):
-        if self.context_order < 3:
+        if self.context_order < 3 or self._grammar is not None:
             return super(CTCGraphGen, self).collapse(frame_labels)
         arcs, final = self._tri                  # the arcs as built (dead ends never reach a final state)
         return collapse_by_arcs(frame_labels, arcs, final)
 
     def _to_openfst(self, arc_type="log"):
-        if self.context_order < 3:
+        if self.context_order < 3 or self._grammar is not None:
             return super(CTCGraphGen, self)._to_openfst(arc_type)
         try:
             import pywrapfst as fst
