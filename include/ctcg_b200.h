@@ -309,6 +309,13 @@ int ctcg_logits_post(const float* log_probs, int32_t T, int32_t B, int32_t V, in
 
 const char* ctcg_strerror(int status);
 
+/* Detail of the calling thread's most recent CTCG_ECUDA (which runtime call or
+ * launch failed, source line, CUDA error name and string) or alignment refusal;
+ * "" if there was none.  The pointer stays valid for the thread's lifetime; the
+ * text is overwritten by the next failure.  (The reference raises Python
+ * exceptions with a message; status codes alone would lose it.) */
+const char* ctcg_last_error_detail(void);
+
 /* Number of kernel launches issued by this library since load (bench.py's
  * gpu_launches claim is read from here, not guessed). */
 uint64_t ctcg_launch_count(void);

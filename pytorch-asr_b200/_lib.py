@@ -25,7 +25,7 @@ EXPORTS = (
     "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
     "ctcg_decoder_from_arcs", "ctcg_decoder_num_states", "ctcg_decoder_graph", "ctcg_decoder_training_graphs",
     "ctcg_decoder_free", "ctcg_graph_cache_info", "ctcg_graph_cache_clear",
-    "ctcg_path_count", "ctcg_loss_host", "ctcg_upload_logits", "ctcg_strerror", "ctcg_launch_count",
+    "ctcg_path_count", "ctcg_loss_host", "ctcg_upload_logits", "ctcg_strerror", "ctcg_last_error_detail", "ctcg_launch_count",
     "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
 
@@ -98,6 +98,8 @@ def lib():
     L.ctcg_logits_post.argtypes = [f32p, i32, i32, i32, i32, vp, vp]
     L.ctcg_strerror.argtypes = [C.c_int]
     L.ctcg_strerror.restype = C.c_char_p
+    L.ctcg_last_error_detail.argtypes = []
+    L.ctcg_last_error_detail.restype = C.c_char_p
     L.ctcg_launch_count.argtypes = []
     L.ctcg_launch_count.restype = C.c_uint64
     L.ctcg_profile_enable.argtypes = [C.c_int]
@@ -118,7 +120,8 @@ def check(status):
         raise ValueError(msg)
     if status == EINVAL:
         raise AssertionError("ctcg: " + msg)  # the reference asserts on shape mismatches
-    raise RuntimeError("ctcg: %s (status %d)" % (msg, status))
+    detail = lib().ctcg_last_error_detail().decode() if status in (ECUDA, EUNSUPPORTED) else ""
+    raise RuntimeError("ctcg: %s (status %d)%s" % (msg, status, ": " + detail if detail else ""))
 
 
 def launch_count():
@@ -370,7 +373,10 @@ def _prep_logits(x):
     x = x.detach()
     if x.dtype != torch.float32:
         x = x.float()
-    return x.contiguous()
+    x = x.contiguous()
+    if x.data_ptr() % 16:        # a view into a larger buffer: the TMA row loads want 16-byte aligned bases
+        x = x.clone()
+    return x
 
 
 def loss_fwd_bwd(logits, act_lens, num, den=None, normalize=NORM_NONE, num_symbols=0,

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -18,13 +19,23 @@ namespace {
 constexpr size_t kAlign = 256;
 inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
-#define CTCG_CUDA(expr)                     \
-  do {                                      \
-    cudaError_t e__ = (expr);               \
-    if (e__ != cudaSuccess) {               \
-      (void)cudaGetLastError();             \
-      return CTCG_ECUDA;                    \
-    }                                       \
+// What failed, for ctcg_last_error_detail(): the status codes stay coarse (CTCG_ECUDA), the detail says which
+// runtime call, where, and the CUDA error string.  One slot per host thread.
+thread_local char g_detail[320] = "";
+void set_detail(const char* what, const char* file, int line, cudaError_t e) {
+  const char* base = std::strrchr(file, '/');
+  std::snprintf(g_detail, sizeof(g_detail), "%s:%d: %s -> %s (%s)", base ? base + 1 : file, line, what,
+                cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+#define CTCG_CUDA(expr)                                  \
+  do {                                                   \
+    cudaError_t e__ = (expr);                            \
+    if (e__ != cudaSuccess) {                            \
+      set_detail(#expr, __FILE__, __LINE__, e__);        \
+      (void)cudaGetLastError();                          \
+      return CTCG_ECUDA;                                 \
+    }                                                    \
   } while (0)
 
 struct Plan {
@@ -419,7 +430,11 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   // A per-frame softmax normaliser cancels between numerator and denominator.
   const bool softmax = (normalize == CTCG_NORM_SOFTMAX) && !den;
   const bool fused_den = den && p.sw.ok && aligned16(logits) && aligned16(grad);
-  if (den && p.sw.ok && !fused_den) return CTCG_EUNSUPPORTED;  // misaligned tensors: the workspace was planned for the fused kernel
+  if (den && p.sw.ok && !fused_den) {  // misaligned tensors: the workspace was planned for the fused kernel
+    std::snprintf(g_detail, sizeof(g_detail), "logits / grad must be 16-byte aligned for the bi-char denominator (%p, %p)",
+                  (const void*)logits, (const void*)grad);
+    return CTCG_EUNSUPPORTED;
+  }
   // 1. compact the label columns each utterance touches (the split sweeps take them as (exponent, mantissa)
   // pairs).  Before the fork: next to the denominator sweeps, which hold most of every SM's registers, these
   // wide streaming kernels get one CTA per SM and take three times as long.
@@ -461,7 +476,9 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     if (side) CTCG_CUDA(cudaEventRecord(side->fork, st));
     for (int g = 0; g < ngroups && st_ == CTCG_OK; ++g) {
       if (side) CTCG_CUDA(cudaStreamWaitEvent(side->stream[g], side->fork, 0));
-      if (launch_bisweep(group_args(g), p.sw, group_stream(g)) != cudaSuccess) {
+      const cudaError_t le = launch_bisweep(group_args(g), p.sw, group_stream(g));
+      if (le != cudaSuccess) {
+        set_detail("launch_bisweep", __FILE__, __LINE__, le);
         (void)cudaGetLastError();
         st_ = CTCG_ECUDA;
       }
@@ -756,6 +773,8 @@ int ensure(void** p, size_t* have, size_t need) {
 // is copied as one strided block per run of frames with the same number of live utterances -- frame t holds
 // its live utterances as a prefix of the (B, V) row -- so the bus moves sum(lens) * V floats instead of
 // T * B * V (20 % less at lens in [0.6 T, T]).  The padding of the device buffer is zero-filled on the device.
+extern "C" const char* ctcg_last_error_detail(void) { return g_detail; }
+
 extern "C" int ctcg_upload_logits(const float* logits_host, int32_t T, int32_t B, int32_t V,
                                   const int32_t* lens_host, float* logits_dev, void* stream) {
   if (!logits_host || !lens_host || !logits_dev || T < 1 || B < 1 || V < 1) return CTCG_EINVAL;
