@@ -14,6 +14,7 @@
 // The time recursion is serial per utterance; states are spread over the CTA,
 // alpha lives in shared memory (double-buffered, one barrier per frame), the
 // frame's scores arrive through an 8-deep cp.async ring in compact mode.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -73,8 +74,8 @@ int profile_collect(char* names, size_t cap, float* ms, int max_records) {
 
 namespace {
 
-constexpr int NT = 256;
-constexpr int NWARP = NT / 32;
+constexpr int NT = 256;     // narrow graphs (numerators: <= 4 arcs per state): one state per thread
+constexpr int NTWIDE = 1024;  // wide graphs (shared denominators: tens of arcs per state): one state per WARP
 constexpr int RING = 8;
 
 struct SmemPlan {
@@ -83,7 +84,7 @@ struct SmemPlan {
 };
 
 __host__ __device__ inline SmemPlan plan_smem(int max_states, int width, int max_labels, int alpha_row,
-                                              int stage_arcs, bool compact) {
+                                              int stage_arcs, bool compact, int NWARP, bool wide = false) {
   SmemPlan p;
   p.np = pad4(max_states);
   p.gw = pad4(width);
@@ -92,10 +93,12 @@ __host__ __device__ inline SmemPlan plan_smem(int max_states, int width, int max
   p.arcs = stage_arcs;
   size_t f = 2 * (size_t)p.np + 2 * (size_t)p.gw + 4 * NWARP + (size_t)RING * p.xw + (size_t)RING * p.ar;
   p.bytes = f * 4 + (size_t)stage_arcs * 24;
+  if (wide) p.bytes += 2 * (size_t)(p.np + 4) * 4;  // the two CSR row-pointer arrays (one L2 round trip less per state)
   return p;
 }
 
 // Block-wide max over per-warp partials written to red[0..NWARP).
+template <int NWARP>
 __device__ __forceinline__ float read_block_max(const float* red) {
   float m = red[0];
 #pragma unroll
@@ -103,8 +106,13 @@ __device__ __forceinline__ float read_block_max(const float* red) {
   return m;
 }
 
-template <bool COMPACT>
+// WIDE: a warp owns a state and its lanes the state's arcs -- the CSR keeps them contiguous, so the arc tables
+// are read in coalesced 128-byte lines and each lane keeps its first two arc scores in registers between the
+// max and the sum (with one state per thread, the 51 arcs of a bi-char state are 51 strided loads per lane,
+// twice).  NT threads: 256 for numerators, 1024 for the wide graphs, whose frames are latency-bound.
+template <bool COMPACT, bool WIDE, int NT>
 __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, const int stage_arcs) {
+  constexpr int NWARP = NT / 32;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const GraphDev& g = a.g;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -114,7 +122,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   const int n = g.state_off[gi + 1] - so;
   const int ro = so + gi;
   const int len = min(a.lens[b], a.T);
-  const SmemPlan P = plan_smem(g.max_states, a.g_width, g.max_labels, a.alpha_row, stage_arcs, COMPACT);
+  const SmemPlan P = plan_smem(g.max_states, a.g_width, g.max_labels, a.alpha_row, stage_arcs, COMPACT, NWARP, WIDE);
 
   float* abuf = reinterpret_cast<float*>(smem_raw);
   float* grow = abuf + 2 * P.np;
@@ -133,6 +141,16 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   const int32_t* out_ptr = g.out_ptr + ro;
   const int arc0 = in_ptr[0];
   const int narcs = in_ptr[n] - arc0;
+  if (WIDE) {  // row pointers in shared memory (behind the arc staging area, which wide graphs do not use)
+    int32_t* sp = reinterpret_cast<int32_t*>(s_out_w + stage_arcs);
+    for (int i = tid; i <= n; i += NT) {
+      sp[i] = in_ptr[i];
+      sp[P.np + 4 + i] = out_ptr[i];
+    }
+    in_ptr = sp;
+    out_ptr = sp + P.np + 4;
+    __syncthreads();
+  }
   const bool staged = stage_arcs > 0 && narcs <= stage_arcs;
 
   // Arc tables: shared-memory copies when they fit (numerator graphs), else global.
@@ -168,6 +186,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
     out_w = g.out_w;
     wscale = kLog2e;
   }
+  const bool unit = g.unit_weights != 0;  // every arc weight is One: no weight loads
   const float* final_w = g.final_w + so;
   const float* xb = a.x + (long long)b * a.x_stride_b;
   float* arow_base = a.alpha_ws + (long long)b * a.T * a.alpha_row;
@@ -197,7 +216,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
     if (COMPACT) cp_async_wait<RING - 2>();
     __syncthreads();
     if (COMPACT) issue_fwd(t + RING - 1);
-    float mx = read_block_max(wred + (t & 1) * NWARP);
+    float mx = read_block_max<NWARP>(wred + (t & 1) * NWARP);
     if (!(mx > neg_inf())) mx = 0.f;
     c += (double)mx;
     const float* xrow = COMPACT ? (xring + (t % RING) * P.xw) : (xb + (long long)t * a.x_stride_t);
@@ -208,25 +227,65 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
       arow[a.alpha_row - 1] = (float)(c - (double)hi);
     }
     float lm = neg_inf();
-    for (int s = tid; s < n; s += NT) {
-      arow[s] = a_cur[s] - mx;
-      const int lo = in_ptr[s], hi = in_ptr[s + 1];
-      float M = neg_inf();
-      for (int e = lo; e < hi; ++e) {
-        const float v = in_w[e] * wscale + (a_cur[in_src[e]] - mx) + xrow[in_lab[e]] * a.x_scale;
-        M = fmaxf(M, v);
-      }
-      float r = neg_inf();
-      if (M > neg_inf()) {
-        float acc = 0.f;
-        for (int e = lo; e < hi; ++e) {
-          const float v = in_w[e] * wscale + (a_cur[in_src[e]] - mx) + xrow[in_lab[e]] * a.x_scale;
-          acc += ex2(v - M);
+    auto fscore = [&](int e) {
+      const float w = unit ? 0.f : in_w[e] * wscale;
+      return w + (a_cur[in_src[e]] - mx) + xrow[in_lab[e]] * a.x_scale;
+    };
+    if (WIDE) {
+      // two states per iteration: their (L2-latency) pointer and arc loads overlap
+      for (int s = warp; s < n; s += 2 * NWARP) {
+        const int s2 = s + NWARP;
+        const bool two = s2 < n;
+        const int lo = in_ptr[s], hi = in_ptr[s + 1];
+        const int lo2 = two ? in_ptr[s2] : 0, hi2 = two ? in_ptr[s2 + 1] : 0;
+        if (lane == 0) {
+          arow[s] = a_cur[s] - mx;
+          if (two) arow[s2] = a_cur[s2] - mx;
         }
-        r = M + lg2(acc);
+        const int e0 = lo + lane, f0 = lo2 + lane;
+        const float v0 = e0 < hi ? fscore(e0) : neg_inf();
+        const float u0 = f0 < hi2 ? fscore(f0) : neg_inf();
+        const float v1 = e0 + 32 < hi ? fscore(e0 + 32) : neg_inf();
+        const float u1 = f0 + 32 < hi2 ? fscore(f0 + 32) : neg_inf();
+        float M = fmaxf(v0, v1), M2 = fmaxf(u0, u1);
+        for (int e = e0 + 64; e < hi; e += 32) M = fmaxf(M, fscore(e));
+        for (int e = f0 + 64; e < hi2; e += 32) M2 = fmaxf(M2, fscore(e));
+        M = warp_max(M);
+        M2 = warp_max(M2);
+        float acc = 0.f, acc2 = 0.f;
+        if (M > neg_inf()) {
+          acc = ex2(v0 - M) + ex2(v1 - M);
+          for (int e = e0 + 64; e < hi; e += 32) acc += ex2(fscore(e) - M);
+        }
+        if (M2 > neg_inf()) {
+          acc2 = ex2(u0 - M2) + ex2(u1 - M2);
+          for (int e = f0 + 64; e < hi2; e += 32) acc2 += ex2(fscore(e) - M2);
+        }
+        acc = warp_sum(acc);
+        acc2 = warp_sum(acc2);
+        const float r = M > neg_inf() ? M + lg2(acc) : neg_inf();
+        const float r2 = M2 > neg_inf() ? M2 + lg2(acc2) : neg_inf();
+        if (lane == 0) {
+          a_nxt[s] = r;
+          if (two) a_nxt[s2] = r2;
+        }
+        lm = fmaxf(lm, fmaxf(r, r2));
       }
-      a_nxt[s] = r;
-      lm = fmaxf(lm, r);
+    } else {
+      for (int s = tid; s < n; s += NT) {
+        arow[s] = a_cur[s] - mx;
+        const int lo = in_ptr[s], hi = in_ptr[s + 1];
+        float M = neg_inf();
+        for (int e = lo; e < hi; ++e) M = fmaxf(M, fscore(e));
+        float r = neg_inf();
+        if (M > neg_inf()) {
+          float acc = 0.f;
+          for (int e = lo; e < hi; ++e) acc += ex2(fscore(e) - M);
+          r = M + lg2(acc);
+        }
+        a_nxt[s] = r;
+        lm = fmaxf(lm, r);
+      }
     }
     lm = warp_max(lm);
     if (lane == 0) wred[((t + 1) & 1) * NWARP + warp] = lm;
@@ -237,7 +296,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   if (COMPACT) cp_async_wait<0>();
   __syncthreads();
   // terminal: cost = c_len + LSE_n(alpha_hat_len[n] + final[n])
-  float mx = (len > 0) ? read_block_max(wred + (len & 1) * NWARP) : 0.f;
+  float mx = (len > 0) ? read_block_max<NWARP>(wred + (len & 1) * NWARP) : 0.f;
   if (!(mx > neg_inf())) mx = 0.f;
   c += (double)mx;
   float* red2 = wred;  // both parities are free between the passes
@@ -247,7 +306,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   __syncthreads();
   if (lane == 0) red2[warp] = tm;
   __syncthreads();
-  float TM = read_block_max(red2);
+  float TM = read_block_max<NWARP>(red2);
   __syncthreads();
   float ts = 0.f;
   if (TM > neg_inf())
@@ -328,7 +387,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
         gr[j] = 0.f;
       }
     }
-    float mxb = read_block_max(wred + (i & 1) * NWARP);
+    float mxb = read_block_max<NWARP>(wred + (i & 1) * NWARP);
     if (!(mxb > neg_inf())) mxb = 0.f;
     d += (double)mxb;
     const float* xrow = COMPACT ? (xring + (i % RING) * P.xw) : (xb + (long long)t * a.x_stride_t);
@@ -338,30 +397,64 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
     float* gr = grow + (i & 1) * P.gw;
     float lm = neg_inf();
     float gsum = 0.f;
-    for (int s = tid; s < n; s += NT) {
-      const int lo = out_ptr[s], hi = out_ptr[s + 1];
-      float M = neg_inf();
-      for (int e = lo; e < hi; ++e) {
-        const float v = out_w[e] * wscale + (b_cur[out_dst[e]] - mxb) + xrow[out_lab[e]] * a.x_scale;
-        M = fmaxf(M, v);
-      }
-      float r = neg_inf();
-      if (M > neg_inf()) {
-        const float f = ex2(M + arow[s] + Kt);  // alpha_hat_t[s] = -inf -> 0
-        float acc = 0.f;
-        for (int e = lo; e < hi; ++e) {
-          const float v = out_w[e] * wscale + (b_cur[out_dst[e]] - mxb) + xrow[out_lab[e]] * a.x_scale;
-          const float ev = ex2(v - M);
-          acc += ev;
+    auto bscore = [&](int e) {
+      const float w = unit ? 0.f : out_w[e] * wscale;
+      return w + (b_cur[out_dst[e]] - mxb) + xrow[out_lab[e]] * a.x_scale;
+    };
+    if (WIDE) {
+      for (int s = warp; s < n; s += NWARP) {
+        const int lo = out_ptr[s], hi = out_ptr[s + 1];
+        const int e0 = lo + lane;
+        const float v0 = e0 < hi ? bscore(e0) : neg_inf();
+        const float v1 = e0 + 32 < hi ? bscore(e0 + 32) : neg_inf();
+        float M = fmaxf(v0, v1);
+        for (int e = e0 + 64; e < hi; e += 32) M = fmaxf(M, bscore(e));
+        M = warp_max(M);
+        float r = neg_inf();
+        if (M > neg_inf()) {
+          const float f = ex2(M + arow[s] + Kt);  // alpha_hat_t[s] = -inf -> 0
+          const float ev0 = ex2(v0 - M), ev1 = ex2(v1 - M);
+          float acc = ev0 + ev1;
           if (f > 0.f) {
-            atomicAdd(&gr[out_lab[e]], ev * f);
-            gsum += ev * f;
+            if (e0 < hi) atomicAdd(&gr[out_lab[e0]], ev0 * f);
+            if (e0 + 32 < hi) atomicAdd(&gr[out_lab[e0 + 32]], ev1 * f);
+            gsum += acc * f;
           }
+          for (int e = e0 + 64; e < hi; e += 32) {
+            const float ev = ex2(bscore(e) - M);
+            acc += ev;
+            if (f > 0.f) {
+              atomicAdd(&gr[out_lab[e]], ev * f);
+              gsum += ev * f;
+            }
+          }
+          r = M + lg2(warp_sum(acc));
         }
-        r = M + lg2(acc);
+        if (lane == 0) b_nxt[s] = r;
+        lm = fmaxf(lm, r);
       }
-      b_nxt[s] = r;
-      lm = fmaxf(lm, r);
+    } else {
+      for (int s = tid; s < n; s += NT) {
+        const int lo = out_ptr[s], hi = out_ptr[s + 1];
+        float M = neg_inf();
+        for (int e = lo; e < hi; ++e) M = fmaxf(M, bscore(e));
+        float r = neg_inf();
+        if (M > neg_inf()) {
+          const float f = ex2(M + arow[s] + Kt);  // alpha_hat_t[s] = -inf -> 0
+          float acc = 0.f;
+          for (int e = lo; e < hi; ++e) {
+            const float ev = ex2(bscore(e) - M);
+            acc += ev;
+            if (f > 0.f) {
+              atomicAdd(&gr[out_lab[e]], ev * f);
+              gsum += ev * f;
+            }
+          }
+          r = M + lg2(acc);
+        }
+        b_nxt[s] = r;
+        lm = fmaxf(lm, r);
+      }
     }
     lm = warp_max(lm);
     gsum = warp_sum(gsum);
@@ -387,27 +480,37 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
 
 }  // namespace
 
+template <bool COMPACT, bool WIDE, int NTT>
+cudaError_t launch_path_variant(const PathArgs& a, int stage, size_t bytes, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(path_fwd_bwd_kernel<COMPACT, WIDE, NTT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)bytes);
+  if (e != cudaSuccess) return e;
+  path_fwd_bwd_kernel<COMPACT, WIDE, NTT><<<a.B, NTT, bytes, st>>>(a, stage);
+  return cudaSuccess;
+}
+
 cudaError_t launch_path_fwd_bwd(const PathArgs& a, bool compact, cudaStream_t st) {
+  // wide graphs (a shared denominator with tens of arcs per state): one warp per state, 1024 threads
+  static const bool narrow_only = [] {   // CTCG_PATH_NARROW=1: the one-state-per-thread kernel for every graph (cross-checks)
+    const char* e = getenv("CTCG_PATH_NARROW");
+    return e && e[0] == '1';
+  }();
+  const bool wide = !narrow_only && (long long)a.g.max_arcs >= 16LL * (long long)max(a.g.max_states, 1);
+  const int nwarp = (wide ? NTWIDE : NT) / 32;
   // stage arc tables in shared memory when every graph's arcs fit in 48 KB
   int stage = 0;
-  const SmemPlan base = plan_smem(a.g.max_states, a.g_width, a.g.max_labels, a.alpha_row, 0, compact);
+  const SmemPlan base = plan_smem(a.g.max_states, a.g_width, a.g.max_labels, a.alpha_row, 0, compact, nwarp, wide);
   const size_t budget = 200 * 1024;
   if (base.bytes > budget) return cudaErrorInvalidConfiguration;
   // a.g.max_in_degree * max_states bounds the arc count of one graph
   long long bound = (long long)a.g.max_states * (long long)max(a.g.max_in_degree, 1);
   if (bound * 24 + (long long)base.bytes <= (long long)budget && bound <= 8192) stage = (int)bound;
-  const SmemPlan P = plan_smem(a.g.max_states, a.g_width, a.g.max_labels, a.alpha_row, stage, compact);
+  const SmemPlan P = plan_smem(a.g.max_states, a.g_width, a.g.max_labels, a.alpha_row, stage, compact, nwarp, wide);
   cudaError_t e;
   ProfScope prof(compact ? "path_fwd_bwd<compact>" : "path_fwd_bwd<dense>", st);
-  if (compact) {
-    e = cudaFuncSetAttribute(path_fwd_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.bytes);
-    if (e != cudaSuccess) return e;
-    path_fwd_bwd_kernel<true><<<a.B, NT, P.bytes, st>>>(a, stage);
-  } else {
-    e = cudaFuncSetAttribute(path_fwd_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.bytes);
-    if (e != cudaSuccess) return e;
-    path_fwd_bwd_kernel<false><<<a.B, NT, P.bytes, st>>>(a, stage);
-  }
+  if (compact) e = wide ? launch_path_variant<true, true, NTWIDE>(a, stage, P.bytes, st) : launch_path_variant<true, false, NT>(a, stage, P.bytes, st);
+  else e = wide ? launch_path_variant<false, true, NTWIDE>(a, stage, P.bytes, st) : launch_path_variant<false, false, NT>(a, stage, P.bytes, st);
+  if (e != cudaSuccess) return e;
   ++g_launches;
   return cudaGetLastError();
 }
