@@ -78,9 +78,11 @@ class ClockSampler(object):
 
     def __init__(self, index):
         self.index = index
-        self.rows = []
+        self.rows = []          # (host time, fields)
         self._stop = threading.Event()
         self._thr = None
+        self._sample = self._nvml()      # NVML set up on the caller's thread, before any barrier: the sampling
+        self.window = None               # thread must not hold the GIL (imports) while the timed loop starts
 
     def _nvml(self):
         """Fast path: NVML in-process (sub-millisecond per sample)."""
@@ -107,18 +109,18 @@ class ClockSampler(object):
             return None
 
     def _run(self):
-        sample = self._nvml()
+        sample = self._sample
         while not self._stop.is_set():
             try:
                 if sample is not None:
-                    self.rows.append(sample())
+                    self.rows.append((time.perf_counter(), sample()))
                     self._stop.wait(0.002)
                     continue
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True,
                                      timeout=5).stdout.strip()
                 if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                    self.rows.append((time.perf_counter(), [c.strip() for c in out.split(",")]))
             except Exception:
                 pass
             self._stop.wait(0.1)
@@ -133,7 +135,11 @@ class ClockSampler(object):
             self._thr.join(timeout=10)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = self.rows
+        if self.window is not None:      # the thread starts before the barrier: keep the samples of the timed region
+            inside = [r for r in rows if self.window[0] <= r[0] <= self.window[1]]
+            rows = inside if inside else rows[-1:]
+        for _, r in rows:
             try:
                 sm.append(float(r[0]))
                 mx.append(float(r[1]))
@@ -307,21 +313,34 @@ def run_ours(args):
         step(i)
     if world > 1:
         meter.total()                        # warm the collective (communicator set-up, first-call costs)
-    parallel.barrier()
-    torch.cuda.synchronize()
-    sampler = ClockSampler(local)
+    # everything that costs host time on one rank only (sampler thread, NVML) happens before the barrier, so the
+    # ranks leave it together: a rank that starts late is waited for in the window's all-reduce by all the others
+    sampler = ClockSampler(local) if rank == 0 else None
     if rank == 0:
         sampler.start()
-    l0 = P._lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     meter = parallel.LossMeter(dev)          # restart the running scalar for the timed steps
+    l0 = P._lib.launch_count()
+    parallel.barrier()
+    torch.cuda.synchronize()
+    w0 = time.perf_counter()
+    trace = [] if os.environ.get("BENCH_TRACE") else None   # debugging aid: an event after every step (stderr)
     ev0.record()
     for i in range(args.steps):
         out = step(i)
+        if trace is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            trace.append((e, time.perf_counter() - w0))
     if world > 1:
         total = meter.total()                # the one NCCL all-reduce (16 bytes), inside the timed region
     ev1.record()
     torch.cuda.synchronize()
+    if trace is not None:
+        sys.stderr.write("rank %d: step end on the GPU (ms since start) / enqueued by the host (ms): %s | window %.3f\n" % (
+            rank, " ".join("%.2f/%.2f" % (ev0.elapsed_time(e), 1e3 * h) for e, h in trace), ev0.elapsed_time(ev1)))
+    if sampler is not None:
+        sampler.window = (w0, time.perf_counter())
     parallel.barrier()
     launches = P._lib.launch_count() - l0
     if world == 1:
