@@ -185,6 +185,12 @@ void ctcg_graph_free(ctcg_graph* g);
 size_t ctcg_workspace_bytes(int32_t T, int32_t B, int32_t V, const ctcg_graph* num,
                             const ctcg_graph* den);
 
+/* The same, for a given `normalize`: CTCG_NORM_CONTEXT together with a
+ * denominator keeps one normalised copy of the scores (T*B*V floats more);
+ * every other combination equals ctcg_workspace_bytes. */
+size_t ctcg_workspace_bytes_norm(int32_t T, int32_t B, int32_t V, const ctcg_graph* num,
+                                 const ctcg_graph* den, int32_t normalize);
+
 /* Fused training loss, replaces FSTDecoder.logits' normalisation +
  * get_fst_loss + the backward of PathLogSumExp (advanced_decoder.py:444-517,
  * fst_utils.py:400-488):
@@ -192,7 +198,9 @@ size_t ctcg_workspace_bytes(int32_t T, int32_t B, int32_t V, const ctcg_graph* n
  *            = -cost_num_b(lp)                           (den == NULL)
  *   grad     = d(sum_b grad_scale[b] * loss[b]) / d logits, written in full
  *              (rows t >= lens[b] are zero), grad_scale NULL = all ones.
- * lp = logits normalised per `normalize`.  lens_host: B int32 on the host
+ * lp = logits normalised per `normalize` (CTCG_NORM_CONTEXT together with a
+ * denominator needs the workspace of ctcg_workspace_bytes_norm: the normalised
+ * scores are materialised there).  lens_host: B int32 on the host
  * (the reference keeps act_lens on the CPU); need not be sorted.
  * grad may be NULL (loss only).  loss/grad_scale are device pointers. */
 int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V,

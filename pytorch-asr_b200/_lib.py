@@ -22,7 +22,7 @@ EXPORTS = (
     "ctcg_decoding_graph", "ctcg_training_graphs", "ctcg_graph_from_padded",
     "ctcg_graph_from_arcs", "ctcg_graph_get_info", "ctcg_graph_padded_dims",
     "ctcg_graph_export_padded", "ctcg_graph_upload", "ctcg_graph_free",
-    "ctcg_workspace_bytes", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
+    "ctcg_workspace_bytes", "ctcg_workspace_bytes_norm", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
     "ctcg_decoder_from_arcs", "ctcg_decoder_num_states", "ctcg_decoder_graph", "ctcg_decoder_training_graphs",
     "ctcg_decoder_free", "ctcg_graph_cache_info", "ctcg_graph_cache_clear",
     "ctcg_path_count", "ctcg_loss_host", "ctcg_upload_logits", "ctcg_strerror", "ctcg_last_error_detail", "ctcg_launch_count",
@@ -73,6 +73,8 @@ def lib():
     L.ctcg_graph_set_generic.restype = None
     L.ctcg_workspace_bytes.argtypes = [i32, i32, i32, vp, vp]
     L.ctcg_workspace_bytes.restype = C.c_size_t
+    L.ctcg_workspace_bytes_norm.argtypes = [i32, i32, i32, vp, vp, i32]
+    L.ctcg_workspace_bytes_norm.restype = C.c_size_t
     L.ctcg_loss_fwd_bwd.argtypes = [f32p, i32, i32, i32, vp, vp, vp, i32, i32, vp, vp, vp, vp,
                                     C.c_size_t, vp]
     L.ctcg_path_sum.argtypes = [f32p, i32, i32, i32, vp, vp, vp, vp, vp, C.c_size_t, vp]
@@ -390,7 +392,7 @@ def loss_fwd_bwd(logits, act_lens, num, den=None, normalize=NORM_NONE, num_symbo
         num.upload(dev)
         if den is not None:
             den.upload(dev)
-        nbytes = lib().ctcg_workspace_bytes(T, B, V, num.ptr, den.ptr if den is not None else None)
+        nbytes = lib().ctcg_workspace_bytes_norm(T, B, V, num.ptr, den.ptr if den is not None else None, int(normalize))
         ws = _workspace(dev, nbytes)
         loss = torch.empty(B, dtype=torch.float32, device=dev)
         grad = torch.empty_like(x) if need_grad else None

@@ -261,6 +261,14 @@ size_t ctcg_workspace_bytes(int32_t T, int32_t B, int32_t V, const ctcg_graph* n
   return need;
 }
 
+size_t ctcg_workspace_bytes_norm(int32_t T, int32_t B, int32_t V, const ctcg_graph* num, const ctcg_graph* den,
+                                 int32_t normalize) {
+  size_t need = align_up(ctcg_workspace_bytes(T, B, V, num, den));
+  // per-context normalisation in front of a denominator: one normalised copy of the scores
+  if (normalize == CTCG_NORM_CONTEXT && den) need += align_up((size_t)T * B * V * 4);
+  return need;
+}
+
 uint64_t ctcg_launch_count(void) { return g_launches; }
 
 void ctcg_profile_enable(int on) { profile_enable(on != 0); }
@@ -405,14 +413,31 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
   int st_ = check_graph(num, B);
   if (st_ != CTCG_OK) return st_;
   if (den && (st_ = check_graph(den, B)) != CTCG_OK) return st_;
-  if (normalize == CTCG_NORM_CONTEXT) {
-    // with a denominator the dense posteriors would also have to pass through the block
-    // softmax; no reference configuration combines the two
-    if (den) return CTCG_EUNSUPPORTED;
-    if (num_symbols < 1 || V % num_symbols != 0) return CTCG_EINVAL;
-  }
+  if (normalize == CTCG_NORM_CONTEXT && (num_symbols < 1 || V % num_symbols != 0)) return CTCG_EINVAL;
   for (int b = 0; b < B; ++b)
     if (lens_host[b] < 0 || lens_host[b] > T) return CTCG_EINVAL;
+  if (normalize == CTCG_NORM_CONTEXT && den) {
+    // With a denominator the dense posteriors pass through the block softmax too (no reference configuration
+    // combines the two, the code allows it: ctc_losses.py:29-43 feeding advanced_decoder.py:488-500): the
+    // normalised scores are materialised behind the ordinary workspace, the un-normalised loss runs on them and
+    // its gradient is pulled back through the softmax in place.  Workspace: ctcg_workspace_bytes_norm.
+    const size_t base = align_up(ctcg_workspace_bytes(T, B, V, num, den));
+    const size_t extra = align_up((size_t)T * B * V * 4);
+    if (workspace_bytes < base + extra) return CTCG_EWORKSPACE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned char* ws = static_cast<unsigned char*>(workspace);
+    float* lp = reinterpret_cast<float*>(ws + base);
+    // the lengths are needed on the device before the inner call uploads them: same slot, same bytes
+    const Plan p0 = make_plan(T, B, V, num, den);
+    int32_t* lens0 = nullptr;
+    if ((st_ = upload_lens(p0, workspace, lens_host, B, st, &lens0)) != CTCG_OK) return st_;
+    CTCG_CUDA(launch_ctx_norm(false, logits, lp, nullptr, T, B, V, num_symbols, lens0, st));
+    st_ = ctcg_loss_fwd_bwd(lp, T, B, V, lens_host, num, den, CTCG_NORM_NONE, num_symbols, grad_scale, loss, grad,
+                            workspace, base, stream);
+    if (st_ != CTCG_OK || !grad) return st_;
+    CTCG_CUDA(launch_ctx_norm(true, logits, lp, grad, T, B, V, num_symbols, lens0, st));
+    return CTCG_OK;
+  }
   if (num->max_label >= V || (den && den->max_label >= V)) return CTCG_EINVAL;
   if (B > 65535) return CTCG_EUNSUPPORTED;  // the combine kernels index the utterance with blockIdx.y
   const Plan p = make_plan(T, B, V, num, den);
@@ -829,7 +854,7 @@ extern "C" int ctcg_loss_host(const float* logits_host, int32_t T, int32_t B, in
   if ((st_ = ensure(&g_cache.logits, &g_cache.logits_bytes, n)) != CTCG_OK) return st_;
   if (grad_host && (st_ = ensure(&g_cache.grad, &g_cache.grad_bytes, n)) != CTCG_OK) return st_;
   if ((st_ = ensure(&g_cache.loss, &g_cache.loss_bytes, (size_t)B * 4)) != CTCG_OK) return st_;
-  const size_t wsb = ctcg_workspace_bytes(T, B, V, num, den);
+  const size_t wsb = ctcg_workspace_bytes_norm(T, B, V, num, den, normalize);
   if ((st_ = ensure(&g_cache.ws, &g_cache.ws_bytes, wsb)) != CTCG_OK) return st_;
   cudaStream_t st = nullptr;
   if ((st_ = ctcg_upload_logits(logits_host, T, B, V, lens_host, static_cast<float*>(g_cache.logits), st)) != CTCG_OK)

@@ -58,6 +58,8 @@ cudaError_t launch_rows(const float* logits, int T, int B, int V, const int32_t*
                         const float* g_scale, float* grad, float* rowlse, cudaStream_t st);
 
 // grad[t][b][lab_list_b[j]] -= scale_b * gg[b][t][j]
+cudaError_t launch_ctx_norm(bool backward, const float* x, float* lp, float* grad, int T, int B, int V, int S,
+                            const int32_t* lens, cudaStream_t st);
 cudaError_t launch_rows_ctx(const float* logits, int T, int B, int V, int S, const int32_t* lens, const GraphDev& num,
                             const float* gg, int nlp, const float* g_scale, float* grad, cudaStream_t st);
 cudaError_t launch_post(const float* in, long long rows, int V, int S, int mode, int transfer, int tile_normalize,

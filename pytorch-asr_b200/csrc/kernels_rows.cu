@@ -201,6 +201,41 @@ __global__ void __launch_bounds__(NT) rows_ctx_kernel(const float* __restrict__ 
   }
 }
 
+// normalize_by_dim = 1 in front of a loss that has a denominator (get_normalized_acts, ctc_losses.py:36-40,
+// feeding advanced_decoder.py:488-500): the dense posteriors pass through the block softmax too, so the
+// normalised scores are materialised once (FWD: lp = x - LSE_block(x), rows t < len only) and the gradient with
+// respect to lp, g, is pulled back in place afterwards (BWD: dL/dx[v] = g[v] - exp(lp[v]) * sum_block g).
+// One warp per context block; both passes stream 8 V bytes per frame.
+template <bool BWD>
+__global__ void __launch_bounds__(NT) ctx_norm_kernel(const float* __restrict__ x, float* __restrict__ lp,
+                                                      float* __restrict__ grad, int T, int B, int V, int S,
+                                                      const int32_t* __restrict__ lens) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nblk = V / S;
+  const long long blocks = (long long)T * B * nblk;
+  for (long long i = (long long)blockIdx.x * NWARP + warp; i < blocks; i += (long long)gridDim.x * NWARP) {
+    const long long row = i / nblk;
+    const int b = (int)(row % B), t = (int)(row / B);
+    if (t >= lens[b]) continue;  // never read by the loss; its gradient rows are zeros already
+    const long long o = i * S;
+    if (!BWD) {
+      float m = neg_inf();
+      for (int l = lane; l < S; l += 32) m = fmaxf(m, x[o + l]);
+      m = warp_max(m);
+      float sum = 0.f;
+      for (int l = lane; l < S; l += 32) sum += ex2((x[o + l] - m) * kLog2e);
+      sum = warp_sum(sum);
+      const float lse = m + lg2(sum) * (float)kLn2;
+      for (int l = lane; l < S; l += 32) lp[o + l] = x[o + l] - lse;
+    } else {
+      float G = 0.f;
+      for (int l = lane; l < S; l += 32) G += grad[o + l];
+      G = warp_sum(G);
+      for (int l = lane; l < S; l += 32) grad[o + l] = fmaf(-ex2(lp[o + l] * kLog2e), G, grad[o + l]);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(NT) scatter_sub_kernel(int T, int B, int V, const int32_t* __restrict__ lens,
                                                          GraphDev g, const float* __restrict__ gg, int nlp,
                                                          const float* __restrict__ g_scale,
@@ -307,6 +342,17 @@ cudaError_t launch_rows_ctx(const float* logits, int T, int B, int V, int S, con
   cudaError_t e = cudaFuncSetAttribute(rows_ctx_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   rows_ctx_kernel<<<grid, NT, smem, st>>>(logits, T, B, V, S, lens, num, gg, nlp, g_scale, grad);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ctx_norm(bool backward, const float* x, float* lp, float* grad, int T, int B, int V, int S,
+                            const int32_t* lens, cudaStream_t st) {
+  const long long blocks = (long long)T * B * (V / S);
+  const unsigned grid = (unsigned)std::min<long long>((blocks + NWARP - 1) / NWARP, 148LL * 16);
+  ProfScope prof(backward ? "ctx_norm_bwd" : "ctx_norm_fwd", st);
+  if (backward) ctx_norm_kernel<true><<<grid, NT, 0, st>>>(x, lp, grad, T, B, V, S, lens);
+  else ctx_norm_kernel<false><<<grid, NT, 0, st>>>(x, lp, grad, T, B, V, S, lens);
   ++g_launches;
   return cudaGetLastError();
 }

@@ -77,16 +77,8 @@ def fst_loss(logits, act_lens, numerator, denominator=None, normalize_by_dim=Non
 
 
 def _fst_loss(logits, lens, num, den, mode, num_symbols):
-    if mode == _lib.NORM_CONTEXT and den is not None:
-        # Per-context softmax together with a denominator (ctc_losses.py:29-43 feeding
-        # advanced_decoder.py:497-500; no shipped configuration combines them): the kernels fuse that
-        # normalisation for the numerator only, so here it is a device-side log_softmax whose backward
-        # autograd chains in front of the un-normalised loss.
-        V = logits.size(2)
-        S = int(num_symbols)
-        assert S > 0 and V % S == 0
-        lp = torch.log_softmax(logits.view(logits.size(0), logits.size(1), V // S, S), -1).view_as(logits)
-        return _FstLoss.apply(lp, lens, num, den, _lib.NORM_NONE, 0)
+    # (per-context softmax together with a denominator, ctc_losses.py:29-43 feeding advanced_decoder.py:497-500,
+    # is handled inside ctcg_loss_fwd_bwd since round 2: normalised copy, loss, gradient pulled back in place)
     return _FstLoss.apply(logits, lens, num, den, mode, num_symbols)
 
 

@@ -539,6 +539,27 @@ def test_context_normalisation_together_with_a_denominator(P):
     loss, grad = _run_fused(P, logits, lens, gen.get_training_graphs(seqs), gen.get_decoding_graph(), 1, S)
     assert _rel(loss, want_loss.numpy()) < LOSS_RTOL
     assert np.abs(grad - want_grad.numpy()).max() < GRAD_ATOL
+    # straight through the C entry point (normalised copy, loss, gradient pulled back in place), with per-utterance
+    # weights; the plain workspace size is refused, the host-buffer entry point sizes its own
+    num, den = gen.get_training_graphs(seqs), gen.get_decoding_graph()
+    w = torch.tensor([0.5, -1.5, 2.0])
+    l2, g2 = P._lib.loss_fwd_bwd(torch.from_numpy(logits).cuda(), lens, num, den, P.NORM_CONTEXT, S, grad_scale=w)
+    assert _rel(l2.cpu().numpy(), want_loss.numpy()) < LOSS_RTOL
+    assert np.abs(g2.cpu().double().numpy() - want_grad.numpy() * w.numpy()[None, :, None]).max() < 2 * GRAD_ATOL
+    L = P._lib.lib()
+    V = S * S
+    small = L.ctcg_workspace_bytes(T, B, V, num.ptr, den.ptr)
+    assert L.ctcg_workspace_bytes_norm(T, B, V, num.ptr, den.ptr, P.NORM_CONTEXT) >= small + T * B * V * 4
+    assert L.ctcg_workspace_bytes_norm(T, B, V, num.ptr, den.ptr, P.NORM_NONE) - small < 256
+    ws = torch.empty(small, dtype=torch.uint8, device="cuda")
+    x = torch.from_numpy(logits).cuda()
+    lo, gr = torch.empty(B, device="cuda"), torch.empty(T, B, V, device="cuda")
+    lens_np = np.asarray(lens, dtype=np.int32)
+    st = L.ctcg_loss_fwd_bwd(x.data_ptr(), T, B, V, lens_np.ctypes.data, num.ptr, den.ptr, P.NORM_CONTEXT, S, None,
+                             lo.data_ptr(), gr.data_ptr(), ws.data_ptr(), small, None)
+    assert st == 7                                                   # CTCG_EWORKSPACE
+    lh, gh = P._lib.loss_host(torch.from_numpy(logits), lens, num, den, P.NORM_CONTEXT, S)
+    assert _rel(lh.numpy(), want_loss.numpy()) < LOSS_RTOL and np.abs(gh.double().numpy() - want_grad.numpy()).max() < GRAD_ATOL
 
 
 def test_per_utterance_grad_output_scales_rows_on_the_device(P):
