@@ -150,6 +150,27 @@ def _stream_ptr(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+class _on_device(object):
+    """``with torch.cuda.device(d)`` costs ~15 us per use even when ``d`` is already current; the loss path enters
+    it several times per step.  This switches only when it has to."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, device):
+        self.idx = device.index if device.index is not None else torch.cuda.current_device()
+        self.prev = -1
+
+    def __enter__(self):
+        cur = torch.cuda.current_device()
+        if cur != self.idx:
+            self.prev = cur
+            torch.cuda.set_device(self.idx)
+
+    def __exit__(self, *exc):
+        if self.prev >= 0:
+            torch.cuda.set_device(self.prev)
+        return False
+
+
 def _require_cuda(t, what):
     if not (torch.is_tensor(t) and t.is_cuda):
         raise RuntimeError("ctcg: %s must be a CUDA tensor -- this engine has no CPU path" % what)
@@ -276,11 +297,14 @@ class Graph(object):
         return states, labels, weights, terminal
 
     def upload(self, device=None):
+        if device is not None and getattr(self, "_on", None) == device:   # already there (one device copy per handle)
+            return self
         if not torch.cuda.is_available():
             raise RuntimeError("ctcg: no CUDA device -- this engine has no CPU path")
         device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-        with torch.cuda.device(device):
+        with _on_device(device):
             check(lib().ctcg_graph_upload(self._ptr, _stream_ptr(device)))
+        self._on = device
         return self
 
 
@@ -388,7 +412,7 @@ def loss_fwd_bwd(logits, act_lens, num, den=None, normalize=NORM_NONE, num_symbo
     T, B, V = x.shape
     lens = _lens_array(act_lens, B)
     dev = x.device
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         num.upload(dev)
         if den is not None:
             den.upload(dev)
@@ -448,7 +472,7 @@ def scale_grad(grad, grad_output):
     stride = 0 if (go.numel() == 1 or go.stride() == (0,)) else 1
     go = go if stride == 0 else go.contiguous()
     go = go.to(device=grad.device, dtype=torch.float32)
-    with torch.cuda.device(grad.device):
+    with _on_device(grad.device):
         check(lib().ctcg_scale_grad(grad.data_ptr(), T, B, V, go.data_ptr(), stride, _stream_ptr(grad.device)))
     return grad
 
@@ -537,6 +561,9 @@ def loss_host(logits_host, act_lens, num, den=None, normalize=NORM_NONE, num_sym
         loss_out = torch.empty(B, dtype=torch.float32)
     if want_grad and grad_out is None:
         grad_out = torch.empty_like(x)
+    num._on = None        # the C call uploads to the current device itself: drop the wrapper's "already there" marks
+    if den is not None:
+        den._on = None
     check(lib().ctcg_loss_host(x.data_ptr(), T, B, V, _np_ptr(lens), num.ptr,
                                den.ptr if den is not None else None, int(normalize), int(num_symbols),
                                loss_out.data_ptr(), grad_out.data_ptr() if want_grad else None))

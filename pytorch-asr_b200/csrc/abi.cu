@@ -122,23 +122,37 @@ cudaError_t stage_and_copy(void* dst, const void* src, size_t bytes, cudaStream_
     size_t cap = 0;
     cudaEvent_t done = nullptr;
   };
-  constexpr int kSlots = 4, kMaxDev = 64;
-  // one ring per host thread AND device: a slot's event belongs to the device it was created on
-  thread_local Slot rings[kMaxDev][kSlots];
-  thread_local int nexts[kMaxDev] = {};
+  // two rings per host thread AND device (a slot's event belongs to the device it was created on): 32 small slots
+  // for the per-call lengths, so that the host can run that many calls ahead of the GPU before it waits for a slot,
+  // and 4 large ones for graph blobs (their pinned buffers are allocated on first use: not 32 of those)
+  constexpr int kSmall = 32, kLarge = 4, kMaxDev = 64;
+  constexpr size_t kSmallBytes = size_t{1} << 14;
+  thread_local Slot small_ring[kMaxDev][kSmall], large_ring[kMaxDev][kLarge];
+  thread_local int small_next[kMaxDev] = {}, large_next[kMaxDev] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
-  Slot& s = rings[dev][nexts[dev]];
-  nexts[dev] = (nexts[dev] + 1) % kSlots;
+  const bool is_small = bytes <= kSmallBytes;
+  if (is_small && !small_ring[dev][0].p) {  // the small slots are carved out of one pinned block, made once
+    void* block = nullptr;
+    if ((e = cudaHostAlloc(&block, kSmall * kSmallBytes, cudaHostAllocDefault)) != cudaSuccess) return e;
+    for (int i = 0; i < kSmall; ++i) {
+      small_ring[dev][i].p = static_cast<unsigned char*>(block) + (size_t)i * kSmallBytes;
+      small_ring[dev][i].cap = kSmallBytes;
+      if ((e = cudaEventCreateWithFlags(&small_ring[dev][i].done, cudaEventDisableTiming)) != cudaSuccess) return e;
+    }
+  }
+  Slot& s = is_small ? small_ring[dev][small_next[dev]] : large_ring[dev][large_next[dev]];
+  if (is_small) small_next[dev] = (small_next[dev] + 1) % kSmall;
+  else large_next[dev] = (large_next[dev] + 1) % kLarge;
   if (!s.done && (e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)) != cudaSuccess) return e;
   if ((e = cudaEventSynchronize(s.done)) != cudaSuccess) return e;  // never-recorded events are complete
   if (s.cap < bytes) {
     if (s.p) cudaFreeHost(s.p);
     s.p = nullptr;
     s.cap = 0;
-    const size_t cap = std::max<size_t>(bytes + bytes / 2, size_t{1} << 20);
+    const size_t cap = is_small ? kSmallBytes : std::max<size_t>(bytes + bytes / 2, size_t{1} << 20);
     if ((e = cudaHostAlloc(&s.p, cap, cudaHostAllocDefault)) != cudaSuccess) return e;
     s.cap = cap;
   }

@@ -36,6 +36,21 @@ struct PathArgs {
 
 // compact = 1: x / gout are the per-utterance compact label columns produced by
 // launch_gather (16-byte aligned rows, prescaled), staged through a cp.async ring.
+// cudaFuncAttributeMaxDynamicSharedMemorySize once per (kernel instantiation, device, size): the attribute call
+// costs about as much as a launch and the step has ~20 of them.  `cache` is a static int[64] of the call site,
+// initialised to zero (the attribute is per device).
+template <class Kernel>
+inline cudaError_t smem_attr_once(Kernel kernel, int bytes, int* cache) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (cache[dev] >= bytes + 1) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) cache[dev] = bytes + 1;
+  return e;
+}
+
 cudaError_t launch_path_fwd_bwd(const PathArgs& a, bool compact, cudaStream_t st);
 
 // Numerator on the compact columns (kernels_num.cu): alpha and beta sweeps on separate CTAs at the same

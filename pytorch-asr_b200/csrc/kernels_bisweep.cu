@@ -899,8 +899,8 @@ cudaError_t launch_bisweep(const BisweepArgs& a_in, const BisweepPlan& p, cudaSt
     ProfScope prof("bisweep", st);
 #define CTCG_SWEEP(SCT, MAXT)                                                                               \
   do {                                                                                                   \
-    e = cudaFuncSetAttribute(bisweep_kernel<SCT, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
-                             (int)p.smem_bytes);                                                         \
+    static int attr_cache_##SCT[64] = {};                                                                 \
+    e = smem_attr_once(bisweep_kernel<SCT, MAXT>, (int)p.smem_bytes, attr_cache_##SCT);                   \
     if (e != cudaSuccess) return e;                                                                      \
     bisweep_kernel<SCT, MAXT><<<grid, p.threads, p.smem_bytes, st>>>(a);                                \
   } while (0)

@@ -481,7 +481,8 @@ int sweep_smem_bytes(const PathArgs& a) { return sweep_plan(a.g.max_states, (int
 template <bool UNIT, int SPT, int DK>
 static cudaError_t launch_sweep_dk(const PathArgs& a, int nsweeps, cudaStream_t st) {
   const int bytes = sweep_smem_bytes(a);
-  cudaError_t e = cudaFuncSetAttribute(num_sweep_kernel<UNIT, SPT, DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  static int attr_cache[64] = {};
+  cudaError_t e = smem_attr_once(num_sweep_kernel<UNIT, SPT, DK>, bytes, attr_cache);
   if (e != cudaSuccess) return e;
   num_sweep_kernel<UNIT, SPT, DK><<<nsweeps, NT, bytes, st>>>(a, a.g.max_states);
   return cudaGetLastError();
@@ -528,11 +529,13 @@ cudaError_t launch_num_combine(const PathArgs& a, cudaStream_t st) {
   const dim3 grid((a.T + cb_fr - 1) / cb_fr, a.B);
   cudaError_t e;
   if (small) {
-    e = cudaFuncSetAttribute(num_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    static int attr_cache[64] = {};
+    e = smem_attr_once(num_combine_kernel<true>, bytes, attr_cache);
     if (e != cudaSuccess) return e;
     num_combine_kernel<true><<<grid, warps * 32, bytes, st>>>(a, a.g.max_states, a.g.max_labels);
   } else {
-    e = cudaFuncSetAttribute(num_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    static int attr_cache[64] = {};
+    e = smem_attr_once(num_combine_kernel<false>, bytes, attr_cache);
     if (e != cudaSuccess) return e;
     num_combine_kernel<false><<<grid, warps * 32, bytes, st>>>(a, a.g.max_states, a.g.max_labels);
   }
