@@ -315,6 +315,14 @@ int ctcg_logits_post_width(int32_t V, int32_t flags);
 int ctcg_logits_post(const float* log_probs, int32_t T, int32_t B, int32_t V, int32_t flags,
                      float* out, void* stream);
 
+/* Captured steps: ctcg_loss_fwd_bwd replays a CUDA graph of its launch
+ * sequence for a call whose every argument (pointers, sizes, lengths, graph
+ * uploads, stream) equals an earlier call's; counters since load: calls
+ * replayed, captures made, calls that took the ordinary path while the cache
+ * was consulted.  CTCG_STEP_GRAPHS=0 in the environment turns the cache off.
+ * No reference counterpart (the reference launches ~17 ATen kernels per frame). */
+void ctcg_step_graph_info(uint64_t* replays, uint64_t* captures, uint64_t* ordinary);
+
 const char* ctcg_strerror(int status);
 
 /* Detail of the calling thread's most recent CTCG_ECUDA (which runtime call or

@@ -25,7 +25,7 @@ EXPORTS = (
     "ctcg_workspace_bytes", "ctcg_workspace_bytes_norm", "ctcg_loss_fwd_bwd", "ctcg_path_sum", "ctcg_viterbi", "ctcg_viterbi_static", "ctcg_graph_set_generic", "ctcg_scale_grad",
     "ctcg_decoder_from_arcs", "ctcg_decoder_num_states", "ctcg_decoder_graph", "ctcg_decoder_training_graphs",
     "ctcg_decoder_free", "ctcg_graph_cache_info", "ctcg_graph_cache_clear",
-    "ctcg_path_count", "ctcg_loss_host", "ctcg_upload_logits", "ctcg_strerror", "ctcg_last_error_detail", "ctcg_launch_count",
+    "ctcg_path_count", "ctcg_loss_host", "ctcg_upload_logits", "ctcg_strerror", "ctcg_last_error_detail", "ctcg_step_graph_info", "ctcg_launch_count",
     "ctcg_profile_enable", "ctcg_profile_collect", "ctcg_logits_post", "ctcg_logits_post_width",
 )
 
@@ -100,6 +100,8 @@ def lib():
     L.ctcg_logits_post.argtypes = [f32p, i32, i32, i32, i32, vp, vp]
     L.ctcg_strerror.argtypes = [C.c_int]
     L.ctcg_strerror.restype = C.c_char_p
+    L.ctcg_step_graph_info.argtypes = [C.POINTER(C.c_uint64)] * 3
+    L.ctcg_step_graph_info.restype = None
     L.ctcg_last_error_detail.argtypes = []
     L.ctcg_last_error_detail.restype = C.c_char_p
     L.ctcg_launch_count.argtypes = []
@@ -310,6 +312,13 @@ class Graph(object):
 
 # ---------------------------------------------------------------------------
 _workspaces = {}
+
+
+def step_graph_info():
+    """``(replays, captures, ordinary)`` of the captured-step cache of ``ctcg_loss_fwd_bwd``."""
+    a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    lib().ctcg_step_graph_info(C.byref(a), C.byref(b), C.byref(c))
+    return int(a.value), int(b.value), int(c.value)
 
 
 def graph_cache_info():

@@ -92,6 +92,7 @@ struct ctcg_graph {
   void* dev_stream = nullptr;  // stream the blob was allocated on (stream-ordered free)
   bool dev_async = false;
   ctcg::GraphDev dev{};
+  unsigned long long upload_uid = 0;  // changes with every device copy (identity of the captured-step cache)
 };
 
 namespace ctcg {

@@ -159,6 +159,7 @@ struct ProfScope {
   int idx_;
 };
 void profile_enable(bool on);
+bool profile_is_on();
 int profile_collect(char* names, size_t cap, float* ms, int max_records);
 
 }  // namespace ctcg

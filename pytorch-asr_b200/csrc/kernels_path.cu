@@ -46,6 +46,7 @@ ProfScope::~ProfScope() {
   if (idx_ >= 0) cudaEventRecord(g_prof[idx_].b, st_);
 }
 void profile_enable(bool on) { g_prof_on = on; }
+bool profile_is_on() { return g_prof_on; }
 int profile_collect(char* names, size_t cap, float* ms, int max_records) {
   int n = 0;
   size_t off = 0;

@@ -820,3 +820,58 @@ def test_misaligned_logits_and_error_detail(P):
                              loss.data_ptr(), grad.data_ptr(), ws.data_ptr(), need, None)
     assert st == 8                                        # CTCG_EUNSUPPORTED
     assert b"16-byte aligned" in L.ctcg_last_error_detail()
+
+
+def test_repeated_identical_calls_replay_a_captured_step(P):
+    """``ctcg_loss_fwd_bwd`` replays a CUDA graph for a call whose every argument equals an earlier one's (captured
+    on the third sighting).  The logits' CONTENTS are read anew, the kernel count is the same as on the ordinary
+    path, other lengths / graphs / buffers never match, and the results are bit-identical to the ordinary path
+    (the numerator's posteriors carry no atomics; B >= 64 so that the length groups and their streams are in it)."""
+    rng = np.random.default_rng(11)
+    S, T, B = 49, 60, 64
+    V = S * S
+    lens = sorted([T] + rng.integers(int(0.6 * T), T + 1, size=B - 1).tolist(), reverse=True)
+    seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens]
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S)
+    num, den = gen.get_training_graphs(seqs), gen.get_decoding_graph()
+    a = torch.from_numpy((rng.standard_normal((T, B, V)) * 3).astype(np.float32)).cuda()
+    b = torch.from_numpy((rng.standard_normal((T, B, V)) * 3).astype(np.float32)).cuda()
+    L = P._lib.lib()
+    num.upload(a.device), den.upload(a.device)
+    need = L.ctcg_workspace_bytes(T, B, V, num.ptr, den.ptr)
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    x = a.clone()
+    loss, grad = torch.empty(B, device="cuda"), torch.empty(T, B, V, device="cuda")
+    lens_np = np.asarray(lens, dtype=np.int32)
+
+    def call(xt, lens_arr, lo, gr):
+        st = L.ctcg_loss_fwd_bwd(xt.data_ptr(), T, B, V, lens_arr.ctypes.data, num.ptr, den.ptr, 0, S, None,
+                                 lo.data_ptr(), gr.data_ptr(), ws.data_ptr(), need, None)
+        assert st == 0
+        torch.cuda.synchronize()
+        return lo.clone(), gr.clone()
+
+    n0 = P._lib.launch_count()
+    i0 = P._lib.step_graph_info()
+    la1, ga1 = call(x, lens_np, loss, grad)              # first sighting: ordinary path
+    per_call = P._lib.launch_count() - n0
+    call(x, lens_np, loss, grad)                         # second: ordinary
+    la2, ga2 = call(x, lens_np, loss, grad)              # third: captured, then replayed
+    la3, ga3 = call(x, lens_np, loss, grad)              # fourth: replay
+    assert P._lib.launch_count() - n0 == 4 * per_call
+    i1 = P._lib.step_graph_info()
+    assert (i1[0] - i0[0], i1[1] - i0[1], i1[2] - i0[2]) == (2, 1, 2)
+    assert torch.equal(la1, la2) and torch.equal(la1, la3) and torch.equal(ga1, ga2) and torch.equal(ga1, ga3)
+    x.copy_(b)                                           # same buffers, new contents
+    lb_replay, gb_replay = call(x, lens_np, loss, grad)
+    other_loss, other_grad = torch.empty(B, device="cuda"), torch.empty(T, B, V, device="cuda")
+    lb, gb = call(b, lens_np, other_loss, other_grad)    # other buffers: never seen, ordinary path
+    assert torch.equal(lb_replay, lb) and torch.equal(gb_replay, gb)
+    assert not torch.equal(lb, la1)
+    # other lengths in the same buffers: a new signature, and the old one still replays afterwards
+    lens2 = np.asarray([T] + [max(1, v - 1) for v in lens[1:]], dtype=np.int32)
+    lc, gc = call(x, lens2, loss, grad)
+    want_c = P._lib.loss_fwd_bwd(b, lens2.tolist(), num, den, P.NORM_NONE, S)
+    assert torch.equal(lc, want_c[0]) and torch.equal(gc, want_c[1])
+    ld, gd = call(x, lens_np, loss, grad)
+    assert torch.equal(ld, lb) and torch.equal(gd, gb)
