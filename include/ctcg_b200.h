@@ -173,8 +173,10 @@ int ctcg_graph_export_padded(const ctcg_graph* g, int32_t index, int32_t out_edg
  * releases the first copy (stream-ordered on the stream it was uploaded on), so a
  * graph shared by several GPUs needs one handle per GPU -- what one process per GPU
  * gives.  The entry points that take lens_host copy them through a pinned staging
- * slot and may wait for the copy of four calls ago: they are stream-ordered but not
- * capturable into a CUDA graph (ctcg_viterbi_static is the allocation-free variant). */
+ * slot and may wait for an earlier call's copy: they are stream-ordered, but a
+ * CALLER's stream capture may not contain them (ctcg_viterbi_static is the
+ * allocation-free variant; ctcg_loss_fwd_bwd keeps CUDA graphs of its own for
+ * repeated calls, see ctcg_step_graph_info). */
 int ctcg_graph_upload(ctcg_graph* g, void* stream);
 
 void ctcg_graph_free(ctcg_graph* g);

@@ -11,6 +11,9 @@ for W in cfg2 cfg2s cfg4 cfg5; do
 done
 CTCG_SERIAL=1 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > $OUT/${TAG}_bench_cfg3_serial.json 2>> $OUT/${TAG}_bench_cfg3.err
 CTCG_GROUPS=1 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > $OUT/${TAG}_bench_cfg3_groups1.json 2>> $OUT/${TAG}_bench_cfg3.err
+# (the ncu passes run with the captured-step cache off: the same kernels in the same order, launched one by one,
+#  so that the launch counts skipped below are those of the warm-up alone)
+export CTCG_STEP_GRAPHS=0
 # launch list of the bench command (every launch with its device time: compare SHARES, not absolutes)
 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $OUT/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches_cfg3.csv \

@@ -660,7 +660,7 @@ static int loss_fwd_bwd_impl(const float* logits, int32_t T, int32_t B, int32_t 
 // earlier call's is replayed from a CUDA graph captured on the third sighting (one cudaGraphLaunch; the logits'
 // CONTENTS are of course read anew).  That is the shape of a loop over a fixed set of buffers: evaluation passes,
 // gradient accumulation over a cached batch, benchmarks; a trainer whose lengths and transcripts change every
-// step never repeats a signature and pays one 8-entry look-up per call.  The caller's stream may be the legacy
+// step never repeats a signature and pays one 16-entry look-up per call.  The caller's stream may be the legacy
 // default stream, which cannot be captured: the graph runs on a stream of the library, ordered against the
 // caller's by two events.  Off while profiling (ctcg_profile_enable) and with CTCG_STEP_GRAPHS=0.
 namespace {
@@ -693,7 +693,7 @@ struct StepGraph {
 };
 
 struct StepGraphCache {
-  static constexpr int kEntries = 8;
+  static constexpr int kEntries = 16;
   StepGraph e[kEntries];
   unsigned long long clock = 0;
   cudaStream_t stream = nullptr;
@@ -814,9 +814,17 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
     g.failed = true;  // this signature stays on the ordinary path
     if (rc != CTCG_OK && rc != CTCG_ECUDA) return rc;
   } else if (!hit) {
-    StepGraph* slot = &c->e[0];
+    // victim: the least recently used entry WITHOUT a captured graph (a stream of never-repeating signatures, e.g. a
+    // trainer's, must not push captured graphs out -- destroying one costs as much as a step); a captured one only
+    // when every entry holds a graph
+    StepGraph* slot = nullptr;
     for (StepGraph& g : c->e)
-      if (g.stamp < slot->stamp) slot = &g;
+      if (!g.exec && (!slot || g.stamp < slot->stamp)) slot = &g;
+    if (!slot) {
+      slot = &c->e[0];
+      for (StepGraph& g : c->e)
+        if (g.stamp < slot->stamp) slot = &g;
+    }
     slot->reset();
     slot->sig = sig;
     slot->lens.assign(lens_host, lens_host + B);
