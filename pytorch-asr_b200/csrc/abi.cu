@@ -386,11 +386,7 @@ SideStream* side_stream() {
 // 4 groups).  Only while every sweep CTA of the batch is resident at once (2 B <= SMs): beyond that the sweeps
 // run in waves, the SMs are never idle and smaller grids only fragment the waves (cfg5, B=256: 2.75 -> 3.05 ms).
 // CTCG_GROUPS=n forces n groups (1 turns it off).
-int group_count(int B, const int32_t* lens_host) {
-  static const int forced = [] {
-    const char* e = std::getenv("CTCG_GROUPS");
-    return e ? std::atoi(e) : 0;
-  }();
+int sm_count() {
   static const int sms = [] {
     int dev = 0, n = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
@@ -399,6 +395,15 @@ int group_count(int B, const int32_t* lens_host) {
     }
     return n;
   }();
+  return sms;
+}
+
+int group_count(int B, const int32_t* lens_host) {
+  static const int forced = [] {
+    const char* e = std::getenv("CTCG_GROUPS");
+    return e ? std::atoi(e) : 0;
+  }();
+  const int sms = sm_count();
   static const int per_group = [] {
     const char* e = std::getenv("CTCG_GROUP_MIN");
     return e ? std::max(1, std::atoi(e)) : 8;
@@ -736,7 +741,10 @@ int ctcg_loss_fwd_bwd(const float* logits, int32_t T, int32_t B, int32_t V, cons
                       size_t workspace_bytes, void* stream) {
   StepGraphCache* c = nullptr;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (logits && lens_host && loss && workspace && num && B >= 1 && !tls_capture_lens &&
+  // Only steps short enough for the host to matter (every sweep CTA resident at once, the rule of the length
+  // groups): at B = 256 a step is 3 ms, the 0.1 ms of launches is hidden anyway, and the graph's own scheduling of
+  // the concurrent branches loses 10 % against the streams' (cfg4 2.95 -> 3.24 ms, cfg5 2.76 -> 3.04 ms).
+  if (logits && lens_host && loss && workspace && num && B >= 1 && 2 * B <= sm_count() && !tls_capture_lens &&
       !(normalize == CTCG_NORM_CONTEXT && den)) {
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(st, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) c = step_graphs();
