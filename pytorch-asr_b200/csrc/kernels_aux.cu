@@ -22,10 +22,14 @@ namespace {
 constexpr int NT = 256;
 constexpr int NWARP = NT / 32;
 
+// WIDE (graphs with tens of arcs per state, as in kernels_path.cu): a warp owns a state, its lanes the state's
+// contiguous in-arcs; the arg-max keeps the lowest arc index among equal scores, like the serial loop.
+template <bool WIDE, int NT>
 __global__ void __launch_bounds__(NT) viterbi_kernel(const float* __restrict__ x, int T, int B, int V,
                                                      const int32_t* __restrict__ lens, GraphDev g,
                                                      int32_t* __restrict__ back_ws, int row,
                                                      float* __restrict__ score, int32_t* __restrict__ frame_labels) {
+  constexpr int NWARP = NT / 32;
   extern __shared__ __align__(16) float vbuf[];  // 2*np + NWARP*2 + NWARP ints
   const int np = pad4(g.max_states);
   float* wred = vbuf + 2 * np;
@@ -54,19 +58,47 @@ __global__ void __launch_bounds__(NT) viterbi_kernel(const float* __restrict__ x
     c += (double)mx;
     const float* xrow = x + ((long long)t * B + b) * V;
     float lm = neg_inf();
-    for (int s = tid; s < n; s += NT) {
-      float best = neg_inf();
-      int arg = -1;
-      for (int e = in_ptr[s]; e < in_ptr[s + 1]; ++e) {
-        const float v = g.in_w[e] + (v_cur[g.in_src[e]] - mx) + xrow[g.in_lab[e]];
-        if (v > best) {
-          best = v;
-          arg = e;
+    if (WIDE) {
+      for (int s = warp; s < n; s += NWARP) {
+        float best = neg_inf();
+        int arg = 0x7fffffff;
+        for (int e = in_ptr[s] + lane; e < in_ptr[s + 1]; e += 32) {
+          const float v = g.in_w[e] + (v_cur[g.in_src[e]] - mx) + xrow[g.in_lab[e]];
+          if (v > best) {  // ascending e within a lane: the first maximum is the lowest index
+            best = v;
+            arg = e;
+          }
         }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+          const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+          if (ov > best || (ov == best && oa < arg)) {
+            best = ov;
+            arg = oa;
+          }
+        }
+        if (lane == 0) {
+          v_nxt[s] = best;
+          back[(long long)t * row + s] = best > neg_inf() ? arg : -1;
+        }
+        lm = fmaxf(lm, best);
       }
-      v_nxt[s] = best;
-      back[(long long)t * row + s] = arg;
-      lm = fmaxf(lm, best);
+    } else {
+      for (int s = tid; s < n; s += NT) {
+        float best = neg_inf();
+        int arg = -1;
+        for (int e = in_ptr[s]; e < in_ptr[s + 1]; ++e) {
+          const float v = g.in_w[e] + (v_cur[g.in_src[e]] - mx) + xrow[g.in_lab[e]];
+          if (v > best) {
+            best = v;
+            arg = e;
+          }
+        }
+        v_nxt[s] = best;
+        back[(long long)t * row + s] = arg;
+        lm = fmaxf(lm, best);
+      }
     }
     lm = warp_max(lm);
     if (lane == 0) wred[((t + 1) & 1) * NWARP + warp] = lm;
@@ -330,12 +362,20 @@ __global__ void __launch_bounds__(NT) count_kernel(int B, const int32_t* __restr
 
 cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* lens, const GraphDev& g,
                            int32_t* back_ws, int row, float* score, int32_t* frame_labels, cudaStream_t st) {
-  const size_t smem = (size_t)(2 * pad4(g.max_states) + 4 * NWARP) * 4;
+  static const bool narrow_only = [] {
+    const char* e = getenv("CTCG_PATH_NARROW");
+    return e && e[0] == '1';
+  }();
+  const bool wide = !narrow_only && (long long)g.max_arcs >= 16LL * (long long)max(g.max_states, 1);
+  constexpr int NTW = 1024;
+  const size_t smem = (size_t)(2 * pad4(g.max_states) + 4 * ((wide ? NTW : NT) / 32)) * 4;
   if (smem > 200 * 1024) return cudaErrorInvalidConfiguration;
-  cudaError_t e = cudaFuncSetAttribute(viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = wide ? cudaFuncSetAttribute(viterbi_kernel<true, NTW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                       : cudaFuncSetAttribute(viterbi_kernel<false, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   ProfScope prof("viterbi", st);
-  viterbi_kernel<<<B, NT, smem, st>>>(x, T, B, V, lens, g, back_ws, row, score, frame_labels);
+  if (wide) viterbi_kernel<true, NTW><<<B, NTW, smem, st>>>(x, T, B, V, lens, g, back_ws, row, score, frame_labels);
+  else viterbi_kernel<false, NT><<<B, NT, smem, st>>>(x, T, B, V, lens, g, back_ws, row, score, frame_labels);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -440,11 +480,11 @@ extern "C" int ctcg_viterbi_static(const float* log_probs, int32_t T, int32_t B,
   int32_t* lens = reinterpret_cast<int32_t*>(scratch);
   int32_t* back = reinterpret_cast<int32_t*>(scratch + lens_bytes);
   clamp_lens_kernel<<<(B + 127) / 128, 128, 0, st>>>(lens_dev, B, T, lens);
-  if (cudaFuncSetAttribute(viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+  if (cudaFuncSetAttribute(viterbi_kernel<false, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
     (void)cudaGetLastError();
     return CTCG_ECUDA;
   }
-  viterbi_kernel<<<B, NT, smem, st>>>(log_probs, T, B, V, lens, graph->dev, back, row, score, frame_labels);
+  viterbi_kernel<false, NT><<<B, NT, smem, st>>>(log_probs, T, B, V, lens, graph->dev, back, row, score, frame_labels);
   g_launches += 2;
   if (cudaGetLastError() != cudaSuccess) return CTCG_ECUDA;
   return CTCG_OK;

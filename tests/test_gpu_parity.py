@@ -875,3 +875,39 @@ def test_repeated_identical_calls_replay_a_captured_step(P):
     assert torch.equal(lc, want_c[0]) and torch.equal(gc, want_c[1])
     ld, gd = call(x, lens_np, loss, grad)
     assert torch.equal(ld, lb) and torch.equal(gd, gb)
+
+
+def test_captured_step_cache_under_many_interleaved_signatures(P):
+    """More live signatures than the cache has entries, visited in a random order often enough for captures and
+    evictions to happen: every call must return what the ordinary path returns for the same arguments
+    (reference values computed once per signature with the cache bypassed through fresh output buffers)."""
+    rng = np.random.default_rng(2024)
+    S, T, B = 12, 24, 16
+    V = S * S
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S)
+    den = gen.get_decoding_graph()
+    L = P._lib.lib()
+    sigs = []
+    for k in range(20):                                   # 20 signatures > 16 entries
+        lens = sorted([T] + rng.integers(T // 2, T + 1, size=B - 1).tolist(), reverse=True)
+        seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens]
+        num = gen.get_training_graphs(seqs)
+        x = torch.from_numpy((rng.standard_normal((T, B, V)) * 2).astype(np.float32)).cuda()
+        num.upload(x.device), den.upload(x.device)
+        need = L.ctcg_workspace_bytes(T, B, V, num.ptr, den.ptr)
+        ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+        loss, grad = torch.empty(B, device="cuda"), torch.empty(T, B, V, device="cuda")
+        want = P._lib.loss_fwd_bwd(x, lens, num, den, P.NORM_NONE, S)          # wrapper: its own buffers, first sighting
+        sigs.append(dict(x=x, lens=np.asarray(lens, dtype=np.int32), num=num, ws=ws, need=need, loss=loss, grad=grad,
+                         want=want))
+    i0 = P._lib.step_graph_info()
+    order = rng.integers(0, len(sigs), size=160).tolist() + [3] * 6 + [17] * 6
+    for k in order:
+        s = sigs[k]
+        s["loss"].fill_(-7.0), s["grad"].fill_(-7.0)
+        st = L.ctcg_loss_fwd_bwd(s["x"].data_ptr(), T, B, V, s["lens"].ctypes.data, s["num"].ptr, den.ptr, 0, S, None,
+                                 s["loss"].data_ptr(), s["grad"].data_ptr(), s["ws"].data_ptr(), s["need"], None)
+        assert st == 0
+        assert torch.equal(s["loss"], s["want"][0]) and torch.equal(s["grad"], s["want"][1]), k
+    i1 = P._lib.step_graph_info()
+    assert i1[1] - i0[1] >= 2 and i1[0] - i0[0] >= 8      # captures and replays did happen
