@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -91,7 +92,7 @@ Plan make_plan(int T, int B, int V, const ctcg_graph* num, const ctcg_graph* den
       p.fin = take((size_t)B * sizeof(BiFin));
     } else {
       p.arow_den = pad4(den->max_states + 2);
-      p.alpha_den = take(TB * p.arow_den * 4);
+      p.alpha_den = take((TB + (size_t)std::max(B, 1)) * p.arow_den * 4);  // T + 1 rows per utterance
     }
   }
   p.total = off;
@@ -209,6 +210,36 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   append(&blob, g->lab_w, &o[17]);
   append(&blob, g->slab_ptr, &o[18]);
   append(&blob, g->slab_state, &o[19]);
+  // transposed arc tables for wide shared graphs (see GraphDev): built here, from the CSR
+  const bool ell = g->num_graphs == 1 && g->max_states > 0 && (long long)g->max_arcs >= 16LL * g->max_states &&
+                   (long long)(g->max_in_degree + g->max_out_degree) * g->max_states <= (1LL << 24);
+  const int ell_np = ell ? (g->max_states + 31) / 32 * 32 : 0;
+  size_t oe[6] = {0, 0, 0, 0, 0, 0};
+  if (ell) {
+    const int n = g->max_states, kin = g->max_in_degree, kout = g->max_out_degree;
+    std::vector<int32_t> es((size_t)kin * ell_np, 0), el((size_t)kin * ell_np, 0);
+    std::vector<float> ew((size_t)kin * ell_np, -INFINITY);
+    for (int s = 0; s < n; ++s)
+      for (int e = g->in_ptr[s], k = 0; e < g->in_ptr[s + 1]; ++e, ++k) {
+        es[(size_t)k * ell_np + s] = g->in_src[e];
+        el[(size_t)k * ell_np + s] = g->in_lab[e];
+        ew[(size_t)k * ell_np + s] = g->in_w[e];
+      }
+    append(&blob, es, &oe[0]);
+    append(&blob, el, &oe[1]);
+    append(&blob, ew, &oe[2]);
+    std::vector<int32_t> od((size_t)kout * ell_np, 0), ol((size_t)kout * ell_np, 0);
+    std::vector<float> ow((size_t)kout * ell_np, -INFINITY);
+    for (int s = 0; s < n; ++s)
+      for (int e = g->out_ptr[s], k = 0; e < g->out_ptr[s + 1]; ++e, ++k) {
+        od[(size_t)k * ell_np + s] = g->out_dst[e];
+        ol[(size_t)k * ell_np + s] = g->out_lab[e];
+        ow[(size_t)k * ell_np + s] = g->out_w[e];
+      }
+    append(&blob, od, &oe[3]);
+    append(&blob, ol, &oe[4]);
+    append(&blob, ow, &oe[5]);
+  }
   // Stream-ordered allocation and a pinned staging ring: nothing here waits for work already
   // queued on the stream (e.g. the H2D copy of the logits), so graph upload overlaps it.
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -255,6 +286,15 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   v.lab_w = reinterpret_cast<const float*>(p + o[17]);
   v.slab_ptr = reinterpret_cast<const int32_t*>(p + o[18]);
   v.slab_state = reinterpret_cast<const int32_t*>(p + o[19]);
+  v.ell_np = ell_np;
+  v.ell_kin = ell ? g->max_in_degree : 0;
+  v.ell_kout = ell ? g->max_out_degree : 0;
+  v.ell_in_src = ell ? reinterpret_cast<const int32_t*>(p + oe[0]) : nullptr;
+  v.ell_in_lab = ell ? reinterpret_cast<const int32_t*>(p + oe[1]) : nullptr;
+  v.ell_in_w = ell ? reinterpret_cast<const float*>(p + oe[2]) : nullptr;
+  v.ell_out_dst = ell ? reinterpret_cast<const int32_t*>(p + oe[3]) : nullptr;
+  v.ell_out_lab = ell ? reinterpret_cast<const int32_t*>(p + oe[4]) : nullptr;
+  v.ell_out_w = ell ? reinterpret_cast<const float*>(p + oe[5]) : nullptr;
   v.max_arcs = g->max_arcs;
   v.unit_weights = g->unit_weights;
   v.in_label_uniform = g->in_label_uniform;
@@ -644,6 +684,7 @@ static int loss_fwd_bwd_impl(const float* logits, int32_t T, int32_t B, int32_t 
     d.g_sign = 1.f;
     d.g_scale = grad_scale;
     d.write_grad = grad != nullptr;
+    d.alpha_rows_plus1 = 1;
     CTCG_CUDA(launch_path_fwd_bwd(d, false, st));
     if (grad) CTCG_CUDA(launch_scatter_sub(T, B, V, lens, num->dev, gg, p.nlp, grad_scale, grad, st));
   } else if (grad && normalize == CTCG_NORM_CONTEXT) {
@@ -939,6 +980,7 @@ int ctcg_path_sum(const float* log_probs, int32_t T, int32_t B, int32_t V, const
   d.g_sign = 1.f;
   d.g_scale = nullptr;
   d.write_grad = grad != nullptr;
+  d.alpha_rows_plus1 = 1;  // alpha_num is planned with T + 1 rows
   CTCG_CUDA(launch_path_fwd_bwd(d, false, st));
   CTCG_CUDA(launch_cost_to_float(B, cost64, cost, st));
   return CTCG_OK;

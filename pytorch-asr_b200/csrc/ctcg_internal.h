@@ -50,6 +50,16 @@ struct GraphDev {
   // the graph (ascending within a label).  States without in-arcs are not listed (never occupied after frame 0).
   const int32_t* slab_ptr;
   const int32_t* slab_state;
+  // Transposed arc tables of a wide shared graph (one graph, >= 16 arcs per state on average; null otherwise):
+  // slot k of state s at [k * ell_np + s], so that one-state-per-thread loops read them coalesced.  In-arcs in CSR
+  // order (slot = position among the state's in-arcs), padding: other state 0, label 0, weight -inf.
+  int32_t ell_np, ell_kin, ell_kout;
+  const int32_t* ell_in_src;
+  const int32_t* ell_in_lab;
+  const float* ell_in_w;   // natural log
+  const int32_t* ell_out_dst;
+  const int32_t* ell_out_lab;
+  const float* ell_out_w;
   int32_t max_arcs;      // most arcs of any one graph
   int32_t unit_weights;  // every arc weight is 0 (semiring One)
   int32_t in_label_uniform;  // all arcs into a state carry the same label (true for every H o C o transcript graph)

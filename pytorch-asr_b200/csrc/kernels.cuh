@@ -32,6 +32,7 @@ struct PathArgs {
   const float* g_scale;   // nullable, per-utterance multiplier
   int32_t write_grad;
   int32_t dbg;            // reserved for timing experiments; 0 in production
+  int32_t alpha_rows_plus1;  // generic kernel: alpha_ws holds T + 1 rows per utterance (lets it take the transposed-table mode)
 };
 
 // compact = 1: x / gout are the per-utterance compact label columns produced by

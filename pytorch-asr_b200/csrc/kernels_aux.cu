@@ -22,8 +22,9 @@ namespace {
 constexpr int NT = 256;
 constexpr int NWARP = NT / 32;
 
-// WIDE (graphs with tens of arcs per state, as in kernels_path.cu): a warp owns a state, its lanes the state's
-// contiguous in-arcs; the arg-max keeps the lowest arc index among equal scores, like the serial loop.
+// WIDE (shared graphs with tens of arcs per state, as in kernels_path.cu): one state per thread over the transposed
+// arc tables of GraphDev, 1024 threads.  (One state per WARP over the CSR was tried first: 184 warp instructions per
+// state, issue-bound, no faster than the 256-thread CSR loop -- profiles/micro/generic_viterbi.py.)
 template <bool WIDE, int NT>
 __global__ void __launch_bounds__(NT) viterbi_kernel(const float* __restrict__ x, int T, int B, int V,
                                                      const int32_t* __restrict__ lens, GraphDev g,
@@ -59,29 +60,23 @@ __global__ void __launch_bounds__(NT) viterbi_kernel(const float* __restrict__ x
     const float* xrow = x + ((long long)t * B + b) * V;
     float lm = neg_inf();
     if (WIDE) {
-      for (int s = warp; s < n; s += NWARP) {
+      // transposed tables: slot k of state s at [k * np + s] -- consecutive lanes, consecutive addresses; the
+      // back-pointer is the slot (lowest slot among equal scores = lowest arc index of the CSR loop)
+      const int enp = g.ell_np, K = g.ell_kin;
+      for (int s = tid; s < n; s += NT) {
         float best = neg_inf();
-        int arg = 0x7fffffff;
-        for (int e = in_ptr[s] + lane; e < in_ptr[s + 1]; e += 32) {
-          const float v = g.in_w[e] + (v_cur[g.in_src[e]] - mx) + xrow[g.in_lab[e]];
-          if (v > best) {  // ascending e within a lane: the first maximum is the lowest index
+        int arg = -1;
+#pragma unroll 4
+        for (int k = 0; k < K; ++k) {
+          const int i = k * enp + s;
+          const float v = g.ell_in_w[i] + (v_cur[g.ell_in_src[i]] - mx) + xrow[g.ell_in_lab[i]];
+          if (v > best) {
             best = v;
-            arg = e;
+            arg = k;
           }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          const float ov = __shfl_xor_sync(0xffffffffu, best, o);
-          const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
-          if (ov > best || (ov == best && oa < arg)) {
-            best = ov;
-            arg = oa;
-          }
-        }
-        if (lane == 0) {
-          v_nxt[s] = best;
-          back[(long long)t * row + s] = best > neg_inf() ? arg : -1;
-        }
+        v_nxt[s] = best;
+        back[(long long)t * row + s] = arg;
         lm = fmaxf(lm, best);
       }
     } else {
@@ -153,8 +148,13 @@ __global__ void __launch_bounds__(NT) viterbi_kernel(const float* __restrict__ x
       int s = bi;
       for (int t = len - 1; t >= 0; --t) {
         const int e = back[(long long)t * row + s];
-        frame_labels[(long long)t * B + b] = g.in_lab[e];
-        s = g.in_src[e];
+        if (WIDE) {  // e is a slot of state s
+          frame_labels[(long long)t * B + b] = g.ell_in_lab[e * g.ell_np + s];
+          s = g.ell_in_src[e * g.ell_np + s];
+        } else {
+          frame_labels[(long long)t * B + b] = g.in_lab[e];
+          s = g.in_src[e];
+        }
       }
     }
   }
@@ -366,7 +366,7 @@ cudaError_t launch_viterbi(const float* x, int T, int B, int V, const int32_t* l
     const char* e = getenv("CTCG_PATH_NARROW");
     return e && e[0] == '1';
   }();
-  const bool wide = !narrow_only && (long long)g.max_arcs >= 16LL * (long long)max(g.max_states, 1);
+  const bool wide = !narrow_only && g.ell_in_src != nullptr;  // transposed arc tables (wide shared graphs)
   constexpr int NTW = 1024;
   const size_t smem = (size_t)(2 * pad4(g.max_states) + 4 * ((wide ? NTW : NT) / 32)) * 4;
   if (smem > 200 * 1024) return cudaErrorInvalidConfiguration;

@@ -111,8 +111,14 @@ __device__ __forceinline__ float read_block_max(const float* red) {
 // are read in coalesced 128-byte lines and each lane keeps its first two arc scores in registers between the
 // max and the sum (with one state per thread, the 51 arcs of a bi-char state are 51 strided loads per lane,
 // twice).  NT threads: 256 for numerators, 1024 for the wide graphs, whose frames are latency-bound.
-template <bool COMPACT, bool WIDE, int NT>
+// MODE 2 (shared graphs with >= 512 states and transposed arc tables, GraphDev::ell_*): one state per THREAD over
+// the tables -- slot k of consecutive states at consecutive addresses, a tenth of MODE 1's warp instructions (ncu:
+// MODE 1 is issue-bound at ~180 warp instructions per state) -- and, where every arc into a state carries the same
+// label, the gradient from the per-STATE occupancy alpha_{t+1}[d] beta_{t+1}[d] (one shared-memory atomic per
+// state and frame instead of one per arc); the forward pass spills one more alpha row (row len) for it.
+template <bool COMPACT, int MODE, int NT>
 __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, const int stage_arcs) {
+  constexpr bool WIDE = MODE == 1, ELL = MODE == 2;
   constexpr int NWARP = NT / 32;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const GraphDev& g = a.g;
@@ -190,7 +196,7 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   const bool unit = g.unit_weights != 0;  // every arc weight is One: no weight loads
   const float* final_w = g.final_w + so;
   const float* xb = a.x + (long long)b * a.x_stride_b;
-  float* arow_base = a.alpha_ws + (long long)b * a.T * a.alpha_row;
+  float* arow_base = a.alpha_ws + (long long)b * (a.T + (ELL ? 1 : 0)) * a.alpha_row;
   const int nl = COMPACT ? (g.lab_off[gi + 1] - g.lab_off[gi]) : a.g_width;
   const int xcopy = COMPACT ? pad4(nl) / 4 : 0;  // 16-byte chunks per score row
 
@@ -232,7 +238,30 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
       const float w = unit ? 0.f : in_w[e] * wscale;
       return w + (a_cur[in_src[e]] - mx) + xrow[in_lab[e]] * a.x_scale;
     };
-    if (WIDE) {
+    if (ELL) {
+      const int enp = g.ell_np, K = g.ell_kin;
+      for (int s = tid; s < n; s += NT) {
+        arow[s] = a_cur[s] - mx;
+        float M = neg_inf();
+#pragma unroll 4
+        for (int k = 0; k < K; ++k) {
+          const int i = k * enp + s;
+          M = fmaxf(M, g.ell_in_w[i] * kLog2e + (a_cur[g.ell_in_src[i]] - mx) + xrow[g.ell_in_lab[i]] * a.x_scale);
+        }
+        float r = neg_inf();
+        if (M > neg_inf()) {
+          float acc = 0.f;
+#pragma unroll 4
+          for (int k = 0; k < K; ++k) {
+            const int i = k * enp + s;
+            acc += ex2(g.ell_in_w[i] * kLog2e + (a_cur[g.ell_in_src[i]] - mx) + xrow[g.ell_in_lab[i]] * a.x_scale - M);
+          }
+          r = M + lg2(acc);
+        }
+        a_nxt[s] = r;
+        lm = fmaxf(lm, r);
+      }
+    } else if (WIDE) {
       // two states per iteration: their (L2-latency) pointer and arc loads overlap
       for (int s = warp; s < n; s += 2 * NWARP) {
         const int s2 = s + NWARP;
@@ -300,6 +329,15 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
   float mx = (len > 0) ? read_block_max<NWARP>(wred + (len & 1) * NWARP) : 0.f;
   if (!(mx > neg_inf())) mx = 0.f;
   c += (double)mx;
+  if (ELL) {  // alpha_hat_len and its offset: the occupancy of the last frame needs them
+    float* arow = arow_base + (long long)len * a.alpha_row;
+    for (int s = tid; s < n; s += NT) arow[s] = a_cur[s] - mx;
+    if (tid == 0) {
+      const float hi = (float)c;
+      arow[a.alpha_row - 2] = hi;
+      arow[a.alpha_row - 1] = (float)(c - (double)hi);
+    }
+  }
   float* red2 = wred;  // both parities are free between the passes
   float tm = neg_inf();
   for (int s = tid; s < n; s += NT) tm = fmaxf(tm, (a_cur[s] - mx) + final_w[s] * kLog2e);
@@ -402,7 +440,50 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
       const float w = unit ? 0.f : out_w[e] * wscale;
       return w + (b_cur[out_dst[e]] - mxb) + xrow[out_lab[e]] * a.x_scale;
     };
-    if (WIDE) {
+    if (ELL) {
+      const int enp = g.ell_np, K = g.ell_kout;
+      const bool uniform = g.in_label_uniform != 0;
+      if (uniform) {
+        // posterior of frame t by state: gamma_t[label into d] += alpha_{t+1}[d] beta_{t+1}[d] / Z
+        const float* arow1 = arow_base + (long long)(t + 1) * a.alpha_row;
+        const double c1 = (double)arow1[a.alpha_row - 2] + (double)arow1[a.alpha_row - 1];
+        const float K1 = (float)(c1 + d - cost2);
+        for (int s = tid; s < n; s += NT) {
+          const float occ = ex2(arow1[s] + (b_cur[s] - mxb) + K1);
+          if (occ > 0.f) {
+            atomicAdd(&gr[g.ell_in_lab[s]], occ);  // slot 0: the label every arc into s carries
+            gsum += occ;
+          }
+        }
+      }
+      for (int s = tid; s < n; s += NT) {
+        float M = neg_inf();
+#pragma unroll 4
+        for (int k = 0; k < K; ++k) {
+          const int i = k * enp + s;
+          M = fmaxf(M, g.ell_out_w[i] * kLog2e + (b_cur[g.ell_out_dst[i]] - mxb) + xrow[g.ell_out_lab[i]] * a.x_scale);
+        }
+        float r = neg_inf();
+        if (M > neg_inf()) {
+          const float f = uniform ? 0.f : ex2(M + arow[s] + Kt);
+          float acc = 0.f;
+#pragma unroll 4
+          for (int k = 0; k < K; ++k) {
+            const int i = k * enp + s;
+            const int lab = g.ell_out_lab[i];
+            const float ev = ex2(g.ell_out_w[i] * kLog2e + (b_cur[g.ell_out_dst[i]] - mxb) + xrow[lab] * a.x_scale - M);
+            acc += ev;
+            if (f > 0.f && ev > 0.f) {
+              atomicAdd(&gr[lab], ev * f);
+              gsum += ev * f;
+            }
+          }
+          r = M + lg2(acc);
+        }
+        b_nxt[s] = r;
+        lm = fmaxf(lm, r);
+      }
+    } else if (WIDE) {
       for (int s = warp; s < n; s += NWARP) {
         const int lo = out_ptr[s], hi = out_ptr[s + 1];
         const int e0 = lo + lane;
@@ -481,12 +562,12 @@ __global__ void __launch_bounds__(NT) path_fwd_bwd_kernel(const PathArgs a, cons
 
 }  // namespace
 
-template <bool COMPACT, bool WIDE, int NTT>
+template <bool COMPACT, int MODE, int NTT>
 cudaError_t launch_path_variant(const PathArgs& a, int stage, size_t bytes, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(path_fwd_bwd_kernel<COMPACT, WIDE, NTT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaError_t e = cudaFuncSetAttribute(path_fwd_bwd_kernel<COMPACT, MODE, NTT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)bytes);
   if (e != cudaSuccess) return e;
-  path_fwd_bwd_kernel<COMPACT, WIDE, NTT><<<a.B, NTT, bytes, st>>>(a, stage);
+  path_fwd_bwd_kernel<COMPACT, MODE, NTT><<<a.B, NTT, bytes, st>>>(a, stage);
   return cudaSuccess;
 }
 
@@ -509,8 +590,12 @@ cudaError_t launch_path_fwd_bwd(const PathArgs& a, bool compact, cudaStream_t st
   const SmemPlan P = plan_smem(a.g.max_states, a.g_width, a.g.max_labels, a.alpha_row, stage, compact, nwarp, wide);
   cudaError_t e;
   ProfScope prof(compact ? "path_fwd_bwd<compact>" : "path_fwd_bwd<dense>", st);
-  if (compact) e = wide ? launch_path_variant<true, true, NTWIDE>(a, stage, P.bytes, st) : launch_path_variant<true, false, NT>(a, stage, P.bytes, st);
-  else e = wide ? launch_path_variant<false, true, NTWIDE>(a, stage, P.bytes, st) : launch_path_variant<false, false, NT>(a, stage, P.bytes, st);
+  // transposed arc tables and enough states to fill the CTA: one state per thread over them (dense mode: the
+  // shared graphs; the caller's alpha workspace holds T + 1 rows per utterance, a.alpha_rows_plus1)
+  const bool ell = wide && !compact && a.g.ell_in_src != nullptr && a.g.max_states >= 512 && a.alpha_rows_plus1;
+  if (compact) e = wide ? launch_path_variant<true, 1, NTWIDE>(a, stage, P.bytes, st) : launch_path_variant<true, 0, NT>(a, stage, P.bytes, st);
+  else if (ell) e = launch_path_variant<false, 2, NTWIDE>(a, stage, P.bytes, st);
+  else e = wide ? launch_path_variant<false, 1, NTWIDE>(a, stage, P.bytes, st) : launch_path_variant<false, 0, NT>(a, stage, P.bytes, st);
   if (e != cudaSuccess) return e;
   ++g_launches;
   return cudaGetLastError();
