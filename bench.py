@@ -61,7 +61,11 @@ def make_batch(workload, rank=0, world=1, scaling="weak", T_override=None):
         B = len(lens)
         T = lens[0]                      # this rank's longest utterance
     else:
-        seed = 1000 + CFG_INDEX[workload] + 7919 * rank
+        # weak scaling = the SAME work on every GPU: every rank's batch has the lengths and transcripts of the
+        # N=1 batch (the seed does not depend on the rank), its own logits (their seed does, below).  With a
+        # per-rank draw the ranks' frame counts differ by a few per cent and the whole-job figure measures the luck
+        # of the draw next to the overheads.
+        seed = 1000 + CFG_INDEX[workload]
         rng = np.random.default_rng(seed)
         lens = sorted([T] + rng.integers(int(0.6 * T), T + 1, size=B - 1).tolist(), reverse=True)
         seqs = [rng.integers(1, S, size=max(1, ln // 4)).tolist() for ln in lens]
@@ -233,7 +237,9 @@ def workload_config(workload, batch, n_gpus):
                workload, batch["name"], batch["B"], batch["T"], batch["V"], batch["S"]),
            "global_batch": batch["B"] * n_gpus if batch["scaling"] == "weak" else STRONG_TOTAL_B,
            "frames_per_step_per_gpu": int(sum(batch["lens"])),
-           "parallelism": "utterance-sharded dp%d" % n_gpus,
+           "parallelism": "utterance-sharded dp%d" % n_gpus + (
+               "; every rank's batch has the lengths and transcripts of the N=1 batch and its own logits"
+               if n_gpus > 1 and batch["scaling"] == "weak" else ""),
            "l2": ("logits+grad per step (%.0f MB) exceed the 126 MB L2; input buffers rotated" if tb > 126e6 else
                   "logits+grad per step (%.0f MB) fit the 126 MB L2 (parity-size workload, not the bench "
                   "configuration); input buffers rotated") % (tb / 1e6)}
