@@ -290,3 +290,34 @@ def test_bigram_grammar_at_the_full_vocabulary_matches_the_fp64_oracle(lib_built
     l0, _ = P._lib.loss_fwd_bwd(torch.from_numpy(x).cuda(), lens, plain.get_training_graphs(seqs), plain.get_decoding_graph(),
                                 P.NORM_NONE, S)
     assert (l0 - loss).abs().min() > 1e-3
+
+
+def test_grammar_composes_with_the_trichar_topology(lib_built, tmp_path):
+    """Order 3 (fst_utils.py:926-1050) under a bigram grammar: the tri-char state already knows the last symbol, so
+    the composed graph keeps the topology's states and arcs and only gains weights; every transcript's numerator
+    is below the denominator (fp64 oracle engine on the exported matrices), and the decode collapse walks the
+    composed arcs."""
+    P = lib_built
+    path = tmp_path / "toy.fst.gz"
+    path.write_bytes(gzip.compress(_write_openfst(TOY, 0, SYMS)))
+    S = len(VOCAB)
+    args = {"use_context_blanks": True}
+    gen = P.CTCGraphGen(context_order=3, graph_build_args=dict(args), num_symbols=S, grammar_fst=str(path), vocabulary=VOCAB)
+    plain = P.CTCGraphGen(context_order=3, graph_build_args=dict(args), num_symbols=S)
+    gi, pi = gen.get_decoding_graph().info(), plain.get_decoding_graph().info()
+    assert (gi.max_states, gi.total_arcs) == (pi.max_states, pi.total_arcs) and gi.structured == 0
+    rng = np.random.default_rng(0)
+    T = 12
+    x = torch.as_tensor(rng.standard_normal((T, 1, S ** 3)))
+    den, _, _ = engine.path_logsumexp(x, [T], [m.numpy() for m in gen.get_decoding_matrices()], dtype=torch.float64)
+    den0, _, _ = engine.path_logsumexp(x, [T], [m.numpy() for m in plain.get_decoding_matrices()], dtype=torch.float64)
+    assert float(den[0]) < float(den0[0])                      # probabilities below one on every emitting arc
+    for text in ([2, 3, 2], [3], [2, 2, 3, 1, 2]):
+        nm = gen.get_training_matrices(torch.as_tensor(text))
+        num, _, _ = engine.path_logsumexp(x, [T], [m.unsqueeze(0).numpy() for m in nm], dtype=torch.float64)
+        assert float(num[0]) < float(den[0])
+        nm0 = plain.get_training_matrices(torch.as_tensor(text))
+        num0, _, _ = engine.path_logsumexp(x, [T], [m.unsqueeze(0).numpy() for m in nm0], dtype=torch.float64)
+        gr = _gr(P)
+        lm = _all_paths_weight(*gr.grammar_acceptor(str(path), VOCAB), tuple(text))
+        assert abs((float(num[0]) - float(num0[0])) - lm) < 1e-5   # the numerator carries exactly the grammar's weight
