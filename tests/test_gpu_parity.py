@@ -911,3 +911,49 @@ def test_captured_step_cache_under_many_interleaved_signatures(P):
         assert torch.equal(s["loss"], s["want"][0]) and torch.equal(s["grad"], s["want"][1]), k
     i1 = P._lib.step_graph_info()
     assert i1[1] - i0[1] >= 2 and i1[0] - i0[0] >= 8      # captures and replays did happen
+
+
+def _sweep_cases():
+    """24 seeded random configurations over the flags, sizes and corner shapes (B=1, T=1, S at the limits of the
+    factorised kernels' templates, odd V, ragged lengths down to one frame, per-utterance weights)."""
+    rng = np.random.default_rng(20260)
+    flagsets = [{}, {"use_contextual_blanks": True}, {"allow_nonblank_selfloops": False},
+                {"loop_using_symbol_repetitions": True}, {"use_contextual_blanks": True, "allow_nonblank_selfloops": False}]
+    cases = []
+    for i in range(24):
+        order = 2 if i % 4 else 1
+        S = int(rng.choice([4, 5, 7, 9, 13, 16, 23, 36, 49] if order == 2 else [3, 8, 30, 49]))
+        T = int(rng.choice([1, 2, 7, 8, 9, 16, 17, 31, 64, 65, 100]))
+        B = int(rng.choice([1, 2, 3, 8, 17]))
+        args = dict(flagsets[int(rng.integers(len(flagsets)))]) if order == 2 else {}
+        use_den = bool(rng.integers(2))
+        nbd = None if use_den and rng.random() < 0.7 else [None, 0, 1][int(rng.integers(3))]
+        if order == 1 and nbd == 1:
+            nbd = 0
+        cases.append((i, order, S, args, use_den, nbd, T, B))
+    return cases
+
+
+@pytest.mark.parametrize("i,order,S,args,use_den,nbd,T,B", _sweep_cases())
+def test_random_sweep_of_shapes_and_flags_matches_fp64_oracle(P, i, order, S, args, use_den, nbd, T, B):
+    rng = np.random.default_rng(5000 + i)
+    V = S ** order
+    lens = sorted([T] + rng.integers(1, T + 1, size=B - 1).tolist(), reverse=True)      # ragged, down to one frame
+    seqs = [rng.integers(1, S, size=max(1, min(ln, rng.integers(1, max(2, ln // 2 + 1))))).tolist() for ln in lens]
+    logits = (rng.standard_normal((T, B, V)) * 3).astype(np.float32)
+    want_loss, want_grad = _oracle(order, S, args, logits, lens, seqs, use_den, nbd)
+    gen = P.CTCGraphGen(context_order=order, graph_build_args=args, num_symbols=S)
+    num = gen.get_training_graphs(seqs)
+    den = gen.get_decoding_graph() if use_den else None
+    w = torch.from_numpy(rng.uniform(-2, 2, size=B).astype(np.float32))
+    x = torch.from_numpy(logits).cuda().requires_grad_(True)
+    loss = P.fst_loss(x, lens, num, den, normalize_by_dim=nbd, num_symbols=S)
+    (loss * w.cuda()).sum().backward()
+    got, wl = loss.detach().cpu().double().numpy(), want_loss.numpy()
+    feasible = np.abs(wl) < 1e19                           # T too short for the transcript: ~1e20 in both, zero gradient
+    assert (np.abs(got[~feasible]) > 1e19).all()
+    if feasible.any():
+        assert np.abs(got[feasible] - wl[feasible]).max() <= LOSS_RTOL * max(1.0, np.abs(wl[feasible]).max())
+    wg = want_grad.numpy() * w.numpy()[None, :, None]
+    wg[:, ~feasible] = 0
+    assert np.abs(x.grad.cpu().double().numpy() - wg).max() < 2 * GRAD_ATOL * max(1.0, float(w.abs().max()))
