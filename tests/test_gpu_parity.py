@@ -957,3 +957,49 @@ def test_random_sweep_of_shapes_and_flags_matches_fp64_oracle(P, i, order, S, ar
     wg = want_grad.numpy() * w.numpy()[None, :, None]
     wg[:, ~feasible] = 0
     assert np.abs(x.grad.cpu().double().numpy() - wg).max() < 2 * GRAD_ATOL * max(1.0, float(w.abs().max()))
+
+
+@pytest.mark.parametrize("n_states,deg,uniform", [(600, 20, False), (700, 18, True), (300, 24, False)])
+def test_generic_kernels_on_wide_irregular_weighted_graphs(P, n_states, deg, uniform):
+    """The generic CSR kernels on a random wide graph with weights and irregular in-degree, imported arc by arc:
+    >= 512 states take the transposed arc tables (per-arc posteriors when the arcs into a state carry different
+    labels, per-state occupancy when they share one), fewer the warp-per-state shape.  Path sum, gradient, Viterbi
+    score and frame labels against the fp64 oracle engine on the exported matrices; the loss with this graph as
+    the denominator of a small CTC numerator as well."""
+    rng = np.random.default_rng(n_states + deg)
+    V = 64
+    arcs = []
+    state_label = rng.integers(0, V, size=n_states)
+    for s in range(n_states):
+        if uniform:                                   # label = the target's: arcs into a state share it; targets with
+            dst, seen = [], set()                     # distinct labels keep the graph input-deterministic
+            for d in rng.permutation(n_states).tolist():
+                if state_label[d] not in seen:
+                    seen.add(int(state_label[d]))
+                    dst.append(d)
+                if len(dst) == deg:
+                    break
+            labs = [int(state_label[d]) for d in dst]
+        else:
+            dst = rng.choice(n_states, size=deg, replace=False).tolist()
+            labs = rng.choice(V, size=deg, replace=False).tolist()
+        for d, l in zip(dst, labs):
+            arcs.append((s, int(d), int(l), float(-rng.uniform(0, 3))))
+    final = np.where(rng.random(n_states) < 0.5, -rng.uniform(0, 2, size=n_states), -np.inf).astype(np.float32)
+    final[0] = 0.0
+    g = P.Graph.from_arcs([(n_states, arcs, final)])
+    info = g.info()
+    assert info.total_arcs >= 16 * n_states and info.structured == 0
+    T, B = 23, 3
+    lens = [23, 17, 9]
+    x = (rng.standard_normal((T, B, V)) * 2).astype(np.float32)
+    mats = [m.unsqueeze(0).numpy() for m in P.padded_matrices(g, 0)]
+    want_cost, want_grad, _ = engine.path_logsumexp(torch.as_tensor(x), lens, mats, dtype=torch.float64)
+    cost, grad = P._lib.path_sum(torch.from_numpy(x).cuda(), lens, g)
+    assert _rel(cost.cpu().numpy(), want_cost.numpy()) < LOSS_RTOL
+    assert np.abs(grad.cpu().double().numpy() - want_grad.numpy()).max() < GRAD_ATOL
+    want_score, want_labels = engine.path_viterbi(torch.as_tensor(x), lens, mats)
+    score, labels = P._lib.viterbi(torch.from_numpy(x).cuda(), lens, g)
+    assert _rel(score.cpu().numpy(), np.asarray(want_score)) < 1e-6
+    for b, ln in enumerate(lens):
+        assert np.array_equal(labels.cpu().numpy()[:ln, b], np.asarray(want_labels)[:ln, b])
