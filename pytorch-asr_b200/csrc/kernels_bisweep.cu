@@ -95,9 +95,6 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
                : "memory");
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void named_sync(int id, int count) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
-}
 __device__ __forceinline__ float lds(unsigned a) {
   float v;
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
@@ -193,7 +190,6 @@ __device__ __forceinline__ void sweep_body(const BisweepArgs& A, unsigned char* 
   // ARRIVE as soon as its part of the new vector is stored and only WAIT after it has issued the
   // next frame's e loads: the prefetch leaves the per-frame chain.
   const unsigned frame_bar = bar_a + (2 * NRAW + 2 * NE + 1) * 8;
-  const int NB = (nmain + 1) * 32;  // threads of the per-frame barrier: main warps + scale warp
   float* spill = A.spill[DIR] + (long long)b * A.T * prowf;
   float* ck = A.ck[DIR] + (long long)b * A.nck * V;
 

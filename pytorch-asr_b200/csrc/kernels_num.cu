@@ -72,15 +72,7 @@ __device__ __forceinline__ int2 lds64(unsigned a) {
 __device__ __forceinline__ void sts64(unsigned a, int2 v) {
   asm volatile("st.shared.v2.s32 [%0], {%1,%2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory");
 }
-__device__ __forceinline__ float lds32(unsigned a) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
-  return v;
-}
 __device__ __forceinline__ unsigned sm_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
-__device__ __forceinline__ void cp_async4(unsigned dst, const void* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-}
 
 // x (log2 units, clamped) -> (E, f): 2^x = f * 2^E with E = rint(x), f = 2^(x - E) in [0.707, 1.415]
 __device__ __forceinline__ int2 split_pow2(float xs) {
@@ -146,8 +138,6 @@ __global__ void __launch_bounds__(NT) num_sweep_kernel(const PathArgs a, const i
   const int so = g.state_off[gi];
   const int n = g.state_off[gi + 1] - so;
   const int ro = so + gi;
-  const int lo = g.lab_off[gi];
-  const int nl = g.lab_off[gi + 1] - lo;
   const int len = min(a.lens[b], a.T);
   const int nlp = (int)a.x_stride_t, arow2 = a.alpha_row / 2;
   const SweepPlan P = sweep_plan(maxN, nlp);
