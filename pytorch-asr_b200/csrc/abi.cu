@@ -212,7 +212,7 @@ int ctcg_graph_upload(ctcg_graph* g, void* stream) {
   append(&blob, g->slab_state, &o[19]);
   // transposed arc tables for wide shared graphs (see GraphDev): built here, from the CSR
   const bool ell = g->num_graphs == 1 && g->max_states > 0 && (long long)g->max_arcs >= 16LL * g->max_states &&
-                   (long long)(g->max_in_degree + g->max_out_degree) * g->max_states <= (1LL << 24);
+                   (long long)(g->max_in_degree + g->max_out_degree) * g->max_states <= (1LL << 22);  // <= 50 MB of tables
   const int ell_np = ell ? (g->max_states + 31) / 32 * 32 : 0;
   size_t oe[6] = {0, 0, 0, 0, 0, 0};
   if (ell) {
