@@ -153,7 +153,10 @@ void ctcg_graph_cache_clear(void) {
 }
 
 void ctcg_graph_set_generic(ctcg_graph* g) {
-  if (g) g->structured = ctcg::Structured{0, 0, 0, 0, 0};
+  if (!g) return;
+  g->structured = ctcg::Structured{0, 0, 0, 0, 0};
+  // the handle now selects other kernels: steps captured with it (abi.cu, step graphs) must not be replayed
+  g->upload_uid += 1ull << 40;
 }
 
 int ctcg_decoding_graph(const ctcg_topology* topo, ctcg_graph** out) {
