@@ -354,17 +354,34 @@ class BaseGraphGen(object):
                  context_order=None, nc_weight=-1e20, for_forward_only=False,
                  grammar_fst=None, vocabulary=None, **kwargs):
         super(BaseGraphGen, self).__init__(**kwargs)
-        if ngram_to_class_file is not None:
-            raise NotImplementedError("ngram_to_class_file (a pruned n-gram table) is not supported")
         self.num_classes = num_classes
         self.num_symbols = num_symbols
-        self.context_order = 1 if context_order is None else context_order
-        num_symbols, num_classes, ngram_to_class = make_full_ngram_table(
-            self.context_order, num_symbols, num_classes)
-        setattr_matched(self, "num_symbols", num_symbols)
-        setattr_matched(self, "num_classes", num_classes)
-        self.ngram_to_class = ngram_to_class
-        self.ngrams = ngram_to_class.tolist()
+        self.context_order = context_order
+        if ngram_to_class_file is None:
+            self.context_order = 1 if context_order is None else context_order
+            num_symbols, num_classes, ngram_to_class = make_full_ngram_table(
+                self.context_order, num_symbols, num_classes)
+            setattr_matched(self, "num_symbols", num_symbols)
+            setattr_matched(self, "num_classes", num_classes)
+            self.ngram_to_class = ngram_to_class
+            self.ngrams = ngram_to_class.tolist()
+        else:
+            # fst_utils.py:567-577: a pruned n-gram table, one n-gram of symbol ids per line, class = line number
+            # (num_symbols is not checked against it: the file may hold fewer symbols)
+            with open(ngram_to_class_file, "r") as f:
+                self.ngrams = [[int(n) for n in line.split()] for line in f]
+            if self.context_order is None:
+                self.context_order = len(self.ngrams[0])
+            assert all(len(ngr) == self.context_order for ngr in self.ngrams)
+            setattr_matched(self, "num_classes", len(self.ngrams))
+            self.ngram_to_class = torch.LongTensor(self.ngrams)
+            if self.context_order < 3:
+                # the mono- and bi-char builders number their classes by the full table whatever the file says
+                # (fst_utils.py:694-712, 765-817): only a file that IS the full table is consistent with them
+                full = make_full_ngram_table(self.context_order, self.num_symbols, None)[2].tolist()
+                if self.ngrams != full:
+                    raise NotImplementedError("a pruned n-gram table with context_order < 3 (the reference's "
+                                              "builders ignore it and index classes by the full table)")
         self.grammar_fst_path = grammar_fst     # fst_utils.py:580-584
         self.vocabulary = None if grammar_fst is None else grammar.read_vocabulary(vocabulary)
         self.nc_weight = nc_weight

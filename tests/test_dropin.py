@@ -185,3 +185,43 @@ def test_dense_state_machines_equal_the_reference_matrices(lib_built, order, kw)
             want |= {(i + 1, j + 1, emit[j]) for i in range(N) for j in range(N) if A[i, j] != 0}
             assert {(a, b, c) for a, b, c, _ in arcs} == want and len(arcs) == len(want)
             assert [i for i in range(n) if final[i] == 0] == list(range(N + 1 - n_term, N + 1))
+
+
+@needs_ref
+@pytest.mark.parametrize("args", [{}, {"use_context_blanks": True}])
+def test_pruned_trigram_table_equals_the_reference(lib_built, tmp_path, args):
+    """``ngram_to_class_file`` (fst_utils.py:567-577): a pruned tri-char table, class = line number.  Same decoding
+    FST (arcs in the same order) and training matrices as the reference's generator reading the same file."""
+    import contextlib
+    import io
+    import itertools
+    P = lib_built
+    fu, _ = ref_loader.load()
+    S = 5
+    keep = [tg for tg in itertools.product(range(S), repeat=3)
+            if not (tg[0] == 3 and tg[1] == 4) and not (tg[1] == 2 and tg[2] == 2 and tg[0] != 0)]
+    path = tmp_path / "trigrams.txt"
+    path.write_text("".join("%d %d %d\n" % tg for tg in keep))
+    with contextlib.redirect_stdout(io.StringIO()):
+        rgen = fu.CTCGraphGen(context_order=3, graph_build_args=dict(args), num_symbols=S, ngram_to_class_file=str(path))
+    gen = P.CTCGraphGen(context_order=3, graph_build_args=dict(args), num_symbols=S, ngram_to_class_file=str(path))
+    assert gen.num_classes == rgen.num_classes == len(keep) < S ** 3
+    assert torch.equal(gen.ngram_to_class, rgen.ngram_to_class)
+
+    def arcs(f):
+        return [(s, a.ilabel, a.olabel, a.nextstate) for s in f.states() for a in f.arcs(s)]
+    assert gen.decoding_fst.num_states() == rgen.decoding_fst.num_states()
+    assert arcs(gen.decoding_fst) == arcs(rgen.decoding_fst)
+    for labels in ([1, 2, 3], [4, 1, 1, 3, 2], [2], [1, 4, 3, 1]):          # none needs a pruned trigram
+        want_m = rgen.get_training_matrices(torch.as_tensor(labels))
+        got_m = gen.get_training_matrices(torch.as_tensor(labels))
+        for a, b in zip(got_m, want_m):
+            assert a.dtype == b.dtype and torch.equal(a, b)
+    # orders 1 and 2 index their classes by the full table whatever the file says: only the full table is accepted
+    full = tmp_path / "bigrams.txt"
+    full.write_text("".join("%d %d\n" % bg for bg in itertools.product(range(S), repeat=2)))
+    assert P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S, ngram_to_class_file=str(full)).num_classes == S * S
+    pruned = tmp_path / "bigrams_pruned.txt"
+    pruned.write_text("".join("%d %d\n" % bg for bg in itertools.product(range(S), repeat=2) if bg != (3, 4)))
+    with pytest.raises(NotImplementedError):
+        P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S, ngram_to_class_file=str(pruned))
