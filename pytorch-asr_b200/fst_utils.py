@@ -344,6 +344,27 @@ def trigram_decoding_arcs(trigrams, use_context_blanks=False, prevent_epsilons=T
     return len(trigrams), np.asarray(arcs, dtype=np.int64).reshape(-1, 5), final
 
 
+def build_chain_fst(labels, arc_type="log", vocab=None):
+    """fst_utils.py:195-219 for callers that want the OpenFst object (``FSTDecoder.decode`` of the reference builds
+    one per utterance, advanced_decoder.py:559-563; this package's ``decode`` does not).  Needs pywrapfst."""
+    try:
+        import pywrapfst as fst
+    except ImportError:
+        raise ImportError("build_chain_fst returns an OpenFst object and needs pywrapfst; the loss and decode paths "
+                          "of this package do not use it")
+    f = fst.Fst(arc_type=arc_type)
+    one = fst.Weight.One(f.weight_type())
+    s = f.add_state()
+    f.set_start(s)
+    for l in labels:
+        nxt = f.add_state()
+        f.add_arc(s, fst.Arc(int(l), int(l), one, nxt))
+        s = nxt
+    f.set_final(s)
+    f.arcsort("ilabel")
+    return f
+
+
 class BaseGraphGen(object):
     """fst_utils.py:546-676 without OpenFst; ``grammar_fst`` (an OpenFst binary file) is read and composed by
     :mod:`grammar`."""
@@ -502,6 +523,17 @@ class BaseGraphGen(object):
         if self._grammar is not None:
             return self._decoder.training(label_seqs, modulo=self.num_symbols)
         return Graph.training(self.context_order, self.num_symbols, label_seqs, **self._build_args())
+
+    def get_transcript_fst(self, labels):
+        """fst_utils.py:592-601: the chain acceptor of a transcript (labels taken modulo ``num_symbols`` when the
+        dataset hands over bi-char ids) as an OpenFst object -- only where pywrapfst is importable; nothing on the
+        loss path uses it (the native compiler composes transcripts itself)."""
+        if torch.is_tensor(labels):
+            labels = labels.cpu().numpy()
+        labels = np.asarray(labels)
+        if np.any(labels > self.num_symbols):
+            labels = labels % self.num_symbols
+        return build_chain_fst(labels)
 
     def get_training_fst(self, labels):
         if torch.is_tensor(labels):

@@ -225,3 +225,17 @@ def test_pruned_trigram_table_equals_the_reference(lib_built, tmp_path, args):
     pruned.write_text("".join("%d %d\n" % bg for bg in itertools.product(range(S), repeat=2) if bg != (3, 4)))
     with pytest.raises(NotImplementedError):
         P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=S, ngram_to_class_file=str(pruned))
+
+
+@needs_ref
+def test_transcript_fst_is_the_reference_chain(lib_built):
+    """``get_transcript_fst`` / ``build_chain_fst`` (fst_utils.py:195-219, :592-601) on the OpenFst stand-in."""
+    P = lib_built
+    fu, _ = ref_loader.load()
+    gen = P.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=7)
+    rgen = fu.CTCGraphGen(context_order=2, graph_build_args={}, num_symbols=7)
+    for labels in ([3, 1, 1, 6], [8, 22, 45]):                # the second: bi-char dataset ids, taken modulo S
+        mine = gen.get_transcript_fst(torch.as_tensor(labels))
+        want = rgen.get_transcript_fst(torch.as_tensor(labels))
+        arcs = lambda f: [(s, a.ilabel, a.olabel, a.nextstate) for s in f.states() for a in f.arcs(s)]  # noqa: E731
+        assert mine.num_states() == want.num_states() and arcs(mine) == arcs(want)
