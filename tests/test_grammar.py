@@ -321,3 +321,29 @@ def test_grammar_composes_with_the_trichar_topology(lib_built, tmp_path):
         gr = _gr(P)
         lm = _all_paths_weight(*gr.grammar_acceptor(str(path), VOCAB), tuple(text))
         assert abs((float(num[0]) - float(num0[0])) - lm) < 1e-5   # the numerator carries exactly the grammar's weight
+
+
+def test_epsilon_removal_on_random_automata(lib_built):
+    """Random weighted automata with acyclic epsilon arcs (chains of back-offs, epsilons into and out of final
+    states, parallel arcs): the epsilon-free automaton gives every string up to length 4 the same total weight."""
+    P = lib_built
+    gr = _gr(P)
+    rng = np.random.default_rng(77)
+    for trial in range(25):
+        n = int(rng.integers(2, 7))
+        arcs = []
+        for s in range(n):
+            for _ in range(int(rng.integers(1, 5))):
+                arcs.append((s, int(rng.integers(n)), int(rng.integers(1, 4)), float(-rng.uniform(0, 2))))
+            for d in range(s + 1, n):                       # epsilons only forwards: acyclic
+                if rng.random() < 0.4:
+                    arcs.append((s, d, 0, float(-rng.uniform(0, 2))))
+        final = np.where(rng.random(n) < 0.5, -rng.uniform(0, 2, size=n), -np.inf)
+        final[n - 1] = 0.0
+        g = (n, 0, arcs, final)
+        ge = gr.remove_epsilons(*g)
+        assert all(l != 0 for _, _, l, _ in ge[2])
+        for length in range(0, 5):
+            for string in itertools.product([1, 2, 3], repeat=length):
+                a, b = _all_paths_weight(*g, string), _all_paths_weight(*ge, string)
+                assert (a == b == -math.inf) or abs(a - b) < 1e-9, (trial, string, a, b)
